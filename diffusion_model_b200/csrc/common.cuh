@@ -1,0 +1,144 @@
+// Shared helpers for libegnn_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/egnn_b200.h"
+
+void egnn_set_error(const char* fmt, ...);
+
+#define EGNN_REQUIRE(cond, ...)              \
+    do {                                     \
+        if (!(cond)) {                       \
+            egnn_set_error(__VA_ARGS__);     \
+            return EGNN_ERR_ARG;             \
+        }                                    \
+    } while (0)
+
+#define EGNN_CHECK_LAUNCH(name)                                       \
+    do {                                                              \
+        cudaError_t e__ = cudaGetLastError();                         \
+        if (e__ != cudaSuccess) {                                     \
+            egnn_set_error("%s: %s", name, cudaGetErrorString(e__));  \
+            return EGNN_ERR_CUDA;                                     \
+        }                                                             \
+    } while (0)
+
+#define EGNN_CUDA(call)                                                   \
+    do {                                                                  \
+        cudaError_t e__ = (call);                                         \
+        if (e__ != cudaSuccess) {                                         \
+            egnn_set_error("%s: %s", #call, cudaGetErrorString(e__));     \
+            return EGNN_ERR_CUDA;                                         \
+        }                                                                 \
+    } while (0)
+
+static inline int64_t round_up64(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+__host__ __device__ static inline int round4(int a) { return (a + 3) & ~3; }
+
+// ---- flat parameter layout (reference named_parameters() order, see include/egnn_b200.h) --------------------
+struct LayerOff {
+    int wm1, bm1, wm2, bm2, wx1, bx1, wx2, bx2, wx3, bx3, wh1, bh1, wh2, bh2, wa, ba, total;
+};
+__host__ __device__ static inline LayerOff layer_off(const egnn_net_t& n) {
+    LayerOff o;
+    const int K0 = 2 * n.H + 1;
+    int p = 0;
+    o.wm1 = p; p += n.Mh * K0;
+    o.bm1 = p; p += n.Mh;
+    o.wm2 = p; p += n.Ms * n.Mh;
+    o.bm2 = p; p += n.Ms;
+    o.wx1 = p; p += n.Xh * K0;
+    o.bx1 = p; p += n.Xh;
+    o.wx2 = p; p += n.Xh * n.Xh;
+    o.bx2 = p; p += n.Xh;
+    o.wx3 = p; p += n.Xh;
+    o.bx3 = p; p += 1;
+    o.wh1 = p; p += n.Hh * (n.H + n.Ms);
+    o.bh1 = p; p += n.Hh;
+    o.wh2 = p; p += n.H * n.Hh;
+    o.bh2 = p; p += n.H;
+    o.wa = p; p += n.Ms;
+    o.ba = p; p += 1;
+    o.total = p;
+    return o;
+}
+// packed = K-major transposes used as the B operand of the forward FFMA GEMMs: Wt[k][n] = W[n][k]
+struct PackOff {
+    int wm1t, wm2t, wx1t, wx2t, wh1t, total;
+};
+__host__ __device__ static inline PackOff pack_off(const egnn_net_t& n) {
+    PackOff o;
+    const int K0 = 2 * n.H + 1;
+    int p = 0;
+    o.wm1t = p; p += K0 * n.Mh;
+    o.wm2t = p; p += n.Mh * n.Ms;
+    o.wx1t = p; p += K0 * n.Xh;
+    o.wx2t = p; p += n.Xh * n.Xh;
+    o.wh1t = p; p += (n.H + n.Ms) * n.Hh;
+    o.total = round4(p);
+    return o;
+}
+
+// ---- forward workspace layout (floats).  Kept by the caller between forward and backward. -----------------
+struct FwdWs {
+    int64_t agg;    // [N][Ms+4]   per-receiver sums written directly by edge tiles
+    int64_t part;   // [T][2][Ms+4] head / tail partial sums of tiles
+    int64_t D;      // [N]         per-node sum of |r_e|^2
+    int64_t hl;     // [L][N][H]   input h of layer l (l >= 1; slot 0 unused)
+    int64_t xl;     // [L][N][3]
+    int64_t msum;   // [L][N][Ms]  combined message sums (input of mlp_h)
+    int64_t dxu;    // [L][N][3]   un-normalised coordinate sums
+    int64_t S;      // [L][G]      normaliser per graph
+    int64_t total;
+};
+static inline int edge_tile_for(const egnn_net_t& n) {
+    int dmax = n.Mh;
+    if (n.Ms > dmax) dmax = n.Ms;
+    if (n.Xh > dmax) dmax = n.Xh;
+    int te = 128;
+    while (te > 16 && (int64_t)te * (round4(dmax) + 4) > 128 * 132) te >>= 1;
+    return te;
+}
+static inline FwdWs fwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
+    FwdWs w;
+    const int64_t AGGW = n.Ms + 4;
+    const int64_t T = (E + edge_tile_for(n) - 1) / edge_tile_for(n);
+    int64_t p = 0;
+    auto take = [&](int64_t cnt) { int64_t o = p; p += round_up64(cnt, 4); return o; };
+    w.agg = take(N * AGGW);
+    w.part = take((T + 1) * 2 * AGGW);
+    w.D = take(N);
+    w.hl = take((int64_t)n.L * N * n.H);
+    w.xl = take((int64_t)n.L * N * 3);
+    w.msum = take((int64_t)n.L * N * n.Ms);
+    w.dxu = take((int64_t)n.L * N * 3);
+    w.S = take((int64_t)n.L * G);
+    w.total = p;
+    return w;
+}
+
+// ---- device math ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float sigmoid_f(float z) { return __fdividef(1.f, 1.f + __expf(-z)); }
+__device__ __forceinline__ float silu_f(float z) { return z * sigmoid_f(z); }
+// d/dz SiLU(z) = s (1 + z (1 - s))
+__device__ __forceinline__ float dsilu_f(float z) {
+    const float s = sigmoid_f(z);
+    return s * (1.f + z * (1.f - s));
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// fixed-order block reduction (blockDim.x == 256); result valid in every thread
+__device__ __forceinline__ float block_sum_256(float v, float* red /* [8] smem */) {
+    v = warp_sum(v);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[w];
+    return t;
+}

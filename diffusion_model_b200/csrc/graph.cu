@@ -1,0 +1,264 @@
+// Deterministic edge-list builders and the derived index structures (receiver CSR, sender CSR).
+//
+// Replaces the python double loops of the reference:
+//   parts/train_per_iretation.py:308-313, make_dataset.py:131-136  fully connected, row-major (i outer, j inner, i != j)
+//   something.ipynb:6340-6365                                       strict '<' cutoff on fp32 torch.norm(pos[i]-pos[j])
+// Output order is lexicographic, so every list is receiver-sorted (receiver = edge_index[0]).  Everything here is
+// integer work except the membership test, which is evaluated with explicitly rounded fp32 intrinsics in the
+// operation order the oracle pins against torch.norm (no FMA contraction by the compiler):
+//   dist = sqrt( fma(dz,dz, fma(dy,dy, dx*dx)) ),   periodic:  d_k = dx_k - L_k * rint(dx_k / L_k)
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ float pair_dist(const float* __restrict__ pos, int i, int j, const float* __restrict__ box3) {
+    float dx = __fsub_rn(pos[3 * i + 0], pos[3 * j + 0]);
+    float dy = __fsub_rn(pos[3 * i + 1], pos[3 * j + 1]);
+    float dz = __fsub_rn(pos[3 * i + 2], pos[3 * j + 2]);
+    if (box3 != nullptr) {
+        dx = __fsub_rn(dx, __fmul_rn(box3[0], rintf(__fdiv_rn(dx, box3[0]))));
+        dy = __fsub_rn(dy, __fmul_rn(box3[1], rintf(__fdiv_rn(dy, box3[1]))));
+        dz = __fsub_rn(dz, __fmul_rn(box3[2], rintf(__fdiv_rn(dz, box3[2]))));
+    }
+    return __fsqrt_rn(__fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx))));
+}
+
+// one CTA per graph
+__global__ void __launch_bounds__(256) fc_edges_kernel(const int32_t* __restrict__ node_ptr, int G, int64_t E,
+                                                       int64_t* __restrict__ out) {
+    __shared__ long long red[256];
+    const int g = blockIdx.x;
+    long long part = 0;
+    for (int q = threadIdx.x; q < g; q += 256) {
+        const long long n = node_ptr[q + 1] - node_ptr[q];
+        part += n * (n - 1);
+    }
+    red[threadIdx.x] = part;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
+        __syncthreads();
+    }
+    const long long eoff = red[0];
+    const int a = node_ptr[g];
+    const int n = node_ptr[g + 1] - a;
+    const long long cnt = (long long)n * (n - 1);
+    for (long long idx = threadIdx.x; idx < cnt; idx += 256) {
+        const int i = (int)(idx / (n - 1));
+        const int jj = (int)(idx - (long long)i * (n - 1));
+        const int j = jj + (jj >= i ? 1 : 0);
+        out[eoff + idx] = a + i;
+        out[E + eoff + idx] = a + j;
+    }
+}
+
+// one warp per node; FILL == false counts neighbours, FILL == true writes them in ascending j
+template <bool FILL>
+__global__ void __launch_bounds__(256) cutoff_kernel(const float* __restrict__ pos, const int32_t* __restrict__ node_ptr,
+                                                     const int32_t* __restrict__ node_graph, const float* __restrict__ box,
+                                                     float r_c, int N, int32_t* __restrict__ deg,
+                                                     const int32_t* __restrict__ row_ptr, int64_t E,
+                                                     int64_t* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (i >= N) return;
+    const int g = node_graph[i];
+    const int a = node_ptr[g], b = node_ptr[g + 1];
+    const float* box3 = box ? box + 3 * g : nullptr;
+    int count = 0;
+    const int64_t base = FILL ? row_ptr[i] : 0;
+    for (int j0 = a; j0 < b; j0 += 32) {
+        const int j = j0 + lane;
+        bool in = false;
+        if (j < b && j != i) in = pair_dist(pos, i, j, box3) < r_c;
+        const unsigned m = __ballot_sync(0xffffffffu, in);
+        if (FILL && in) {
+            const int64_t p = base + count + __popc(m & ((1u << lane) - 1u));
+            out[p] = i;
+            out[E + p] = j;
+        }
+        count += __popc(m);
+    }
+    if (!FILL && lane == 0) deg[i] = count;
+}
+
+__global__ void __launch_bounds__(1024) scan_kernel(const int32_t* __restrict__ in, int n, int32_t* __restrict__ out) {
+    __shared__ int warp_tot[32];
+    __shared__ int carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int base = 0; base < n; base += 1024) {
+        const int idx = base + threadIdx.x;
+        const int v = idx < n ? in[idx] : 0;
+        int incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) warp_tot[w] = incl;
+        __syncthreads();
+        if (w == 0) {
+            int t = warp_tot[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, t, o);
+                if (lane >= o) t += u;
+            }
+            warp_tot[lane] = t;  // inclusive over warps
+        }
+        __syncthreads();
+        const int carry = carry_s;
+        const int excl = carry + (w ? warp_tot[w - 1] : 0) + incl - v;
+        if (idx < n) out[idx] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = carry + warp_tot[31];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[n] = carry_s;
+}
+
+__global__ void __launch_bounds__(256) convert_edges_kernel(const int64_t* __restrict__ ei, int N, int64_t E,
+                                                            int32_t* __restrict__ recv, int32_t* __restrict__ send,
+                                                            int32_t* __restrict__ flags) {
+    const int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (e >= E) return;
+    const int64_t i = ei[e], j = ei[E + e];
+    const bool bad = i < 0 || i >= N || j < 0 || j >= N;
+    if (bad) flags[1] = 1;
+    if (e > 0 && ei[e - 1] > i) flags[0] = 1;
+    recv[e] = bad ? 0 : (int32_t)i;  // keep the later kernels in bounds; the caller raises on the flag
+    send[e] = bad ? 0 : (int32_t)j;
+}
+
+// ptr[i] = first position p with key[p] >= i  (key non-decreasing), ptr[n_keys] = n
+template <typename T>
+__global__ void __launch_bounds__(256) boundaries_kernel(const T* __restrict__ key, int64_t n, int n_keys,
+                                                         int32_t* __restrict__ ptr) {
+    const int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (e > n) return;
+    const long long prev = e == 0 ? -1 : (long long)key[e - 1];
+    const long long cur = e == n ? n_keys : (long long)key[e];
+    for (long long i = prev + 1 > 0 ? prev + 1 : 0; i <= cur && i <= n_keys; ++i) ptr[i] = (int32_t)e;
+}
+
+__global__ void __launch_bounds__(256) count_senders_kernel(const int32_t* __restrict__ send, int64_t E,
+                                                            int32_t* __restrict__ cnt) {
+    const int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (e < E) atomicAdd(&cnt[send[e]], 1);
+}
+__global__ void __launch_bounds__(256) fill_senders_kernel(const int32_t* __restrict__ send, int64_t E,
+                                                           const int32_t* __restrict__ col_ptr,
+                                                           int32_t* __restrict__ cursor, int32_t* __restrict__ tmp) {
+    const int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (e < E) {
+        const int s = send[e];
+        tmp[col_ptr[s] + atomicAdd(&cursor[s], 1)] = (int32_t)e;
+    }
+}
+// rank sort of every sender segment (edge ids are distinct): the slot order left by the atomics is erased,
+// so col_edge is a pure function of the edge list.  One warp per node.
+__global__ void __launch_bounds__(256) sort_segments_kernel(const int32_t* __restrict__ col_ptr, int N,
+                                                            const int32_t* __restrict__ tmp, int32_t* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (i >= N) return;
+    const int a = col_ptr[i], b = col_ptr[i + 1];
+    for (int p = a + lane; p < b; p += 32) {
+        const int v = tmp[p];
+        int rank = 0;
+        for (int q = a; q < b; ++q) rank += tmp[q] < v;
+        out[a + rank] = v;
+    }
+}
+
+__global__ void __launch_bounds__(256) batch_to_i32_kernel(const int64_t* __restrict__ batch, int N,
+                                                           int32_t* __restrict__ node_graph) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < N) node_graph[i] = (int32_t)batch[i];
+}
+
+inline unsigned blocks_for(int64_t n, int per) { return (unsigned)((n + per - 1) / per > 0 ? (n + per - 1) / per : 1); }
+
+}  // namespace
+
+extern "C" int egnn_build_edges_fc(const int32_t* node_ptr, int32_t G, int32_t N, int64_t E, int64_t* edge_index_out,
+                                   void* stream) {
+    EGNN_REQUIRE(G >= 0 && N >= 0 && E >= 0, "egnn_build_edges_fc: negative size");
+    if (G == 0 || E == 0) return EGNN_OK;
+    fc_edges_kernel<<<G, 256, 0, (cudaStream_t)stream>>>(node_ptr, G, E, edge_index_out);
+    EGNN_CHECK_LAUNCH("fc_edges_kernel");
+    return EGNN_OK;
+}
+
+extern "C" int egnn_cutoff_count(const float* pos, const int32_t* node_ptr, const int32_t* node_graph, const float* box,
+                                 float r_c, int32_t N, int32_t* deg_out, void* stream) {
+    if (N == 0) return EGNN_OK;
+    cutoff_kernel<false><<<blocks_for(N, 8), 256, 0, (cudaStream_t)stream>>>(pos, node_ptr, node_graph, box, r_c, N,
+                                                                            deg_out, nullptr, 0, nullptr);
+    EGNN_CHECK_LAUNCH("cutoff_kernel<count>");
+    return EGNN_OK;
+}
+
+extern "C" int egnn_cutoff_fill(const float* pos, const int32_t* node_ptr, const int32_t* node_graph, const float* box,
+                                float r_c, int32_t N, const int32_t* row_ptr, int64_t E, int64_t* edge_index_out,
+                                void* stream) {
+    if (N == 0 || E == 0) return EGNN_OK;
+    cutoff_kernel<true><<<blocks_for(N, 8), 256, 0, (cudaStream_t)stream>>>(pos, node_ptr, node_graph, box, r_c, N,
+                                                                           nullptr, row_ptr, E, edge_index_out);
+    EGNN_CHECK_LAUNCH("cutoff_kernel<fill>");
+    return EGNN_OK;
+}
+
+extern "C" int egnn_exclusive_scan_i32(const int32_t* in, int32_t n, int32_t* out, void* stream) {
+    EGNN_REQUIRE(n >= 0, "egnn_exclusive_scan_i32: negative n");
+    scan_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(in, n, out);
+    EGNN_CHECK_LAUNCH("scan_kernel");
+    return EGNN_OK;
+}
+
+extern "C" int egnn_graph_prepare(const int64_t* edge_index, int32_t N, int64_t E, int32_t* recv, int32_t* send,
+                                  int32_t* row_ptr, int32_t* col_ptr, int32_t* col_edge, int32_t* scratch,
+                                  int32_t* flags_out, void* stream) {
+    EGNN_REQUIRE(N >= 0 && E >= 0 && E < 2147483647LL, "egnn_graph_prepare: sizes out of range (N=%d E=%lld)", N,
+                 (long long)E);
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t* cnt = scratch;          // [N+1]
+    int32_t* tmp = scratch + N + 1;  // [E]
+    EGNN_CUDA(cudaMemsetAsync(flags_out, 0, 2 * sizeof(int32_t), st));
+    EGNN_CUDA(cudaMemsetAsync(cnt, 0, (size_t)(N + 1) * sizeof(int32_t), st));
+    if (E > 0) {
+        convert_edges_kernel<<<blocks_for(E, 256), 256, 0, st>>>(edge_index, N, E, recv, send, flags_out);
+        EGNN_CHECK_LAUNCH("convert_edges_kernel");
+    }
+    boundaries_kernel<int32_t><<<blocks_for(E + 1, 256), 256, 0, st>>>(recv, E, N, row_ptr);
+    EGNN_CHECK_LAUNCH("boundaries_kernel");
+    if (E > 0) {
+        count_senders_kernel<<<blocks_for(E, 256), 256, 0, st>>>(send, E, cnt);
+        EGNN_CHECK_LAUNCH("count_senders_kernel");
+    }
+    scan_kernel<<<1, 1024, 0, st>>>(cnt, N, col_ptr);
+    EGNN_CHECK_LAUNCH("scan_kernel");
+    if (E > 0) {
+        EGNN_CUDA(cudaMemsetAsync(cnt, 0, (size_t)(N + 1) * sizeof(int32_t), st));
+        fill_senders_kernel<<<blocks_for(E, 256), 256, 0, st>>>(send, E, col_ptr, cnt, tmp);
+        EGNN_CHECK_LAUNCH("fill_senders_kernel");
+        sort_segments_kernel<<<blocks_for(N, 8), 256, 0, st>>>(col_ptr, N, tmp, col_edge);
+        EGNN_CHECK_LAUNCH("sort_segments_kernel");
+    }
+    return EGNN_OK;
+}
+
+extern "C" int egnn_node_ptr_from_batch(const int64_t* batch, int32_t N, int32_t G, int32_t* node_ptr,
+                                        int32_t* node_graph, void* stream) {
+    EGNN_REQUIRE(N >= 0 && G >= 0, "egnn_node_ptr_from_batch: negative size");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (N > 0) {
+        batch_to_i32_kernel<<<blocks_for(N, 256), 256, 0, st>>>(batch, N, node_graph);
+        EGNN_CHECK_LAUNCH("batch_to_i32_kernel");
+    }
+    boundaries_kernel<int64_t><<<blocks_for((int64_t)N + 1, 256), 256, 0, st>>>(batch, N, G, node_ptr);
+    EGNN_CHECK_LAUNCH("boundaries_kernel<batch>");
+    return EGNN_OK;
+}
