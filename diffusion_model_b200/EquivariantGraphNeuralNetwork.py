@@ -1,0 +1,243 @@
+"""Drop-in for the reference module of the same name (EquivariantGraphNeuralNetwork.py:6-88): ``EGCL`` and
+``EquivariantGNN`` with the reference's constructor arguments, ``forward(edge_index, h, x) -> (h, x)`` and state_dict
+keys (``egcl_list.{l}.mlp_m.{0,2}``, ``.mlp_x.{0,2,4}``, ``.mlp_h.{0,2}``, ``.attention.0``), computed by the sm_100a
+kernels of libegnn_b200 through its C ABI.  There is no PyTorch fallback: CPU tensors raise.
+
+Extras that default to the reference behaviour:
+  * ``forward(..., batch=None, node_ptr=None, norm_scope='call')`` -- ``norm_scope='graph'`` evaluates the global
+    normaliser ``torch.norm(coords_i - coords_j)`` (:64) per graph, i.e. what the reference computes when it samples
+    one structure per call (parts/train_per_iretation.py:299-316);
+  * ``forward(h, x, edge_index, edge_attr=None)`` argument order (BASELINE.json wording) is recognised by dtype;
+  * ``precision`` attribute: 'fp32' (default), 'bf16x3', 'bf16'.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from ._lib import NORM, PREC, NetDesc, call, ptr, stream_ptr
+from .graph import GraphIndex, graph_index_for
+
+_PARAM_ORDER = ("mlp_m.0.weight", "mlp_m.0.bias", "mlp_m.2.weight", "mlp_m.2.bias",
+                "mlp_x.0.weight", "mlp_x.0.bias", "mlp_x.2.weight", "mlp_x.2.bias", "mlp_x.4.weight", "mlp_x.4.bias",
+                "mlp_h.0.weight", "mlp_h.0.bias", "mlp_h.2.weight", "mlp_h.2.bias",
+                "attention.0.weight", "attention.0.bias")
+
+
+class _FlatParams:
+    """Keeps a list of nn.Parameters as views of ONE contiguous fp32 buffer in the C ABI's layout, plus the packed
+    (transposed) copy the kernels read.  state_dict / optimizers keep seeing ordinary parameters."""
+
+    def __init__(self, params):
+        self.params = list(params)
+        self.flat = None
+        self.packed = None
+        self.packed_key = None
+
+    def ensure(self):
+        off, ok = 0, self.flat is not None
+        if ok:
+            base = self.flat.data_ptr()
+            for p in self.params:
+                if p.data_ptr() != base + 4 * off or p.device != self.flat.device or not p.is_contiguous():
+                    ok = False
+                    break
+                off += p.numel()
+        if not ok:
+            # already contiguous inside a larger flat buffer (an EGCL owned by an EquivariantGNN)? then just view it
+            p0 = self.params[0]
+            total = sum(p.numel() for p in self.params)
+            off, shared = 0, p0.dtype == torch.float32 and p0.is_cuda
+            for p in self.params:
+                if not shared:
+                    break
+                shared = (p.data_ptr() == p0.data_ptr() + 4 * off and p.is_contiguous()
+                          and p.untyped_storage().data_ptr() == p0.untyped_storage().data_ptr())
+                off += p.numel()
+            if shared and p0.untyped_storage().nbytes() >= 4 * (p0.storage_offset() + total):
+                self.flat = p0.data.as_strided((total,), (1,), p0.storage_offset())
+                self.packed_key = None
+                return self.flat
+        if not ok:
+            dev = self.params[0].device
+            for p in self.params:
+                if p.dtype != torch.float32:
+                    raise _lib.EgnnError("libegnn_b200 keeps fp32 master weights; got " + str(p.dtype))
+            flat = torch.empty(sum(p.numel() for p in self.params), dtype=torch.float32, device=dev)
+            off = 0
+            for p in self.params:
+                n = p.numel()
+                flat[off:off + n].copy_(p.detach().reshape(-1))
+                p.data = flat[off:off + n].view(p.shape)
+                off += n
+            self.flat = flat
+            self.packed_key = None
+        return self.flat
+
+    def packed_for(self, net):
+        flat = self.ensure()
+        key = (flat.data_ptr(), tuple(p._version for p in self.params))
+        if key != self.packed_key:
+            n = _lib.load().egnn_packed_count(C.byref(net))
+            if self.packed is None or self.packed.numel() != n or self.packed.device != flat.device:
+                self.packed = torch.empty(n, dtype=torch.float32, device=flat.device)
+            call("egnn_pack_weights", C.byref(net), ptr(flat), ptr(self.packed), stream_ptr(flat.device))
+            self.packed_key = key
+        return self.packed
+
+
+class _EGNNFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, h, x, owner, gi, norm_scope, precision, *params):
+        net, fp = owner._net, owner._flat
+        flat = fp.ensure()
+        packed = fp.packed_for(net)
+        h = h.contiguous().float()
+        x = x.contiguous().float()
+        N = h.shape[0]
+        if h.shape[1] != net.H or x.shape != (N, 3) or gi.N != N:
+            raise _lib.EgnnError(f"shape mismatch: h {tuple(h.shape)} x {tuple(x.shape)} for H={net.H}, N={gi.N}")
+        lib = _lib.load()
+        nws = lib.egnn_forward_workspace_floats(C.byref(net), gi.N, gi.E, gi.G)
+        need_grad = any(ctx.needs_input_grad)
+        ws = torch.empty(nws, dtype=torch.float32, device=h.device) if need_grad else owner._workspace(nws, h.device)
+        h_out = torch.empty_like(h)
+        x_out = torch.empty_like(x)
+        call("egnn_net_forward", C.byref(net), gi.ref(), ptr(flat), ptr(packed), ptr(h), ptr(x), ptr(h_out), ptr(x_out),
+             ptr(ws), nws, NORM[norm_scope], PREC[precision], stream_ptr(h.device))
+        if need_grad:
+            ctx.save_for_backward(h, x, ws, flat, packed)
+            ctx.meta = (owner, gi, norm_scope, precision)
+        return h_out, x_out
+
+    @staticmethod
+    def backward(ctx, gh, gx):
+        h, x, ws, flat, packed = ctx.saved_tensors
+        owner, gi, norm_scope, precision = ctx.meta
+        net = owner._net
+        lib = _lib.load()
+        gh = torch.zeros_like(h) if gh is None else gh.contiguous().float()
+        gx = torch.zeros_like(x) if gx is None else gx.contiguous().float()
+        nbw = lib.egnn_backward_workspace_floats(C.byref(net), gi.N, gi.E, gi.G)
+        bws = torch.empty(nbw, dtype=torch.float32, device=h.device)
+        gflat = torch.empty_like(flat)
+        gh_in = torch.empty_like(h)
+        gx_in = torch.empty_like(x)
+        call("egnn_net_backward", C.byref(net), gi.ref(), ptr(flat), ptr(packed), ptr(h), ptr(x), ptr(ws), ptr(gh),
+             ptr(gx), ptr(gh_in), ptr(gx_in), ptr(gflat), ptr(bws), nbw, NORM[norm_scope], PREC[precision],
+             stream_ptr(h.device))
+        owner._last_grad_flat = gflat
+        grads, off = [], 0
+        for p in owner._flat.params:
+            n = p.numel()
+            grads.append(gflat[off:off + n].view(p.shape))
+            off += n
+        return (gh_in, gx_in, None, None, None, None) + tuple(grads)
+
+
+class _KernelBacked(nn.Module):
+    """Shared plumbing of EGCL (one layer) and EquivariantGNN (L layers)."""
+
+    precision = "fp32"
+
+    def _setup(self, L, layers, sizes):
+        m_input, m_hidden, m_output, x_input, x_hidden, x_output, h_input, h_hidden, h_output = sizes
+        H = h_output
+        if m_input != 2 * H + 1 or x_input != 2 * H + 1:
+            raise ValueError(f"m_input and x_input must equal 2*h_output+1 = {2 * H + 1} (message input is "
+                             "cat(h_i, h_j, d^2), EquivariantGraphNeuralNetwork.py:56)")
+        if h_input != H + m_output:
+            raise ValueError("h_input must equal h_output + m_output (mlp_h input is cat(h, sum_message), :69)")
+        if x_output != 1:
+            raise ValueError("x_output must be 1 (phi_x is a scalar per edge, :64)")
+        object.__setattr__(self, "_net", NetDesc(L, H, m_hidden, m_output, x_hidden, h_hidden))
+        plist = []
+        for layer in layers:
+            named = dict(layer.named_parameters())
+            plist += [named[k] for k in _PARAM_ORDER]
+        object.__setattr__(self, "_flat", _FlatParams(plist))
+        object.__setattr__(self, "_ws", {})
+        object.__setattr__(self, "_last_grad_flat", None)
+
+    def _workspace(self, n, device):
+        w = self._ws.get((n, device))
+        if w is None:
+            self._ws.clear()
+            w = self._ws[(n, device)] = torch.empty(n, dtype=torch.float32, device=device)
+        return w
+
+    def forward_into(self, graph, h, x, h_out, x_out, norm_scope="call"):
+        """Inference-only launch into caller-owned buffers (no autograd, no allocation: CUDA-graph capturable)."""
+        net = self._net
+        flat = self._flat.ensure()
+        packed = self._flat.packed_for(net)
+        nws = _lib.load().egnn_forward_workspace_floats(C.byref(net), graph.N, graph.E, graph.G)
+        ws = self._workspace(nws, h.device)
+        call("egnn_net_forward", C.byref(net), graph.ref(), ptr(flat), ptr(packed), ptr(h, torch.float32),
+             ptr(x, torch.float32), ptr(h_out), ptr(x_out), ptr(ws), nws, NORM[norm_scope], PREC[self.precision],
+             stream_ptr(h.device))
+        return h_out, x_out
+
+    def flat_parameters(self):
+        """The contiguous fp32 parameter buffer (C-ABI layout) all parameters are views of."""
+        return self._flat.ensure()
+
+    def _run(self, a, b, c, batch=None, node_ptr=None, norm_scope="call", graph=None):
+        if torch.is_floating_point(a):  # forward(h, x, edge_index[, edge_attr]) wording of BASELINE.json
+            h, x, edge_index = a, b, c
+        else:
+            edge_index, h, x = a, b, c
+        if not (h.is_cuda and x.is_cuda):
+            raise _lib.EgnnError("EquivariantGNN runs on CUDA tensors only (no CPU fallback); move the inputs to 'cuda'")
+        if self._flat.params[0].device != h.device:
+            raise _lib.EgnnError("module parameters and inputs are on different devices; call .to('cuda') first")
+        if graph is None:
+            edge_index = edge_index.to(h.device)
+            graph = graph_index_for(edge_index, h.shape[0], batch=batch, node_ptr=node_ptr)
+        return _EGNNFunction.apply(h, x, self, graph, norm_scope, self.precision, *self._flat.params)
+
+
+def _linear_stack(*dims_and_acts):
+    return nn.Sequential(*dims_and_acts)
+
+
+class EGCL(_KernelBacked):
+    """One equivariant graph convolution layer (EquivariantGraphNeuralNetwork.py:6-71)."""
+
+    def __init__(self, m_input, m_hidden, m_output, x_input, x_hidden, x_output, h_input, h_hidden, h_output,
+                 flow="target_to_source", aggr="sum", activation="SiLU"):
+        super().__init__()
+        if flow != "target_to_source" or aggr != "sum" or activation != "SiLU":
+            raise ValueError("only flow='target_to_source', aggr='sum', activation='SiLU' (the reference defaults)")
+        self.flow, self.aggr = flow, aggr
+        # construction order == the reference's (mlp_m, mlp_x, mlp_h, attention): same seed -> same initial weights
+        self.mlp_m = nn.Sequential(nn.Linear(m_input, m_hidden), nn.SiLU(), nn.Linear(m_hidden, m_output), nn.SiLU())
+        self.mlp_x = nn.Sequential(nn.Linear(x_input, x_hidden), nn.SiLU(), nn.Linear(x_hidden, x_hidden), nn.SiLU(),
+                                   nn.Linear(x_hidden, x_output))
+        self.mlp_h = nn.Sequential(nn.Linear(h_input, h_hidden), nn.SiLU(), nn.Linear(h_hidden, h_output))
+        self.attention = nn.Sequential(nn.Linear(m_output, 1), nn.Sigmoid())
+        self._sizes = (m_input, m_hidden, m_output, x_input, x_hidden, x_output, h_input, h_hidden, h_output)
+        self._setup(1, [self], self._sizes)
+
+    def forward(self, edge_index, h, coords, **kw):
+        return self._run(edge_index, h, coords, **kw)
+
+
+class EquivariantGNN(_KernelBacked):
+    """L stacked EGCLs (EquivariantGraphNeuralNetwork.py:73-88)."""
+
+    def __init__(self, L, m_input, m_hidden, m_output, x_input, x_hidden, x_output, h_input, h_hidden, h_output):
+        super().__init__()
+        self.L = L
+        sizes = (m_input, m_hidden, m_output, x_input, x_hidden, x_output, h_input, h_hidden, h_output)
+        self.egcl_list = nn.ModuleList([EGCL(*sizes) for _ in range(L)])
+        self._setup(L, list(self.egcl_list), sizes)
+
+    def forward(self, edge_index, h, x, edge_attr=None, **kw):
+        return self._run(edge_index, h, x, **kw)
+
+
+__all__ = ["EGCL", "EquivariantGNN", "GraphIndex"]

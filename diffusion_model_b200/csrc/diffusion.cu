@@ -133,8 +133,8 @@ struct StepArgs {
     const float *x_out, *h_out, *noise_x, *noise_h;
     const float* coef;     // device [T+1][8]: a_ts, s2_ts, sig_t, std, t_next column, alpha_0, sigma_0, -
     const int32_t* t_dev;  // current t (device), NULL when final
-    int t_base;
-    long long stride_x, stride_h;  // noise of step t lives at noise + (t_base - t) * stride
+    int t_base, period;
+    long long stride_x, stride_h;  // noise of step t lives at noise + ((t_base - t) % period) * stride
     float onehot_scale;
     const int32_t* node_ptr;
     int H, A, final_step;
@@ -148,8 +148,10 @@ __global__ void __launch_bounds__(256) sampler_step_kernel(StepArgs p) {
     if (a >= b) return;
     const int t = p.final_step ? 0 : *p.t_dev;
     const float* cf = p.coef + 8 * t;
-    const float* nx = p.noise_x + (p.final_step ? 0 : (long long)(p.t_base - t) * p.stride_x);
-    const float* nh = p.noise_h + (p.final_step ? 0 : (long long)(p.t_base - t) * p.stride_h);
+    int slot = p.final_step ? 0 : p.t_base - t;
+    if (p.period > 0) slot %= p.period;
+    const float* nx = p.noise_x + (long long)slot * p.stride_x;
+    const float* nh = p.noise_h + (long long)slot * p.stride_h;
     float dmean[3], nmean[3];
     graph_mean3(p.x_out, p.z_x, 3, a, b, red, dmean);  // eps_x = P(x' - z_x)
     graph_mean3(nx, nullptr, 3, a, b, red, nmean);     // noise is made COM-free for positions
@@ -259,14 +261,14 @@ extern "C" int egnn_loss_fwd_bwd(const float* x_out, const float* h_out, const f
 
 extern "C" int egnn_sampler_step(float* z_x, float* h_in, const float* x_out, const float* h_out, const float* noise_x,
                                  const float* noise_h, const float* coef, const int32_t* t_dev, int32_t t_base,
-                                 int64_t noise_stride_x, int64_t noise_stride_h, float onehot_scale,
-                                 const int32_t* node_ptr, int32_t G, int32_t H, int32_t A, int32_t final_step,
+                                 int64_t noise_stride_x, int64_t noise_stride_h, int32_t noise_period,
+                                 float onehot_scale, const int32_t* node_ptr, int32_t G, int32_t H, int32_t A, int32_t final_step,
                                  float* z_h_out, int32_t* finite_flag, void* stream) {
     EGNN_REQUIRE(z_x && h_in && x_out && h_out && noise_x && noise_h && coef && node_ptr && finite_flag,
                  "egnn_sampler_step: NULL pointer");
     EGNN_REQUIRE(final_step ? z_h_out != nullptr : t_dev != nullptr, "egnn_sampler_step: t_dev / z_h_out missing");
     EGNN_REQUIRE(G >= 1 && H >= 1 && A >= 1 && A < H, "egnn_sampler_step: bad sizes");
-    StepArgs p{z_x, h_in, x_out, h_out, noise_x, noise_h, coef, t_dev, t_base, noise_stride_x, noise_stride_h,
+    StepArgs p{z_x, h_in, x_out, h_out, noise_x, noise_h, coef, t_dev, t_base, noise_period, noise_stride_x, noise_stride_h,
                onehot_scale, node_ptr, H, A, final_step, z_h_out, finite_flag};
     sampler_step_kernel<<<G, 256, 0, (cudaStream_t)stream>>>(p);
     EGNN_CHECK_LAUNCH("sampler_step_kernel");

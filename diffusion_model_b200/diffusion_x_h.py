@@ -1,0 +1,158 @@
+"""Drop-in for the reference's diffusion_x_h.py: ``remove_mean`` and ``E3DiffusionProcess`` (joint x+h diffusion).
+
+Same constructor, attributes (``alpha_schedule``, ``sigma_schedule``, ``t``, ``num_diffusion_timestep``) and methods
+(``alpha``, ``sigma``, ``diffuse_zero_to_t``, ``calculate_mu``, ``reverse_diffuse_one_step``) as diffusion_x_h.py:16-106.
+The schedule tables are built once, on the host, by the reference's own formulae (:92-106; the array the reference
+calls ``alphas2`` is used as alpha, :25-26).  Centre-of-mass removal and the batched hot loops run in libegnn_b200
+kernels; ``loss()`` and ``sample()`` are the fused entry points BASELINE.json's wording asks for.
+Only ``noise_schedule='predefined'`` is supported (the learned gamma network, SNR.py, is outside the hot path).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import call, ptr, stream_ptr
+
+I32 = torch.int32
+
+
+def _node_ptr_of(batch_index):
+    """int32 [G+1] boundaries of a non-decreasing PyG ``batch`` vector (one host sync for G, as the reference :9)."""
+    N = batch_index.numel()
+    G = int(batch_index.max().item()) + 1
+    b = batch_index.to(torch.int64).contiguous()
+    node_ptr = torch.empty(G + 1, dtype=I32, device=b.device)
+    node_graph = torch.empty(N, dtype=I32, device=b.device)
+    call("egnn_node_ptr_from_batch", ptr(b), N, G, ptr(node_ptr), ptr(node_graph), stream_ptr(b.device))
+    return node_ptr, G
+
+
+class _RemoveMean(torch.autograd.Function):
+    """x <- x - per-graph column mean.  The projector is symmetric and idempotent, so backward applies it to the grad."""
+
+    @staticmethod
+    def forward(ctx, x, node_ptr, G, inplace):
+        if not x.is_cuda:
+            raise _lib.EgnnError("remove_mean runs on CUDA tensors only (no CPU fallback)")
+        if inplace:
+            if not x.is_contiguous() or x.dtype != torch.float32:
+                raise _lib.EgnnError("in-place remove_mean needs a contiguous fp32 tensor")
+            ctx.mark_dirty(x)
+            out = x
+        else:
+            out = x.detach().float().contiguous().clone()
+        call("egnn_remove_mean", ptr(out), out.shape[1], ptr(node_ptr), G, stream_ptr(out.device))
+        ctx.node_ptr, ctx.G = node_ptr, G
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        g = g.contiguous().float().clone()
+        call("egnn_remove_mean", ptr(g), g.shape[1], ptr(ctx.node_ptr), ctx.G, stream_ptr(g.device))
+        return g, None, None, None
+
+
+def remove_mean(x, batch_index=None):
+    """diffusion_x_h.py:5-14.  Global mean -> new tensor; with ``batch_index`` the per-graph means are removed IN PLACE."""
+    if x.dim() != 2:
+        raise ValueError("remove_mean expects a [N,C] tensor")
+    if batch_index is None:
+        node_ptr = torch.tensor([0, x.shape[0]], dtype=I32, device=x.device)
+        return _RemoveMean.apply(x, node_ptr, 1, False)
+    node_ptr, G = _node_ptr_of(batch_index.to(x.device))
+    return _RemoveMean.apply(x, node_ptr, G, True)
+
+
+def remove_mean_ptr(x, node_ptr, inplace=True):
+    """Same projector with precomputed int32 graph boundaries (no host sync)."""
+    return _RemoveMean.apply(x, node_ptr, node_ptr.numel() - 1, inplace)
+
+
+class E3DiffusionProcess(torch.nn.Module):
+    def __init__(self, s, power, num_diffusion_timestep: int, noise_schedule: str = "predefined"):
+        super().__init__()
+        if noise_schedule != "predefined":
+            raise NotImplementedError("only noise_schedule='predefined' (SNR.GammaNetwork is outside the hot path)")
+        self.noise_schedule = noise_schedule
+        self.noise_precision = s
+        self.power = power
+        self.num_diffusion_timestep = num_diffusion_timestep
+        T = num_diffusion_timestep
+        self.t = torch.linspace(0, T, T + 1, device="cpu")
+        self.alpha_schedule = self.polynomial_schedule(T, s=s, power=power)
+        self.sigma_schedule = torch.sqrt(1 - self.alpha_schedule ** 2)
+        self._dev = {}
+
+    # -- schedule (diffusion_x_h.py:92-106) -----------------------------------------------------------------
+    def clip_noise_schedule(self, alphas2, clip_value=0.001):
+        alphas2 = torch.cat([torch.ones(1, device="cpu"), alphas2], dim=0)
+        step = torch.clamp(alphas2[1:] / alphas2[:-1], min=clip_value, max=1.0)
+        return torch.cumprod(step, dim=0)
+
+    def polynomial_schedule(self, timesteps: int, s=1e-4, power=3.0):
+        x = torch.linspace(0, timesteps, timesteps + 1, device="cpu")
+        a = torch.pow(1 - torch.pow(x / timesteps, power), 2)
+        a = self.clip_noise_schedule(a, clip_value=0.001)
+        return (1 - 2 * s) * a + s
+
+    def alpha(self, t: int):
+        return self.alpha_schedule[t]
+
+    def sigma(self, t: int):
+        return self.sigma_schedule[t]
+
+    def step_scalars(self, t: int):
+        """(alpha_ts, sigma2_ts, sigma_t, std) as fp32 CPU scalars, computed exactly as :61-84 does."""
+        a_t, a_s = self.alpha(t), self.alpha(t - 1)
+        s2_t, s2_s = 1 - a_t ** 2, 1 - a_s ** 2
+        a_ts = a_t / a_s
+        s2_ts = s2_t - torch.pow(a_ts, 2) * s2_s
+        return a_ts, s2_ts, torch.sqrt(s2_t), torch.sqrt(s2_ts * s2_s / s2_t)
+
+    def device_tables(self, device):
+        """(alpha [T+1], sigma [T+1], coef [T+1,8]) on `device`; coef row t = a_ts, s2_ts, sig_t, std, (t-1)/T, a0, s0, 0."""
+        device = torch.device(device)
+        tabs = self._dev.get(device)
+        if tabs is None:
+            T = self.num_diffusion_timestep
+            coef = torch.zeros(T + 1, 8, dtype=torch.float32)
+            for t in range(1, T + 1):
+                a_ts, s2_ts, sig_t, std = self.step_scalars(t)
+                coef[t, 0], coef[t, 1], coef[t, 2], coef[t, 3] = a_ts, s2_ts, sig_t, std
+                coef[t, 4] = torch.tensor((t - 1) / T, dtype=torch.float32)  # generate():340 python float -> fp32
+            coef[:, 5], coef[:, 6] = self.alpha(0), self.sigma(0)
+            tabs = (self.alpha_schedule.to(device).contiguous(), self.sigma_schedule.to(device).contiguous(),
+                    coef.to(device).contiguous())
+            self._dev[device] = tabs
+        return tabs
+
+    # -- single-graph API of the reference (:51-90) ------------------------------------------------------------
+    def diffuse_zero_to_t(self, z, t: int, mode="pos"):
+        noise = torch.zeros_like(z, dtype=torch.float).normal_(mean=0, std=1)
+        if mode == "pos":
+            noise = remove_mean(noise)
+        return self.alpha(t).to(z.device) * z + self.sigma(t).to(z.device) * noise, noise
+
+    def calculate_mu(self, z, epsilon, t: int):
+        a_ts, s2_ts, sig_t, _ = (v.to(z.device) for v in self.step_scalars(t))
+        return z / a_ts - s2_ts * epsilon / a_ts / sig_t
+
+    def reverse_diffuse_one_step(self, z, epsilon, t: int, mode="pos"):
+        mu = self.calculate_mu(z, epsilon, t)
+        std = self.step_scalars(t)[3].to(z.device)
+        noise = torch.zeros_like(z).normal_(mean=0, std=1)
+        if mode == "pos":
+            noise = remove_mean(noise)
+        return mu + std * noise
+
+    # -- fused entry points -------------------------------------------------------------------------------------
+    def loss(self, egnn, batch_data, params=None, t=None, noise_pos=None, noise_h=None, cond=None):
+        """eps-prediction loss of one minibatch (parts/train_per_iretation.py:130-169) -> scalar tensor with grad."""
+        from .train_per_iretation import batch_loss
+        return batch_loss(egnn, batch_data, self, params or {}, t=t, noise_pos=noise_pos, noise_h=noise_h, cond=cond)[0]
+
+    def sample(self, egnn, num_atoms, num_structures=1, **kw):
+        """Ancestral sampling of `num_structures` structures of `num_atoms` atoms in ONE batched call."""
+        from .sampler import sample_structures
+        return sample_structures(egnn, self, num_atoms, num_structures, **kw)

@@ -144,14 +144,15 @@ int egnn_loss_fwd_bwd(const float* x_out, const float* h_out, const float* z_x, 
  * coef: DEVICE table [T+1][8], row t = {a_ts, s2_ts, sig_t, std, time column of t-1, alpha_0, sigma_0, 0}, filled on
  * the host by the reference's own fp32 formulae (diffusion_x_h.py:61-84).  The current t is read from *t_dev so that
  * one captured CUDA graph of a step can be replayed for every t (egnn_counter_add decrements it); the noise of step t
- * is read at noise + (t_base - t) * noise_stride (stride 0: the caller refills one buffer per step).
+ * is read at noise + ((t_base - t) mod noise_period) * noise_stride (noise_period 0: no wrap; the caller refills the
+ * ring between replays).
  * final_step != 0 selects the t = 0 form (parts/train_per_iretation.py:416-426): z <- z/a0 - s0*eps/a0 + s0*noise/a0,
  * positions in place, atom-type logits to z_h_out [N,A]; t_dev is not read.
  * finite_flag [G] is cleared for a graph when anything written for it is not finite (:376-389). */
 int egnn_sampler_step(float* z_x, float* h_in, const float* x_out, const float* h_out, const float* noise_x,
                       const float* noise_h, const float* coef, const int32_t* t_dev, int32_t t_base,
-                      int64_t noise_stride_x, int64_t noise_stride_h, float onehot_scale, const int32_t* node_ptr,
-                      int32_t G, int32_t H, int32_t A, int32_t final_step, float* z_h_out, int32_t* finite_flag,
+                      int64_t noise_stride_x, int64_t noise_stride_h, int32_t noise_period, float onehot_scale,
+                      const int32_t* node_ptr, int32_t G, int32_t H, int32_t A, int32_t final_step, float* z_h_out, int32_t* finite_flag,
                       void* stream);
 int egnn_counter_add(int32_t* counter, int32_t delta, void* stream);
 

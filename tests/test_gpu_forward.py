@@ -1,0 +1,267 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA path, called through the C ABI, against the golden
+vectors frozen from the unmodified reference and against the CPU oracle on the same seeded inputs.
+
+Bars: bit-exact for edge lists and index structures; fp32 mode max|err|/max|ref| <= 1e-4 per layer (BASELINE north_star).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import diffusion_ref as D
+from oracle import egnn_ref, graphs_ref as G, loops_ref as LP
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+TOL = 1e-4
+
+
+def load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + ".npz"), allow_pickle=False)
+
+
+def state_dict_of(z):
+    return {k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w:")}
+
+
+def sizes_of(z):
+    return {str(k): int(v) for k, v in zip(z["size_keys"], z["sizes"])}
+
+
+def relerr(a, b):
+    a, b = torch.as_tensor(a).detach().cpu().double(), torch.as_tensor(b).detach().cpu().double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def make_net(z):
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    net = EquivariantGNN(**sizes_of(z))
+    net.load_state_dict(state_dict_of(z))
+    return net.to(DEV)
+
+
+# ---------------------------------------------------------------- edge builders: bit exact
+def test_fc_edges_bit_exact(lib, golden_dir):
+    from diffusion_model_b200.graph import build_edges_fc
+    z = load(golden_dir, "edges")
+    for n in (2, 5, 24):
+        assert np.array_equal(build_edges_fc([n]).cpu().numpy(), z[f"fc_{n}"].reshape(2, -1))
+    assert build_edges_fc([1]).shape == (2, 0)
+    sizes = [3, 1, 24, 7, 192]
+    assert np.array_equal(build_edges_fc(sizes).cpu().numpy(), G.fc_edges_batch(sizes))
+
+
+def test_cutoff_edges_bit_exact(lib, golden_dir):
+    from diffusion_model_b200.graph import build_edges_cutoff
+    z = load(golden_dir, "edges")
+    for k in ("dense", "lattice"):
+        e = build_edges_cutoff(torch.from_numpy(z[f"open_{k}_pos"]).to(DEV), 2.0)
+        assert np.array_equal(e.cpu().numpy(), z[f"open_{k}_edges"]), k
+    e = build_edges_cutoff(torch.from_numpy(z["per_pos"]).to(DEV), 5.0,
+                           node_ptr=torch.from_numpy(z["per_graph_ptr"]), box=torch.from_numpy(z["per_boxes"]))
+    assert np.array_equal(e.cpu().numpy(), z["per_edges"])
+    # near-cutoff stress: pairs within a few ulp of r_c, oracle as the checker
+    rng = np.random.default_rng(3)
+    v = rng.normal(size=(300, 3)).astype(np.float32)
+    v *= (np.float32(2.0) / np.linalg.norm(v.astype(np.float64), axis=1)).astype(np.float32)[:, None]
+    v[::2] = np.nextafter(v[::2], np.float32(3.0))
+    pos = np.concatenate([np.zeros((1, 3), np.float32), v])
+    e = build_edges_cutoff(torch.from_numpy(pos).to(DEV), 2.0)
+    assert np.array_equal(e.cpu().numpy(), G.cutoff_edges(pos, 2.0, None, fallback=False))
+    # full-size config-2 shaped batch (64 x 192 atoms, periodic 5 A): against the oracle
+    b = G.make_batch(8, 192, seed=5, edges="cutoff_periodic")
+    e = build_edges_cutoff(torch.from_numpy(b["pos"]).to(DEV), 5.0, node_ptr=torch.from_numpy(b["graph_ptr"]),
+                           box=torch.from_numpy(b["boxes"]))
+    assert np.array_equal(e.cpu().numpy(), b["edge_index"])
+
+
+def test_graph_index_structures(lib):
+    from diffusion_model_b200.graph import GraphIndex
+    from diffusion_model_b200 import EgnnError
+    b = G.make_batch(3, 40, seed=9, edges="cutoff_open", r_c=4.0)
+    ei = torch.from_numpy(b["edge_index"]).to(DEV)
+    N, E = b["pos"].shape[0], ei.shape[1]
+    gi = GraphIndex(ei, N, batch=torch.from_numpy(b["batch"]).to(DEV))
+    recv, send = b["edge_index"]
+    assert np.array_equal(gi.recv[:E].cpu().numpy(), recv) and np.array_equal(gi.send[:E].cpu().numpy(), send)
+    row_ptr = np.searchsorted(recv, np.arange(N + 1))
+    assert np.array_equal(gi.row_ptr.cpu().numpy(), row_ptr)
+    order = np.argsort(send, kind="stable")
+    col_ptr = np.searchsorted(send[order], np.arange(N + 1))
+    assert np.array_equal(gi.col_ptr.cpu().numpy(), col_ptr)
+    assert np.array_equal(gi.col_edge[:E].cpu().numpy(), order)
+    assert np.array_equal(gi.node_ptr.cpu().numpy(), b["graph_ptr"])
+    with pytest.raises(EgnnError):
+        GraphIndex(ei.flip(1).contiguous(), N)
+    with pytest.raises(EgnnError):
+        GraphIndex(ei + 1000, N)
+    gi0 = GraphIndex(torch.zeros(2, 0, dtype=torch.int64, device=DEV), 5)  # empty edge list
+    assert gi0.row_ptr.tolist() == [0] * 6
+
+
+# ---------------------------------------------------------------- EGNN forward, fp32 mode
+@pytest.mark.parametrize("name", ["cfg1", "cfg2", "cfg4", "ragged"])
+def test_egnn_forward_matches_reference_layers(lib, golden_dir, name):
+    z = load(golden_dir, "egnn_" + name)
+    net = make_net(z)
+    L = sizes_of(z)["L"]
+    h = torch.from_numpy(z["h"]).to(DEV)
+    x = torch.from_numpy(z["x"]).to(DEV)
+    ei = torch.from_numpy(z["edge_index"]).to(DEV)
+    batch = torch.from_numpy(z["batch"]).to(DEV)
+    with torch.no_grad():
+        hh, xx = h, x
+        for l in range(L):  # layer by layer through the EGCL drop-in, fed with the reference's previous output
+            hh, xx = net.egcl_list[l](ei, torch.from_numpy(z[f"h_l{l - 1}"]).to(DEV) if l else h,
+                                      torch.from_numpy(z[f"x_l{l - 1}"]).to(DEV) if l else x)
+            assert relerr(hh, z[f"h_l{l}"]) <= TOL, (name, l, relerr(hh, z[f"h_l{l}"]))
+            assert relerr(xx, z[f"x_l{l}"]) <= TOL, (name, l, relerr(xx, z[f"x_l{l}"]))
+        ho, xo = net(ei, h, x)
+        assert relerr(ho, z[f"h_l{L - 1}"]) <= TOL and relerr(xo, z[f"x_l{L - 1}"]) <= TOL
+        h2, x2 = net(h, x, ei)  # north_star argument order
+        assert torch.equal(h2, ho) and torch.equal(x2, xo)
+        hg, xg = net(ei, h, x, batch=batch, norm_scope="graph")
+        assert relerr(hg, z["h_graph"]) <= TOL and relerr(xg, z["x_graph"]) <= TOL
+        # bit-identical reruns (no atomics, fixed reduction order)
+        h3, x3 = net(ei, h, x)
+        assert torch.equal(h3, ho) and torch.equal(x3, xo)
+
+
+def test_egnn_forward_edge_cases(lib):
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    torch.manual_seed(0)
+    sz = egnn_ref.net_sizes(2, 32)
+    net = EquivariantGNN(**sz).to(DEV)
+    sd = {k: v.detach().cpu() for k, v in net.state_dict().items()}
+    gen = torch.Generator().manual_seed(1)
+    # (a) isolated nodes + a 300-edge receiver crossing tile boundaries; (b) no edges at all
+    n = 320
+    recv = np.concatenate([np.full(300, 2), np.full(5, 7), np.full(200, 9)]).astype(np.int64)
+    send = np.concatenate([np.arange(10, 310), np.arange(0, 5), np.arange(100, 300)]).astype(np.int64)
+    for ei in (torch.from_numpy(np.stack([recv, send])), torch.zeros(2, 0, dtype=torch.int64)):
+        h, x = torch.randn(n, 3, generator=gen), torch.randn(n, 3, generator=gen)
+        with torch.no_grad():
+            ho, xo = net(ei.to(DEV), h.to(DEV), x.to(DEV))
+            hr, xr = egnn_ref.egnn_forward(sd, 2, ei, h, x)
+        assert relerr(ho, hr) <= TOL and relerr(xo, xr) <= TOL
+
+
+# ---------------------------------------------------------------- diffusion kernels
+def test_remove_mean(lib, golden_dir):
+    from diffusion_model_b200.diffusion_x_h import remove_mean
+    z = load(golden_dir, "diffusion_kat")
+    x = torch.from_numpy(z["rm_in"]).to(DEV)
+    out = remove_mean(x, torch.from_numpy(z["rm_batch"]).to(DEV))
+    assert out.data_ptr() == x.data_ptr()  # in place, like the reference
+    assert np.array_equal(out.cpu().numpy(), z["rm_out"])
+    assert np.array_equal(remove_mean(torch.from_numpy(z["rm_in"]).to(DEV)).cpu().numpy(), z["rm_out_global"])
+    gen = torch.Generator().manual_seed(4)
+    big = torch.randn(1000, 3, generator=gen)
+    b = torch.repeat_interleave(torch.arange(5), 200)
+    ref = D.remove_mean(big.clone(), b)
+    got = remove_mean(big.clone().to(DEV), b.to(DEV))
+    assert relerr(got, ref) < 1e-6
+
+
+def test_schedule_and_step_scalars(lib, golden_dir):
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    z = load(golden_dir, "diffusion_kat")
+    dp = E3DiffusionProcess(s=float(z["s"]), power=float(z["power"]), num_diffusion_timestep=int(z["T"]))
+    assert np.array_equal(dp.alpha_schedule.numpy(), z["alpha"]) and np.array_equal(dp.sigma_schedule.numpy(), z["sigma"])
+    _, _, coef = dp.device_tables(DEV)
+    for t in z["ts"].tolist():
+        assert np.array_equal(coef[t, :4].cpu().numpy(), z[f"t{t}_scalars"])
+    assert np.array_equal(coef[1:, 4].cpu().numpy(), z["time_col"][:-1])
+
+
+def test_sampler_step_kernel(lib, golden_dir):
+    from diffusion_model_b200._lib import call, ptr, stream_ptr
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    z = load(golden_dir, "diffusion_kat")
+    T = int(z["T"])
+    sch = D.Schedule(float(z["s"]), float(z["power"]), T)
+    dp = E3DiffusionProcess(s=float(z["s"]), power=float(z["power"]), num_diffusion_timestep=T)
+    _, _, coef = dp.device_tables(DEV)
+    gen = torch.Generator().manual_seed(8)
+    S, n, A, H = 3, 24, 2, 3
+    N = S * n
+    node_ptr = (torch.arange(S + 1) * n).to(torch.int32).to(DEV)
+    batch = torch.repeat_interleave(torch.arange(S), n)
+    for t in (1000, 500, 1):
+        z_x, x_out = torch.randn(N, 3, generator=gen), torch.randn(N, 3, generator=gen)
+        h_in, h_out = torch.randn(N, H, generator=gen), torch.randn(N, H, generator=gen)
+        nx, nh = torch.randn(N, 3, generator=gen), torch.randn(N, A, generator=gen)
+        # oracle, structure by structure
+        ex, eh_ = [], []
+        for s_ in range(S):
+            sl = slice(s_ * n, (s_ + 1) * n)
+            eps = D.remove_mean(x_out[sl] - z_x[sl])
+            ex.append(D.reverse_diffuse_one_step(sch, z_x[sl], eps, t, nx[sl].clone(), "pos"))
+            eh_.append(D.reverse_diffuse_one_step(sch, h_in[sl, :A], h_out[sl, :A], t, nh[sl].clone(), "h"))
+        zx_d, hin_d = z_x.to(DEV), h_in.to(DEV)
+        xo_d, ho_d, nx_d, nh_d = x_out.to(DEV), h_out.to(DEV), nx.to(DEV), nh.to(DEV)  # keep alive across the launch
+        finite = torch.ones(S, dtype=torch.int32, device=DEV)
+        t_dev = torch.tensor([t], dtype=torch.int32, device=DEV)
+        call("egnn_sampler_step", ptr(zx_d), ptr(hin_d), ptr(xo_d), ptr(ho_d), ptr(nx_d), ptr(nh_d), ptr(coef),
+             ptr(t_dev), t, 0, 0, 0, 1.0, ptr(node_ptr), S, H, A, 0, None, ptr(finite), stream_ptr())
+        assert torch.equal(hin_d[:, :A].cpu(), torch.cat(eh_))  # h mode: bit exact (no reduction involved)
+        assert relerr(zx_d, torch.cat(ex)) < 2e-6
+        assert torch.equal(hin_d[:, H - 1].cpu(), torch.full((N,), (t - 1) / T, dtype=torch.float32))
+        assert finite.tolist() == [1] * S
+    # non-finite input of structure 1 clears only its flag
+    zx_d = torch.randn(N, 3, generator=gen).to(DEV)
+    zx_d[n + 3, 0] = float("nan")
+    finite = torch.ones(S, dtype=torch.int32, device=DEV)
+    call("egnn_sampler_step", ptr(zx_d), ptr(hin_d), ptr(xo_d), ptr(ho_d), ptr(nx_d), ptr(nh_d), ptr(coef),
+         ptr(t_dev), 1, 0, 0, 0, 1.0, ptr(node_ptr), S, H, A, 0, None, ptr(finite), stream_ptr())
+    assert finite.tolist() == [1, 0, 1]
+
+
+def test_diffuse_as_batch_against_oracle(lib, golden_dir):
+    from diffusion_model_b200.data import Batch, Data
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.train_per_iretation import diffuse_as_batch
+    z = load(golden_dir, "loss_cfg1")
+    dp = E3DiffusionProcess(s=1e-5, power=2.0, num_diffusion_timestep=1000)
+    sch = D.Schedule(1e-5, 2.0, 1000)
+    pos, x1h, batch = torch.from_numpy(z["pos"]), torch.from_numpy(z["x"]), torch.from_numpy(z["batch"])
+    bd = Data(x=x1h.to(DEV), pos=pos.to(DEV), edge_index=torch.from_numpy(z["edge_index"]).to(DEV))
+    bd.batch = batch.to(DEV)
+    t = z["t"].tolist()
+    out = diffuse_as_batch(bd, bd.batch, dict(num_diffusion_timestep=1000, spectrum_size=0, onehot_scaling_factor=1.0),
+                           dp, t=t, noise_pos=torch.from_numpy(z["noise_pos"]).to(DEV),
+                           noise_h=torch.from_numpy(z["noise_h"]).to(DEV))
+    assert relerr(out.pos_at_t, z["pos_t"]) < 1e-6
+    assert relerr(out.y_for_noise_pos, z["eps_pos"]) < 1e-6
+    assert torch.equal(out.h_at_t.cpu(), torch.from_numpy(z["h_in"][:, :2]))  # bit exact: no reduction
+    assert out.each_time_list.shape == (96, 1) and out.each_time_list[:, 0].cpu().tolist() == sum([[q] * 24 for q in t], [])
+
+
+def test_trajectory_matches_reference(lib, golden_dir):
+    """T = 1000 ancestral steps of one 24-atom structure with injected noise, against the trajectory the unmodified
+    reference modules produced (oracle/make_golden.py: tamed weights, s = 0.05)."""
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.sampler import sample_structures
+    zt = load(golden_dir, "traj_cfg1")
+    zl = load(golden_dir, "loss_cfg1")
+    sd = egnn_ref.tame_state_dict(state_dict_of(zl), 4)
+    net = EquivariantGNN(**egnn_ref.net_sizes(4, 64))
+    net.load_state_dict(sd)
+    net = net.to(DEV)
+    n, T = int(zt["n"]), int(zt["T"])
+    dp = E3DiffusionProcess(s=float(zt["s"]), power=2.0, num_diffusion_timestep=T)
+    noises = LP.make_noises(n, T, 2, torch.Generator().manual_seed(int(zt["seed"])))
+    assert np.array_equal(noises["init_x"].numpy(), zt["init_x"])
+    keep = [int(k) for k in zt["keep"]]
+    for graphs in (False, True):
+        out = sample_structures(net, dp, n, 1, noises=noises, record_steps=() if graphs else keep,
+                                use_cuda_graph=graphs)
+        tol = max(50 * float(zt["fp32_vs_fp64_relerr"]), 5e-4)  # the trajectory's own fp32 sensitivity sets the bar
+        assert bool(out["finite"][0]) == bool(zt["finite"])
+        assert relerr(out["pos"][0], zt["pos"]) < tol, relerr(out["pos"][0], zt["pos"])
+        assert relerr(out["h"][0], zt["h"]) < tol
+        assert np.array_equal(out["atoms"][0].cpu().numpy(), zt["atoms"])
+        for t, (zx, zh) in out["record"].items():
+            assert relerr(zx, zt[f"zx_t{t}"]) < tol and relerr(zh, zt[f"zh_t{t}"]) < tol, t

@@ -1,0 +1,138 @@
+"""CPU tests: the oracle restatement against the golden vectors frozen from the UNMODIFIED reference
+(oracle/make_golden.py), and the C-ABI surface (library loads, exports every symbol the header declares)."""
+import os
+import re
+
+import numpy as np
+import torch
+
+from oracle import diffusion_ref as D
+from oracle import egnn_ref, graphs_ref as G, loops_ref as LP
+
+torch.set_num_threads(4)
+
+
+def load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + ".npz"), allow_pickle=False)
+
+
+def state_dict_of(z):
+    return {k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w:")}
+
+
+def sizes_of(z):
+    return {str(k): int(v) for k, v in zip(z["size_keys"], z["sizes"])}
+
+
+def relerr(a, b):
+    a, b = torch.as_tensor(a), torch.as_tensor(b)
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def test_schedule_kat(golden_dir):
+    z = load(golden_dir, "diffusion_kat")
+    sch = D.Schedule(float(z["s"]), float(z["power"]), int(z["T"]))
+    assert np.array_equal(sch.alpha.numpy(), z["alpha"])
+    assert np.array_equal(sch.sigma.numpy(), z["sigma"])
+    # SURVEY 3.4 known answers
+    assert abs(float(sch.alpha[500]) - 0.56249851) < 1e-7
+    assert abs(float(sch.sigma[1000]) - 1.0) < 1e-7
+
+
+def test_remove_mean_kat(golden_dir):
+    z = load(golden_dir, "diffusion_kat")
+    out = D.remove_mean(torch.from_numpy(z["rm_in"]).clone(), torch.from_numpy(z["rm_batch"]))
+    assert np.array_equal(out.numpy(), z["rm_out"])
+    assert np.array_equal(D.remove_mean(torch.from_numpy(z["rm_in"]).clone()).numpy(), z["rm_out_global"])
+
+
+def test_reverse_step_and_mu(golden_dir):
+    z = load(golden_dir, "diffusion_kat")
+    sch = D.Schedule(float(z["s"]), float(z["power"]), int(z["T"]))
+    zz, eps = torch.from_numpy(z["z"]), torch.from_numpy(z["eps"])
+    zh, eh = torch.from_numpy(z["zh"]), torch.from_numpy(z["eh"])
+    for t in z["ts"].tolist():
+        assert np.array_equal(D.calculate_mu(sch, zz, eps, t).numpy(), z[f"t{t}_mu"])
+        out = D.reverse_diffuse_one_step(sch, zz, eps, t, torch.from_numpy(z[f"t{t}_noise"]).clone(), "pos")
+        assert np.array_equal(out.numpy(), z[f"t{t}_z"])
+        outh = D.reverse_diffuse_one_step(sch, zh, eh, t, torch.from_numpy(z[f"t{t}_noise_h"]).clone(), "h")
+        assert np.array_equal(outh.numpy(), z[f"t{t}_zh"])
+        zt, nz = D.diffuse_zero_to_t(sch, zz, t, torch.from_numpy(z[f"t{t}_raw"]).clone(), "pos")
+        assert np.array_equal(zt.numpy(), z[f"t{t}_zt"]) and np.array_equal(nz.numpy(), z[f"t{t}_nz"])
+        assert np.array_equal(D.calculate_mu_xonly(sch, zz, eps, t).numpy(), z[f"t{t}_mu_xonly"])
+
+
+def test_edge_builders(golden_dir):
+    z = load(golden_dir, "edges")
+    for n in (1, 2, 5, 24):
+        assert np.array_equal(G.fc_edges(n), z[f"fc_{n}"].reshape(2, -1))
+    for k in ("dense", "sparse", "lattice"):
+        assert np.array_equal(G.cutoff_edges(z[f"open_{k}_pos"], 2.0, None), z[f"open_{k}_edges"])
+    e = G.cutoff_edges_batch(z["per_pos"], z["per_graph_ptr"], 5.0, z["per_boxes"])
+    assert np.array_equal(e, z["per_edges"])
+
+
+def test_egnn_layers_against_reference(golden_dir):
+    for name in ("cfg1", "ragged"):
+        z = load(golden_dir, "egnn_" + name)
+        sd, sz = state_dict_of(z), sizes_of(z)
+        h, x, ei = torch.from_numpy(z["h"]), torch.from_numpy(z["x"]), torch.from_numpy(z["edge_index"])
+        with torch.no_grad():
+            _, _, layers = egnn_ref.egnn_forward(sd, sz["L"], ei, h, x, "call", return_layers=True)
+            hg, xg = egnn_ref.egnn_forward(sd, sz["L"], ei, h, x, "graph", batch=torch.from_numpy(z["batch"]))
+        for l, (a, c) in enumerate(layers):
+            assert relerr(a, z[f"h_l{l}"]) < 5e-6 and relerr(c, z[f"x_l{l}"]) < 5e-6
+        assert relerr(hg, z["h_graph"]) < 5e-6 and relerr(xg, z["x_graph"]) < 5e-6
+
+
+def test_loss_against_reference(golden_dir):
+    z = load(golden_dir, "loss_cfg1")
+    sd = state_dict_of(z)
+    sch = D.Schedule(1e-5, 2.0, 1000)
+    egnn = lambda e, h, x: egnn_ref.egnn_forward(sd, 4, e, h, x)
+    with torch.no_grad():
+        loss, aux = LP.train_loss(egnn, sch, torch.from_numpy(z["pos"]), torch.from_numpy(z["x"]),
+                                  torch.from_numpy(z["edge_index"]), torch.from_numpy(z["batch"]),
+                                  torch.from_numpy(z["t"]), torch.from_numpy(z["noise_pos"]), torch.from_numpy(z["noise_h"]))
+    assert abs(float(loss) - float(z["loss"])) < 1e-5 * abs(float(z["loss"]))
+    assert np.array_equal(aux["pos_t"].numpy(), z["pos_t"])
+
+
+def test_abi_exports_every_declared_symbol(lib):
+    from diffusion_model_b200 import _lib
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "egnn_b200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(egnn_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    assert declared == set(_lib.SIGNATURES), (declared ^ set(_lib.SIGNATURES))
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.egnn_b200_version() == 1
+    net = _lib.NetDesc(6, 3, 128, 128, 128, 128)
+    import ctypes as C
+    assert lib.egnn_param_count(C.byref(net)) == 315678  # cfg 2 network
+    net = _lib.NetDesc(4, 3, 64, 64, 64, 64)
+    assert lib.egnn_param_count(C.byref(net)) == 56084
+
+
+def test_product_refuses_cpu_tensors(lib):
+    import pytest
+    from diffusion_model_b200 import EgnnError
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    net = EquivariantGNN(**egnn_ref.net_sizes(1, 8))
+    ei = torch.from_numpy(G.fc_edges(4))
+    with pytest.raises(EgnnError):
+        net(ei, torch.zeros(4, 3), torch.zeros(4, 3))
+
+
+def test_state_dict_keys_match_reference(golden_dir):
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    z = load(golden_dir, "egnn_cfg1")
+    sd, sz = state_dict_of(z), sizes_of(z)
+    torch.manual_seed(2024)
+    net = EquivariantGNN(**sz)
+    mine = net.state_dict()
+    assert list(mine.keys()) == list(sd.keys())
+    # same construction order under the same seed -> identical initial weights as the reference module
+    assert all(torch.equal(mine[k], sd[k]) for k in sd)
