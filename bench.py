@@ -1,0 +1,357 @@
+#!/usr/bin/env python
+"""Headline benchmark: BASELINE.json configs[1] -- eps-prediction TRAINING step of the EGNN denoiser (6 layers, hidden
+128) on a batch of 64 amorphous-SiO2-like 192-atom periodic cutoff graphs (r_c = 5 A) per GPU.
+
+One step = diffuse_as_batch + EGNN forward + loss + backward + optimizer step over one batch (the body of
+train_epoch, parts/train_per_iretation.py:122-179).  metric = denoiser graph-steps/s (graphs trained per second,
+whole job).  `value` is timed with the batch resident in HBM; `e2e` goes through the public API from pinned HOST
+buffers every step (H2D of the batch, edge-index preparation, D2H of the loss).  N > 1: one rank per GPU, each its own
+64-graph batch (weak scaling), one NCCL all-reduce of the flat gradient per step.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+--impl reference times the CPU restatement of the reference path (oracle/, torch CPU with all host threads) on a
+bounded sample of the same workload; the unmodified reference cannot run here (needs torch_geometric, absent).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import random
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFG = dict(L=6, d=128, H=3, A=2, graphs=64, atoms=192, r_c=5.0, T=1000, s=1e-5, power=2.0, lr=1e-5, seed=2024)
+DENSITY = 0.0662  # atoms / A^3, a-SiO2
+
+
+def synth_batch(num_graphs, n_atoms, seed):
+    """Seeded SiO2-like cells: n/3 Si + 2n/3 O uniform in a cubic cell of side (n/0.0662)^(1/3) A with a
+    1.4 A periodic min-distance rejection, zero COM.  Returns host tensors pos [N,3], onehot [N,2], box [G,3]."""
+    rng = np.random.default_rng(seed)
+    side = float((n_atoms / DENSITY) ** (1.0 / 3.0))
+    pos_all, oh_all = [], []
+    for _ in range(num_graphs):
+        pts = np.zeros((n_atoms, 3))
+        k = 0
+        while k < n_atoms:
+            c = rng.uniform(0.0, side, size=3)
+            if k:
+                d = pts[:k] - c
+                d -= side * np.rint(d / side)
+                if np.min(np.einsum("ij,ij->i", d, d)) < 1.4 * 1.4:
+                    continue
+            pts[k] = c
+            k += 1
+        pos_all.append((pts - pts.mean(axis=0)).astype(np.float32))
+        species = np.zeros(n_atoms, np.int64)
+        species[rng.permutation(n_atoms)[: n_atoms // 3]] = 1
+        oh = np.zeros((n_atoms, 2), np.float32)
+        oh[np.arange(n_atoms), species] = 1.0  # [1,0] = O, [0,1] = Si (make_dataset.py:112-117)
+        oh_all.append(oh)
+    pos = torch.from_numpy(np.concatenate(pos_all))
+    onehot = torch.from_numpy(np.concatenate(oh_all))
+    box = torch.full((num_graphs, 3), side, dtype=torch.float32)
+    return pos, onehot, box
+
+
+def net_sizes(L, d, H):
+    K0 = 2 * H + 1
+    return dict(L=L, m_input=K0, m_hidden=d, m_output=d, x_input=K0, x_hidden=d, x_output=1, h_input=H + d, h_hidden=d,
+                h_output=H)
+
+
+def fwd_flops(L, d, H, N, E):
+    """Algorithmic forward FLOPs of one call, SURVEY.md 8(d)."""
+    K0 = 2 * H + 1
+    return L * (E * (4 * K0 * d + 4 * d * d + 4 * d) + N * (2 * (H + d) * d + 2 * d * H))
+
+
+class ClockSampler:
+    """nvidia-smi samples of SM clock and throttle reasons DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        rows = [r for r in self.rows if len(r) >= 6 and r[0].isdigit()]
+        if not rows:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["no samples"])
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[k] for r in rows for k in range(4) if r[2 + k].lower().startswith("active")})
+        return dict(sm_mhz=statistics.median(int(r[0]) for r in rows), sm_max_mhz=int(rows[0][1]), reasons=reasons,
+                    samples=len(rows))
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        z = json.load(open(p))
+        return dict(hbm_gbs=z["hbm_gbs"], tflops=z.get("bf16_tflops_sustained", z["bf16_tflops"]), source="measured")
+    return dict(hbm_gbs=6650.0, tflops=1400.0, source="fallback")
+
+
+# ------------------------------------------------------------------------------------------- CPU arm (oracle port)
+def cpu_train_steps(pos, onehot, edge_index, batch, sd, steps, warmup, threads):
+    """Training steps of the CPU restatement (oracle/): egnn_ref forward with autograd, reference loss, torch Adam."""
+    from oracle import diffusion_ref as D, egnn_ref, loops_ref as LP
+    torch.set_num_threads(threads)
+    sch = D.Schedule(CFG["s"], CFG["power"], CFG["T"])
+    params = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    opt = torch.optim.Adam(list(params.values()), lr=CFG["lr"])
+    G = int(batch.max()) + 1
+    gen = torch.Generator().manual_seed(1)
+    rnd = random.Random(CFG["seed"])
+    times = []
+    for k in range(warmup + steps):
+        t0 = time.perf_counter()
+        t = torch.tensor([rnd.choice(range(1, CFG["T"] + 1)) for _ in range(G)])
+        n_pos = torch.randn(pos.shape[0], 3, generator=gen)
+        n_h = torch.randn(pos.shape[0], CFG["A"], generator=gen)
+        opt.zero_grad()
+        loss, _ = LP.train_loss(lambda e, h, x: egnn_ref.egnn_forward(params, CFG["L"], e, h, x), sch, pos, onehot,
+                                edge_index, batch, t, n_pos, n_h, A=CFG["A"])
+        loss.backward()
+        opt.step()
+        float(loss.detach())
+        if k >= warmup:
+            times.append(time.perf_counter() - t0)
+    return times
+
+
+def cpu_sample(pos, onehot, edge_index, node_ptr, graphs):
+    """First `graphs` graphs of the batch as CPU tensors (edge list cut at the graph boundary)."""
+    n_nodes = int(node_ptr[graphs])
+    keep = edge_index[0] < n_nodes
+    batch = torch.repeat_interleave(torch.arange(graphs), (node_ptr[1:graphs + 1] - node_ptr[:graphs]).long())
+    return pos[:n_nodes].clone(), onehot[:n_nodes].clone(), edge_index[:, keep].clone(), batch
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    pos, onehot, box = synth_batch(CFG["graphs"], CFG["atoms"], CFG["seed"] + 1)
+    node_ptr = torch.arange(CFG["graphs"] + 1) * CFG["atoms"]
+    from oracle import egnn_ref, graphs_ref as G
+    torch.manual_seed(CFG["seed"])
+    sd = egnn_ref.init_state_dict(**net_sizes(CFG["L"], CFG["d"], CFG["H"]))
+    graphs = 8
+    ei = torch.from_numpy(G.cutoff_edges_batch(pos[: graphs * CFG["atoms"]].numpy(), node_ptr[: graphs + 1].numpy(),
+                                               CFG["r_c"], box[:graphs].numpy()))
+    p, o, e, b = cpu_sample(pos, onehot, ei, node_ptr, graphs)
+    probe = cpu_train_steps(p, o, e, b, sd, 1, 1, threads)[0]
+    while graphs > 1 and probe * (args.steps + args.warmup) > 240.0:
+        graphs //= 2
+        probe /= 2
+    p, o, e, b = cpu_sample(pos, onehot, ei, node_ptr, graphs)
+    times = cpu_train_steps(p, o, e, b, sd, args.steps, args.warmup, threads)
+    total = sum(times)
+    value = graphs * len(times) / total
+    sample = f"{graphs} of the 64 graphs of the batch per step ({p.shape[0]} atoms, {e.shape[1]} edges), fp32, torch CPU"
+    line = dict(impl="reference", metric="denoiser graph-steps/s (training fwd+bwd+optimizer)", value=value,
+                unit="graph-steps/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                ms_per_step=1e3 * total / len(times), higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="fp32", data="synthetic", config=workload_config("fp32"),
+                cpu_baseline=dict(value=value, unit="graph-steps/s", cores=threads, kind="port", sample=sample),
+                e2e=dict(value=value, unit="graph-steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                note="CPU restatement of the reference path (oracle/); the unmodified reference needs torch_geometric")
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(precision):
+    return dict(workload="cfg2: eps-pred training step, 64 x 192-atom periodic cutoff graphs (r_c=5A) per GPU, EGNN L=6 d=128 H=3, "
+                         "T=1000, Adam lr=1e-5", graphs_per_gpu=CFG["graphs"], atoms=CFG["atoms"], r_c=CFG["r_c"], L=CFG["L"],
+                hidden=CFG["d"], precision=precision, parallelism="data-parallel, one NCCL all-reduce of the flat gradient per step",
+                l2="256 MB buffer written between timed steps (L2 flush, inside the timed region)")
+
+
+# ------------------------------------------------------------------------------------------- product arm (B200)
+def run_product(args, rank, world, local):
+    import torch.distributed as dist
+    from diffusion_model_b200 import _lib
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    from diffusion_model_b200.data import Data
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.distributed import allreduce_gradients, broadcast_parameters
+    from diffusion_model_b200.graph import build_edges_cutoff
+    from diffusion_model_b200.optim import FlatAdam
+    from diffusion_model_b200.train_per_iretation import batch_loss
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    lib = _lib.load()
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    torch.manual_seed(CFG["seed"])
+    random.seed(CFG["seed"] + rank)
+    G_, n = CFG["graphs"], CFG["atoms"]
+    pos_h, oh_h, box_h = synth_batch(G_, n, CFG["seed"] + 1 + 1000 * rank)
+    node_ptr_h = (torch.arange(G_ + 1) * n).to(torch.int32)
+    net = EquivariantGNN(**net_sizes(CFG["L"], CFG["d"], CFG["H"])).to(dev)
+    net.precision = args.precision
+    sd_cpu = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
+    broadcast_parameters(net)
+    opt = FlatAdam(net, lr=CFG["lr"])
+    dp = E3DiffusionProcess(s=CFG["s"], power=CFG["power"], num_diffusion_timestep=CFG["T"])
+    dp.device_tables(dev)
+    prm = dict(atom_type_size=CFG["A"], norm_scope="call")
+
+    # resident batch: edge_index from the CUDA builder (bit-exact against the oracle in tests/)
+    pos_d, oh_d, box_d, node_ptr_d = pos_h.to(dev), oh_h.to(dev), box_h.to(dev), node_ptr_h.to(dev)
+    ei_d = build_edges_cutoff(pos_d, CFG["r_c"], node_ptr=node_ptr_d, box=box_d)
+    N, E = pos_d.shape[0], ei_d.shape[1]
+    resident = Data(x=oh_d, pos=pos_d, edge_index=ei_d)
+    resident.node_ptr = node_ptr_d
+    ei_h = ei_d.cpu().pin_memory()
+    pos_p, oh_p, np_p = pos_h.pin_memory(), oh_h.pin_memory(), node_ptr_h.pin_memory()
+
+    def train_step(b):
+        opt.zero_grad()
+        loss, _, _ = batch_loss(net, b, dp, prm)
+        loss.backward()
+        if world > 1:
+            allreduce_gradients(net)
+        opt.step(grad_scale=1.0 / world)
+        return loss
+
+    def e2e_step():
+        b = Data(x=oh_p.to(dev, non_blocking=True), pos=pos_p.to(dev, non_blocking=True),
+                 edge_index=ei_h.to(dev, non_blocking=True))
+        b.node_ptr = np_p.to(dev, non_blocking=True)
+        return train_step(b).item()  # D2H read of the step's loss
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        clocks = ClockSampler(local)
+        l0 = lib.egnn_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            flush.zero_()
+            fn()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), lib.egnn_launch_count() - l0, clocks.stop()
+
+    ms, launches, clocks = timed(lambda: train_step(resident), args.steps, args.warmup)
+    value = G_ * world * args.steps / (ms * 1e-3)
+    ms_e2e, _, _ = timed(e2e_step, args.steps, max(args.warmup, 3))
+    e2e_value = G_ * world * args.steps / (ms_e2e * 1e-3)
+    h2d = pos_p.numel() * 4 + oh_p.numel() * 4 + ei_h.numel() * 8 + np_p.numel() * 4 + G_ * 4
+
+    # per-kernel device times (CUDA events on the launching stream, separate short pass after the timed regions)
+    import ctypes as C
+    lib.egnn_profile_enable(1)
+    prof_steps = 3
+    for _ in range(prof_steps):
+        flush.zero_()
+        train_step(resident)
+    torch.cuda.synchronize(dev)
+    names = {0: "egcl_edge_fwd", 1: "egcl_node_fwd", 2: "egcl_xupdate", 3: "egcl_edge_bwd", 4: "egcl_node_bwd",
+             5: "egcl_gather_bwd", 7: "tc_edge_fwd", 8: "tc_edge_bwd"}
+    prof = {}
+    for kind, name in names.items():
+        tot, cnt = C.c_double(0), C.c_int64(0)
+        lib.egnn_profile_read(kind, C.byref(tot), C.byref(cnt))
+        if cnt.value:
+            prof[name] = dict(ms_per_launch=tot.value / cnt.value, launches_per_step=cnt.value / prof_steps,
+                              ms_per_step=tot.value / prof_steps)
+    lib.egnn_profile_enable(0)
+    K0, d = 2 * CFG["H"] + 1, CFG["d"]
+    edge_flops = E * (4 * K0 * d + 4 * d * d + 4 * d)  # algorithmic forward FLOPs of the edge MLPs of one layer
+    algo = {"egcl_edge_fwd": edge_flops, "tc_edge_fwd": edge_flops, "egcl_edge_bwd": 2 * edge_flops,
+            "tc_edge_bwd": 2 * edge_flops}
+    peaks = measured_peaks()
+    top = max(prof, key=lambda k: prof[k]["ms_per_step"]) if prof else None
+    roofline = None
+    if top in algo:
+        ach = algo[top] / (prof[top]["ms_per_launch"] * 1e-3) / 1e12
+        roofline = dict(bound="tensor", kernel=top, achieved=ach, peak=peaks["tflops"], unit="TFLOP/s",
+                        frac=ach / peaks["tflops"], traffic=None, peak_source=peaks["source"] + " bf16 sustained",
+                        share_of_step=prof[top]["ms_per_step"] / (ms / args.steps),
+                        flops_per_launch=algo[top], ms_per_launch=prof[top]["ms_per_launch"])
+    line = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer)", value=value, unit="graph-steps/s",
+                n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=ms / args.steps, higher_is_better=True,
+                scaling="weak", vs_baseline=None, dtype=args.precision, data="synthetic",
+                config=dict(workload_config(args.precision), nodes_per_gpu=N, edges_per_gpu=E),
+                e2e=dict(value=e2e_value, unit="graph-steps/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4,
+                         ms_per_step=ms_e2e / args.steps),
+                gpu_launches=int(launches), clocks=clocks, roofline=roofline, kernels=prof,
+                train_flops_per_step=3 * fwd_flops(CFG["L"], d, CFG["H"], N, E))
+    if rank == 0 and world == 1:
+        threads = os.cpu_count() or 1
+        graphs = 8
+        p, o, e, b = cpu_sample(pos_h, oh_h, ei_d.cpu(), node_ptr_h.long(), graphs)
+        times = cpu_train_steps(p, o, e, b, sd_cpu, 2, 1, threads)
+        line["cpu_baseline"] = dict(value=graphs * len(times) / sum(times), unit="graph-steps/s", cores=threads, kind="port",
+                                    sample=f"{graphs} of the 64 graphs per step ({e.shape[1]} edges), 2 timed steps, oracle/ "
+                                           "restatement with torch CPU autograd + Adam")
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16x3", "bf16"])
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args, int(os.environ.get("RANK", "0")))
+        return
+    from diffusion_model_b200.distributed import init_from_env
+    rank, world, local = init_from_env("nccl")
+    try:
+        run_product(args, rank, world, local)
+    finally:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -36,6 +36,9 @@ _NET, _GR = C.POINTER(NetDesc), C.POINTER(GraphDesc)
 SIGNATURES = {
     "egnn_b200_last_error": (C.c_char_p, []),
     "egnn_b200_version": (C.c_int, []),
+    "egnn_launch_count": (_I64, []),
+    "egnn_profile_enable": (C.c_int, [_I32]),
+    "egnn_profile_read": (C.c_int, [_I32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "egnn_param_count": (_I64, [_NET]),
     "egnn_packed_count": (_I64, [_NET]),
     "egnn_forward_workspace_floats": (_I64, [_NET, _I32, _I32, _I32]),

@@ -6,6 +6,13 @@
 #include "../../include/egnn_b200.h"
 
 void egnn_set_error(const char* fmt, ...);
+void egnn_count_launch();
+bool egnn_prof_on();
+void egnn_prof_begin(int kind, cudaStream_t st);
+void egnn_prof_end(cudaStream_t st);
+// kernel families the profiler can bracket (egnn_profile_read)
+enum { EGNN_K_EDGE_FWD = 0, EGNN_K_NODE_FWD = 1, EGNN_K_XUPDATE = 2, EGNN_K_EDGE_BWD = 3, EGNN_K_NODE_BWD = 4,
+       EGNN_K_GATHER_BWD = 5, EGNN_K_REDUCE = 6, EGNN_K_TC_EDGE_FWD = 7, EGNN_K_TC_EDGE_BWD = 8 };
 
 #define EGNN_REQUIRE(cond, ...)              \
     do {                                     \
@@ -18,6 +25,7 @@ void egnn_set_error(const char* fmt, ...);
 #define EGNN_CHECK_LAUNCH(name)                                       \
     do {                                                              \
         cudaError_t e__ = cudaGetLastError();                         \
+        egnn_count_launch();                                          \
         if (e__ != cudaSuccess) {                                     \
             egnn_set_error("%s: %s", name, cudaGetErrorString(e__));  \
             return EGNN_ERR_CUDA;                                     \

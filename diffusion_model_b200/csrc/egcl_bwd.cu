@@ -406,7 +406,9 @@ int launch_edge_bwd(const EdgeBwdArgs& a, int grid, size_t smem, cudaStream_t st
         EGNN_CUDA(cudaFuncSetAttribute(egcl_edge_bwd<RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         configured = true;
     }
+    egnn_prof_begin(EGNN_K_EDGE_BWD, st);
     egcl_edge_bwd<RT><<<grid, 256, smem, st>>>(a);
+    egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("egcl_edge_bwd");
     return EGNN_OK;
 }
@@ -466,7 +468,9 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
         {
             NodeBwdArgs na{*net, N, (N + TNB - 1) / TNB, hl, fwd_ws_ptr + fw.msum + (size_t)l * N * net->Ms, P, Pk, gho,
                            ws + bw.gh_node, ws + bw.gM, ws + bw.part + (size_t)bw.gridE * lo.total};
+            egnn_prof_begin(EGNN_K_NODE_BWD, st);
             egcl_node_bwd<<<bw.gridN, 256, smemN, st>>>(na);
+            egnn_prof_end(st);
             EGNN_CHECK_LAUNCH("egcl_node_bwd");
         }
         if (E > 0) {
@@ -484,7 +488,9 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
         {
             GatherArgs ga{N, H, g->row_ptr, g->col_ptr, g->col_edge, ws + bw.gh_node, gxo, ws + bw.Gr, ws + bw.Gs, ghi, gxi};
             const long long tot = (long long)N * (H + 3);
+            egnn_prof_begin(EGNN_K_GATHER_BWD, st);
             egcl_gather_bwd<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(ga);
+            egnn_prof_end(st);
             EGNN_CHECK_LAUNCH("egcl_gather_bwd");
         }
         reduce_partials_kernel<<<(lo.total + 255) / 256, 256, 0, st>>>(ws + bw.part, rows, lo.total,

@@ -262,7 +262,9 @@ int launch_edge_fwd(const EdgeFwdArgs& a, size_t smem, cudaStream_t st) {
     }
     const int TE = 4 * RT;
     const int tiles = (a.E + TE - 1) / TE;
+    egnn_prof_begin(EGNN_K_EDGE_FWD, st);
     egcl_edge_fwd<RT><<<tiles, 256, smem, st>>>(a);
+    egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("egcl_edge_fwd");
     return EGNN_OK;
 }
@@ -327,11 +329,15 @@ int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const f
             EGNN_CUDA(cudaFuncSetAttribute(egcl_node_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
             configured = true;
         }
+        egnn_prof_begin(EGNN_K_NODE_FWD, st);
         egcl_node_fwd<<<(g.N + TN - 1) / TN, 256, smem, st>>>(na);
+        egnn_prof_end(st);
         EGNN_CHECK_LAUNCH("egcl_node_fwd");
     }
+    egnn_prof_begin(EGNN_K_XUPDATE, st);
     egcl_xupdate<<<g.G, 256, 0, st>>>(x, ws + w.dxu + (size_t)l * g.N * 3, ws + w.D, g.node_ptr, g.N, norm_scope, x_out,
                                       ws + w.S + (size_t)l * g.G);
+    egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("egcl_xupdate");
     return EGNN_OK;
 }

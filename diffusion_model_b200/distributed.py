@@ -1,0 +1,98 @@
+"""One process per GPU (torchrun): data-parallel training with ONE collective per step -- an all-reduce (sum) of the
+flat fp32 gradient buffer over NCCL/NVLink -- and communication-free batch-sharded sampling.
+
+The reference is single-process (main.py:125); nothing here replaces reference code, it shards its two loops:
+  * training: whole graphs of the minibatch are split across ranks; each rank's loss is sum/num_graph over ITS graphs
+    (parts/train_per_iretation.py:169), so averaging the summed gradients by the world size reproduces a single-GPU
+    step over the concatenated batch, except that EGCL's global normaliser (EquivariantGraphNeuralNetwork.py:64) is
+    evaluated per rank (use norm_scope='graph' for exact equivalence).
+  * sampling: structures [r*S/W, (r+1)*S/W) go to rank r; no data-path collective; results are gathered at the end.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.distributed as dist
+
+from .optim import flat_grad_of, scatter_flat_grad
+
+
+def init_from_env(backend=None):
+    """Initialise torch.distributed from torchrun's environment.  Returns (rank, world_size, local_rank)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+    return rank, world, local
+
+
+def shard_range(total, rank, world):
+    """Contiguous, balanced [lo, hi) share of `total` independent units for `rank` (first `total % world` ranks get +1)."""
+    base, rem = divmod(int(total), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def allreduce_flat(flat, world=None, group=None):
+    """In-place sum over ranks of one flat tensor (the only collective of a training step)."""
+    if dist.is_initialized() and (world or dist.get_world_size(group)) > 1:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    return flat
+
+
+def allreduce_gradients(module, group=None):
+    """Sum the module's parameter gradients over ranks as ONE buffer.  Returns the reduced flat gradient; the caller
+    divides by the world size (FlatAdam.step(grad_scale=1/world)) to average."""
+    g, zero_copy = flat_grad_of(module)
+    allreduce_flat(g, group=group)
+    if not zero_copy:
+        scatter_flat_grad(module, g)
+    return g
+
+
+def broadcast_parameters(module, src=0, group=None):
+    """Make every rank start from rank `src`'s weights (one broadcast of the flat parameter buffer)."""
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.broadcast(module.flat_parameters(), src=src, group=group)
+        module._flat.packed_key = None
+
+
+def sample_sharded(egnn, dp, num_atoms, num_structures, seed=2024, gather=True, **kw):
+    """Batch-sharded sampling: this rank draws its share with generator seed `seed + rank`; optionally all-gathers.
+
+    Returns the dict of sampler.sample_structures for the local share, plus (when gather) 'pos_all' [S,n,3],
+    'atoms_all' [S,n,A], 'finite_all' [S] on every rank."""
+    from .sampler import sample_structures
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    lo, hi = shard_range(num_structures, rank, world)
+    dev = torch.device(kw.pop("device", "cuda"))
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(seed + rank)
+    out = sample_structures(egnn, dp, num_atoms, hi - lo, generator=gen, device=dev, **kw)
+    out["range"] = (lo, hi)
+    if gather and world > 1:
+        sizes = [shard_range(num_structures, r, world) for r in range(world)]
+        mx = max(b - a for a, b in sizes)
+
+        def gather_cat(t):
+            pad = torch.zeros((mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+            pad[: t.shape[0]] = t
+            bufs = [torch.empty_like(pad) for _ in range(world)]
+            dist.all_gather(bufs, pad)
+            return torch.cat([b[: hi_ - lo_] for b, (lo_, hi_) in zip(bufs, sizes)])
+
+        out["pos_all"] = gather_cat(out["pos"].contiguous())
+        out["atoms_all"] = gather_cat(out["atoms"].contiguous())
+        out["finite_all"] = gather_cat(out["finite"].to(torch.int32)).bool()
+    elif gather:
+        out["pos_all"], out["atoms_all"], out["finite_all"] = out["pos"], out["atoms"], out["finite"]
+    return out

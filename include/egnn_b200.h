@@ -73,6 +73,13 @@ typedef struct {
 const char* egnn_b200_last_error(void);
 int egnn_b200_version(void);
 
+/* ---- instrumentation (bench.py): number of kernels the library has launched in this process; optional CUDA-event
+ *      brackets around one kernel family (kind: 0 edge fwd, 1 node fwd, 2 x-update, 3 edge bwd, 4 node bwd,
+ *      5 gather bwd, 7 tcgen05 edge fwd, 8 tcgen05 edge bwd), summed by egnn_profile_read into HOST variables ---- */
+int64_t egnn_launch_count(void);
+int egnn_profile_enable(int32_t on);
+int egnn_profile_read(int32_t kind, double* total_ms_host, int64_t* launches_host);
+
 /* ---- sizes ----------------------------------------------------------------------------------------------- */
 int64_t egnn_param_count(const egnn_net_t* net);          /* floats in the flat parameter buffer */
 int64_t egnn_packed_count(const egnn_net_t* net);         /* floats in the packed (transposed) weight buffer */
