@@ -39,6 +39,7 @@ SIGNATURES = {
     "egnn_launch_count": (_I64, []),
     "egnn_profile_enable": (C.c_int, [_I32]),
     "egnn_profile_read": (C.c_int, [_I32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    "egnn_tc_selftest": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _I32, _P, _P]),
     "egnn_param_count": (_I64, [_NET]),
     "egnn_packed_count": (_I64, [_NET]),
     "egnn_forward_workspace_floats": (_I64, [_NET, _I32, _I32, _I32]),

@@ -91,10 +91,12 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+// bounded spin (a malformed MMA must not hang the GPU): returns false after ~2^26 polls
+__device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
     uint32_t done = 0;
-    while (!done) {
+    for (uint32_t spin = 0; !done; ++spin) {
+        if (spin > (1u << 26)) return false;
         asm volatile(
             "{\n\t"
             ".reg .pred p;\n\t"
@@ -105,6 +107,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
             : "r"(addr), "r"(parity)
             : "memory");
     }
+    return true;
 }
 
 // ---- bf16 split ------------------------------------------------------------------------------------------------
