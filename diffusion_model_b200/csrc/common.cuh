@@ -73,8 +73,14 @@ __host__ __device__ static inline LayerOff layer_off(const egnn_net_t& n) {
 }
 // packed = K-major transposes used as the B operand of the forward FFMA GEMMs: Wt[k][n] = W[n][k]
 struct PackOff {
-    int wm1t, wm2t, wx1t, wx2t, wh1t, total;
+    int wm1t, wm2t, wx1t, wx2t, wh1t, tc, total;
 };
+// the tcgen05 edge kernels cover the uniform-width nets of BASELINE.json: Mh = Ms = Xh = d in {64,128}, 2H+1 <= 16
+__host__ __device__ static inline bool tc_supported(const egnn_net_t& n) {
+    return n.Mh == n.Ms && n.Ms == n.Xh && (n.Mh == 64 || n.Mh == 128) && 2 * n.H + 1 <= 16;
+}
+// bytes of one layer's tcgen05 weight image (see tc_edge.cu: W1 hi/lo [2d x 16], W2m hi/lo, W2x hi/lo [d x d] bf16, fp32 vectors)
+__host__ __device__ static inline int tc_blob_bytes(int d) { return 2 * (2 * d * 32) + 4 * (d * d * 2) + (6 * d + 4) * 4; }
 __host__ __device__ static inline PackOff pack_off(const egnn_net_t& n) {
     PackOff o;
     const int K0 = 2 * n.H + 1;
@@ -84,6 +90,9 @@ __host__ __device__ static inline PackOff pack_off(const egnn_net_t& n) {
     o.wx1t = p; p += K0 * n.Xh;
     o.wx2t = p; p += n.Xh * n.Xh;
     o.wh1t = p; p += (n.H + n.Ms) * n.Hh;
+    p = round4(p);
+    o.tc = p;
+    if (tc_supported(n)) p += (tc_blob_bytes(n.Mh) + 15) / 16 * 4;
     o.total = round4(p);
     return o;
 }
@@ -108,10 +117,12 @@ static inline int edge_tile_for(const egnn_net_t& n) {
     while (te > 16 && (int64_t)te * (round4(dmax) + 4) > 128 * 132) te >>= 1;
     return te;
 }
+// rows of the tile-partial buffer are sized for the finest segmentation any path uses (tcgen05: d/2-edge segments)
+static inline int part_tile_for(const egnn_net_t& n) { return tc_supported(n) ? n.Mh / 2 : edge_tile_for(n); }
 static inline FwdWs fwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     FwdWs w;
     const int64_t AGGW = n.Ms + 4;
-    const int64_t T = (E + edge_tile_for(n) - 1) / edge_tile_for(n);
+    const int64_t T = (E + part_tile_for(n) - 1) / part_tile_for(n);
     int64_t p = 0;
     auto take = [&](int64_t cnt) { int64_t o = p; p += round_up64(cnt, 4); return o; };
     w.agg = take(N * AGGW);

@@ -296,19 +296,26 @@ extern "C" int64_t egnn_forward_workspace_floats(const egnn_net_t* net, int32_t 
     return fwd_ws(*net, N, E, G).total;
 }
 
+int egnn_tc_pack(const egnn_net_t& net, const float* params, float* packed, cudaStream_t st);
+int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
+                         const float* x, float* agg, float* part, int precision, cudaStream_t st);
+
 extern "C" int egnn_pack_weights(const egnn_net_t* net, const float* params, float* packed, void* stream) {
     if (int rc = egnn_validate_net(net)) return rc;
     pack_weights_kernel<<<dim3(32, net->L), 256, 0, (cudaStream_t)stream>>>(*net, params, packed);
     EGNN_CHECK_LAUNCH("pack_weights_kernel");
-    return EGNN_OK;
+    return egnn_tc_pack(*net, params, packed, (cudaStream_t)stream);
 }
 
 // one EGCL layer forward (fp32 path); shared with the backward's recompute-free bookkeeping
 int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const float* P, const float* Pk, const float* h,
                            const float* x, float* h_out, float* x_out, float* ws, const FwdWs& w, int l, int norm_scope,
-                           cudaStream_t st) {
-    const int TE = edge_tile_for(net);
-    if (g.E > 0) {
+                           int precision, cudaStream_t st) {
+    const bool tensor = precision != EGNN_PREC_FP32;
+    const int TE = tensor ? part_tile_for(net) : edge_tile_for(net);
+    if (g.E > 0 && tensor) {
+        if (int rc = egnn_tc_edge_forward(net, g, Pk, h, x, ws + w.agg, ws + w.part, precision, st)) return rc;
+    } else if (g.E > 0) {
         EdgeFwdArgs ea{net, g.N, g.E, g.recv, g.send, g.row_ptr, h, x, P, Pk, ws + w.agg, ws + w.part};
         const size_t smem = egnn_edge_fwd_smem(net, TE);
         int rc;
@@ -357,7 +364,10 @@ extern "C" int egnn_net_forward(const egnn_net_t* net, const egnn_graph_t* g, co
     if (int rc = egnn_validate_graph(g, false)) return rc;
     EGNN_REQUIRE(params && packed && h_in && x_in && h_out && x_out && ws, "egnn_net_forward: NULL tensor pointer");
     EGNN_REQUIRE(norm_scope == EGNN_NORM_CALL || norm_scope == EGNN_NORM_GRAPH, "bad norm_scope %d", norm_scope);
-    EGNN_REQUIRE(precision == EGNN_PREC_FP32, "precision %d not available in this build (fp32 only)", precision);
+    EGNN_REQUIRE(precision == EGNN_PREC_FP32 || precision == EGNN_PREC_BF16X3 || precision == EGNN_PREC_BF16,
+                 "bad precision %d", precision);
+    EGNN_REQUIRE(precision == EGNN_PREC_FP32 || tc_supported(*net),
+                 "tcgen05 precisions need Mh = Ms = Xh in {64,128} and 2H+1 <= 16; use precision fp32 for this network");
     const FwdWs w = fwd_ws(*net, g->N, g->E, g->G);
     if (ws_floats < w.total) {
         egnn_set_error("egnn_net_forward: workspace too small (%lld < %lld floats)", (long long)ws_floats,
@@ -373,7 +383,7 @@ extern "C" int egnn_net_forward(const egnn_net_t* net, const egnn_graph_t* g, co
         float* ho = l == net->L - 1 ? h_out : ws + w.hl + (size_t)(l + 1) * g->N * net->H;
         float* xo = l == net->L - 1 ? x_out : ws + w.xl + (size_t)(l + 1) * g->N * 3;
         if (int rc = egnn_layer_forward_f32(*net, *g, params + (size_t)l * lo.total, packed + (size_t)l * po.total, h, x,
-                                            ho, xo, ws, w, l, norm_scope, st))
+                                            ho, xo, ws, w, l, norm_scope, precision, st))
             return rc;
         h = ho;
         x = xo;

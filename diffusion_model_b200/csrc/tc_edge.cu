@@ -93,3 +93,394 @@ extern "C" int egnn_tc_selftest(const float* A, const float* B, float* D, int32_
     EGNN_CHECK_LAUNCH("tc_selftest_kernel");
     return EGNN_OK;
 }
+
+// =====================================================================================================================
+// Fused EGCL edge kernel on tcgen05 (forward).
+//
+// Per 128-edge tile (one TMEM lane per edge):   u = [h_i, h_j, |r|^2]  (K padded to 16)
+//   GEMM1  [128 x 16] . W1^T   -> TMEM cols [0, 2d)      W1 = [Wm1; Wx1]  (both branches in one N = 2d MMA)
+//   GEMM2x [128 x d]  . Wx2^T  -> TMEM cols [3d, 4d)     A = SiLU(GEMM1[:, d:2d] + bx1)  (bf16 hi/lo in smem)
+//   GEMM2m [128 x d]  . Wm2^T  -> TMEM cols [2d, 3d)     A = SiLU(GEMM1[:, 0:d] + bm1)
+//   phi = wx3 . SiLU(GEMM2x + bx2) + bx3 ;  m = SiLU(GEMM2m + bm2) ;  g = sigmoid(wa . m + ba)
+// followed by the same fixed-order segmented sum as the fp32 path, over d/2-edge segments.
+// NPASS = 3: every product is hi.hi + lo.hi + hi.lo of bf16 splits (fp32-class accuracy, "bf16x3");  NPASS = 1: plain bf16.
+// 256 threads: warp w reads TMEM lane quadrant w % 4 (rows 32(w%4)..+31) and column half w / 4 of each d-wide block.
+// =====================================================================================================================
+namespace {
+
+template <int D>
+struct TcLayout {
+    // weight image (identical in global memory and at the start of shared memory)
+    static constexpr int W1_BYTES = 2 * D * 32;   // [2D rows x 16] bf16
+    static constexpr int W2_BYTES = D * D * 2;    // [D rows x D] bf16
+    static constexpr int w1_hi = 0, w1_lo = W1_BYTES;
+    static constexpr int w2m_hi = 2 * W1_BYTES, w2m_lo = w2m_hi + W2_BYTES;
+    static constexpr int w2x_hi = w2m_lo + W2_BYTES, w2x_lo = w2x_hi + W2_BYTES;
+    static constexpr int vec = w2x_lo + W2_BYTES;  // fp32: bm1 [D] | bx1 [D] | bm2 [D] | bx2 [D] | wa [D] | wx3 [D] | ba, bx3, 0, 0
+    static constexpr int BLOB = vec + (6 * D + 4) * 4;
+    static constexpr int blob_pad = (BLOB + 15) / 16 * 16;
+    // per-tile operands
+    static constexpr int u_hi = blob_pad, u_lo = u_hi + 128 * 32;
+    static constexpr int a1_hi = u_lo + 128 * 32, a1_lo = a1_hi + 128 * D * 2;
+    static constexpr int stage = a1_hi;  // fp32 [128][D] staging of g*m reuses the A1 tiles (needs D*4 <= 2 * D*2: equal)
+    static constexpr int small = a1_lo + 128 * D * 2;
+    // small: sI int[128] | sR float[128][4] | phiPart [2][128] | gatePart [2][128] | sPhi [128] | sGate [128] | bars | slot
+    static constexpr int sI = small, sR = sI + 512, phiPart = sR + 2048, gatePart = phiPart + 1024, sPhi = gatePart + 1024,
+                         sGate = sPhi + 512, bars = sGate + 512, slot = bars + 64;
+    static constexpr int TOTAL = slot + 16;
+};
+
+__global__ void __launch_bounds__(256) tc_pack_kernel(egnn_net_t net, const float* __restrict__ params,
+                                                      float* __restrict__ packed) {
+    const LayerOff lo = layer_off(net);
+    const PackOff po = pack_off(net);
+    const int D = net.Mh, K0 = 2 * net.H + 1;
+    const float* P = params + (size_t)blockIdx.y * lo.total;
+    uint8_t* blob = reinterpret_cast<uint8_t*>(packed + (size_t)blockIdx.y * po.total + po.tc);
+    const int W1B = 2 * D * 32, W2B = D * D * 2;
+    const int stride = gridDim.x * blockDim.x, t0 = blockIdx.x * blockDim.x + threadIdx.x;
+    // W1 = [Wm1; Wx1], K padded to 16: chunks (n, j), j in {0,1}
+    for (int idx = t0; idx < 2 * D * 2; idx += stride) {
+        const int n = idx >> 1, j = idx & 1;
+        const float* row = n < D ? P + lo.wm1 + n * K0 : P + lo.wx1 + (n - D) * K0;
+        uint32_t hi[4], lw[4];
+        for (int q = 0; q < 4; ++q) {
+            const int k = j * 8 + 2 * q;
+            tc::split2(k < K0 ? row[k] : 0.f, k + 1 < K0 ? row[k + 1] : 0.f, hi[q], lw[q]);
+        }
+        *reinterpret_cast<uint4*>(blob + tc::chunk_off(2 * D, n, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(blob + W1B + tc::chunk_off(2 * D, n, j)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+    }
+    for (int which = 0; which < 2; ++which) {
+        const float* W = P + (which == 0 ? lo.wm2 : lo.wx2);
+        uint8_t* dst = blob + 2 * W1B + which * 2 * W2B;
+        for (int idx = t0; idx < D * (D / 8); idx += stride) {
+            const int n = idx / (D / 8), j = idx % (D / 8);
+            uint32_t hi[4], lw[4];
+            for (int q = 0; q < 4; ++q) tc::split2(W[n * D + j * 8 + 2 * q], W[n * D + j * 8 + 2 * q + 1], hi[q], lw[q]);
+            *reinterpret_cast<uint4*>(dst + tc::chunk_off(D, n, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(dst + W2B + tc::chunk_off(D, n, j)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+        }
+    }
+    float* vec = reinterpret_cast<float*>(blob + 2 * W1B + 4 * W2B);
+    for (int c = t0; c < D; c += stride) {
+        vec[c] = P[lo.bm1 + c];
+        vec[D + c] = P[lo.bx1 + c];
+        vec[2 * D + c] = P[lo.bm2 + c];
+        vec[3 * D + c] = P[lo.bx2 + c];
+        vec[4 * D + c] = P[lo.wa + c];
+        vec[5 * D + c] = P[lo.wx3 + c];
+    }
+    if (t0 == 0) {
+        vec[6 * D + 0] = P[lo.ba];
+        vec[6 * D + 1] = P[lo.bx3];
+        vec[6 * D + 2] = 0.f;
+        vec[6 * D + 3] = 0.f;
+    }
+}
+
+}  // namespace
+
+namespace {
+
+struct TcFwdArgs {
+    egnn_net_t net;
+    int N, E, tiles;
+    const int32_t *recv, *send, *row_ptr;
+    const float *h, *x;
+    const uint8_t* blob;  // this layer's weight image
+    float *agg, *part;
+};
+
+template <bool FAST>
+__device__ __forceinline__ float tc_silu(float z) {
+    if (FAST) {  // one MUFU: z * sigmoid(z) = 0.5 z (1 + tanh(z / 2)); ~2^-11 relative, for the bf16 mode only
+        float t;
+        asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * z));
+        return 0.5f * z * (1.f + t);
+    }
+    return silu_f(z);
+}
+
+// this thread's row, columns [c0, c0+32) of a TMEM block: act(acc + bias) packed as bf16 hi/lo pairs
+template <bool FAST>
+__device__ __forceinline__ void tc_epi32(uint32_t taddr, const float* bias, uint32_t (&hi)[16], uint32_t (&lo)[16]) {
+    float v[32];
+    tc::tmem_ld32(taddr, v);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float a = tc_silu<FAST>(v[2 * i] + bias[2 * i]);
+        const float b = tc_silu<FAST>(v[2 * i + 1] + bias[2 * i + 1]);
+        tc::split2(a, b, hi[i], lo[i]);
+    }
+}
+__device__ __forceinline__ void tc_store32(uint8_t* a_hi, uint8_t* a_lo, int r, int c0, const uint32_t (&hi)[16],
+                                           const uint32_t (&lo)[16], bool with_lo) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint32_t off = tc::chunk_off(128, r, (c0 >> 3) + q);
+        *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+        if (with_lo) *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+    }
+}
+
+// one thread: D[128 x N] = A[128 x K] . B[N x K]^T into TMEM column `dcol`, NPASS products
+template <int NPASS>
+__device__ __forceinline__ void tc_issue(uint32_t tmem, int dcol, const uint8_t* a_hi, const uint8_t* a_lo,
+                                         const uint8_t* b_hi, const uint8_t* b_lo, int K, int N) {
+    const uint32_t idesc = tc::make_idesc_bf16(128, N);
+    const uint32_t lboA = 128 * 16, lboB = (uint32_t)N * 16;
+    bool acc = false;
+#pragma unroll
+    for (int p = 0; p < NPASS; ++p) {
+        const uint32_t ta = tc::smem_u32(p == 1 ? a_lo : a_hi), tb = tc::smem_u32(p == 2 ? b_lo : b_hi);
+        for (int s = 0; s < K / 16; ++s) {
+            tc::mma_bf16(tmem + dcol, tc::make_desc(ta + s * 2 * lboA, lboA, 128), tc::make_desc(tb + s * 2 * lboB, lboB, 128),
+                         idesc, acc);
+            acc = true;
+        }
+    }
+}
+
+template <int D, int NPASS>
+__global__ void __launch_bounds__(256, 1) tc_edge_fwd(TcFwdArgs a) {
+    using L = TcLayout<D>;
+    constexpr bool FAST = NPASS == 1;
+    constexpr int HALF = D / 2;          // columns per thread in every D-wide block
+    constexpr int NSEG = 256 / D;        // row segments of the segmented sum (2 for D=128, 4 for D=64)
+    constexpr int TS = 128 / NSEG;       // edges per segment == partial-buffer granularity (part_tile_for)
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q = warp & 3, hf = warp >> 2;
+    const int r = q * 32 + lane;         // this thread's edge row == TMEM lane
+    const int H = a.net.H, K0 = 2 * H + 1, AGGW = D + 4;
+    float* vec = reinterpret_cast<float*>(smem + L::vec);
+    int* sI = reinterpret_cast<int*>(smem + L::sI);
+    float* sR = reinterpret_cast<float*>(smem + L::sR);
+    float* phiPart = reinterpret_cast<float*>(smem + L::phiPart);
+    float* gatePart = reinterpret_cast<float*>(smem + L::gatePart);
+    float* sPhi = reinterpret_cast<float*>(smem + L::sPhi);
+    float* stage = reinterpret_cast<float*>(smem + L::stage);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::bars);  // [0] GEMM1, [1] GEMM2x, [2] GEMM2m
+    uint32_t* slot = reinterpret_cast<uint32_t*>(smem + L::slot);
+
+    // ---- one-time setup: weight image -> smem, TMEM, barriers
+    for (int o = tid * 16; o < L::blob_pad; o += 256 * 16)
+        *reinterpret_cast<uint4*>(smem + o) = __ldg(reinterpret_cast<const uint4*>(a.blob + o));
+    if (warp == 0) tc::tmem_alloc(slot, 4 * D);
+    if (tid == 0) {
+        tc::mbar_init(&bars[0], 1);
+        tc::mbar_init(&bars[1], 1);
+        tc::mbar_init(&bars[2], 1);
+        tc::fence_mbar_init();
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *slot;
+    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    bool ok = true;
+
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < a.tiles; tile += gridDim.x, phase ^= 1) {
+        const int e0 = tile * 128;
+        const int nrows = min(128, a.E - e0);
+        // ---- gather (one thread per edge row): u -> bf16 hi/lo chunks 0,1 of the U tile
+        if (tid < 128) {
+            float u[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) u[k] = 0.f;
+            int i = -1;
+            float rx = 0.f, ry = 0.f, rz = 0.f, dot = 0.f;
+            if (tid < nrows) {
+                i = a.recv[e0 + tid];
+                const int j = a.send[e0 + tid];
+                rx = a.x[3 * i + 0] - a.x[3 * j + 0];
+                ry = a.x[3 * i + 1] - a.x[3 * j + 1];
+                rz = a.x[3 * i + 2] - a.x[3 * j + 2];
+                dot = rx * rx + ry * ry + rz * rz;
+                const float nrm = sqrtf(dot);
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    if (k < H) u[k] = a.h[(size_t)i * H + k];
+                    else if (k < 2 * H) u[k] = a.h[(size_t)j * H + (k - H)];
+                    else if (k == 2 * H) u[k] = nrm * nrm;
+                }
+            }
+            sI[tid] = i;
+            sR[4 * tid + 0] = rx;
+            sR[4 * tid + 1] = ry;
+            sR[4 * tid + 2] = rz;
+            sR[4 * tid + 3] = dot;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int p = 0; p < 4; ++p) tc::split2(u[8 * j + 2 * p], u[8 * j + 2 * p + 1], hi[p], lo[p]);
+                *reinterpret_cast<uint4*>(smem + L::u_hi + tc::chunk_off(128, tid, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(smem + L::u_lo + tc::chunk_off(128, tid, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            }
+        }
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc::fence_after_sync();
+            tc_issue<NPASS>(tmem, 0, smem + L::u_hi, smem + L::u_lo, smem + L::w1_hi, smem + L::w1_lo, 16, 2 * D);
+            tc::mma_commit(&bars[0]);
+        }
+        ok = tc::mbar_wait(&bars[0], phase) && ok;
+        tc::fence_after_sync();
+        // ---- layer-1 epilogue of the coordinate branch -> A1, then GEMM2x
+        {
+            uint32_t hi[16], lo[16];
+#pragma unroll
+            for (int b = 0; b < HALF / 32; ++b) {
+                const int c0 = hf * HALF + 32 * b;
+                tc_epi32<FAST>(trow + D + c0, vec + D + c0, hi, lo);
+                tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, hi, lo, NPASS == 3);
+            }
+        }
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc::fence_after_sync();
+            tc_issue<NPASS>(tmem, 3 * D, smem + L::a1_hi, smem + L::a1_lo, smem + L::w2x_hi, smem + L::w2x_lo, D, D);
+            tc::mma_commit(&bars[1]);
+        }
+        // ---- layer-1 epilogue of the message branch: computed in registers while GEMM2x runs
+        uint32_t mhi[HALF / 32][16], mlo[HALF / 32][16];
+#pragma unroll
+        for (int b = 0; b < HALF / 32; ++b) tc_epi32<FAST>(trow + hf * HALF + 32 * b, vec + hf * HALF + 32 * b, mhi[b], mlo[b]);
+        ok = tc::mbar_wait(&bars[1], phase) && ok;  // GEMM2x has consumed A1
+        tc::fence_after_sync();
+#pragma unroll
+        for (int b = 0; b < HALF / 32; ++b)
+            tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, hf * HALF + 32 * b, mhi[b], mlo[b], NPASS == 3);
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc::fence_after_sync();
+            tc_issue<NPASS>(tmem, 2 * D, smem + L::a1_hi, smem + L::a1_lo, smem + L::w2m_hi, smem + L::w2m_lo, D, D);
+            tc::mma_commit(&bars[2]);
+        }
+        // ---- layer-2 epilogue of the coordinate branch while GEMM2m runs: phi partial over this thread's columns
+        {
+            float s = 0.f;
+#pragma unroll
+            for (int b = 0; b < HALF / 32; ++b) {
+                const int c0 = hf * HALF + 32 * b;
+                float v[32];
+                tc::tmem_ld32(trow + 3 * D + c0, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) s = fmaf(vec[5 * D + c0 + i], tc_silu<FAST>(v[i] + vec[3 * D + c0 + i]), s);
+            }
+            phiPart[hf * 128 + r] = s;
+        }
+        ok = tc::mbar_wait(&bars[2], phase) && ok;
+        tc::fence_after_sync();
+        // ---- layer-2 epilogue of the message branch: m in registers, gate partial
+        float m[HALF];
+        {
+            float s = 0.f;
+#pragma unroll
+            for (int b = 0; b < HALF / 32; ++b) {
+                const int c0 = hf * HALF + 32 * b;
+                float v[32];
+                tc::tmem_ld32(trow + 2 * D + c0, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    m[32 * b + i] = tc_silu<FAST>(v[i] + vec[2 * D + c0 + i]);
+                    s = fmaf(vec[4 * D + c0 + i], m[32 * b + i], s);
+                }
+            }
+            gatePart[hf * 128 + r] = s;
+        }
+        tc::fence_before_sync();
+        __syncthreads();  // both column halves of phi / gate are in smem; GEMM2m is done with A1 -> staging may overwrite it
+        {
+            const float g = sigmoid_f(gatePart[r] + gatePart[128 + r] + vec[6 * D]);
+            if (hf == 0) sPhi[r] = phiPart[r] + phiPart[128 + r] + vec[6 * D + 1];
+#pragma unroll
+            for (int c = 0; c < HALF; ++c) stage[r * D + ((hf * HALF + c) ^ lane)] = g * m[c];
+        }
+        __syncthreads();
+        // ---- fixed-order segmented sums over receivers, NSEG row segments of TS edges
+        {
+            auto seg_sum = [&](int seg, int c) {
+                const int r0 = seg * TS, r1 = min(r0 + TS, nrows);
+                if (r0 >= r1) return;
+                const int es = e0 + r0, ee = es + TS;
+                float* part = a.part + (size_t)(tile * NSEG + seg) * 2 * AGGW;
+                float sum = 0.f;
+                int cur = sI[r0];
+                for (int rr = r0; rr <= r1; ++rr) {
+                    const int i = rr < r1 ? sI[rr] : -2;
+                    if (i != cur) {
+                        const int ra = a.row_ptr[cur], rb = a.row_ptr[cur + 1];
+                        if (ra < es) part[c] = sum;
+                        else if (rb > ee) part[AGGW + c] = sum;
+                        else a.agg[(size_t)cur * AGGW + c] = sum;
+                        sum = 0.f;
+                        cur = i;
+                    }
+                    if (rr < r1) {
+                        float v;
+                        if (c < D) v = stage[rr * D + (c ^ (rr & 31))];
+                        else if (c < D + 3) v = sR[4 * rr + (c - D)] * sPhi[rr];
+                        else v = sR[4 * rr + 3];
+                        sum += v;
+                    }
+                }
+            };
+            seg_sum(tid / D, tid % D);
+            if (tid < 4 * NSEG) seg_sum(tid >> 2, D + (tid & 3));
+        }
+        __syncthreads();
+    }
+    if (!ok) asm volatile("trap;");  // an mbarrier wait timed out: fail loudly instead of returning garbage
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, 4 * D);
+}
+
+}  // namespace
+
+// ---- host side -------------------------------------------------------------------------------------------------
+int egnn_tc_pack(const egnn_net_t& net, const float* params, float* packed, cudaStream_t st) {
+    if (!tc_supported(net)) return EGNN_OK;
+    tc_pack_kernel<<<dim3(16, net.L), 256, 0, st>>>(net, params, packed);
+    EGNN_CHECK_LAUNCH("tc_pack_kernel");
+    return EGNN_OK;
+}
+
+template <int D, int NPASS>
+static int launch_tc_fwd(const TcFwdArgs& a, cudaStream_t st) {
+    static bool configured = false;
+    if (!configured) {
+        EGNN_CUDA(cudaFuncSetAttribute(tc_edge_fwd<D, NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcLayout<D>::TOTAL));
+        configured = true;
+    }
+    const int grid = a.tiles < 148 ? a.tiles : 148;
+    egnn_prof_begin(EGNN_K_TC_EDGE_FWD, st);
+    tc_edge_fwd<D, NPASS><<<grid, 256, TcLayout<D>::TOTAL, st>>>(a);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("tc_edge_fwd");
+    return EGNN_OK;
+}
+
+// edge phase of one layer on the tensor cores; fills agg / part exactly like egcl_edge_fwd (segments of d/2 edges)
+int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
+                         const float* x, float* agg, float* part, int precision, cudaStream_t st) {
+    EGNN_REQUIRE(tc_supported(net), "tcgen05 path needs Mh = Ms = Xh in {64,128} and 2H+1 <= 16 (got Mh=%d Ms=%d Xh=%d H=%d); "
+                 "use precision fp32", net.Mh, net.Ms, net.Xh, net.H);
+    const PackOff po = pack_off(net);
+    TcFwdArgs a{net, g.N, g.E, (g.E + 127) / 128, g.recv, g.send, g.row_ptr, h, x,
+                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), agg, part};
+    const bool x3 = precision == EGNN_PREC_BF16X3;
+    if (net.Mh == 128) return x3 ? launch_tc_fwd<128, 3>(a, st) : launch_tc_fwd<128, 1>(a, st);
+    return x3 ? launch_tc_fwd<64, 3>(a, st) : launch_tc_fwd<64, 1>(a, st);
+}

@@ -39,3 +39,77 @@ def test_tc_selftest_descriptor_convention(lib):
         assert s1 == 0 and s3 == 0, out
         assert e1 < 2e-2, out   # single bf16 product
         assert e3 < 2e-5, out   # hi/lo split, 3 products
+
+
+# ---------------------------------------------------------------- tensor-core edge kernel vs the reference outputs
+import numpy as np  # noqa: E402
+
+from oracle import egnn_ref  # noqa: E402
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _load(name):
+    return np.load(os.path.join(GOLD, name + ".npz"), allow_pickle=False)
+
+
+def _net_from(z):
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    sizes = {str(k): int(v) for k, v in zip(z["size_keys"], z["sizes"])}
+    net = EquivariantGNN(**sizes)
+    net.load_state_dict({k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w:")})
+    return net.to(DEV), sizes
+
+
+def _relerr(a, b):
+    a, b = torch.as_tensor(a).detach().cpu().double(), torch.as_tensor(b).detach().cpu().double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg2"])
+@pytest.mark.parametrize("precision,tol", [("bf16x3", 1e-4), ("bf16", 2e-2)])
+def test_tc_forward_matches_reference_layers(lib, name, precision, tol):
+    z = _load("egnn_" + name)
+    net, sizes = _net_from(z)
+    h, x = torch.from_numpy(z["h"]).to(DEV), torch.from_numpy(z["x"]).to(DEV)
+    ei, batch = torch.from_numpy(z["edge_index"]).to(DEV), torch.from_numpy(z["batch"]).to(DEV)
+    worst = 0.0
+    with torch.no_grad():
+        for l in range(sizes["L"]):
+            layer = net.egcl_list[l]
+            layer.precision = precision
+            hh, xx = layer(ei, torch.from_numpy(z[f"h_l{l - 1}"]).to(DEV) if l else h,
+                           torch.from_numpy(z[f"x_l{l - 1}"]).to(DEV) if l else x)
+            eh, ex = _relerr(hh, z[f"h_l{l}"]), _relerr(xx, z[f"x_l{l}"])
+            worst = max(worst, eh, ex)
+            assert eh <= tol and ex <= tol, (name, precision, l, eh, ex)
+        net.precision = precision
+        hg, xg = net(ei, h, x, batch=batch, norm_scope="graph")
+        h2, x2 = net(ei, h, x, batch=batch, norm_scope="graph")
+        assert torch.equal(hg, h2) and torch.equal(xg, x2)  # deterministic
+        if precision == "bf16x3":
+            assert _relerr(hg, z["h_graph"]) <= 5e-4 and _relerr(xg, z["x_graph"]) <= 5e-4  # L layers compounded
+    print(f"tc forward {name} {precision}: worst per-layer relerr {worst:.2e}")
+
+
+def test_tc_forward_edge_cases_and_unsupported(lib):
+    from diffusion_model_b200 import EgnnError
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    torch.manual_seed(0)
+    net = EquivariantGNN(**egnn_ref.net_sizes(2, 64)).to(DEV)
+    net.precision = "bf16x3"
+    sd = {k: v.detach().cpu() for k, v in net.state_dict().items()}
+    gen = torch.Generator().manual_seed(1)
+    n = 320
+    recv = np.concatenate([np.full(300, 2), np.full(5, 7), np.full(200, 9)]).astype(np.int64)
+    send = np.concatenate([np.arange(10, 310), np.arange(0, 5), np.arange(100, 300)]).astype(np.int64)
+    ei = torch.from_numpy(np.stack([recv, send]))
+    h, x = torch.randn(n, 3, generator=gen), torch.randn(n, 3, generator=gen)
+    with torch.no_grad():
+        ho, xo = net(ei.to(DEV), h.to(DEV), x.to(DEV))
+        hr, xr = egnn_ref.egnn_forward(sd, 2, ei, h, x)
+    assert _relerr(ho, hr) <= 2e-4 and _relerr(xo, xr) <= 2e-4
+    wide = EquivariantGNN(**egnn_ref.net_sizes(1, 256)).to(DEV)
+    wide.precision = "bf16"
+    with pytest.raises(EgnnError):
+        wide(ei.to(DEV), h.to(DEV), x.to(DEV))
