@@ -107,6 +107,7 @@ struct FwdWs {
     int64_t msum;   // [L][N][Ms]  combined message sums (input of mlp_h)
     int64_t dxu;    // [L][N][3]   un-normalised coordinate sums
     int64_t S;      // [L][G]      normaliser per graph
+    int64_t phi;    // [E]         per-edge phi of the current layer (tcgen05 path)
     int64_t total;
 };
 static inline int edge_tile_for(const egnn_net_t& n) {
@@ -133,12 +134,19 @@ static inline FwdWs fwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G)
     w.msum = take((int64_t)n.L * N * n.Ms);
     w.dxu = take((int64_t)n.L * N * 3);
     w.S = take((int64_t)n.L * G);
+    w.phi = take(tc_supported(n) ? E : 0);
     w.total = p;
     return w;
 }
 
 // ---- device math ---------------------------------------------------------------------------------------
-__device__ __forceinline__ float sigmoid_f(float z) { return __fdividef(1.f, 1.f + __expf(-z)); }
+// sigmoid via two MUFU ops (ex2, rcp; ~3 ulp): 1 / (1 + 2^(-z log2 e)).  z -> -inf gives rcp(inf) = 0, z -> +inf gives 1.
+__device__ __forceinline__ float sigmoid_f(float z) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * -1.4426950408889634f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
+    return r;
+}
 __device__ __forceinline__ float silu_f(float z) { return z * sigmoid_f(z); }
 // d/dz SiLU(z) = s (1 + z (1 - s))
 __device__ __forceinline__ float dsilu_f(float z) {

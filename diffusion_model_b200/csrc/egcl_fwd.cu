@@ -169,6 +169,11 @@ struct NodeFwdArgs {
     const float *P, *Pk;
     const float *agg, *part;
     float *h_out, *msum, *dxu, *D;
+    // tcgen05 path: the edge kernel leaves phi_e per edge instead of the 4 extra aggregate columns; dxu / D are then
+    // summed here over the receiver's edges (8 lanes per node, fixed order)
+    const float* phi_edge;
+    const int32_t* send;
+    const float* x;
 };
 
 // combined per-receiver sum of column c (see header comment)
@@ -211,13 +216,44 @@ __global__ void __launch_bounds__(256) egcl_node_fwd(NodeFwdArgs a) {
         }
         A[idx] = v;
     }
-    for (int idx = tid; idx < TN * 4; idx += 256) {
-        const int r = idx >> 2, c = idx & 3;
+    if (a.phi_edge == nullptr) {
+        for (int idx = tid; idx < TN * 4; idx += 256) {
+            const int r = idx >> 2, c = idx & 3;
+            const int i = n0 + r;
+            if (i < a.N) {
+                const float v = combine_agg(a.agg, a.part, a.row_ptr, i, Ms + c, AGGW, a.TE);
+                if (c < 3) a.dxu[(size_t)i * 3 + c] = v;
+                else a.D[i] = v;
+            }
+        }
+    } else {
+        const int r = tid >> 3, sub = tid & 7;  // 8 lanes per node
         const int i = n0 + r;
+        float sx = 0.f, sy = 0.f, sz = 0.f, sd = 0.f;
         if (i < a.N) {
-            const float v = combine_agg(a.agg, a.part, a.row_ptr, i, Ms + c, AGGW, a.TE);
-            if (c < 3) a.dxu[(size_t)i * 3 + c] = v;
-            else a.D[i] = v;
+            const float xi = a.x[3 * i], yi = a.x[3 * i + 1], zi = a.x[3 * i + 2];
+            for (int e = a.row_ptr[i] + sub; e < a.row_ptr[i + 1]; e += 8) {
+                const int j = a.send[e];
+                const float rx = xi - a.x[3 * j], ry = yi - a.x[3 * j + 1], rz = zi - a.x[3 * j + 2];
+                const float ph = a.phi_edge[e];
+                sx = fmaf(rx, ph, sx);
+                sy = fmaf(ry, ph, sy);
+                sz = fmaf(rz, ph, sz);
+                sd += rx * rx + ry * ry + rz * rz;
+            }
+        }
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) {
+            sx += __shfl_xor_sync(0xffffffffu, sx, o);
+            sy += __shfl_xor_sync(0xffffffffu, sy, o);
+            sz += __shfl_xor_sync(0xffffffffu, sz, o);
+            sd += __shfl_xor_sync(0xffffffffu, sd, o);
+        }
+        if (i < a.N && sub == 0) {
+            a.dxu[(size_t)i * 3 + 0] = sx;
+            a.dxu[(size_t)i * 3 + 1] = sy;
+            a.dxu[(size_t)i * 3 + 2] = sz;
+            a.D[i] = sd;
         }
     }
     __syncthreads();
@@ -298,7 +334,7 @@ extern "C" int64_t egnn_forward_workspace_floats(const egnn_net_t* net, int32_t 
 
 int egnn_tc_pack(const egnn_net_t& net, const float* params, float* packed, cudaStream_t st);
 int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
-                         const float* x, float* agg, float* part, int precision, cudaStream_t st);
+                         const float* x, float* agg, float* part, float* phi_edge, int precision, cudaStream_t st);
 
 extern "C" int egnn_pack_weights(const egnn_net_t* net, const float* params, float* packed, void* stream) {
     if (int rc = egnn_validate_net(net)) return rc;
@@ -314,7 +350,7 @@ int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const f
     const bool tensor = precision != EGNN_PREC_FP32;
     const int TE = tensor ? part_tile_for(net) : edge_tile_for(net);
     if (g.E > 0 && tensor) {
-        if (int rc = egnn_tc_edge_forward(net, g, Pk, h, x, ws + w.agg, ws + w.part, precision, st)) return rc;
+        if (int rc = egnn_tc_edge_forward(net, g, Pk, h, x, ws + w.agg, ws + w.part, ws + w.phi, precision, st)) return rc;
     } else if (g.E > 0) {
         EdgeFwdArgs ea{net, g.N, g.E, g.recv, g.send, g.row_ptr, h, x, P, Pk, ws + w.agg, ws + w.part};
         const size_t smem = egnn_edge_fwd_smem(net, TE);
@@ -329,7 +365,8 @@ int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const f
     }
     {
         NodeFwdArgs na{net, g.N, TE, g.row_ptr, h, P, Pk, ws + w.agg, ws + w.part, h_out,
-                       ws + w.msum + (size_t)l * g.N * net.Ms, ws + w.dxu + (size_t)l * g.N * 3, ws + w.D};
+                       ws + w.msum + (size_t)l * g.N * net.Ms, ws + w.dxu + (size_t)l * g.N * 3, ws + w.D,
+                       tensor ? ws + w.phi : nullptr, g.send, x};
         const size_t smem = sizeof(float) * (size_t)TN * ((round4(net.H + net.Ms) + 4) + (round4(net.Hh) + 4));
         static bool configured = false;
         if (!configured) {

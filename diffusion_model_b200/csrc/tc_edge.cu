@@ -124,9 +124,9 @@ struct TcLayout {
     static constexpr int a1_hi = u_lo + 128 * 32, a1_lo = a1_hi + 128 * D * 2;
     static constexpr int stage = a1_hi;  // fp32 [128][D] staging of g*m reuses the A1 tiles (needs D*4 <= 2 * D*2: equal)
     static constexpr int small = a1_lo + 128 * D * 2;
-    // small: sI int[128] | sR float[128][4] | phiPart [2][128] | gatePart [2][128] | sPhi [128] | sGate [128] | bars | slot
+    // small: sI int[128] | sR float[128][4] | phiPart [2][128] | gatePart [2][128] | sPhi [128] | sDst int[128] | bars | slot
     static constexpr int sI = small, sR = sI + 512, phiPart = sR + 2048, gatePart = phiPart + 1024, sPhi = gatePart + 1024,
-                         sGate = sPhi + 512, bars = sGate + 512, slot = bars + 64;
+                         sDst = sPhi + 512, bars = sDst + 512, slot = bars + 64;
     static constexpr int TOTAL = slot + 16;
 };
 
@@ -190,6 +190,7 @@ struct TcFwdArgs {
     const float *h, *x;
     const uint8_t* blob;  // this layer's weight image
     float *agg, *part;
+    float* phi_edge;  // [E] phi_e of this layer (dxu / D are summed per receiver by the node kernel)
 };
 
 template <bool FAST>
@@ -253,13 +254,11 @@ __global__ void __launch_bounds__(256, 1) tc_edge_fwd(TcFwdArgs a) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int q = warp & 3, hf = warp >> 2;
     const int r = q * 32 + lane;         // this thread's edge row == TMEM lane
-    const int H = a.net.H, K0 = 2 * H + 1, AGGW = D + 4;
+    const int H = a.net.H, AGGW = D + 4;
     float* vec = reinterpret_cast<float*>(smem + L::vec);
-    int* sI = reinterpret_cast<int*>(smem + L::sI);
-    float* sR = reinterpret_cast<float*>(smem + L::sR);
     float* phiPart = reinterpret_cast<float*>(smem + L::phiPart);
     float* gatePart = reinterpret_cast<float*>(smem + L::gatePart);
-    float* sPhi = reinterpret_cast<float*>(smem + L::sPhi);
+    int* sDst = reinterpret_cast<int*>(smem + L::sDst);
     float* stage = reinterpret_cast<float*>(smem + L::stage);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::bars);  // [0] GEMM1, [1] GEMM2x, [2] GEMM2m
     uint32_t* slot = reinterpret_cast<uint32_t*>(smem + L::slot);
@@ -308,11 +307,17 @@ __global__ void __launch_bounds__(256, 1) tc_edge_fwd(TcFwdArgs a) {
                     else if (k == 2 * H) u[k] = nrm * nrm;
                 }
             }
-            sI[tid] = i;
-            sR[4 * tid + 0] = rx;
-            sR[4 * tid + 1] = ry;
-            sR[4 * tid + 2] = rz;
-            sR[4 * tid + 3] = dot;
+            // segmented-sum bookkeeping: is this row the last of its receiver run inside its TS-row segment, and where
+            // does the finished sum go?  >= 0: agg[node]; -1: head partial; -2: tail partial; -3: keep accumulating
+            int dst = -3;
+            if (tid < nrows) {
+                const bool last = tid == nrows - 1 || (tid + 1) % TS == 0 || a.recv[e0 + tid + 1] != i;
+                if (last) {
+                    const int es = e0 + (tid / TS) * TS;
+                    dst = a.row_ptr[i] < es ? -1 : (a.row_ptr[i + 1] > es + TS ? -2 : i);
+                }
+            }
+            sDst[tid] = dst;
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
                 uint32_t hi[4], lo[4];
@@ -403,41 +408,27 @@ __global__ void __launch_bounds__(256, 1) tc_edge_fwd(TcFwdArgs a) {
         __syncthreads();  // both column halves of phi / gate are in smem; GEMM2m is done with A1 -> staging may overwrite it
         {
             const float g = sigmoid_f(gatePart[r] + gatePart[128 + r] + vec[6 * D]);
-            if (hf == 0) sPhi[r] = phiPart[r] + phiPart[128 + r] + vec[6 * D + 1];
+            if (hf == 0 && r < nrows) a.phi_edge[e0 + r] = phiPart[r] + phiPart[128 + r] + vec[6 * D + 1];
 #pragma unroll
             for (int c = 0; c < HALF; ++c) stage[r * D + ((hf * HALF + c) ^ lane)] = g * m[c];
         }
         __syncthreads();
-        // ---- fixed-order segmented sums over receivers, NSEG row segments of TS edges
+        // ---- fixed-order segmented sums over receivers: thread (segment, column) walks its TS rows in edge order
         {
-            auto seg_sum = [&](int seg, int c) {
-                const int r0 = seg * TS, r1 = min(r0 + TS, nrows);
-                if (r0 >= r1) return;
-                const int es = e0 + r0, ee = es + TS;
-                float* part = a.part + (size_t)(tile * NSEG + seg) * 2 * AGGW;
-                float sum = 0.f;
-                int cur = sI[r0];
-                for (int rr = r0; rr <= r1; ++rr) {
-                    const int i = rr < r1 ? sI[rr] : -2;
-                    if (i != cur) {
-                        const int ra = a.row_ptr[cur], rb = a.row_ptr[cur + 1];
-                        if (ra < es) part[c] = sum;
-                        else if (rb > ee) part[AGGW + c] = sum;
-                        else a.agg[(size_t)cur * AGGW + c] = sum;
-                        sum = 0.f;
-                        cur = i;
-                    }
-                    if (rr < r1) {
-                        float v;
-                        if (c < D) v = stage[rr * D + (c ^ (rr & 31))];
-                        else if (c < D + 3) v = sR[4 * rr + (c - D)] * sPhi[rr];
-                        else v = sR[4 * rr + 3];
-                        sum += v;
-                    }
+            const int seg = tid / D, c = tid % D;
+            const int r0 = seg * TS, r1 = min(r0 + TS, nrows);
+            float* part = a.part + (size_t)(tile * NSEG + seg) * 2 * AGGW;
+            float sum = 0.f;
+#pragma unroll 8
+            for (int rr = r0; rr < r1; ++rr) {
+                sum += stage[rr * D + (c ^ (rr & 31))];
+                const int dst = sDst[rr];
+                if (dst != -3) {
+                    if (dst >= 0) a.agg[(size_t)dst * AGGW + c] = sum;
+                    else part[(dst == -1 ? 0 : AGGW) + c] = sum;
+                    sum = 0.f;
                 }
-            };
-            seg_sum(tid / D, tid % D);
-            if (tid < 4 * NSEG) seg_sum(tid >> 2, D + (tid & 3));
+            }
         }
         __syncthreads();
     }
@@ -474,12 +465,12 @@ static int launch_tc_fwd(const TcFwdArgs& a, cudaStream_t st) {
 
 // edge phase of one layer on the tensor cores; fills agg / part exactly like egcl_edge_fwd (segments of d/2 edges)
 int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
-                         const float* x, float* agg, float* part, int precision, cudaStream_t st) {
+                         const float* x, float* agg, float* part, float* phi_edge, int precision, cudaStream_t st) {
     EGNN_REQUIRE(tc_supported(net), "tcgen05 path needs Mh = Ms = Xh in {64,128} and 2H+1 <= 16 (got Mh=%d Ms=%d Xh=%d H=%d); "
                  "use precision fp32", net.Mh, net.Ms, net.Xh, net.H);
     const PackOff po = pack_off(net);
     TcFwdArgs a{net, g.N, g.E, (g.E + 127) / 128, g.recv, g.send, g.row_ptr, h, x,
-                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), agg, part};
+                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), agg, part, phi_edge};
     const bool x3 = precision == EGNN_PREC_BF16X3;
     if (net.Mh == 128) return x3 ? launch_tc_fwd<128, 3>(a, st) : launch_tc_fwd<128, 1>(a, st);
     return x3 ? launch_tc_fwd<64, 3>(a, st) : launch_tc_fwd<64, 1>(a, st);
