@@ -7,35 +7,40 @@ namespace {
 
 // D[128 x N] = A[128 x K] . B[N x K]^T   (one CTA, 128 threads; K % 16 == 0, N % 16 == 0, N <= 256)
 //   npass 1: bf16(A) bf16(B);  npass 3: hi.hi + lo.hi + hi.lo  (fp32-class accuracy)
-//   swap != 0 exchanges the LBO / SBO fields of the descriptors (convention probe)
+//   flags bit0: exchange the LBO / SBO fields of K-major descriptors (convention probe)
+//         bit1: A is staged MN-major (tile rows = k, 16-byte chunks = 8 consecutive m), bit2: same for B
+//         bit3: exchange LBO / SBO of the MN-major descriptors
 __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restrict__ A, const float* __restrict__ B,
-                                                          float* __restrict__ D, int K, int N, int npass, int swap,
+                                                          float* __restrict__ D, int K, int N, int npass, int flags,
                                                           int* __restrict__ status) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t bar;
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int KC = K / 8;
+    const bool swapk = flags & 1, amn = flags & 2, bmn = flags & 4, swapmn = flags & 8;
     uint8_t* a_hi = smem;
     uint8_t* a_lo = a_hi + 128 * K * 2;
     uint8_t* b_hi = a_lo + 128 * K * 2;
     uint8_t* b_lo = b_hi + N * K * 2;
-    for (int j = 0; j < KC; ++j) {
-        uint32_t hi[4], lo[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) tc::split2(A[tid * K + j * 8 + 2 * q], A[tid * K + j * 8 + 2 * q + 1], hi[q], lo[q]);
-        *reinterpret_cast<uint4*>(a_hi + tc::chunk_off(128, tid, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-        *reinterpret_cast<uint4*>(a_lo + tc::chunk_off(128, tid, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-    }
-    for (int n = tid; n < N; n += 128) {
-        for (int j = 0; j < KC; ++j) {
+    // element (row, col) of an [R x C] row-major matrix; K-major: tile rows = row, chunks over col;
+    // MN-major: tile rows = col (the K index), chunks over row
+    auto stage = [&](const float* M, int R, int C, bool mn, uint8_t* hi_t, uint8_t* lo_t) {
+        const int rows = mn ? C : R, chunks = (mn ? R : C) / 8;
+        for (int idx = tid; idx < rows * chunks; idx += 128) {
+            const int r = idx % rows, j = idx / rows;
             uint32_t hi[4], lo[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) tc::split2(B[n * K + j * 8 + 2 * q], B[n * K + j * 8 + 2 * q + 1], hi[q], lo[q]);
-            *reinterpret_cast<uint4*>(b_hi + tc::chunk_off(N, n, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-            *reinterpret_cast<uint4*>(b_lo + tc::chunk_off(N, n, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            for (int q = 0; q < 4; ++q) {
+                const float v0 = mn ? M[(j * 8 + 2 * q) * C + r] : M[r * C + j * 8 + 2 * q];
+                const float v1 = mn ? M[(j * 8 + 2 * q + 1) * C + r] : M[r * C + j * 8 + 2 * q + 1];
+                tc::split2(v0, v1, hi[q], lo[q]);
+            }
+            *reinterpret_cast<uint4*>(hi_t + tc::chunk_off(rows, r, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(lo_t + tc::chunk_off(rows, r, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         }
-    }
+    };
+    stage(A, 128, K, amn, a_hi, a_lo);
+    stage(B, N, K, bmn, b_hi, b_lo);
     if (warp == 0) tc::tmem_alloc(&tmem_slot, 256);
     if (tid == 0) {
         tc::mbar_init(&bar, 1);
@@ -47,17 +52,23 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
     tc::fence_after_sync();
     const uint32_t tmem = tmem_slot;
     if (tid == 0) {
-        const uint32_t idesc = tc::make_idesc_bf16(128, N);
-        const uint32_t lboA = 128 * 16, lboB = N * 16, sbo = 128;
+        const uint32_t idesc = tc::make_idesc_bf16(128, N) | (amn ? 1u << 15 : 0u) | (bmn ? 1u << 16 : 0u);
+        // K-major: chunk stride (LBO) = rows*16, 8-row group stride (SBO) = 128, k-step = 2 chunks
+        // MN-major: tile rows = K index; stride between 8-wide M/N blocks = K*16, between 8-deep K blocks = 128
+        auto desc = [&](const uint8_t* t, int rows, bool mn, int s) {
+            if (!mn) {
+                const uint32_t lbo = rows * 16, sbo = 128, addr = tc::smem_u32(t) + s * 2 * lbo;
+                return swapk ? tc::make_desc(addr, sbo, lbo) : tc::make_desc(addr, lbo, sbo);
+            }
+            const uint32_t mnstride = K * 16, kstride = 128, addr = tc::smem_u32(t) + s * 2 * kstride;
+            return swapmn ? tc::make_desc(addr, kstride, mnstride) : tc::make_desc(addr, mnstride, kstride);
+        };
         bool acc = false;
         for (int p = 0; p < npass; ++p) {
             const uint8_t* ta = p == 1 ? a_lo : a_hi;
             const uint8_t* tb = p == 2 ? b_lo : b_hi;
             for (int s = 0; s < K / 16; ++s) {
-                const uint32_t aa = tc::smem_u32(ta) + s * 2 * lboA, ba = tc::smem_u32(tb) + s * 2 * lboB;
-                const uint64_t da = swap ? tc::make_desc(aa, sbo, lboA) : tc::make_desc(aa, lboA, sbo);
-                const uint64_t db = swap ? tc::make_desc(ba, sbo, lboB) : tc::make_desc(ba, lboB, sbo);
-                tc::mma_bf16(tmem, da, db, idesc, acc);
+                tc::mma_bf16(tmem, desc(ta, 128, amn, s), desc(tb, N, bmn, s), idesc, acc);
                 acc = true;
             }
         }
@@ -83,13 +94,13 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
 }  // namespace
 
 extern "C" int egnn_tc_selftest(const float* A, const float* B, float* D, int32_t K, int32_t N, int32_t npass,
-                                int32_t swap_lbo_sbo, int32_t* status_dev, void* stream) {
+                                int32_t flags, int32_t* status_dev, void* stream) {
     EGNN_REQUIRE(A && B && D && status_dev, "egnn_tc_selftest: NULL pointer");
     EGNN_REQUIRE(K >= 16 && K % 16 == 0 && K <= 128 && N >= 16 && N % 16 == 0 && N <= 256 && (npass == 1 || npass == 3),
                  "egnn_tc_selftest: unsupported shape K=%d N=%d npass=%d", K, N, npass);
     const size_t smem = 200 * 1024;  // fixed and ample: the swapped-descriptor probe must stay inside the allocation
     EGNN_CUDA(cudaFuncSetAttribute(tc_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    tc_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, D, K, N, npass, swap_lbo_sbo, status_dev);
+    tc_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, D, K, N, npass, flags, status_dev);
     EGNN_CHECK_LAUNCH("tc_selftest_kernel");
     return EGNN_OK;
 }
@@ -475,3 +486,109 @@ int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const flo
     if (net.Mh == 128) return x3 ? launch_tc_fwd<128, 3>(a, st) : launch_tc_fwd<128, 1>(a, st);
     return x3 ? launch_tc_fwd<64, 3>(a, st) : launch_tc_fwd<64, 1>(a, st);
 }
+
+// =====================================================================================================================
+// Fused EGCL edge kernel on tcgen05 (backward).  Each CTA owns ONE branch (blockIdx.x & 1: 0 = mlp_m + gate,
+// 1 = mlp_x) and walks its 128-edge tiles; per tile
+//   recompute   z1 = U.W1^T (block A),  a1 = SiLU(z1+b1) -> tile A1,  z2 = a1.W2^T (block B)
+//   upstream    gz2 = dL/dz2 -> tile G            (gate / phi algebra of SURVEY.md Appendix A on the CUDA cores)
+//   dgrad       ga1 = gz2 . W2   (block B)        B operand = the SAME W2 image viewed MN-major
+//   wgrad       dW2 += gz2^T . a1,  db2 += gz2^T . 1        (persistent TMEM accumulators; tile G / A1 / U viewed MN-major)
+//   gz1 = ga1 * SiLU'(z1+b1) -> tile G;   gu = gz1 . W1 (16 columns),  dW1 += gz1^T . U  (slot 15 of u is 1 -> db1)
+// Shared-memory tiles are written once by the thread that owns the edge row (16-byte chunks) and serve both as
+// K-major operands (row = edge) and as MN-major operands (K = edge) -- same bytes, two descriptor views.
+// Weight gradients stay in TMEM over all tiles of the CTA and are written once to the CTA's private partial row.
+// =====================================================================================================================
+namespace {
+
+template <int D>
+struct TcBwdLayout {
+    static constexpr int W1_BYTES = 2 * D * 32, W2_BYTES = D * D * 2;
+    static constexpr int w1_hi = 0, w1_lo = W1_BYTES;                 // both branches (rows [0,D) = m, [D,2D) = x)
+    static constexpr int w2_hi = 2 * W1_BYTES, w2_lo = w2_hi + W2_BYTES;  // this CTA's branch only
+    static constexpr int vec = w2_lo + W2_BYTES;                      // fp32 vectors as in TcLayout
+    static constexpr int VEC_BYTES = (6 * D + 4) * 4;
+    static constexpr int u_hi = (vec + VEC_BYTES + 15) / 16 * 16, u_lo = u_hi + 128 * 32;
+    static constexpr int a1_hi = u_lo + 128 * 32, a1_lo = a1_hi + 128 * D * 2;
+    static constexpr int g_hi = a1_lo + 128 * D * 2, g_lo = g_hi + 128 * D * 2;
+    static constexpr int small = g_lo + 128 * D * 2;
+    // small: sI int[128] | sR float[128][4] | rowA [2][128] | rowB [2][128] | colred [8][64] | bars | slot
+    static constexpr int sI = small, sR = sI + 512, rowA = sR + 2048, rowB = rowA + 1024, colred = rowB + 1024,
+                         bars = colred + 2048, slot = bars + 64;
+    static constexpr int TOTAL = slot + 16;
+};
+
+struct TcBwdArgs {
+    egnn_net_t net;
+    int N, E, tiles;
+    const int32_t *recv, *send, *node_graph;
+    const float *h, *x;
+    const uint8_t* blob;
+    const float *gM, *gdx, *coefS;
+    float *Gr, *Gs;  // [2][E][H+3]: branch-major; the gather kernel adds both branches
+    float* part;     // [gridDim.x][layer param count], zero-initialised
+};
+
+struct TcOperand {
+    uint32_t hi, lo;        // shared-memory addresses of the hi / lo tiles
+    uint32_t chunk_stride;  // bytes between consecutive 16-byte chunk columns (rows * 16)
+    bool mn;                // viewed MN-major (K index = tile row)
+};
+__device__ __forceinline__ uint64_t tc_op_desc(const TcOperand& o, bool use_lo, int s) {
+    const uint32_t base = use_lo ? o.lo : o.hi;
+    return o.mn ? tc::make_desc(base + s * 256, 128, o.chunk_stride)
+                : tc::make_desc(base + s * 2 * o.chunk_stride, o.chunk_stride, 128);
+}
+// one thread: D[128 x N] (+)= A . B^T over K, NPASS split products, into TMEM column dcol
+template <int NPASS>
+__device__ __forceinline__ void tc_issue_op(uint32_t tmem, int dcol, const TcOperand& A, const TcOperand& B, int K, int N,
+                                            bool acc) {
+    const uint32_t idesc = tc::make_idesc_bf16(128, N) | (A.mn ? 1u << 15 : 0u) | (B.mn ? 1u << 16 : 0u);
+#pragma unroll
+    for (int p = 0; p < NPASS; ++p) {
+        for (int s = 0; s < K / 16; ++s) {
+            tc::mma_bf16(tmem + dcol, tc_op_desc(A, p == 1, s), tc_op_desc(B, p == 2, s), idesc, acc);
+            acc = true;
+        }
+    }
+}
+
+// warp reduce-scatter of 64 per-thread values over the 32 lanes (fixed order): lane L ends with the sums of
+// columns 2L and 2L+1 over the warp's 32 rows
+__device__ __forceinline__ void warp_colsum64(float (&v)[64], int lane, float& out0, float& out1) {
+    // offsets 16, 8, 4, 2, 1 halve the live range 64 -> 32 -> 16 -> 8 -> 4 -> 2
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+        const bool hiL = lane & 16;
+        const float send = hiL ? v[k] : v[k + 32], keep = hiL ? v[k + 32] : v[k];
+        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const bool hiL = lane & 8;
+        const float send = hiL ? v[k] : v[k + 16], keep = hiL ? v[k + 16] : v[k];
+        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const bool hiL = lane & 4;
+        const float send = hiL ? v[k] : v[k + 8], keep = hiL ? v[k + 8] : v[k];
+        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const bool hiL = lane & 2;
+        const float send = hiL ? v[k] : v[k + 4], keep = hiL ? v[k + 4] : v[k];
+        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const bool hiL = lane & 1;
+        const float send = hiL ? v[k] : v[k + 2], keep = hiL ? v[k + 2] : v[k];
+        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+    }
+    out0 = v[0];
+    out1 = v[1];
+}
+
+}  // namespace

@@ -81,9 +81,10 @@ int egnn_profile_enable(int32_t on);
 int egnn_profile_read(int32_t kind, double* total_ms_host, int64_t* launches_host);
 
 /* one-tile tcgen05 GEMM used by the tests to pin the shared-memory descriptor conventions on hardware:
- * D[128,N] = A[128,K] . B[N,K]^T, fp32 in/out, bf16 operands (npass 1) or hi/lo split with 3 products (npass 3) */
+ * D[128,N] = A[128,K] . B[N,K]^T, fp32 in/out, bf16 operands (npass 1) or hi/lo split with 3 products (npass 3);
+ * flags: 1 swap LBO/SBO (K-major), 2 stage A MN-major, 4 stage B MN-major, 8 swap LBO/SBO of MN-major descriptors */
 int egnn_tc_selftest(const float* A, const float* B, float* D, int32_t K, int32_t N, int32_t npass,
-                     int32_t swap_lbo_sbo, int32_t* status_dev, void* stream);
+                     int32_t flags, int32_t* status_dev, void* stream);
 
 /* ---- sizes ----------------------------------------------------------------------------------------------- */
 int64_t egnn_param_count(const egnn_net_t* net);          /* floats in the flat parameter buffer */

@@ -33,6 +33,12 @@ def test_tc_selftest_descriptor_convention(lib):
                 err, st = _selftest(K, N, npass, swap)
                 out[f"K{K}_N{N}_p{npass}_swap{swap}"] = (err, st)
                 json.dump(out, open("gpurun_out/tc_selftest.json", "w"), indent=1)
+    # MN-major operands (backward kernels view an edge tile [e][n] as the transposed operand): probe both conventions
+    for flags in (2, 2 | 8, 4, 4 | 8, 6, 6 | 8):
+        for K, N in ((16, 16), (64, 64), (128, 128), (128, 16)):
+            err, st = _selftest(K, N, 3, flags)
+            out[f"K{K}_N{N}_p3_flags{flags}"] = (err, st)
+            json.dump(out, open("gpurun_out/tc_selftest.json", "w"), indent=1)
     for K, N in ((16, 16), (16, 256), (64, 64), (128, 128)):
         e1, s1 = out[f"K{K}_N{N}_p1_swap0"]
         e3, s3 = out[f"K{K}_N{N}_p3_swap0"]
