@@ -119,6 +119,7 @@ struct GatherArgs {
     int N, H;
     const int32_t *row_ptr, *col_ptr, *col_edge;
     const float *gh_node, *gx_out, *Gr, *Gs;
+    const float *Gr2, *Gs2;  // second per-branch slab of the tensor-core edge backward (nullptr on the FFMA path)
     float *gh_in, *gx_in;
 };
 __global__ void __launch_bounds__(256) egcl_gather_bwd(GatherArgs a) {
@@ -127,8 +128,16 @@ __global__ void __launch_bounds__(256) egcl_gather_bwd(GatherArgs a) {
     if (idx >= (long long)a.N * W) return;
     const int i = (int)(idx / W), c = (int)(idx - (long long)i * W);
     float s = c < a.H ? a.gh_node[(size_t)i * a.H + c] : a.gx_out[(size_t)i * 3 + (c - a.H)];
-    for (int e = a.row_ptr[i]; e < a.row_ptr[i + 1]; ++e) s += a.Gr[(size_t)e * W + c];
-    for (int q = a.col_ptr[i]; q < a.col_ptr[i + 1]; ++q) s += a.Gs[(size_t)a.col_edge[q] * W + c];
+    if (a.Gr2) {
+        for (int e = a.row_ptr[i]; e < a.row_ptr[i + 1]; ++e) s += a.Gr[(size_t)e * W + c] + a.Gr2[(size_t)e * W + c];
+        for (int q = a.col_ptr[i]; q < a.col_ptr[i + 1]; ++q) {
+            const size_t o = (size_t)a.col_edge[q] * W + c;
+            s += a.Gs[o] + a.Gs2[o];
+        }
+    } else {
+        for (int e = a.row_ptr[i]; e < a.row_ptr[i + 1]; ++e) s += a.Gr[(size_t)e * W + c];
+        for (int q = a.col_ptr[i]; q < a.col_ptr[i + 1]; ++q) s += a.Gs[(size_t)a.col_edge[q] * W + c];
+    }
     if (c < a.H) a.gh_in[(size_t)i * a.H + c] = s;
     else a.gx_in[(size_t)i * 3 + (c - a.H)] = s;
 }
@@ -357,6 +366,10 @@ __global__ void __launch_bounds__(256) egcl_edge_bwd(EdgeBwdArgs a) {
 size_t egnn_edge_fwd_smem(const egnn_net_t& net, int TE);
 int egnn_validate_net(const egnn_net_t* net);
 int egnn_validate_graph(const egnn_graph_t* g, bool need_sender_csr);
+int egnn_tc_bwd_grid(int64_t E);
+int egnn_tc_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
+                          const float* x, const float* gM, const float* gdx, const float* coefS, float* Gr, float* Gs,
+                          float* part, int precision, cudaStream_t st);
 
 namespace {
 
@@ -375,6 +388,7 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     w.TEB = edge_tile_bwd(n);
     const int64_t tilesE = (E + w.TEB - 1) / w.TEB, tilesN = (N + TNB - 1) / TNB;
     w.gridE = (int)(tilesE < kNumSM ? tilesE : kNumSM);
+    if (tc_supported(n) && E > 0 && egnn_tc_bwd_grid(E) > w.gridE) w.gridE = egnn_tc_bwd_grid(E);
     w.gridN = (int)(tilesN < kNumSM ? tilesN : kNumSM);
     const int64_t W = n.H + 3;
     int64_t p = 0;
@@ -383,8 +397,8 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     w.coefS = take(G);
     w.gM = take(N * n.Ms);
     w.gh_node = take(N * n.H);
-    w.Gr = take(E * W);
-    w.Gs = take(E * W);
+    w.Gr = take(2 * E * W);  // two slabs: the tensor-core path writes one per branch
+    w.Gs = take(2 * E * W);
     w.ghb = take(2 * N * n.H);
     w.gxb = take(2 * N * 3);
     w.part = take((int64_t)(w.gridE + w.gridN) * layer_off(n).total);
@@ -429,7 +443,10 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
                  "egnn_net_backward: NULL tensor pointer");
     EGNN_REQUIRE(norm_scope == EGNN_NORM_CALL || norm_scope == EGNN_NORM_GRAPH, "bad norm_scope %d", norm_scope);
     EGNN_REQUIRE(g->node_graph != nullptr, "egnn_net_backward: node_graph is NULL");
-    (void)precision;  // the backward always runs in fp32 on the CUDA cores
+    EGNN_REQUIRE(precision >= EGNN_PREC_FP32 && precision <= EGNN_PREC_BF16, "bad precision %d", precision);
+    const bool use_tc = precision != EGNN_PREC_FP32;  // edge phase on tcgen05 (bf16x3 split products or plain bf16)
+    if (use_tc)
+        EGNN_REQUIRE(tc_supported(*net), "tcgen05 path needs Mh = Ms = Xh in {64,128} and 2H+1 <= 16; use precision fp32");
     const FwdWs fw = fwd_ws(*net, g->N, g->E, g->G);
     const BwdWs bw = bwd_ws(*net, g->N, g->E, g->G);
     if (ws_floats < bw.total) {
@@ -473,7 +490,11 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
             egnn_prof_end(st);
             EGNN_CHECK_LAUNCH("egcl_node_bwd");
         }
-        if (E > 0) {
+        if (E > 0 && use_tc) {
+            if (int rc = egnn_tc_edge_backward(*net, *g, Pk, hl, xl, ws + bw.gM, ws + bw.gdx, ws + bw.coefS, ws + bw.Gr,
+                                               ws + bw.Gs, ws + bw.part, precision, st))
+                return rc;
+        } else if (E > 0) {
             EdgeBwdArgs ea{*net, N, E, (E + bw.TEB - 1) / bw.TEB, g->recv, g->send, g->node_graph, hl, xl, P, Pk,
                            ws + bw.gM, ws + bw.gdx, ws + bw.coefS, ws + bw.Gr, ws + bw.Gs, ws + bw.part};
             int rc;
@@ -486,7 +507,9 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
             if (rc) return rc;
         }
         {
-            GatherArgs ga{N, H, g->row_ptr, g->col_ptr, g->col_edge, ws + bw.gh_node, gxo, ws + bw.Gr, ws + bw.Gs, ghi, gxi};
+            GatherArgs ga{N, H, g->row_ptr, g->col_ptr, g->col_edge, ws + bw.gh_node, gxo, ws + bw.Gr, ws + bw.Gs,
+                          use_tc ? ws + bw.Gr + (size_t)E * (H + 3) : nullptr,
+                          use_tc ? ws + bw.Gs + (size_t)E * (H + 3) : nullptr, ghi, gxi};
             const long long tot = (long long)N * (H + 3);
             egnn_prof_begin(EGNN_K_GATHER_BWD, st);
             egcl_gather_bwd<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(ga);

@@ -553,42 +553,419 @@ __device__ __forceinline__ void tc_issue_op(uint32_t tmem, int dcol, const TcOpe
     }
 }
 
-// warp reduce-scatter of 64 per-thread values over the 32 lanes (fixed order): lane L ends with the sums of
-// columns 2L and 2L+1 over the warp's 32 rows
-__device__ __forceinline__ void warp_colsum64(float (&v)[64], int lane, float& out0, float& out1) {
-    // offsets 16, 8, 4, 2, 1 halve the live range 64 -> 32 -> 16 -> 8 -> 4 -> 2
+// warp reduce-scatter of NV per-thread values over the 32 lanes (fixed order): lane L ends with the sums over the
+// warp's 32 rows of columns L*(NV/32) + k, k < NV/32, in v[0 .. NV/32)
+template <int NV>
+__device__ __forceinline__ void warp_colsum(float (&v)[NV], int lane) {
 #pragma unroll
-    for (int k = 0; k < 32; ++k) {
-        const bool hiL = lane & 16;
-        const float send = hiL ? v[k] : v[k + 32], keep = hiL ? v[k + 32] : v[k];
-        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-    }
+    for (int st = 0; st < 5; ++st) {
+        const int off = 16 >> st, live = NV >> (st + 1);
+        const bool hiL = lane & off;
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        const bool hiL = lane & 8;
-        const float send = hiL ? v[k] : v[k + 16], keep = hiL ? v[k + 16] : v[k];
-        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        for (int k = 0; k < NV / 2; ++k) {
+            if (k < live) {
+                const float send = hiL ? v[k] : v[k + live], keep = hiL ? v[k + live] : v[k];
+                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+        }
     }
+}
+
+// split + store 32 consecutive columns [c0, c0+32) of row r into a 128-row tile
+__device__ __forceinline__ void tc_split_store32(uint8_t* t_hi, uint8_t* t_lo, int r, int c0, const float (&v)[32], bool with_lo) {
+    uint32_t hi[16], lo[16];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const bool hiL = lane & 4;
-        const float send = hiL ? v[k] : v[k + 8], keep = hiL ? v[k + 8] : v[k];
-        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const bool hiL = lane & 2;
-        const float send = hiL ? v[k] : v[k + 4], keep = hiL ? v[k + 4] : v[k];
-        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    }
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        const bool hiL = lane & 1;
-        const float send = hiL ? v[k] : v[k + 2], keep = hiL ? v[k + 2] : v[k];
-        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
-    }
-    out0 = v[0];
-    out1 = v[1];
+    for (int i = 0; i < 16; ++i) tc::split2(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+    tc_store32(t_hi, t_lo, r, c0, hi, lo, with_lo);
 }
 
 }  // namespace
+
+namespace {
+
+template <bool FAST>
+__device__ __forceinline__ float tc_sigmoid(float z) {
+    if (FAST) {
+        float t;
+        asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * z));
+        return fmaf(0.5f, t, 0.5f);
+    }
+    return sigmoid_f(z);
+}
+
+template <int D, int NPASS>
+__global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
+    using L = TcBwdLayout<D>;
+    constexpr bool FAST = NPASS == 1;
+    constexpr bool LO = NPASS == 3;
+    constexpr int HALF = D / 2, NB = HALF / 32, NVL = HALF / 32;
+    constexpr int cA = 0, cB = D, cP2 = 2 * D, cPB = 3 * D;  // TMEM columns: z1|gu, z2|ga1, dW2, [db2 (16) | dW1+db1 (16)]
+    constexpr uint32_t TS = 128 * 16;                        // chunk stride of a 128-row tile
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q = warp & 3, hf = warp >> 2;
+    const int r = q * 32 + lane;
+    const int branch = blockIdx.x & 1;  // 0: mlp_m + gate, 1: mlp_x
+    const int H = a.net.H, K0 = 2 * H + 1, W = H + 3;
+    float* vec = reinterpret_cast<float*>(smem + L::vec);
+    int* sI = reinterpret_cast<int*>(smem + L::sI);
+    float4* sR = reinterpret_cast<float4*>(smem + L::sR);
+    float* rowA = reinterpret_cast<float*>(smem + L::rowA);
+    float* rowB = reinterpret_cast<float*>(smem + L::rowB);
+    float* colred = reinterpret_cast<float*>(smem + L::colred);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::bars);
+    uint32_t* slot = reinterpret_cast<uint32_t*>(smem + L::slot);
+
+    // ---- one-time setup: W1 (both branches), this branch's W2, vectors -> smem; TMEM; barriers
+    {
+        const uint8_t* w2src = a.blob + 2 * L::W1_BYTES + (size_t)branch * 2 * L::W2_BYTES;
+        const uint8_t* vsrc = a.blob + 2 * L::W1_BYTES + 4 * L::W2_BYTES;
+        for (int o = tid * 16; o < 2 * L::W1_BYTES; o += 256 * 16)
+            *reinterpret_cast<uint4*>(smem + L::w1_hi + o) = __ldg(reinterpret_cast<const uint4*>(a.blob + o));
+        for (int o = tid * 16; o < 2 * L::W2_BYTES; o += 256 * 16)
+            *reinterpret_cast<uint4*>(smem + L::w2_hi + o) = __ldg(reinterpret_cast<const uint4*>(w2src + o));
+        for (int o = tid * 16; o < L::VEC_BYTES; o += 256 * 16)
+            *reinterpret_cast<uint4*>(smem + L::vec + o) = __ldg(reinterpret_cast<const uint4*>(vsrc + o));
+    }
+    if (warp == 0) tc::tmem_alloc(slot, 4 * D);
+    if (tid == 0) {
+        for (int b = 0; b < 4; ++b) tc::mbar_init(&bars[b], 1);
+        tc::fence_mbar_init();
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *slot;
+    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    bool ok = true;
+
+    const uint32_t sb = tc::smem_u32(smem);
+    const TcOperand opU{sb + L::u_hi, sb + L::u_lo, TS, false}, opUmn{sb + L::u_hi, sb + L::u_lo, TS, true};
+    const TcOperand opA1{sb + L::a1_hi, sb + L::a1_lo, TS, false}, opA1mn{sb + L::a1_hi, sb + L::a1_lo, TS, true};
+    const TcOperand opG{sb + L::g_hi, sb + L::g_lo, TS, false}, opGmn{sb + L::g_hi, sb + L::g_lo, TS, true};
+    const uint32_t w1off = (uint32_t)(branch * (D / 8) * 128);  // this branch's rows inside the [2D x 16] W1 image
+    const TcOperand opW1{sb + L::w1_hi + w1off, sb + L::w1_lo + w1off, 2 * D * 16, false};
+    const TcOperand opW1mn{sb + L::w1_hi + w1off, sb + L::w1_lo + w1off, 2 * D * 16, true};
+    const TcOperand opW2{sb + L::w2_hi, sb + L::w2_lo, D * 16, false}, opW2mn{sb + L::w2_hi, sb + L::w2_lo, D * 16, true};
+
+    const float* b1 = vec + branch * D;
+    const float* b2 = vec + 2 * D + branch * D;
+    const float* wv = vec + 4 * D + branch * D;  // wa (gate) or wx3 (phi head)
+    const float bv = vec[6 * D + branch];
+    float* Grb = a.Gr + (size_t)branch * a.E * W;
+    float* Gsb = a.Gs + (size_t)branch * a.E * W;
+
+    float accv[NVL];  // running column sums of coef_e * out_e (grad of wa / wx3), this warp's rows
+#pragma unroll
+    for (int k = 0; k < NVL; ++k) accv[k] = 0.f;
+    float accs = 0.f;  // running sum of coef_e over this thread's row (grad of ba / bx3)
+
+    uint32_t phase = 0;
+    bool first = true;
+    for (int tile = blockIdx.x >> 1; tile < a.tiles; tile += gridDim.x >> 1, phase ^= 1, first = false) {
+        const int e0 = tile * 128;
+        const int nrows = min(128, a.E - e0);
+        // ---- gather: u -> U tile (slot 15 carries the constant 1 that turns the wgrad MMAs into bias gradients too)
+        if (tid < 128) {
+            float u[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) u[k] = 0.f;
+            int i = 0;
+            float rx = 0.f, ry = 0.f, rz = 0.f;
+            if (tid < nrows) {
+                i = a.recv[e0 + tid];
+                const int j = a.send[e0 + tid];
+                rx = a.x[3 * i + 0] - a.x[3 * j + 0];
+                ry = a.x[3 * i + 1] - a.x[3 * j + 1];
+                rz = a.x[3 * i + 2] - a.x[3 * j + 2];
+                const float nrm = sqrtf(rx * rx + ry * ry + rz * rz);
+#pragma unroll
+                for (int k = 0; k < 15; ++k) {
+                    if (k < H) u[k] = a.h[(size_t)i * H + k];
+                    else if (k < 2 * H) u[k] = a.h[(size_t)j * H + (k - H)];
+                    else if (k == 2 * H) u[k] = nrm * nrm;
+                }
+                u[15] = 1.f;
+            }
+            sI[tid] = i;
+            sR[tid] = make_float4(rx, ry, rz, tid < nrows ? 1.f : 0.f);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int p = 0; p < 4; ++p) tc::split2(u[8 * j + 2 * p], u[8 * j + 2 * p + 1], hi[p], lo[p]);
+                *reinterpret_cast<uint4*>(smem + L::u_hi + tc::chunk_off(128, tid, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(smem + L::u_lo + tc::chunk_off(128, tid, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            }
+        }
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc::fence_after_sync();
+            tc_issue_op<NPASS>(tmem, cA, opU, opW1, 16, D, false);  // z1 = U . W1^T
+            tc::mma_commit(&bars[0]);
+        }
+        ok = tc::mbar_wait(&bars[0], phase) && ok;
+        tc::fence_after_sync();
+        // ---- a1 = SiLU(z1 + b1) -> tile A1 (z1 stays in TMEM for SiLU' later)
+        {
+            uint32_t hi[16], lo[16];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                const int c0 = hf * HALF + 32 * b;
+                tc_epi32<FAST>(trow + cA + c0, b1 + c0, hi, lo);
+                tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, hi, lo, LO);
+            }
+        }
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc::fence_after_sync();
+            tc_issue_op<NPASS>(tmem, cB, opA1, opW2, D, D, false);  // z2 = a1 . W2^T
+            tc::mma_commit(&bars[1]);
+        }
+        ok = tc::mbar_wait(&bars[1], phase) && ok;
+        tc::fence_after_sync();
+        // ---- upstream gradient of z2: z, sigmoid(z) of this thread's columns in registers
+        {
+            float z[HALF], sg[HALF];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                const int c0 = hf * HALF + 32 * b;
+                float v[32];
+                tc::tmem_ld32(trow + cB + c0, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    z[32 * b + i] = v[i] + b2[c0 + i];
+                    sg[32 * b + i] = tc_sigmoid<FAST>(z[32 * b + i]);
+                }
+            }
+            const float4 rr = sR[r];
+            const int i = sI[r];
+            const float* wvh = wv + hf * HALF;
+            float c_row, c_g = 0.f;  // gz2[c] = (c_g * gM[i][c] + c_row * wv[c]) * SiLU'(z[c]);  d wv[c] += c_row * out[c]
+            const float4* gMi = reinterpret_cast<const float4*>(a.gM + (size_t)i * D + hf * HALF);
+            if (branch == 0) {
+                // gate g = sigmoid(wa.m + ba);  t = gM[i].m;  c_row = gs = t g (1-g);  c_g = g
+                float sdot = 0.f, tdot = 0.f;
+#pragma unroll
+                for (int c4 = 0; c4 < HALF / 4; ++c4) {
+                    const float4 gm = __ldg(gMi + c4);
+                    const float m0 = z[4 * c4] * sg[4 * c4], m1 = z[4 * c4 + 1] * sg[4 * c4 + 1];
+                    const float m2 = z[4 * c4 + 2] * sg[4 * c4 + 2], m3 = z[4 * c4 + 3] * sg[4 * c4 + 3];
+                    sdot = fmaf(wvh[4 * c4], m0, sdot);
+                    sdot = fmaf(wvh[4 * c4 + 1], m1, sdot);
+                    sdot = fmaf(wvh[4 * c4 + 2], m2, sdot);
+                    sdot = fmaf(wvh[4 * c4 + 3], m3, sdot);
+                    tdot = fmaf(gm.x, m0, tdot);
+                    tdot = fmaf(gm.y, m1, tdot);
+                    tdot = fmaf(gm.z, m2, tdot);
+                    tdot = fmaf(gm.w, m3, tdot);
+                }
+                rowA[hf * 128 + r] = sdot;
+                rowB[hf * 128 + r] = tdot;
+                __syncthreads();
+                const float g = sigmoid_f(rowA[r] + rowA[128 + r] + bv);
+                const float t = rowB[r] + rowB[128 + r];
+                c_row = rr.w * t * g * (1.f - g);
+                c_g = rr.w * g;
+            } else {
+                // phi = wx3.q + bx3 (needed for the coordinate output);  c_row = gphi = gdx[i].r
+                float pdot = 0.f;
+#pragma unroll
+                for (int c = 0; c < HALF; ++c) pdot = fmaf(wvh[c], z[c] * sg[c], pdot);
+                rowA[hf * 128 + r] = pdot;
+                const float* gd = a.gdx + (size_t)i * 3;
+                c_row = rr.w * (gd[0] * rr.x + gd[1] * rr.y + gd[2] * rr.z);
+            }
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                float gz[32];
+#pragma unroll
+                for (int c4 = 0; c4 < 8; ++c4) {
+                    float4 gm = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (branch == 0) gm = __ldg(gMi + 8 * b + c4);
+                    const float gmv[4] = {gm.x, gm.y, gm.z, gm.w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int c = 32 * b + 4 * c4 + k;
+                        const float d2 = sg[c] * fmaf(z[c], 1.f - sg[c], 1.f);
+                        gz[4 * c4 + k] = fmaf(c_g, gmv[k], c_row * wvh[c]) * d2;
+                        z[c] = c_row * (z[c] * sg[c]);  // coef_e * out_e[c] for the column sums below
+                    }
+                }
+                tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, hf * HALF + 32 * b, gz, LO);
+            }
+            warp_colsum<HALF>(z, lane);
+#pragma unroll
+            for (int k = 0; k < NVL; ++k) accv[k] += z[k];
+            accs += c_row;
+        }
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc::fence_after_sync();
+            tc_issue_op<NPASS>(tmem, cB, opG, opW2mn, D, D, false);        // ga1 = gz2 . W2
+            tc_issue_op<NPASS>(tmem, cP2, opGmn, opA1mn, 128, D, !first);  // dW2 += gz2^T . a1
+            tc_issue_op<NPASS>(tmem, cPB, opGmn, opUmn, 128, 16, !first);  // column 15: db2 += gz2^T . 1
+            tc::mma_commit(&bars[2]);
+        }
+        ok = tc::mbar_wait(&bars[2], phase) && ok;
+        tc::fence_after_sync();
+        // ---- gz1 = ga1 * SiLU'(z1 + b1) -> tile G (overwrites gz2: every MMA reading it has completed)
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+            const int c0 = hf * HALF + 32 * b;
+            float ga[32], z1[32];
+            tc::tmem_ld32(trow + cB + c0, ga);
+            tc::tmem_ld32(trow + cA + c0, z1);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float zz = z1[i] + b1[c0 + i];
+                const float s = tc_sigmoid<FAST>(zz);
+                ga[i] *= s * fmaf(zz, 1.f - s, 1.f);
+            }
+            tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, ga, LO);
+        }
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc::fence_after_sync();
+            tc_issue_op<NPASS>(tmem, cA, opG, opW1mn, D, 16, false);            // gu = gz1 . W1   (16 columns)
+            tc_issue_op<NPASS>(tmem, cPB + 16, opGmn, opUmn, 128, 16, !first);  // dW1 += gz1^T . u, column 15: db1
+            tc::mma_commit(&bars[3]);
+        }
+        ok = tc::mbar_wait(&bars[3], phase) && ok;
+        tc::fence_after_sync();
+        // ---- per-edge outputs of this branch: receiver / sender parts of gu, coordinate part through d_e and phi
+        if (hf == 0) {
+            float gu[32];
+            tc::tmem_ld32(trow + cA, gu);
+            if (r < nrows) {
+                const size_t e = (size_t)(e0 + r);
+                const float4 rr = sR[r];
+                const int i = sI[r];
+                float gd = 0.f;
+#pragma unroll
+                for (int k = 0; k < 15; ++k) {
+                    if (k < H) Grb[e * W + k] = gu[k];
+                    else if (k < 2 * H) Gsb[e * W + (k - H)] = gu[k];
+                    else if (k == 2 * H) gd = gu[k];
+                }
+                float cr = 2.f * gd, phi = 0.f;
+                float gx0 = 0.f, gx1 = 0.f, gx2 = 0.f;
+                if (branch == 1) {
+                    phi = rowA[r] + rowA[128 + r] + bv;
+                    cr += a.coefS[a.node_graph[i]];
+                    gx0 = a.gdx[(size_t)i * 3 + 0];
+                    gx1 = a.gdx[(size_t)i * 3 + 1];
+                    gx2 = a.gdx[(size_t)i * 3 + 2];
+                }
+                const float g0 = fmaf(gx0, phi, cr * rr.x), g1 = fmaf(gx1, phi, cr * rr.y), g2 = fmaf(gx2, phi, cr * rr.z);
+                Grb[e * W + H + 0] = g0;
+                Grb[e * W + H + 1] = g1;
+                Grb[e * W + H + 2] = g2;
+                Gsb[e * W + H + 0] = -g0;
+                Gsb[e * W + H + 1] = -g1;
+                Gsb[e * W + H + 2] = -g2;
+            }
+        }
+        tc::fence_before_sync();
+    }
+    if (!ok) asm volatile("trap;");
+    // ---- weight gradients of this CTA's tiles: TMEM accumulators / register column sums -> private partial row
+    const LayerOff lo = layer_off(a.net);
+    float* part = a.part + (size_t)blockIdx.x * lo.total;
+    const int o_w1 = branch ? lo.wx1 : lo.wm1, o_b1 = branch ? lo.bx1 : lo.bm1;
+    const int o_w2 = branch ? lo.wx2 : lo.wm2, o_b2 = branch ? lo.bx2 : lo.bm2;
+    const int o_wv = branch ? lo.wx3 : lo.wa, o_bv = branch ? lo.bx3 : lo.ba;
+    __syncthreads();
+    if (!first) {  // at least one tile went through (the host sizes the grid so this always holds)
+        tc::fence_after_sync();
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+            const int c0 = hf * HALF + 32 * b;
+            float v[32];
+            tc::tmem_ld32(trow + cP2 + c0, v);
+            if (r < D) {
+                float* dst = part + o_w2 + (size_t)r * D + c0;  // partial rows are not 16-byte aligned in general
+#pragma unroll
+                for (int k = 0; k < 32; ++k) dst[k] = v[k];
+            }
+        }
+        if (hf == 0) {
+            float v[32];
+            tc::tmem_ld32(trow + cPB, v);  // [0,16): gz2^T.u (col 15 = db2)   [16,32): dW1 (col 31 = db1)
+            if (r < D) {
+                part[o_b2 + r] = v[15];
+                part[o_b1 + r] = v[31];
+#pragma unroll
+                for (int k = 0; k < 15; ++k)
+                    if (k < K0) part[o_w1 + r * K0 + k] = v[16 + k];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < NVL; ++k) colred[warp * 64 + lane * NVL + k] = accv[k];
+        if (hf == 0) rowB[r] = accs;
+        __syncthreads();
+        if (tid < D) {
+            const int hc = tid / HALF, cc = tid % HALF;
+            float s = 0.f;
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq) s += colred[(hc * 4 + qq) * 64 + cc];
+            part[o_wv + tid] = s;
+        }
+        if (tid == 0) {
+            float s = 0.f;
+            for (int rr = 0; rr < 128; ++rr) s += rowB[rr];
+            part[o_bv] = s;
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, 4 * D);
+}
+
+template <int D, int NPASS>
+int launch_tc_bwd(const TcBwdArgs& a, int grid, cudaStream_t st) {
+    constexpr int SMEM = TcBwdLayout<D>::TOTAL + (D == 64 ? 16 * 1024 : 0);  // D=64: the M=128 wgrad view reads past tile G
+    static bool configured = false;
+    if (!configured) {
+        EGNN_CUDA(cudaFuncSetAttribute(tc_edge_bwd<D, NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        configured = true;
+    }
+    egnn_prof_begin(EGNN_K_TC_EDGE_BWD, st);
+    tc_edge_bwd<D, NPASS><<<grid, 256, SMEM, st>>>(a);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("tc_edge_bwd");
+    return EGNN_OK;
+}
+
+}  // namespace
+
+// number of CTAs (= private partial rows) the tensor-core edge backward uses for E edges: even, <= 148, <= 2 * tiles
+int egnn_tc_bwd_grid(int64_t E) {
+    const int64_t tiles = (E + 127) / 128;
+    const int64_t g = 2 * tiles < 148 ? 2 * tiles : 148;
+    return (int)g;
+}
+
+// edge phase of one layer's backward on the tensor cores.  Gr / Gs hold [2][E][H+3] (one slab per branch).
+int egnn_tc_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
+                          const float* x, const float* gM, const float* gdx, const float* coefS, float* Gr, float* Gs,
+                          float* part, int precision, cudaStream_t st) {
+    EGNN_REQUIRE(tc_supported(net), "tcgen05 path needs Mh = Ms = Xh in {64,128} and 2H+1 <= 16 (got Mh=%d Ms=%d Xh=%d H=%d); "
+                 "use precision fp32", net.Mh, net.Ms, net.Xh, net.H);
+    const PackOff po = pack_off(net);
+    TcBwdArgs a{net, g.N, g.E, (g.E + 127) / 128, g.recv, g.send, g.node_graph, h, x,
+                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), gM, gdx, coefS, Gr, Gs, part};
+    const int grid = egnn_tc_bwd_grid(g.E);
+    const bool x3 = precision == EGNN_PREC_BF16X3;
+    if (net.Mh == 128) return x3 ? launch_tc_bwd<128, 3>(a, grid, st) : launch_tc_bwd<128, 1>(a, grid, st);
+    return x3 ? launch_tc_bwd<64, 3>(a, grid, st) : launch_tc_bwd<64, 1>(a, grid, st);
+}

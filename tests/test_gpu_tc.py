@@ -119,3 +119,66 @@ def test_tc_forward_edge_cases_and_unsupported(lib):
     wide.precision = "bf16"
     with pytest.raises(EgnnError):
         wide(ei.to(DEV), h.to(DEV), x.to(DEV))
+
+
+# ---------------------------------------------------------------- tensor-core edge BACKWARD vs the reference autograd
+def _grad_errors(name, precision, scope="call"):
+    z = _load("egnn_" + name)
+    net, sizes = _net_from(z)
+    net.precision = precision
+    sd = {k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w:")}
+    h0, x0 = torch.from_numpy(z["h"]), torch.from_numpy(z["x"])
+    ei = torch.from_numpy(z["edge_index"])
+    th, tx = torch.from_numpy(z["target_h"]), torch.from_numpy(z["target_x"])
+    h, x = h0.to(DEV).requires_grad_(True), x0.to(DEV).requires_grad_(True)
+    ho, xo = net(ei.to(DEV), h, x)
+    loss = ((ho - th.to(DEV)) ** 2).sum() + ((xo - x - tx.to(DEV)) ** 2).sum()
+    loss.backward()
+    errs = {k: _relerr(p.grad, z["g:" + k]) for k, p in net.named_parameters()}
+    hc, xc = h0.clone().requires_grad_(True), x0.clone().requires_grad_(True)
+    hr, xr = egnn_ref.egnn_forward(sd, sizes["L"], ei, hc, xc)
+    (((hr - th) ** 2).sum() + ((xr - xc - tx) ** 2).sum()).backward()
+    errs["h_in"], errs["x_in"] = _relerr(h.grad, hc.grad), _relerr(x.grad, xc.grad)
+    errs["loss"] = abs(loss.item() - float(z["loss"])) / abs(float(z["loss"]))
+    grads = [p.grad.clone() for p in net.parameters()] + [h.grad.clone(), x.grad.clone()]
+    return errs, grads
+
+
+@pytest.mark.parametrize("name", ["cfg1", "cfg2"])
+@pytest.mark.parametrize("precision,tol", [("bf16x3", 1e-3), ("bf16", 2.5e-1)])  # bf16: stated loose bound
+def test_tc_backward_matches_reference_grads(lib, name, precision, tol):
+    errs, g1 = _grad_errors(name, precision)
+    worst = max(errs, key=errs.get)
+    print(f"tc backward {name} {precision}: worst {worst} {errs[worst]:.2e}")
+    assert errs[worst] <= tol, errs
+    _, g2 = _grad_errors(name, precision)
+    assert all(torch.equal(a, b) for a, b in zip(g1, g2))  # deterministic (no atomics)
+
+
+def test_tc_backward_edge_cases(lib):
+    """d=64 network, a receiver cut by several tiles, isolated nodes, one short tile, no edges"""
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    torch.manual_seed(0)
+    net = EquivariantGNN(**egnn_ref.net_sizes(2, 64)).to(DEV)
+    net.precision = "bf16x3"
+    sd = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
+    gen = torch.Generator().manual_seed(1)
+    n = 320
+    recv = np.concatenate([np.full(300, 2), np.full(5, 7), np.full(200, 9)]).astype(np.int64)
+    send = np.concatenate([np.arange(10, 310), np.arange(0, 5), np.arange(100, 300)]).astype(np.int64)
+    for ei in (torch.from_numpy(np.stack([recv, send])), torch.from_numpy(np.stack([recv[:40], send[:40]])),
+               torch.zeros(2, 0, dtype=torch.int64)):
+        h0, x0 = torch.randn(n, 3, generator=gen), torch.randn(n, 3, generator=gen)
+        sdg = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+        hc, xc = h0.clone().requires_grad_(True), x0.clone().requires_grad_(True)
+        hr, xr = egnn_ref.egnn_forward(sdg, 2, ei, hc, xc)
+        (hr.square().sum() + xr.square().sum()).backward()
+        net.zero_grad()
+        h, x = h0.to(DEV).requires_grad_(True), x0.to(DEV).requires_grad_(True)
+        ho, xo = net(ei.to(DEV), h, x)
+        (ho.square().sum() + xo.square().sum()).backward()
+        for k, p in net.named_parameters():
+            ref = sdg[k].grad if sdg[k].grad is not None else torch.zeros_like(sdg[k])
+            scale = max(float(ref.abs().max()), 1e-3)
+            assert float((p.grad.cpu() - ref).abs().max()) <= 1e-3 * scale, (k, ei.shape)
+        assert _relerr(h.grad, hc.grad) <= 1e-3 and _relerr(x.grad, xc.grad) <= 1e-3
