@@ -489,33 +489,40 @@ int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const flo
 
 // =====================================================================================================================
 // Fused EGCL edge kernel on tcgen05 (backward).  Each CTA owns ONE branch (blockIdx.x & 1: 0 = mlp_m + gate,
-// 1 = mlp_x) and walks its 128-edge tiles; per tile
+// 1 = mlp_x) and walks its 128-edge tiles with 4*D threads (thread = edge row x 32-column group); per tile
 //   recompute   z1 = U.W1^T (block A),  a1 = SiLU(z1+b1) -> tile A1,  z2 = a1.W2^T (block B)
 //   upstream    gz2 = dL/dz2 -> tile G            (gate / phi algebra of SURVEY.md Appendix A on the CUDA cores)
 //   dgrad       ga1 = gz2 . W2   (block B)        B operand = the SAME W2 image viewed MN-major
-//   wgrad       dW2 += gz2^T . a1,  db2 += gz2^T . 1        (persistent TMEM accumulators; tile G / A1 / U viewed MN-major)
-//   gz1 = ga1 * SiLU'(z1+b1) -> tile G;   gu = gz1 . W1 (16 columns),  dW1 += gz1^T . U  (slot 15 of u is 1 -> db1)
+//   wgrad       [dW2 | db2] += gz2^T . [a1 | u]   (persistent TMEM accumulators; slot 15 of u is the constant 1)
+//   gz1 = ga1 * SiLU'(z1+b1) -> tile G;   gu = gz1 . W1 (16 columns),  [dW1 | db1] += gz1^T . u
 // Shared-memory tiles are written once by the thread that owns the edge row (16-byte chunks) and serve both as
 // K-major operands (row = edge) and as MN-major operands (K = edge) -- same bytes, two descriptor views.
-// Weight gradients stay in TMEM over all tiles of the CTA and are written once to the CTA's private partial row.
+// The two wgrad MMAs run behind the CUDA-core work of the next phase (own mbarriers); the U tile is double-buffered and
+// the next tile's gather loads are in flight while GEMM2 runs.  Weight gradients stay in TMEM over all tiles of the
+// CTA and are written once to the CTA's private partial row (summed in CTA order by reduce_partials_kernel).
 // =====================================================================================================================
 namespace {
 
 template <int D>
 struct TcBwdLayout {
-    static constexpr int W1_BYTES = 2 * D * 32, W2_BYTES = D * D * 2;
-    static constexpr int w1_hi = 0, w1_lo = W1_BYTES;                 // both branches (rows [0,D) = m, [D,2D) = x)
-    static constexpr int w2_hi = 2 * W1_BYTES, w2_lo = w2_hi + W2_BYTES;  // this CTA's branch only
-    static constexpr int vec = w2_lo + W2_BYTES;                      // fp32 vectors as in TcLayout
-    static constexpr int VEC_BYTES = (6 * D + 4) * 4;
-    static constexpr int u_hi = (vec + VEC_BYTES + 15) / 16 * 16, u_lo = u_hi + 128 * 32;
-    static constexpr int a1_hi = u_lo + 128 * 32, a1_lo = a1_hi + 128 * D * 2;
-    static constexpr int g_hi = a1_lo + 128 * D * 2, g_lo = g_hi + 128 * D * 2;
-    static constexpr int small = g_lo + 128 * D * 2;
-    // small: sI int[128] | sR float[128][4] | rowA [2][128] | rowB [2][128] | colred [8][64] | bars | slot
-    static constexpr int sI = small, sR = sI + 512, rowA = sR + 2048, rowB = rowA + 1024, colred = rowB + 1024,
-                         bars = colred + 2048, slot = bars + 64;
+    static constexpr int NT = 4 * D, NG = D / 32;
+    static constexpr int TILE = 128 * D * 2, UT = 128 * 32;  // bytes of one hi (or lo) activation tile / U tile
+    static constexpr int g_hi = 0, g_lo = TILE;
+    // hi group u0 | a1 | u1 and the same for lo: the wgrad B operand [u0 | a1] (even tiles) or [a1 | u1] (odd tiles) is
+    // one MN-major tile of D/8 + 2 chunk columns
+    static constexpr int u0_hi = 2 * TILE, a1_hi = u0_hi + UT, u1_hi = a1_hi + TILE;
+    static constexpr int u0_lo = u1_hi + UT, a1_lo = u0_lo + UT, u1_lo = a1_lo + TILE;
+    static constexpr int w1_hi = u1_lo + UT, w1_lo = w1_hi + D * 32;  // this branch's [D x 16] image
+    static constexpr int w2_hi = w1_lo + D * 32, w2_lo = w2_hi + D * D * 2;
+    static constexpr int vec = w2_lo + D * D * 2;  // b1 | b2 | wv (D each) | bv, 0, 0, 0
+    static constexpr int VEC_BYTES = (3 * D + 4) * 4;
+    static constexpr int sI = vec + VEC_BYTES;           // int   [2][128]
+    static constexpr int sR = sI + 1024;                 // float4 [2][128]: r_e, valid
+    static constexpr int rowA = sR + 4096;               // float [NG][128]   (reused as colred [NT/32][32] at the end)
+    static constexpr int rowB = rowA + NG * 512;         // float [NG][128]
+    static constexpr int bars = rowB + NG * 512, slot = bars + 64;
     static constexpr int TOTAL = slot + 16;
+    static_assert(TOTAL <= 227 * 1024, "tc_edge_bwd shared memory");
 };
 
 struct TcBwdArgs {
@@ -553,16 +560,15 @@ __device__ __forceinline__ void tc_issue_op(uint32_t tmem, int dcol, const TcOpe
     }
 }
 
-// warp reduce-scatter of NV per-thread values over the 32 lanes (fixed order): lane L ends with the sums over the
-// warp's 32 rows of columns L*(NV/32) + k, k < NV/32, in v[0 .. NV/32)
-template <int NV>
-__device__ __forceinline__ void warp_colsum(float (&v)[NV], int lane) {
+// warp reduce-scatter of 32 per-thread values over the 32 lanes (fixed order): v[0] of lane L ends as the sum over the
+// warp's 32 rows of column L
+__device__ __forceinline__ void warp_colsum32(float (&v)[32], int lane) {
 #pragma unroll
     for (int st = 0; st < 5; ++st) {
-        const int off = 16 >> st, live = NV >> (st + 1);
+        const int off = 16 >> st, live = 16 >> st;
         const bool hiL = lane & off;
 #pragma unroll
-        for (int k = 0; k < NV / 2; ++k) {
+        for (int k = 0; k < 16; ++k) {
             if (k < live) {
                 const float send = hiL ? v[k] : v[k + live], keep = hiL ? v[k + live] : v[k];
                 v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
@@ -579,10 +585,6 @@ __device__ __forceinline__ void tc_split_store32(uint8_t* t_hi, uint8_t* t_lo, i
     tc_store32(t_hi, t_lo, r, c0, hi, lo, with_lo);
 }
 
-}  // namespace
-
-namespace {
-
 template <bool FAST>
 __device__ __forceinline__ float tc_sigmoid(float z) {
     if (FAST) {
@@ -593,115 +595,142 @@ __device__ __forceinline__ float tc_sigmoid(float z) {
     return sigmoid_f(z);
 }
 
+struct TcEdgeRow {  // one gathered edge held in registers between its global loads and its shared-memory stores
+    int i;
+    float rx, ry, rz, valid;
+    float u[16];
+};
+
 template <int D, int NPASS>
-__global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
+__global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     using L = TcBwdLayout<D>;
     constexpr bool FAST = NPASS == 1;
     constexpr bool LO = NPASS == 3;
-    constexpr int HALF = D / 2, NB = HALF / 32, NVL = HALF / 32;
-    constexpr int cA = 0, cB = D, cP2 = 2 * D, cPB = 3 * D;  // TMEM columns: z1|gu, z2|ga1, dW2, [db2 (16) | dW1+db1 (16)]
-    constexpr uint32_t TS = 128 * 16;                        // chunk stride of a 128-row tile
+    constexpr int NT = L::NT, NG = L::NG;
+    // TMEM columns: z1 | gu,  z2 | ga1,  db2 (even tiles),  dW2,  db2 (odd tiles),  dW1 + db1
+    constexpr int cA = 0, cB = D, cBias0 = 2 * D, cW2 = 2 * D + 16, cBias1 = 3 * D + 16, cP1 = 3 * D + 32;
+    constexpr uint32_t TS = 128 * 16;  // chunk stride of a 128-row tile
     extern __shared__ __align__(1024) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int q = warp & 3, hf = warp >> 2;
-    const int r = q * 32 + lane;
-    const int branch = blockIdx.x & 1;  // 0: mlp_m + gate, 1: mlp_x
+    const int q = warp & 3, cg = warp >> 2;
+    const int r = q * 32 + lane;  // edge row == TMEM lane
+    const int c0 = cg * 32;       // this thread's 32 columns
+    const int branch = blockIdx.x & 1;
     const int H = a.net.H, K0 = 2 * H + 1, W = H + 3;
     float* vec = reinterpret_cast<float*>(smem + L::vec);
     int* sI = reinterpret_cast<int*>(smem + L::sI);
     float4* sR = reinterpret_cast<float4*>(smem + L::sR);
     float* rowA = reinterpret_cast<float*>(smem + L::rowA);
     float* rowB = reinterpret_cast<float*>(smem + L::rowB);
-    float* colred = reinterpret_cast<float*>(smem + L::colred);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::bars);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::bars);  // 0 GEMM1, 1 GEMM2, 2 dgrad, 3 wgrad2, 4 gu, 5 wgrad1
     uint32_t* slot = reinterpret_cast<uint32_t*>(smem + L::slot);
 
-    // ---- one-time setup: W1 (both branches), this branch's W2, vectors -> smem; TMEM; barriers
+    // ---- one-time setup: this branch's weight images and vectors -> smem; TMEM; barriers
     {
-        const uint8_t* w2src = a.blob + 2 * L::W1_BYTES + (size_t)branch * 2 * L::W2_BYTES;
-        const uint8_t* vsrc = a.blob + 2 * L::W1_BYTES + 4 * L::W2_BYTES;
-        for (int o = tid * 16; o < 2 * L::W1_BYTES; o += 256 * 16)
-            *reinterpret_cast<uint4*>(smem + L::w1_hi + o) = __ldg(reinterpret_cast<const uint4*>(a.blob + o));
-        for (int o = tid * 16; o < 2 * L::W2_BYTES; o += 256 * 16)
+        constexpr int W1B = 2 * D * 32, W2B = D * D * 2;  // sizes inside the packed image (TcLayout)
+        for (int o = tid * 16; o < 4 * D * 16; o += NT * 16) {  // [hi|lo][chunk j][D*16 bytes of this branch's rows]
+            const int half = o / (2 * D * 16), j = (o / (D * 16)) & 1, off = o % (D * 16);
+            *reinterpret_cast<uint4*>(smem + (half ? L::w1_lo : L::w1_hi) + j * D * 16 + off) =
+                __ldg(reinterpret_cast<const uint4*>(a.blob + half * W1B + j * 2 * D * 16 + branch * D * 16 + off));
+        }
+        const uint8_t* w2src = a.blob + 2 * W1B + (size_t)branch * 2 * W2B;
+        for (int o = tid * 16; o < 2 * W2B; o += NT * 16)
             *reinterpret_cast<uint4*>(smem + L::w2_hi + o) = __ldg(reinterpret_cast<const uint4*>(w2src + o));
-        for (int o = tid * 16; o < L::VEC_BYTES; o += 256 * 16)
-            *reinterpret_cast<uint4*>(smem + L::vec + o) = __ldg(reinterpret_cast<const uint4*>(vsrc + o));
+        const float* vsrc = reinterpret_cast<const float*>(a.blob + 2 * W1B + 4 * W2B);
+        for (int c = tid; c < D; c += NT) {
+            vec[c] = vsrc[branch * D + c];
+            vec[D + c] = vsrc[2 * D + branch * D + c];
+            vec[2 * D + c] = vsrc[4 * D + branch * D + c];
+        }
+        if (tid == 0) vec[3 * D] = vsrc[6 * D + branch];
     }
     if (warp == 0) tc::tmem_alloc(slot, 4 * D);
     if (tid == 0) {
-        for (int b = 0; b < 4; ++b) tc::mbar_init(&bars[b], 1);
+        for (int b = 0; b < 6; ++b) tc::mbar_init(&bars[b], 1);
         tc::fence_mbar_init();
     }
-    tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = *slot;
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-    bool ok = true;
+    for (int cb = cg; cb < 2 * D / 32; cb += NG) tc::tmem_zero32(trow + 2 * D + 32 * cb);  // persistent accumulators = 0
 
     const uint32_t sb = tc::smem_u32(smem);
-    const TcOperand opU{sb + L::u_hi, sb + L::u_lo, TS, false}, opUmn{sb + L::u_hi, sb + L::u_lo, TS, true};
-    const TcOperand opA1{sb + L::a1_hi, sb + L::a1_lo, TS, false}, opA1mn{sb + L::a1_hi, sb + L::a1_lo, TS, true};
+    const TcOperand opA1{sb + L::a1_hi, sb + L::a1_lo, TS, false};
     const TcOperand opG{sb + L::g_hi, sb + L::g_lo, TS, false}, opGmn{sb + L::g_hi, sb + L::g_lo, TS, true};
-    const uint32_t w1off = (uint32_t)(branch * (D / 8) * 128);  // this branch's rows inside the [2D x 16] W1 image
-    const TcOperand opW1{sb + L::w1_hi + w1off, sb + L::w1_lo + w1off, 2 * D * 16, false};
-    const TcOperand opW1mn{sb + L::w1_hi + w1off, sb + L::w1_lo + w1off, 2 * D * 16, true};
+    const TcOperand opW1{sb + L::w1_hi, sb + L::w1_lo, D * 16, false}, opW1mn{sb + L::w1_hi, sb + L::w1_lo, D * 16, true};
     const TcOperand opW2{sb + L::w2_hi, sb + L::w2_lo, D * 16, false}, opW2mn{sb + L::w2_hi, sb + L::w2_lo, D * 16, true};
 
-    const float* b1 = vec + branch * D;
-    const float* b2 = vec + 2 * D + branch * D;
-    const float* wv = vec + 4 * D + branch * D;  // wa (gate) or wx3 (phi head)
-    const float bv = vec[6 * D + branch];
+    const float* b1 = vec;
+    const float* b2 = vec + D;
+    const float* wv = vec + 2 * D;  // wa (gate) or wx3 (phi head)
     float* Grb = a.Gr + (size_t)branch * a.E * W;
     float* Gsb = a.Gs + (size_t)branch * a.E * W;
 
-    float accv[NVL];  // running column sums of coef_e * out_e (grad of wa / wx3), this warp's rows
+    auto gather_load = [&](int tile, TcEdgeRow& g) {
+        const int e = tile * 128 + tid;
 #pragma unroll
-    for (int k = 0; k < NVL; ++k) accv[k] = 0.f;
-    float accs = 0.f;  // running sum of coef_e over this thread's row (grad of ba / bx3)
+        for (int k = 0; k < 16; ++k) g.u[k] = 0.f;
+        g.i = 0;
+        g.rx = g.ry = g.rz = g.valid = 0.f;
+        if (e < a.E) {
+            const int i = a.recv[e], j = a.send[e];
+            g.i = i;
+            g.rx = a.x[3 * i + 0] - a.x[3 * j + 0];
+            g.ry = a.x[3 * i + 1] - a.x[3 * j + 1];
+            g.rz = a.x[3 * i + 2] - a.x[3 * j + 2];
+            g.valid = 1.f;
+            const float nrm = sqrtf(g.rx * g.rx + g.ry * g.ry + g.rz * g.rz);
+#pragma unroll
+            for (int k = 0; k < 15; ++k) {
+                if (k < H) g.u[k] = a.h[(size_t)i * H + k];
+                else if (k < 2 * H) g.u[k] = a.h[(size_t)j * H + (k - H)];
+                else if (k == 2 * H) g.u[k] = nrm * nrm;
+            }
+            g.u[15] = 1.f;  // turns the wgrad MMAs into bias gradients as well
+        }
+    };
+    auto gather_store = [&](int buf, const TcEdgeRow& g) {
+        sI[buf * 128 + tid] = g.i;
+        sR[buf * 128 + tid] = make_float4(g.rx, g.ry, g.rz, g.valid);
+        uint8_t* uh = smem + (buf ? L::u1_hi : L::u0_hi);
+        uint8_t* ul = smem + (buf ? L::u1_lo : L::u0_lo);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) tc::split2(g.u[8 * j + 2 * p], g.u[8 * j + 2 * p + 1], hi[p], lo[p]);
+            *reinterpret_cast<uint4*>(uh + tc::chunk_off(128, tid, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(ul + tc::chunk_off(128, tid, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+    };
 
-    uint32_t phase = 0;
-    bool first = true;
-    for (int tile = blockIdx.x >> 1; tile < a.tiles; tile += gridDim.x >> 1, phase ^= 1, first = false) {
+    const int tstride = gridDim.x >> 1;
+    const int tile0 = blockIdx.x >> 1;
+    const int nit = tile0 < a.tiles ? (a.tiles - tile0 + tstride - 1) / tstride : 0;
+    if (tid < 128 && nit > 0) {
+        TcEdgeRow g;
+        gather_load(tile0, g);
+        gather_store(0, g);
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+
+    float accv = 0.f;  // running column sum of coef_e * out_e (grad of wa / wx3): this warp's rows, column c0 + lane
+    float accs = 0.f;  // running sum of coef_e of this thread's row (grad of ba / bx3)
+    bool ok = true;
+
+    for (int it = 0; it < nit; ++it) {
+        const int tile = tile0 + it * tstride;
         const int e0 = tile * 128;
         const int nrows = min(128, a.E - e0);
-        // ---- gather: u -> U tile (slot 15 carries the constant 1 that turns the wgrad MMAs into bias gradients too)
-        if (tid < 128) {
-            float u[16];
-#pragma unroll
-            for (int k = 0; k < 16; ++k) u[k] = 0.f;
-            int i = 0;
-            float rx = 0.f, ry = 0.f, rz = 0.f;
-            if (tid < nrows) {
-                i = a.recv[e0 + tid];
-                const int j = a.send[e0 + tid];
-                rx = a.x[3 * i + 0] - a.x[3 * j + 0];
-                ry = a.x[3 * i + 1] - a.x[3 * j + 1];
-                rz = a.x[3 * i + 2] - a.x[3 * j + 2];
-                const float nrm = sqrtf(rx * rx + ry * ry + rz * rz);
-#pragma unroll
-                for (int k = 0; k < 15; ++k) {
-                    if (k < H) u[k] = a.h[(size_t)i * H + k];
-                    else if (k < 2 * H) u[k] = a.h[(size_t)j * H + (k - H)];
-                    else if (k == 2 * H) u[k] = nrm * nrm;
-                }
-                u[15] = 1.f;
-            }
-            sI[tid] = i;
-            sR[tid] = make_float4(rx, ry, rz, tid < nrows ? 1.f : 0.f);
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                uint32_t hi[4], lo[4];
-#pragma unroll
-                for (int p = 0; p < 4; ++p) tc::split2(u[8 * j + 2 * p], u[8 * j + 2 * p + 1], hi[p], lo[p]);
-                *reinterpret_cast<uint4*>(smem + L::u_hi + tc::chunk_off(128, tid, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<uint4*>(smem + L::u_lo + tc::chunk_off(128, tid, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-            }
-        }
-        tc::fence_async_smem();
-        tc::fence_before_sync();
-        __syncthreads();
+        const int buf = it & 1;
+        const uint32_t phase = it & 1;
+        const bool has_next = it + 1 < nit;
+        const TcOperand opU{sb + (buf ? L::u1_hi : L::u0_hi), sb + (buf ? L::u1_lo : L::u0_lo), TS, false};
+        const TcOperand opUmn{opU.hi, opU.lo, TS, true};
         if (tid == 0) {
             tc::fence_after_sync();
             tc_issue_op<NPASS>(tmem, cA, opU, opW1, 16, D, false);  // z1 = U . W1^T
@@ -712,12 +741,8 @@ __global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
         // ---- a1 = SiLU(z1 + b1) -> tile A1 (z1 stays in TMEM for SiLU' later)
         {
             uint32_t hi[16], lo[16];
-#pragma unroll
-            for (int b = 0; b < NB; ++b) {
-                const int c0 = hf * HALF + 32 * b;
-                tc_epi32<FAST>(trow + cA + c0, b1 + c0, hi, lo);
-                tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, hi, lo, LO);
-            }
+            tc_epi32<FAST>(trow + cA + c0, b1 + c0, hi, lo);
+            tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, hi, lo, LO);
         }
         tc::fence_async_smem();
         tc::fence_before_sync();
@@ -727,32 +752,35 @@ __global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
             tc_issue_op<NPASS>(tmem, cB, opA1, opW2, D, D, false);  // z2 = a1 . W2^T
             tc::mma_commit(&bars[1]);
         }
+        // ---- next tile's gather: global loads in flight while GEMM2 runs
+        TcEdgeRow gnext;
+        if (tid < 128 && has_next) gather_load(tile + tstride, gnext);
         ok = tc::mbar_wait(&bars[1], phase) && ok;
+        if (it > 0) ok = tc::mbar_wait(&bars[5], phase ^ 1) && ok;  // previous tile's dW1 MMA is done with U[buf^1] and tile G
         tc::fence_after_sync();
-        // ---- upstream gradient of z2: z, sigmoid(z) of this thread's columns in registers
+        if (tid < 128 && has_next) gather_store(buf ^ 1, gnext);
+        // ---- upstream gradient of z2: z, sigmoid(z) of this thread's 32 columns in registers
         {
-            float z[HALF], sg[HALF];
-#pragma unroll
-            for (int b = 0; b < NB; ++b) {
-                const int c0 = hf * HALF + 32 * b;
+            float z[32], sg[32];
+            {
                 float v[32];
                 tc::tmem_ld32(trow + cB + c0, v);
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
-                    z[32 * b + i] = v[i] + b2[c0 + i];
-                    sg[32 * b + i] = tc_sigmoid<FAST>(z[32 * b + i]);
+                    z[i] = v[i] + b2[c0 + i];
+                    sg[i] = tc_sigmoid<FAST>(z[i]);
                 }
             }
-            const float4 rr = sR[r];
-            const int i = sI[r];
-            const float* wvh = wv + hf * HALF;
+            const float4 rr = sR[buf * 128 + r];
+            const int i = sI[buf * 128 + r];
+            const float* wvh = wv + c0;
             float c_row, c_g = 0.f;  // gz2[c] = (c_g * gM[i][c] + c_row * wv[c]) * SiLU'(z[c]);  d wv[c] += c_row * out[c]
-            const float4* gMi = reinterpret_cast<const float4*>(a.gM + (size_t)i * D + hf * HALF);
+            const float4* gMi = reinterpret_cast<const float4*>(a.gM + (size_t)i * D + c0);
             if (branch == 0) {
                 // gate g = sigmoid(wa.m + ba);  t = gM[i].m;  c_row = gs = t g (1-g);  c_g = g
                 float sdot = 0.f, tdot = 0.f;
 #pragma unroll
-                for (int c4 = 0; c4 < HALF / 4; ++c4) {
+                for (int c4 = 0; c4 < 8; ++c4) {
                     const float4 gm = __ldg(gMi + c4);
                     const float m0 = z[4 * c4] * sg[4 * c4], m1 = z[4 * c4 + 1] * sg[4 * c4 + 1];
                     const float m2 = z[4 * c4 + 2] * sg[4 * c4 + 2], m3 = z[4 * c4 + 3] * sg[4 * c4 + 3];
@@ -765,43 +793,44 @@ __global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
                     tdot = fmaf(gm.z, m2, tdot);
                     tdot = fmaf(gm.w, m3, tdot);
                 }
-                rowA[hf * 128 + r] = sdot;
-                rowB[hf * 128 + r] = tdot;
+                rowA[cg * 128 + r] = sdot;
+                rowB[cg * 128 + r] = tdot;
                 __syncthreads();
-                const float g = sigmoid_f(rowA[r] + rowA[128 + r] + bv);
-                const float t = rowB[r] + rowB[128 + r];
-                c_row = rr.w * t * g * (1.f - g);
+                float ssum = vec[3 * D], tsum = 0.f;
+#pragma unroll
+                for (int k = 0; k < NG; ++k) {
+                    ssum += rowA[k * 128 + r];
+                    tsum += rowB[k * 128 + r];
+                }
+                const float g = sigmoid_f(ssum);
+                c_row = rr.w * tsum * g * (1.f - g);
                 c_g = rr.w * g;
             } else {
                 // phi = wx3.q + bx3 (needed for the coordinate output);  c_row = gphi = gdx[i].r
                 float pdot = 0.f;
 #pragma unroll
-                for (int c = 0; c < HALF; ++c) pdot = fmaf(wvh[c], z[c] * sg[c], pdot);
-                rowA[hf * 128 + r] = pdot;
+                for (int c = 0; c < 32; ++c) pdot = fmaf(wvh[c], z[c] * sg[c], pdot);
+                rowA[cg * 128 + r] = pdot;
                 const float* gd = a.gdx + (size_t)i * 3;
                 c_row = rr.w * (gd[0] * rr.x + gd[1] * rr.y + gd[2] * rr.z);
             }
+            float gz[32];
 #pragma unroll
-            for (int b = 0; b < NB; ++b) {
-                float gz[32];
+            for (int c4 = 0; c4 < 8; ++c4) {
+                float4 gm = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (branch == 0) gm = __ldg(gMi + c4);
+                const float gmv[4] = {gm.x, gm.y, gm.z, gm.w};
 #pragma unroll
-                for (int c4 = 0; c4 < 8; ++c4) {
-                    float4 gm = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (branch == 0) gm = __ldg(gMi + 8 * b + c4);
-                    const float gmv[4] = {gm.x, gm.y, gm.z, gm.w};
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const int c = 32 * b + 4 * c4 + k;
-                        const float d2 = sg[c] * fmaf(z[c], 1.f - sg[c], 1.f);
-                        gz[4 * c4 + k] = fmaf(c_g, gmv[k], c_row * wvh[c]) * d2;
-                        z[c] = c_row * (z[c] * sg[c]);  // coef_e * out_e[c] for the column sums below
-                    }
+                for (int k = 0; k < 4; ++k) {
+                    const int c = 4 * c4 + k;
+                    const float d2 = sg[c] * fmaf(z[c], 1.f - sg[c], 1.f);
+                    gz[c] = fmaf(c_g, gmv[k], c_row * wvh[c]) * d2;
+                    z[c] = c_row * (z[c] * sg[c]);  // coef_e * out_e[c] for the column sums below
                 }
-                tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, hf * HALF + 32 * b, gz, LO);
             }
-            warp_colsum<HALF>(z, lane);
-#pragma unroll
-            for (int k = 0; k < NVL; ++k) accv[k] += z[k];
+            tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, gz, LO);
+            warp_colsum32(z, lane);
+            accv += z[0];
             accs += c_row;
         }
         tc::fence_async_smem();
@@ -809,17 +838,17 @@ __global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
         __syncthreads();
         if (tid == 0) {
             tc::fence_after_sync();
-            tc_issue_op<NPASS>(tmem, cB, opG, opW2mn, D, D, false);        // ga1 = gz2 . W2
-            tc_issue_op<NPASS>(tmem, cP2, opGmn, opA1mn, 128, D, !first);  // dW2 += gz2^T . a1
-            tc_issue_op<NPASS>(tmem, cPB, opGmn, opUmn, 128, 16, !first);  // column 15: db2 += gz2^T . 1
+            tc_issue_op<NPASS>(tmem, cB, opG, opW2mn, D, D, false);  // ga1 = gz2 . W2
             tc::mma_commit(&bars[2]);
+            // [db2 | dW2] += gz2^T . [u | a1] (even tiles) or [dW2 | db2] += gz2^T . [a1 | u] (odd tiles)
+            const TcOperand opB{sb + (buf ? L::a1_hi : L::u0_hi), sb + (buf ? L::a1_lo : L::u0_lo), TS, true};
+            tc_issue_op<NPASS>(tmem, buf ? cW2 : cBias0, opGmn, opB, 128, D + 16, true);
+            tc::mma_commit(&bars[3]);
         }
         ok = tc::mbar_wait(&bars[2], phase) && ok;
         tc::fence_after_sync();
-        // ---- gz1 = ga1 * SiLU'(z1 + b1) -> tile G (overwrites gz2: every MMA reading it has completed)
-#pragma unroll
-        for (int b = 0; b < NB; ++b) {
-            const int c0 = hf * HALF + 32 * b;
+        // ---- gz1 = ga1 * SiLU'(z1 + b1), computed while the wgrad MMA still reads tiles G and A1
+        {
             float ga[32], z1[32];
             tc::tmem_ld32(trow + cB + c0, ga);
             tc::tmem_ld32(trow + cA + c0, z1);
@@ -829,6 +858,8 @@ __global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
                 const float s = tc_sigmoid<FAST>(zz);
                 ga[i] *= s * fmaf(zz, 1.f - s, 1.f);
             }
+            ok = tc::mbar_wait(&bars[3], phase) && ok;
+            tc::fence_after_sync();
             tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, ga, LO);
         }
         tc::fence_async_smem();
@@ -836,20 +867,21 @@ __global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
         __syncthreads();
         if (tid == 0) {
             tc::fence_after_sync();
-            tc_issue_op<NPASS>(tmem, cA, opG, opW1mn, D, 16, false);            // gu = gz1 . W1   (16 columns)
-            tc_issue_op<NPASS>(tmem, cPB + 16, opGmn, opUmn, 128, 16, !first);  // dW1 += gz1^T . u, column 15: db1
-            tc::mma_commit(&bars[3]);
+            tc_issue_op<NPASS>(tmem, cA, opG, opW1mn, D, 16, false);  // gu = gz1 . W1   (16 columns)
+            tc::mma_commit(&bars[4]);
+            tc_issue_op<NPASS>(tmem, cP1, opGmn, opUmn, 128, 16, true);  // [dW1 | db1] += gz1^T . u
+            tc::mma_commit(&bars[5]);
         }
-        ok = tc::mbar_wait(&bars[3], phase) && ok;
-        tc::fence_after_sync();
         // ---- per-edge outputs of this branch: receiver / sender parts of gu, coordinate part through d_e and phi
-        if (hf == 0) {
+        if (cg == 0) {
+            ok = tc::mbar_wait(&bars[4], phase) && ok;
+            tc::fence_after_sync();
             float gu[32];
             tc::tmem_ld32(trow + cA, gu);
             if (r < nrows) {
                 const size_t e = (size_t)(e0 + r);
-                const float4 rr = sR[r];
-                const int i = sI[r];
+                const float4 rr = sR[buf * 128 + r];
+                const int i = sI[buf * 128 + r];
                 float gd = 0.f;
 #pragma unroll
                 for (int k = 0; k < 15; ++k) {
@@ -860,7 +892,9 @@ __global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
                 float cr = 2.f * gd, phi = 0.f;
                 float gx0 = 0.f, gx1 = 0.f, gx2 = 0.f;
                 if (branch == 1) {
-                    phi = rowA[r] + rowA[128 + r] + bv;
+                    phi = vec[3 * D];
+#pragma unroll
+                    for (int k = 0; k < NG; ++k) phi += rowA[k * 128 + r];
                     cr += a.coefS[a.node_graph[i]];
                     gx0 = a.gdx[(size_t)i * 3 + 0];
                     gx1 = a.gdx[(size_t)i * 3 + 1];
@@ -876,48 +910,48 @@ __global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
             }
         }
         tc::fence_before_sync();
+        __syncthreads();  // gu has been read (next GEMM1 overwrites block A); rowA / rowB are free again
     }
+    if (nit > 0) ok = tc::mbar_wait(&bars[5], (uint32_t)((nit - 1) & 1)) && ok;
     if (!ok) asm volatile("trap;");
+    tc::fence_after_sync();
     // ---- weight gradients of this CTA's tiles: TMEM accumulators / register column sums -> private partial row
-    const LayerOff lo = layer_off(a.net);
-    float* part = a.part + (size_t)blockIdx.x * lo.total;
-    const int o_w1 = branch ? lo.wx1 : lo.wm1, o_b1 = branch ? lo.bx1 : lo.bm1;
-    const int o_w2 = branch ? lo.wx2 : lo.wm2, o_b2 = branch ? lo.bx2 : lo.bm2;
-    const int o_wv = branch ? lo.wx3 : lo.wa, o_bv = branch ? lo.bx3 : lo.ba;
-    __syncthreads();
-    if (!first) {  // at least one tile went through (the host sizes the grid so this always holds)
-        tc::fence_after_sync();
-#pragma unroll
-        for (int b = 0; b < NB; ++b) {
-            const int c0 = hf * HALF + 32 * b;
+    if (nit > 0) {
+        const LayerOff lo = layer_off(a.net);
+        float* part = a.part + (size_t)blockIdx.x * lo.total;
+        const int o_w1 = branch ? lo.wx1 : lo.wm1, o_b1 = branch ? lo.bx1 : lo.bm1;
+        const int o_w2 = branch ? lo.wx2 : lo.wm2, o_b2 = branch ? lo.bx2 : lo.bm2;
+        const int o_wv = branch ? lo.wx3 : lo.wa, o_bv = branch ? lo.bx3 : lo.ba;
+        {
             float v[32];
-            tc::tmem_ld32(trow + cP2 + c0, v);
+            tc::tmem_ld32(trow + cW2 + c0, v);
             if (r < D) {
                 float* dst = part + o_w2 + (size_t)r * D + c0;  // partial rows are not 16-byte aligned in general
 #pragma unroll
                 for (int k = 0; k < 32; ++k) dst[k] = v[k];
             }
         }
-        if (hf == 0) {
-            float v[32];
-            tc::tmem_ld32(trow + cPB, v);  // [0,16): gz2^T.u (col 15 = db2)   [16,32): dW1 (col 31 = db1)
+        if (cg == 0) {
+            float v0[32], v1[32];
+            tc::tmem_ld32(trow + cBias0, v0);  // column 15: db2 of the even tiles
+            tc::tmem_ld32(trow + cBias1, v1);  // column 15: db2 of the odd tiles; [16,32): dW1, column 31: db1
             if (r < D) {
-                part[o_b2 + r] = v[15];
-                part[o_b1 + r] = v[31];
+                part[o_b2 + r] = v0[15] + v1[15];
+                part[o_b1 + r] = v1[31];
 #pragma unroll
                 for (int k = 0; k < 15; ++k)
-                    if (k < K0) part[o_w1 + r * K0 + k] = v[16 + k];
+                    if (k < K0) part[o_w1 + r * K0 + k] = v1[16 + k];
             }
         }
-#pragma unroll
-        for (int k = 0; k < NVL; ++k) colred[warp * 64 + lane * NVL + k] = accv[k];
-        if (hf == 0) rowB[r] = accs;
+        float* colred = rowA;  // [NT/32][32]
+        colred[warp * 32 + lane] = accv;
+        if (cg == 0) rowB[r] = accs;
         __syncthreads();
         if (tid < D) {
-            const int hc = tid / HALF, cc = tid % HALF;
+            const int gc = tid >> 5, cc = tid & 31;
             float s = 0.f;
 #pragma unroll
-            for (int qq = 0; qq < 4; ++qq) s += colred[(hc * 4 + qq) * 64 + cc];
+            for (int qq = 0; qq < 4; ++qq) s += colred[(gc * 4 + qq) * 32 + cc];
             part[o_wv + tid] = s;
         }
         if (tid == 0) {
@@ -933,14 +967,14 @@ __global__ void __launch_bounds__(256, 1) tc_edge_bwd(TcBwdArgs a) {
 
 template <int D, int NPASS>
 int launch_tc_bwd(const TcBwdArgs& a, int grid, cudaStream_t st) {
-    constexpr int SMEM = TcBwdLayout<D>::TOTAL + (D == 64 ? 16 * 1024 : 0);  // D=64: the M=128 wgrad view reads past tile G
+    constexpr int SMEM = TcBwdLayout<D>::TOTAL;
     static bool configured = false;
     if (!configured) {
         EGNN_CUDA(cudaFuncSetAttribute(tc_edge_bwd<D, NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         configured = true;
     }
     egnn_prof_begin(EGNN_K_TC_EDGE_BWD, st);
-    tc_edge_bwd<D, NPASS><<<grid, 256, SMEM, st>>>(a);
+    tc_edge_bwd<D, NPASS><<<grid, 4 * D, SMEM, st>>>(a);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("tc_edge_bwd");
     return EGNN_OK;
