@@ -607,8 +607,9 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     constexpr bool FAST = NPASS == 1;
     constexpr bool LO = NPASS == 3;
     constexpr int NT = L::NT, NG = L::NG;
-    // TMEM columns: z1 | gu,  z2 | ga1,  db2 (even tiles),  dW2,  db2 (odd tiles),  dW1 + db1
-    constexpr int cA = 0, cB = D, cBias0 = 2 * D, cW2 = 2 * D + 16, cBias1 = 3 * D + 16, cP1 = 3 * D + 32;
+    // TMEM columns: z1 -> SiLU'(z1),  z2 | ga1,  db2 (even tiles),  dW2,  db2 (odd tiles),  dW1 + db1,  gu
+    constexpr int cA = 0, cB = D, cBias0 = 2 * D, cW2 = 2 * D + 16, cBias1 = 3 * D + 16, cP1 = 3 * D + 32,
+                  cGU = 3 * D + 48;
     constexpr uint32_t TS = 128 * 16;  // chunk stride of a 128-row tile
     extern __shared__ __align__(1024) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -709,6 +710,38 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     const int tstride = gridDim.x >> 1;
     const int tile0 = blockIdx.x >> 1;
     const int nit = tile0 < a.tiles ? (a.tiles - tile0 + tstride - 1) / tstride : 0;
+    auto edge_outputs = [&](int e0p, int nrowsp, int bufp, float phi) {  // cg == 0 warps: this branch's per-edge outputs
+        float gu[32];
+        tc::tmem_ld32(trow + cGU, gu);
+        if (r < nrowsp) {
+            const size_t e = (size_t)(e0p + r);
+            const float4 rr = sR[bufp * 128 + r];
+            const int i = sI[bufp * 128 + r];
+            float gd = 0.f;
+#pragma unroll
+            for (int k = 0; k < 15; ++k) {
+                if (k < H) Grb[e * W + k] = gu[k];
+                else if (k < 2 * H) Gsb[e * W + (k - H)] = gu[k];
+                else if (k == 2 * H) gd = gu[k];
+            }
+            float cr = 2.f * gd;
+            float gx0 = 0.f, gx1 = 0.f, gx2 = 0.f;
+            if (branch == 1) {
+                cr += a.coefS[a.node_graph[i]];
+                gx0 = a.gdx[(size_t)i * 3 + 0];
+                gx1 = a.gdx[(size_t)i * 3 + 1];
+                gx2 = a.gdx[(size_t)i * 3 + 2];
+            }
+            const float g0 = fmaf(gx0, phi, cr * rr.x), g1 = fmaf(gx1, phi, cr * rr.y), g2 = fmaf(gx2, phi, cr * rr.z);
+            Grb[e * W + H + 0] = g0;
+            Grb[e * W + H + 1] = g1;
+            Grb[e * W + H + 2] = g2;
+            Gsb[e * W + H + 0] = -g0;
+            Gsb[e * W + H + 1] = -g1;
+            Gsb[e * W + H + 2] = -g2;
+        }
+    };
+
     if (tid < 128 && nit > 0) {
         TcEdgeRow g;
         gather_load(tile0, g);
@@ -717,32 +750,39 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
+    if (tid == 0 && nit > 0) {
+        tc::fence_after_sync();
+        const TcOperand opU0{sb + L::u0_hi, sb + L::u0_lo, TS, false};
+        tc_issue_op<NPASS>(tmem, cA, opU0, opW1, 16, D, false);  // z1 of the first tile
+        tc::mma_commit(&bars[0]);
+    }
 
     float accv = 0.f;  // running column sum of coef_e * out_e (grad of wa / wx3): this warp's rows, column c0 + lane
     float accs = 0.f;  // running sum of coef_e of this thread's row (grad of ba / bx3)
+    float phi_prev = 0.f;  // phi_e of the previous tile (coordinate branch), consumed by its deferred edge_outputs
     bool ok = true;
 
     for (int it = 0; it < nit; ++it) {
         const int tile = tile0 + it * tstride;
-        const int e0 = tile * 128;
-        const int nrows = min(128, a.E - e0);
         const int buf = it & 1;
         const uint32_t phase = it & 1;
         const bool has_next = it + 1 < nit;
-        const TcOperand opU{sb + (buf ? L::u1_hi : L::u0_hi), sb + (buf ? L::u1_lo : L::u0_lo), TS, false};
-        const TcOperand opUmn{opU.hi, opU.lo, TS, true};
-        if (tid == 0) {
-            tc::fence_after_sync();
-            tc_issue_op<NPASS>(tmem, cA, opU, opW1, 16, D, false);  // z1 = U . W1^T
-            tc::mma_commit(&bars[0]);
-        }
-        ok = tc::mbar_wait(&bars[0], phase) && ok;
+        const TcOperand opUmn{sb + (buf ? L::u1_hi : L::u0_hi), sb + (buf ? L::u1_lo : L::u0_lo), TS, true};
+        ok = tc::mbar_wait(&bars[0], phase) && ok;  // z1 = U . W1^T of this tile (issued one phase ahead)
         tc::fence_after_sync();
-        // ---- a1 = SiLU(z1 + b1) -> tile A1 (z1 stays in TMEM for SiLU' later)
+        // ---- a1 = SiLU(z1 + b1) -> tile A1;  SiLU'(z1 + b1) replaces z1 in TMEM (read back by the gz1 phase)
         {
-            uint32_t hi[16], lo[16];
-            tc_epi32<FAST>(trow + cA + c0, b1 + c0, hi, lo);
-            tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, hi, lo, LO);
+            float v[32], act[32];
+            tc::tmem_ld32(trow + cA + c0, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float zz = v[i] + b1[c0 + i];
+                const float s = tc_sigmoid<FAST>(zz);
+                act[i] = zz * s;
+                v[i] = s * fmaf(zz, 1.f - s, 1.f);
+            }
+            tc_split_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, act, LO);
+            tc::tmem_st32(trow + cA + c0, v);
         }
         tc::fence_async_smem();
         tc::fence_before_sync();
@@ -752,14 +792,20 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             tc_issue_op<NPASS>(tmem, cB, opA1, opW2, D, D, false);  // z2 = a1 . W2^T
             tc::mma_commit(&bars[1]);
         }
-        // ---- next tile's gather: global loads in flight while GEMM2 runs
+        // ---- in the shadow of GEMM2: next tile's gather loads, previous tile's per-edge outputs
         TcEdgeRow gnext;
         if (tid < 128 && has_next) gather_load(tile + tstride, gnext);
+        if (it > 0 && cg == 0) {
+            ok = tc::mbar_wait(&bars[4], phase ^ 1) && ok;
+            tc::fence_after_sync();
+            edge_outputs((tile - tstride) * 128, min(128, a.E - (tile - tstride) * 128), buf ^ 1, phi_prev);
+        }
         ok = tc::mbar_wait(&bars[1], phase) && ok;
         if (it > 0) ok = tc::mbar_wait(&bars[5], phase ^ 1) && ok;  // previous tile's dW1 MMA is done with U[buf^1] and tile G
         tc::fence_after_sync();
         if (tid < 128 && has_next) gather_store(buf ^ 1, gnext);
         // ---- upstream gradient of z2: z, sigmoid(z) of this thread's 32 columns in registers
+        float cs[32];  // coef_e * out_e[c]: column sums taken after the MMAs below have been issued
         {
             float z[32], sg[32];
             {
@@ -825,12 +871,10 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
                     const int c = 4 * c4 + k;
                     const float d2 = sg[c] * fmaf(z[c], 1.f - sg[c], 1.f);
                     gz[c] = fmaf(c_g, gmv[k], c_row * wvh[c]) * d2;
-                    z[c] = c_row * (z[c] * sg[c]);  // coef_e * out_e[c] for the column sums below
+                    cs[c] = c_row * (z[c] * sg[c]);
                 }
             }
             tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, gz, LO);
-            warp_colsum32(z, lane);
-            accv += z[0];
             accs += c_row;
         }
         tc::fence_async_smem();
@@ -845,19 +889,24 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             tc_issue_op<NPASS>(tmem, buf ? cW2 : cBias0, opGmn, opB, 128, D + 16, true);
             tc::mma_commit(&bars[3]);
         }
+        // ---- in the shadow of dgrad: column sums for d wa / d wx3; phi_e of this tile for its deferred outputs
+        warp_colsum32(cs, lane);
+        accv += cs[0];
+        if (branch == 1 && cg == 0) {
+            float phi = vec[3 * D];
+#pragma unroll
+            for (int k = 0; k < NG; ++k) phi += rowA[k * 128 + r];
+            phi_prev = phi;
+        }
         ok = tc::mbar_wait(&bars[2], phase) && ok;
         tc::fence_after_sync();
         // ---- gz1 = ga1 * SiLU'(z1 + b1), computed while the wgrad MMA still reads tiles G and A1
         {
-            float ga[32], z1[32];
+            float ga[32], d1[32];
             tc::tmem_ld32(trow + cB + c0, ga);
-            tc::tmem_ld32(trow + cA + c0, z1);
+            tc::tmem_ld32(trow + cA + c0, d1);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const float zz = z1[i] + b1[c0 + i];
-                const float s = tc_sigmoid<FAST>(zz);
-                ga[i] *= s * fmaf(zz, 1.f - s, 1.f);
-            }
+            for (int i = 0; i < 32; ++i) ga[i] *= d1[i];
             ok = tc::mbar_wait(&bars[3], phase) && ok;
             tc::fence_after_sync();
             tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, ga, LO);
@@ -867,52 +916,27 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         __syncthreads();
         if (tid == 0) {
             tc::fence_after_sync();
-            tc_issue_op<NPASS>(tmem, cA, opG, opW1mn, D, 16, false);  // gu = gz1 . W1   (16 columns)
+            if (has_next) {  // next tile's z1 first: its epilogue overlaps the two narrow MMAs below
+                const TcOperand opUn{sb + (buf ? L::u0_hi : L::u1_hi), sb + (buf ? L::u0_lo : L::u1_lo), TS, false};
+                tc_issue_op<NPASS>(tmem, cA, opUn, opW1, 16, D, false);
+                tc::mma_commit(&bars[0]);
+            }
+            tc_issue_op<NPASS>(tmem, cGU, opG, opW1mn, D, 16, false);  // gu = gz1 . W1   (16 columns)
             tc::mma_commit(&bars[4]);
             tc_issue_op<NPASS>(tmem, cP1, opGmn, opUmn, 128, 16, true);  // [dW1 | db1] += gz1^T . u
             tc::mma_commit(&bars[5]);
         }
-        // ---- per-edge outputs of this branch: receiver / sender parts of gu, coordinate part through d_e and phi
-        if (cg == 0) {
-            ok = tc::mbar_wait(&bars[4], phase) && ok;
-            tc::fence_after_sync();
-            float gu[32];
-            tc::tmem_ld32(trow + cA, gu);
-            if (r < nrows) {
-                const size_t e = (size_t)(e0 + r);
-                const float4 rr = sR[buf * 128 + r];
-                const int i = sI[buf * 128 + r];
-                float gd = 0.f;
-#pragma unroll
-                for (int k = 0; k < 15; ++k) {
-                    if (k < H) Grb[e * W + k] = gu[k];
-                    else if (k < 2 * H) Gsb[e * W + (k - H)] = gu[k];
-                    else if (k == 2 * H) gd = gu[k];
-                }
-                float cr = 2.f * gd, phi = 0.f;
-                float gx0 = 0.f, gx1 = 0.f, gx2 = 0.f;
-                if (branch == 1) {
-                    phi = vec[3 * D];
-#pragma unroll
-                    for (int k = 0; k < NG; ++k) phi += rowA[k * 128 + r];
-                    cr += a.coefS[a.node_graph[i]];
-                    gx0 = a.gdx[(size_t)i * 3 + 0];
-                    gx1 = a.gdx[(size_t)i * 3 + 1];
-                    gx2 = a.gdx[(size_t)i * 3 + 2];
-                }
-                const float g0 = fmaf(gx0, phi, cr * rr.x), g1 = fmaf(gx1, phi, cr * rr.y), g2 = fmaf(gx2, phi, cr * rr.z);
-                Grb[e * W + H + 0] = g0;
-                Grb[e * W + H + 1] = g1;
-                Grb[e * W + H + 2] = g2;
-                Gsb[e * W + H + 0] = -g0;
-                Gsb[e * W + H + 1] = -g1;
-                Gsb[e * W + H + 2] = -g2;
-            }
-        }
-        tc::fence_before_sync();
-        __syncthreads();  // gu has been read (next GEMM1 overwrites block A); rowA / rowB are free again
     }
-    if (nit > 0) ok = tc::mbar_wait(&bars[5], (uint32_t)((nit - 1) & 1)) && ok;
+    if (nit > 0) {
+        const int lt = tile0 + (nit - 1) * tstride;
+        const uint32_t lp = (uint32_t)((nit - 1) & 1);
+        if (cg == 0) {
+            ok = tc::mbar_wait(&bars[4], lp) && ok;
+            tc::fence_after_sync();
+            edge_outputs(lt * 128, min(128, a.E - lt * 128), (nit - 1) & 1, phi_prev);
+        }
+        ok = tc::mbar_wait(&bars[5], lp) && ok;
+    }
     if (!ok) asm volatile("trap;");
     tc::fence_after_sync();
     // ---- weight gradients of this CTA's tiles: TMEM accumulators / register column sums -> private partial row
