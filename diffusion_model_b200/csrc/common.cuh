@@ -81,6 +81,12 @@ __host__ __device__ static inline bool tc_supported(const egnn_net_t& n) {
 }
 // bytes of one layer's tcgen05 weight image (see tc_edge.cu: W1 hi/lo [2d x 16], W2m hi/lo, W2x hi/lo [d x d] bf16, fp32 vectors)
 __host__ __device__ static inline int tc_blob_bytes(int d) { return 2 * (2 * d * 32) + 4 * (d * d * 2) + (6 * d + 4) * 4; }
+// the tcgen05 node backward additionally needs Hh = d (mlp_h hidden width) and room for the constant-1 column
+__host__ __device__ static inline bool tc_node_supported(const egnn_net_t& n) {
+    return tc_supported(n) && n.Hh == n.Ms && n.H + 1 <= 16;
+}
+// node part of the image, appended to the edge part: Wh1 hi/lo as a K-major [d x (d+16)] bf16 tile (columns >= H+Ms zero)
+__host__ __device__ static inline int tc_node_blob_bytes(int d) { return 2 * (d * (d + 16) * 2); }
 __host__ __device__ static inline PackOff pack_off(const egnn_net_t& n) {
     PackOff o;
     const int K0 = 2 * n.H + 1;
@@ -93,6 +99,7 @@ __host__ __device__ static inline PackOff pack_off(const egnn_net_t& n) {
     p = round4(p);
     o.tc = p;
     if (tc_supported(n)) p += (tc_blob_bytes(n.Mh) + 15) / 16 * 4;
+    if (tc_node_supported(n)) p += tc_node_blob_bytes(n.Mh) / 4;
     o.total = round4(p);
     return o;
 }

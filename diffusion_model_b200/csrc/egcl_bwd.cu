@@ -9,6 +9,8 @@
 //
 // Only the layer inputs and per-node aggregates are kept from the forward; edge activations are recomputed.
 // No atomics: every CTA adds into its own partial row, rows are summed in a fixed order -> bit-identical reruns.
+#include <algorithm>
+
 #include "tile_gemm.cuh"
 #include "tile_wgrad.cuh"
 
@@ -106,12 +108,24 @@ __global__ void __launch_bounds__(256) egcl_node_bwd(NodeBwdArgs a) {
     }
 }
 
-__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ part, int rows, int n,
+// grad[p] = sum of the partial rows that hold parameter p, in row order.  branch_rows: the tensor-core edge backward
+// gives even rows to the mlp_m + attention parameters and odd rows to the mlp_x parameters (other entries of a row are
+// never written, so they must not be read); otherwise every edge row holds every edge parameter.
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ part, int rowsE, int rowsN, int n,
+                                                              int x_begin, int h_begin, int h_end, int branch_rows,
                                                               float* __restrict__ out) {
     const int p = blockIdx.x * 256 + threadIdx.x;
     if (p >= n) return;
+    int r0 = 0, r1 = rowsE, step = 1;
+    if (p >= h_begin && p < h_end) {
+        r0 = rowsE;
+        r1 = rowsE + rowsN;
+    } else if (branch_rows) {
+        step = 2;
+        r0 = (p >= x_begin && p < h_begin) ? 1 : 0;
+    }
     float s = 0.f;
-    for (int r = 0; r < rows; ++r) s += part[(size_t)r * n + p];
+    for (int r = r0; r < r1; r += step) s += part[(size_t)r * n + p];
     out[p] = s;
 }
 
@@ -367,6 +381,10 @@ size_t egnn_edge_fwd_smem(const egnn_net_t& net, int TE);
 int egnn_validate_net(const egnn_net_t* net);
 int egnn_validate_graph(const egnn_graph_t* g, bool need_sender_csr);
 int egnn_tc_bwd_grid(int64_t E);
+int egnn_tc_node_bwd_grid(int64_t N);
+int egnn_tc_node_backward(const egnn_net_t& net, int N, const float* params_layer, const float* packed_layer, const float* h,
+                          const float* msum, const float* gh_out, float* gh_node, float* gM, float* part, int precision,
+                          cudaStream_t st);
 int egnn_tc_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
                           const float* x, const float* gM, const float* gdx, const float* coefS, float* Gr, float* Gs,
                           float* part, int precision, cudaStream_t st);
@@ -389,6 +407,7 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     const int64_t tilesE = (E + w.TEB - 1) / w.TEB, tilesN = (N + TNB - 1) / TNB;
     w.gridE = (int)(tilesE < kNumSM ? tilesE : kNumSM);
     if (tc_supported(n) && E > 0 && egnn_tc_bwd_grid(E) > w.gridE) w.gridE = egnn_tc_bwd_grid(E);
+    if (tc_node_supported(n) && egnn_tc_node_bwd_grid(N) > w.gridN) w.gridN = egnn_tc_node_bwd_grid(N);
     w.gridN = (int)(tilesN < kNumSM ? tilesN : kNumSM);
     const int64_t W = n.H + 3;
     int64_t p = 0;
@@ -466,7 +485,10 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
         EGNN_CUDA(cudaFuncSetAttribute(egcl_node_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         node_configured = true;
     }
-    const int rows = bw.gridE + bw.gridN;
+    const bool node_tc = use_tc && tc_node_supported(*net);
+    // rows actually used by this call's kernels (the workspace is sized for the larger of the two paths)
+    const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : (int)std::min<int64_t>((E + bw.TEB - 1) / bw.TEB, kNumSM)) : 0;
+    const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : (int)std::min<int64_t>((N + TNB - 1) / TNB, kNumSM);
     for (int l = net->L - 1; l >= 0; --l) {
         const float* P = params + (size_t)l * lo.total;
         const float* Pk = packed + (size_t)l * po.total;
@@ -481,12 +503,20 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
                                                fwd_ws_ptr + fw.S + (size_t)l * g->G, g->node_ptr, N, norm_scope,
                                                ws + bw.gdx, ws + bw.coefS);
         EGNN_CHECK_LAUNCH("egcl_xupdate_bwd");
-        EGNN_CUDA(cudaMemsetAsync(ws + bw.part, 0, sizeof(float) * (size_t)rows * lo.total, st));
-        {
+        // the tensor-core kernels overwrite exactly the entries the reduction reads; the FFMA kernels accumulate
+        if (!use_tc) EGNN_CUDA(cudaMemsetAsync(ws + bw.part, 0, sizeof(float) * (size_t)(rowsE + rowsN) * lo.total, st));
+        else if (!node_tc)
+            EGNN_CUDA(cudaMemsetAsync(ws + bw.part + (size_t)rowsE * lo.total, 0, sizeof(float) * (size_t)rowsN * lo.total, st));
+        if (node_tc) {
+            if (int rc = egnn_tc_node_backward(*net, N, P, Pk, hl, fwd_ws_ptr + fw.msum + (size_t)l * N * net->Ms, gho,
+                                               ws + bw.gh_node, ws + bw.gM, ws + bw.part + (size_t)rowsE * lo.total,
+                                               precision, st))
+                return rc;
+        } else {
             NodeBwdArgs na{*net, N, (N + TNB - 1) / TNB, hl, fwd_ws_ptr + fw.msum + (size_t)l * N * net->Ms, P, Pk, gho,
-                           ws + bw.gh_node, ws + bw.gM, ws + bw.part + (size_t)bw.gridE * lo.total};
+                           ws + bw.gh_node, ws + bw.gM, ws + bw.part + (size_t)rowsE * lo.total};
             egnn_prof_begin(EGNN_K_NODE_BWD, st);
-            egcl_node_bwd<<<bw.gridN, 256, smemN, st>>>(na);
+            egcl_node_bwd<<<rowsN, 256, smemN, st>>>(na);
             egnn_prof_end(st);
             EGNN_CHECK_LAUNCH("egcl_node_bwd");
         }
@@ -499,10 +529,10 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
                            ws + bw.gM, ws + bw.gdx, ws + bw.coefS, ws + bw.Gr, ws + bw.Gs, ws + bw.part};
             int rc;
             switch (bw.TEB) {
-                case 64: rc = launch_edge_bwd<16>(ea, bw.gridE, smemE, st); break;
-                case 32: rc = launch_edge_bwd<8>(ea, bw.gridE, smemE, st); break;
-                case 16: rc = launch_edge_bwd<4>(ea, bw.gridE, smemE, st); break;
-                default: rc = launch_edge_bwd<2>(ea, bw.gridE, smemE, st); break;
+                case 64: rc = launch_edge_bwd<16>(ea, rowsE, smemE, st); break;
+                case 32: rc = launch_edge_bwd<8>(ea, rowsE, smemE, st); break;
+                case 16: rc = launch_edge_bwd<4>(ea, rowsE, smemE, st); break;
+                default: rc = launch_edge_bwd<2>(ea, rowsE, smemE, st); break;
             }
             if (rc) return rc;
         }
@@ -516,7 +546,8 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
             egnn_prof_end(st);
             EGNN_CHECK_LAUNCH("egcl_gather_bwd");
         }
-        reduce_partials_kernel<<<(lo.total + 255) / 256, 256, 0, st>>>(ws + bw.part, rows, lo.total,
+        reduce_partials_kernel<<<(lo.total + 255) / 256, 256, 0, st>>>(ws + bw.part, rowsE, rowsN, lo.total, lo.wx1, lo.wh1,
+                                                                      lo.wa, use_tc ? 1 : 0,
                                                                       grad_params + (size_t)l * lo.total);
         EGNN_CHECK_LAUNCH("reduce_partials_kernel");
     }

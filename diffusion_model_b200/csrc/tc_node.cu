@@ -1,0 +1,256 @@
+// tcgen05 path of the node backward (mlp_h): one CTA per 128-node tile, 4*D threads (thread = node row x 32 columns).
+//   z1 = [h, M, 0.., 1] . Wh1^T                      GEMM1, K = D + 16 (the constant-1 column makes db1 an MMA column)
+//   s1 = SiLU(z1 + b1) -> tile S;   dWh2^T = s1^T . gh'          (tile S viewed MN-major, K = 128 nodes)
+//   gz1 = SiLU'(z1 + b1) * (gh' . Wh2) -> tile S (reused);  g[h, M] = gz1 . Wh1   (the Wh1 image viewed MN-major)
+//   [dWh1 | db1] = gz1^T . [h, M, 0.., 1]
+// Every CTA writes its weight-gradient block to its own partial row (no accumulation, no zero-fill needed).
+// Reference: EGCL.forward's node update, EquivariantGraphNeuralNetwork.py:26-30, 69 (adjoint of it).
+#include "tc_tile.cuh"
+
+namespace {
+
+template <int D>
+struct TcNodeLayout {
+    static constexpr int NT = 4 * D, NG = D / 32, KP = D + 16, NCH = KP / 8;
+    static constexpr int s_hi = 0, s_lo = 128 * D * 2;                 // S, later gz1
+    static constexpr int a_hi = 2 * 128 * D * 2, a_lo = a_hi + NCH * 2048;  // [128 x KP]
+    static constexpr int w_hi = a_lo + NCH * 2048, w_lo = w_hi + NCH * D * 16;  // Wh1 image [D x KP]
+    static constexpr int gh_hi = w_lo + NCH * D * 16, gh_lo = gh_hi + 4096;     // gh' [128 x 16]
+    static constexpr int vec = gh_lo + 4096;          // b1 [D] | Wh2 [8][D]
+    static constexpr int sGH = vec + 9 * D * 4;       // float [128][8]
+    static constexpr int red = sGH + 4096;            // float [NT/32][8]
+    static constexpr int bars = red + (NT / 32) * 32, slot = bars + 32;
+    static constexpr int TOTAL = slot + 16;
+    static_assert(TOTAL <= 227 * 1024, "tc_node_bwd shared memory");
+};
+
+struct TcNodeBwdArgs {
+    egnn_net_t net;
+    int N;
+    const float *h, *msum, *gh_out;
+    const float* P;        // this layer's fp32 parameters
+    const uint8_t* nblob;  // Wh1 image (hi | lo)
+    float *gh_node, *gM;
+    float* part;           // [gridDim.x][layer param count]
+};
+
+template <int D, int NPASS>
+__global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
+    using L = TcNodeLayout<D>;
+    constexpr bool FAST = NPASS == 1;
+    constexpr bool LO = NPASS == 3;
+    constexpr int NT = L::NT, NG = L::NG, KP = L::KP;
+    constexpr int cZ = 0, cG = D, cW1 = 2 * D + 32, cW2T = 3 * D + 48;  // TMEM columns (512 allocated)
+    constexpr uint32_t TS = 128 * 16;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q = warp & 3, cg = warp >> 2;
+    const int r = q * 32 + lane, c0 = cg * 32;
+    const int H = a.net.H, KA = H + D;
+    const LayerOff lo = layer_off(a.net);
+    float* vec = reinterpret_cast<float*>(smem + L::vec);
+    float* sGH = reinterpret_cast<float*>(smem + L::sGH);
+    float* red = reinterpret_cast<float*>(smem + L::red);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::bars);
+    uint32_t* slot = reinterpret_cast<uint32_t*>(smem + L::slot);
+    const int n = blockIdx.x * 128 + r;
+    const bool valid = n < a.N;
+
+    for (int o = tid * 16; o < 2 * L::NCH * D * 16; o += NT * 16)
+        *reinterpret_cast<uint4*>(smem + L::w_hi + o) = __ldg(reinterpret_cast<const uint4*>(a.nblob + o));
+    for (int c = tid; c < D; c += NT) vec[c] = a.P[lo.bh1 + c];
+    for (int c = tid; c < 8 * D; c += NT) vec[D + c] = c < H * D ? a.P[lo.wh2 + c] : 0.f;
+    if (warp == 0) tc::tmem_alloc(slot, 512);
+    if (tid == 0) {
+        for (int b = 0; b < 3; ++b) tc::mbar_init(&bars[b], 1);
+        tc::fence_mbar_init();
+    }
+    // ---- A tile = [h | M | 0 .. | 1] of this thread's row, 32 columns (+ the 16 trailing columns by column group 0)
+    {
+        float v[32];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            const int c = c0 + k;
+            v[k] = !valid ? 0.f : (c < H ? a.h[(size_t)n * H + c] : a.msum[(size_t)n * D + (c - H)]);
+        }
+        tc_split_store32(smem + L::a_hi, smem + L::a_lo, r, c0, v, true);
+        if (cg == 0) {
+            float t[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const int c = D + k;
+                t[k] = !valid ? 0.f : (c < KA ? a.msum[(size_t)n * D + (c - H)] : (c == KP - 1 ? 1.f : 0.f));
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint32_t hi[4], lw[4];
+#pragma unroll
+                for (int p = 0; p < 4; ++p) tc::split2(t[8 * j + 2 * p], t[8 * j + 2 * p + 1], hi[p], lw[p]);
+                *reinterpret_cast<uint4*>(smem + L::a_hi + tc::chunk_off(128, r, D / 8 + j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(smem + L::a_lo + tc::chunk_off(128, r, D / 8 + j)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            }
+        }
+        if (cg == NG - 1) {  // gh' row: fp32 copy for the CUDA cores, bf16 tile for the wgrad MMA
+            float t[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) t[k] = (valid && k < H) ? a.gh_out[(size_t)n * H + k] : 0.f;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) sGH[r * 8 + k] = t[k];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint32_t hi[4], lw[4];
+#pragma unroll
+                for (int p = 0; p < 4; ++p) tc::split2(t[8 * j + 2 * p], t[8 * j + 2 * p + 1], hi[p], lw[p]);
+                *reinterpret_cast<uint4*>(smem + L::gh_hi + tc::chunk_off(128, r, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(smem + L::gh_lo + tc::chunk_off(128, r, j)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            }
+            // db2[o] = sum over nodes of gh'[n][o]: warp sums now, cross-warp sum at the end
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float s = warp_sum(t[k]);
+                if (lane == 0) red[q * 8 + k] = s;
+            }
+        }
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *slot;
+    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    const uint32_t sb = tc::smem_u32(smem);
+    const TcOperand opA{sb + L::a_hi, sb + L::a_lo, TS, false}, opAmn{sb + L::a_hi, sb + L::a_lo, TS, true};
+    const TcOperand opW{sb + L::w_hi, sb + L::w_lo, D * 16, false}, opWmn{sb + L::w_hi, sb + L::w_lo, D * 16, true};
+    const TcOperand opS{sb + L::s_hi, sb + L::s_lo, TS, false}, opSmn{sb + L::s_hi, sb + L::s_lo, TS, true};
+    const TcOperand opGHmn{sb + L::gh_hi, sb + L::gh_lo, TS, true};
+    bool ok = true;
+    if (tid == 0) {
+        tc_issue_op<NPASS>(tmem, cZ, opA, opW, KP, D, false);  // z1
+        tc::mma_commit(&bars[0]);
+    }
+    ok = tc::mbar_wait(&bars[0], 0) && ok;
+    tc::fence_after_sync();
+    float gz[32];
+    {
+        float v[32], act[32];
+        tc::tmem_ld32(trow + cZ + c0, v);
+        float gh[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) gh[k] = sGH[r * 8 + k];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const float zz = v[i] + vec[c0 + i];
+            const float s = tc_sigmoid<FAST>(zz);
+            act[i] = zz * s;
+            float t = 0.f;
+#pragma unroll
+            for (int o = 0; o < 8; ++o)
+                if (o < H) t = fmaf(gh[o], vec[D + o * D + c0 + i], t);
+            gz[i] = t * s * fmaf(zz, 1.f - s, 1.f);
+        }
+        tc_split_store32(smem + L::s_hi, smem + L::s_lo, r, c0, act, LO);
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+        tc::fence_after_sync();
+        tc_issue_op<NPASS>(tmem, cW2T, opSmn, opGHmn, 128, 16, false);  // dWh2^T [k][o] = s1^T . gh'
+        tc::mma_commit(&bars[1]);
+    }
+    ok = tc::mbar_wait(&bars[1], 0) && ok;
+    tc::fence_after_sync();
+    tc_split_store32(smem + L::s_hi, smem + L::s_lo, r, c0, gz, LO);  // tile S now holds gz1
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    if (tid == 0) {
+        tc::fence_after_sync();
+        tc_issue_op<NPASS>(tmem, cG, opS, opWmn, D, KP, false);      // g[h, M] = gz1 . Wh1
+        tc_issue_op<NPASS>(tmem, cW1, opSmn, opAmn, 128, KP, false);  // [dWh1 | db1] = gz1^T . [h, M, 0.., 1]
+        tc::mma_commit(&bars[2]);
+    }
+    ok = tc::mbar_wait(&bars[2], 0) && ok;
+    if (!ok) asm volatile("trap;");
+    tc::fence_after_sync();
+    float* part = a.part + (size_t)blockIdx.x * lo.total;
+    {
+        float v[32];
+        tc::tmem_ld32(trow + cG + c0, v);
+        if (valid) {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+                const int c = c0 + k;
+                if (c < H) a.gh_node[(size_t)n * H + c] = v[k];
+                else a.gM[(size_t)n * D + (c - H)] = v[k];
+            }
+        }
+        tc::tmem_ld32(trow + cW1 + c0, v);
+        if (r < D) {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) part[lo.wh1 + r * KA + c0 + k] = v[k];
+        }
+    }
+    if (cg == 0) {
+        float v[32];
+        tc::tmem_ld32(trow + cG + D, v);
+        if (valid) {
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+                if (D + k < KA) a.gM[(size_t)n * D + (D + k - H)] = v[k];
+        }
+        tc::tmem_ld32(trow + cW1 + D, v);
+        if (r < D) {
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+                if (D + k < KA) part[lo.wh1 + r * KA + D + k] = v[k];
+            part[lo.bh1 + r] = v[15];
+        }
+    }
+    if (cg == NG - 1) {
+        float v[32];
+        tc::tmem_ld32(trow + cW2T, v);
+        if (r < D) {
+#pragma unroll
+            for (int o = 0; o < 8; ++o)
+                if (o < H) part[lo.wh2 + o * D + r] = v[o];
+        }
+    }
+    if (tid < H) part[lo.bh2 + tid] = red[tid] + red[8 + tid] + red[16 + tid] + red[24 + tid];
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+template <int D, int NPASS>
+int launch_tc_node_bwd(const TcNodeBwdArgs& a, int grid, cudaStream_t st) {
+    constexpr int SMEM = TcNodeLayout<D>::TOTAL;
+    static bool configured = false;
+    if (!configured) {
+        EGNN_CUDA(cudaFuncSetAttribute(tc_node_bwd<D, NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        configured = true;
+    }
+    egnn_prof_begin(EGNN_K_NODE_BWD, st);
+    tc_node_bwd<D, NPASS><<<grid, 4 * D, SMEM, st>>>(a);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("tc_node_bwd");
+    return EGNN_OK;
+}
+
+}  // namespace
+
+int egnn_tc_node_bwd_grid(int64_t N) { return (int)((N + 127) / 128); }
+
+// node phase of one layer's backward on the tensor cores; partial rows [grid][layer param count], mlp_h block fully written
+int egnn_tc_node_backward(const egnn_net_t& net, int N, const float* params_layer, const float* packed_layer, const float* h,
+                          const float* msum, const float* gh_out, float* gh_node, float* gM, float* part, int precision,
+                          cudaStream_t st) {
+    EGNN_REQUIRE(tc_node_supported(net), "tcgen05 node path needs Hh = Ms = d in {64,128}");
+    const PackOff po = pack_off(net);
+    const uint8_t* blob = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    TcNodeBwdArgs a{net, N, h, msum, gh_out, params_layer, blob + (tc_blob_bytes(net.Mh) + 15) / 16 * 16, gh_node, gM, part};
+    const int grid = egnn_tc_node_bwd_grid(N);
+    const bool x3 = precision == EGNN_PREC_BF16X3;
+    if (net.Mh == 128) return x3 ? launch_tc_node_bwd<128, 3>(a, grid, st) : launch_tc_node_bwd<128, 1>(a, grid, st);
+    return x3 ? launch_tc_node_bwd<64, 3>(a, grid, st) : launch_tc_node_bwd<64, 1>(a, grid, st);
+}

@@ -1,0 +1,99 @@
+// Shared device helpers of the tcgen05 kernels (edge forward / backward, node backward): activation epilogues, bf16 hi/lo
+// tile stores, operand descriptors for the K-major and MN-major views of a SWIZZLE_NONE tile, MMA issue loops.
+#pragma once
+#include "tc_common.cuh"
+
+namespace {
+
+template <bool FAST>
+__device__ __forceinline__ float tc_silu(float z) {
+    if (FAST) {  // one MUFU: z * sigmoid(z) = 0.5 z (1 + tanh(z / 2)); ~2^-11 relative, for the bf16 mode only
+        float t;
+        asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * z));
+        return 0.5f * z * (1.f + t);
+    }
+    return silu_f(z);
+}
+
+// this thread's row, columns [c0, c0+32) of a TMEM block: act(acc + bias) packed as bf16 hi/lo pairs
+template <bool FAST>
+__device__ __forceinline__ void tc_epi32(uint32_t taddr, const float* bias, uint32_t (&hi)[16], uint32_t (&lo)[16]) {
+    float v[32];
+    tc::tmem_ld32(taddr, v);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float a = tc_silu<FAST>(v[2 * i] + bias[2 * i]);
+        const float b = tc_silu<FAST>(v[2 * i + 1] + bias[2 * i + 1]);
+        tc::split2(a, b, hi[i], lo[i]);
+    }
+}
+__device__ __forceinline__ void tc_store32(uint8_t* a_hi, uint8_t* a_lo, int r, int c0, const uint32_t (&hi)[16],
+                                           const uint32_t (&lo)[16], bool with_lo) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint32_t off = tc::chunk_off(128, r, (c0 >> 3) + q);
+        *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+        if (with_lo) *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+    }
+}
+
+struct TcOperand {
+    uint32_t hi, lo;        // shared-memory addresses of the hi / lo tiles
+    uint32_t chunk_stride;  // bytes between consecutive 16-byte chunk columns (rows * 16)
+    bool mn;                // viewed MN-major (K index = tile row)
+};
+__device__ __forceinline__ uint64_t tc_op_desc(const TcOperand& o, bool use_lo, int s) {
+    const uint32_t base = use_lo ? o.lo : o.hi;
+    return o.mn ? tc::make_desc(base + s * 256, 128, o.chunk_stride)
+                : tc::make_desc(base + s * 2 * o.chunk_stride, o.chunk_stride, 128);
+}
+// one thread: D[128 x N] (+)= A . B^T over K, NPASS split products, into TMEM column dcol
+template <int NPASS>
+__device__ __forceinline__ void tc_issue_op(uint32_t tmem, int dcol, const TcOperand& A, const TcOperand& B, int K, int N,
+                                            bool acc) {
+    const uint32_t idesc = tc::make_idesc_bf16(128, N) | (A.mn ? 1u << 15 : 0u) | (B.mn ? 1u << 16 : 0u);
+#pragma unroll
+    for (int p = 0; p < NPASS; ++p) {
+        for (int s = 0; s < K / 16; ++s) {
+            tc::mma_bf16(tmem + dcol, tc_op_desc(A, p == 1, s), tc_op_desc(B, p == 2, s), idesc, acc);
+            acc = true;
+        }
+    }
+}
+
+// warp reduce-scatter of 32 per-thread values over the 32 lanes (fixed order): v[0] of lane L ends as the sum over the
+// warp's 32 rows of column L
+__device__ __forceinline__ void warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int st = 0; st < 5; ++st) {
+        const int off = 16 >> st, live = 16 >> st;
+        const bool hiL = lane & off;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (k < live) {
+                const float send = hiL ? v[k] : v[k + live], keep = hiL ? v[k + live] : v[k];
+                v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+        }
+    }
+}
+
+// split + store 32 consecutive columns [c0, c0+32) of row r into a 128-row tile
+__device__ __forceinline__ void tc_split_store32(uint8_t* t_hi, uint8_t* t_lo, int r, int c0, const float (&v)[32], bool with_lo) {
+    uint32_t hi[16], lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) tc::split2(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+    tc_store32(t_hi, t_lo, r, c0, hi, lo, with_lo);
+}
+
+template <bool FAST>
+__device__ __forceinline__ float tc_sigmoid(float z) {
+    if (FAST) {
+        float t;
+        asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * z));
+        return fmaf(0.5f, t, 0.5f);
+    }
+    return sigmoid_f(z);
+}
+
+}  // namespace
