@@ -120,3 +120,38 @@ def sample_structure_xonly(egnn, sch, edge_index, x_onehot, noises, s=1.0):
         mu = D.calculate_mu_xonly(sch, pos, eps, t)
         pos = D.reverse_diffuse_one_step_xonly(sch, mu, t, noises["step_x"][T - t].clone())
     return pos
+
+
+def sample_structures_batched(sd, L, sch, n, S, noises, A=2, s=1.0):
+    """S independent runs of sample_structure() evaluated as ONE batch of S graphs (faster on the CPU, same arithmetic
+    per structure): per-graph COM removal (diffusion_x_h.py:10-13 with a batch vector) and the per-graph normaliser
+    (norm_scope='graph'), which is what calling generate() once per structure (parts/train_per_iretation.py:299-316)
+    computes.  noises: dict as make_noises() with a leading structure axis flattened into the node axis
+    (init_x [S*n,3], step_x [T,S*n,3], ...).  Returns (pos [S,n,3], h [S,n,A], finite [S])."""
+    from . import egnn_ref, graphs_ref
+    T = sch.T
+    batch = torch.arange(S).repeat_interleave(n)
+    ei = torch.as_tensor(graphs_ref.fc_edges_batch([n] * S))
+    fwd = lambda h, x: egnn_ref.egnn_forward(sd, L, ei, h, x, "graph", batch=batch)
+
+    def rm(x, _b=None):  # per-graph COM removal; equal-size graphs -> one strided mean instead of the mask loop
+        v = x.view(S, n, 3)
+        return (v - v.mean(dim=1, keepdim=True)).reshape(S * n, 3)
+    z_x = rm(noises["init_x"].clone())
+    z_h = noises["init_h"].clone()
+    for t in range(T, 0, -1):
+        k = T - t
+        h = torch.cat([s * z_h, torch.full((S * n, 1), t / T, dtype=torch.float32)], dim=1)
+        new_h, new_x = fwd(h, z_x)
+        eps_x = rm(new_x - z_x)
+        z_x = D.reverse_diffuse_one_step(sch, z_x, eps_x, t, rm(noises["step_x"][k].clone()), "h")
+        z_h = D.reverse_diffuse_one_step(sch, h[:, :A], new_h[:, :A], t, noises["step_h"][k].clone(), "h")
+    h = torch.cat([s * z_h, torch.zeros((S * n, 1), dtype=torch.float32)], dim=1)
+    new_h, new_x = fwd(h, z_x)
+    eps_x = rm(new_x - z_x)
+    a0, s0 = sch.alpha[0], sch.sigma[0]
+    pos = z_x / a0 - s0 * eps_x / a0 + s0 * rm(noises["final_x"].clone()) / a0
+    hf = h[:, :A] / a0 - s0 * new_h[:, :A] / a0 + s0 * noises["final_h"] / a0
+    pos, hf = pos.view(S, n, 3), hf.view(S, n, A)
+    finite = torch.isfinite(pos).all(dim=(1, 2)) & torch.isfinite(hf).all(dim=(1, 2))
+    return pos, hf, finite

@@ -136,3 +136,38 @@ def test_state_dict_keys_match_reference(golden_dir):
     assert list(mine.keys()) == list(sd.keys())
     # same construction order under the same seed -> identical initial weights as the reference module
     assert all(torch.equal(mine[k], sd[k]) for k in sd)
+
+
+def test_eval_functions_against_reference(golden_dir):
+    """RDF / CN2 angle / bond-length restatement (oracle/eval_ref.py) vs outputs of the unmodified reference functions"""
+    from oracle import eval_ref as E
+    z = load(golden_dir, "eval_kat")
+    for k in range(3):
+        R, dR = (float(v) for v in z[f"par{k}"])
+        pos = torch.from_numpy(z[f"pos{k}"])
+        assert np.array_equal(E.rdf(pos, R=R, dR=dR), z[f"rdf{k}"])
+        assert np.array_equal(E.rdf(pos, R=R, dR=dR, Normalize=True), z[f"rdfn{k}"])
+        ang, b1, b2 = z[f"cn2_{k}"]
+        assert E.angle_cn2(pos[:3]) == ang and E.bond_lengths_cn2(pos[:3]) == (b1, b2)
+    a, b = z["rdf0"], z["rdf1"][: len(z["rdf0"])]
+    assert E.cos_similarity(a, b) == float(z["cos01"]) and E.wasserstein(a, b) == float(z["wd01"])
+
+
+def test_batched_oracle_sampler_equals_per_structure_loop():
+    """the batched CPU sampler used by the distribution test is the per-structure loop of generate() run S times"""
+    torch.manual_seed(0)
+    sizes = egnn_ref.net_sizes(2, 32)
+    sd = egnn_ref.tame_state_dict(egnn_ref.init_state_dict(**sizes), 2)
+    n, S, T = 12, 3, 40
+    sch = D.Schedule(0.05, 2.0, T)
+    gen = torch.Generator().manual_seed(1)
+    per = [LP.make_noises(n, T, 2, gen) for _ in range(S)]
+    cat = {k: torch.cat([p[k] for p in per], dim=1 if k.startswith("step") else 0) for k in per[0]}
+    ei = torch.as_tensor(G.fc_edges(n))
+    with torch.no_grad():
+        pos, hf, fin = LP.sample_structures_batched(sd, 2, sch, n, S, cat)
+        for k in range(S):
+            p1, h1, _, f1 = LP.sample_structure(lambda e, h, x: egnn_ref.egnn_forward(sd, 2, e, h, x), sch, ei, n, per[k])
+            assert bool(fin[k]) == f1
+            assert float((pos[k] - p1).abs().max()) <= 1e-4 * float(p1.abs().max())
+            assert float((hf[k] - h1).abs().max()) <= 1e-4 * max(1.0, float(h1.abs().max()))
