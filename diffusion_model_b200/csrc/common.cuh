@@ -125,8 +125,8 @@ static inline int edge_tile_for(const egnn_net_t& n) {
     while (te > 16 && (int64_t)te * (round4(dmax) + 4) > 128 * 132) te >>= 1;
     return te;
 }
-// rows of the tile-partial buffer are sized for the finest segmentation any path uses (tcgen05: d/2-edge segments)
-static inline int part_tile_for(const egnn_net_t& n) { return tc_supported(n) ? n.Mh / 2 : edge_tile_for(n); }
+// rows of the tile-partial buffer are sized for the finest segmentation any path uses (tcgen05: 32-edge segments)
+static inline int part_tile_for(const egnn_net_t& n) { return tc_supported(n) ? 32 : edge_tile_for(n); }
 static inline FwdWs fwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     FwdWs w;
     const int64_t AGGW = n.Ms + 4;

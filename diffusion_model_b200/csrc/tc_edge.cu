@@ -115,7 +115,6 @@ extern "C" int egnn_tc_selftest(const float* A, const float* B, float* D, int32_
 //   phi = wx3 . SiLU(GEMM2x + bx2) + bx3 ;  m = SiLU(GEMM2m + bm2) ;  g = sigmoid(wa . m + ba)
 // followed by the same fixed-order segmented sum as the fp32 path, over d/2-edge segments.
 // NPASS = 3: every product is hi.hi + lo.hi + hi.lo of bf16 splits (fp32-class accuracy, "bf16x3");  NPASS = 1: plain bf16.
-// 256 threads: warp w reads TMEM lane quadrant w % 4 (rows 32(w%4)..+31) and column half w / 4 of each d-wide block.
 // =====================================================================================================================
 namespace {
 
@@ -135,10 +134,11 @@ struct TcLayout {
     static constexpr int a1_hi = u_lo + 128 * 32, a1_lo = a1_hi + 128 * D * 2;
     static constexpr int stage = a1_hi;  // fp32 [128][D] staging of g*m reuses the A1 tiles (needs D*4 <= 2 * D*2: equal)
     static constexpr int small = a1_lo + 128 * D * 2;
-    // small: sI int[128] | sR float[128][4] | phiPart [2][128] | gatePart [2][128] | sPhi [128] | sDst int[128] | bars | slot
-    static constexpr int sI = small, sR = sI + 512, phiPart = sR + 2048, gatePart = phiPart + 1024, sPhi = gatePart + 1024,
-                         sDst = sPhi + 512, bars = sDst + 512, slot = bars + 64;
+    // small: phiPart [D/32][128] | gatePart [D/32][128] | sDst int[128] | sMask u32[4] | bars | slot
+    static constexpr int phiPart = small, gatePart = phiPart + (D / 32) * 512, sDst = gatePart + (D / 32) * 512,
+                         sMask = sDst + 512, bars = sMask + 16, slot = bars + 64;
     static constexpr int TOTAL = slot + 16;
+    static_assert(TOTAL <= 227 * 1024, "tc_edge_fwd shared memory");
 };
 
 __global__ void __launch_bounds__(256) tc_pack_kernel(egnn_net_t net, const float* __restrict__ params,
@@ -219,53 +219,101 @@ struct TcFwdArgs {
     float* phi_edge;  // [E] phi_e of this layer (dxu / D are summed per receiver by the node kernel)
 };
 
-// one thread: D[128 x N] = A[128 x K] . B[N x K]^T into TMEM column `dcol`, NPASS products
-template <int NPASS>
-__device__ __forceinline__ void tc_issue(uint32_t tmem, int dcol, const uint8_t* a_hi, const uint8_t* a_lo,
-                                         const uint8_t* b_hi, const uint8_t* b_lo, int K, int N) {
-    const uint32_t idesc = tc::make_idesc_bf16(128, N);
-    const uint32_t lboA = 128 * 16, lboB = (uint32_t)N * 16;
-    bool acc = false;
-#pragma unroll
-    for (int p = 0; p < NPASS; ++p) {
-        const uint32_t ta = tc::smem_u32(p == 1 ? a_lo : a_hi), tb = tc::smem_u32(p == 2 ? b_lo : b_hi);
-        for (int s = 0; s < K / 16; ++s) {
-            tc::mma_bf16(tmem + dcol, tc::make_desc(ta + s * 2 * lboA, lboA, 128), tc::make_desc(tb + s * 2 * lboB, lboB, 128),
-                         idesc, acc);
-            acc = true;
-        }
-    }
-}
-
+// 4*D threads: warp w owns TMEM lane quadrant w % 4 (edge rows 32(w%4)..+31) and the 32-column group w / 4 of every
+// D-wide block.  Per 128-edge tile:
+//   GEMM1 (both branches, issued one tile ahead) -> SiLU of the coordinate branch -> tile A1 -> GEMM2x
+//   SiLU of the message branch in registers while GEMM2x runs -> tile A1 -> GEMM2m (+ next tile's GEMM1)
+//   phi partial dots while GEMM2m runs -> m, gate -> g*m staged in fp32 (aliases A1) -> fixed-order segmented sums
+// The next tile's gather loads are in flight from the top of the tile; its U tile is stored as soon as GEMM1 of the
+// current tile has completed.
 template <int D, int NPASS>
-__global__ void __launch_bounds__(256, 1) tc_edge_fwd(TcFwdArgs a) {
+__global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
     using L = TcLayout<D>;
     constexpr bool FAST = NPASS == 1;
-    constexpr int HALF = D / 2;          // columns per thread in every D-wide block
-    constexpr int NSEG = 256 / D;        // row segments of the segmented sum (2 for D=128, 4 for D=64)
-    constexpr int TS = 128 / NSEG;       // edges per segment == partial-buffer granularity (part_tile_for)
+    constexpr bool LO = NPASS == 3;
+    constexpr int NT = 4 * D, NG = D / 32;
+    constexpr int TS = 32;  // edges per segment == partial-buffer granularity (part_tile_for)
+    constexpr uint32_t CS = 128 * 16;
     extern __shared__ __align__(1024) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int q = warp & 3, hf = warp >> 2;
-    const int r = q * 32 + lane;         // this thread's edge row == TMEM lane
+    const int q = warp & 3, cg = warp >> 2;
+    const int r = q * 32 + lane;  // this thread's edge row == TMEM lane
+    const int c0 = cg * 32;
     const int H = a.net.H, AGGW = D + 4;
     float* vec = reinterpret_cast<float*>(smem + L::vec);
     float* phiPart = reinterpret_cast<float*>(smem + L::phiPart);
     float* gatePart = reinterpret_cast<float*>(smem + L::gatePart);
     int* sDst = reinterpret_cast<int*>(smem + L::sDst);
+    uint32_t* sMask = reinterpret_cast<uint32_t*>(smem + L::sMask);
     float* stage = reinterpret_cast<float*>(smem + L::stage);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::bars);  // [0] GEMM1, [1] GEMM2x, [2] GEMM2m
     uint32_t* slot = reinterpret_cast<uint32_t*>(smem + L::slot);
 
-    // ---- one-time setup: weight image -> smem, TMEM, barriers
-    for (int o = tid * 16; o < L::blob_pad; o += 256 * 16)
+    for (int o = tid * 16; o < L::blob_pad; o += NT * 16)
         *reinterpret_cast<uint4*>(smem + o) = __ldg(reinterpret_cast<const uint4*>(a.blob + o));
     if (warp == 0) tc::tmem_alloc(slot, 4 * D);
     if (tid == 0) {
-        tc::mbar_init(&bars[0], 1);
-        tc::mbar_init(&bars[1], 1);
-        tc::mbar_init(&bars[2], 1);
+        for (int b = 0; b < 3; ++b) tc::mbar_init(&bars[b], 1);
         tc::fence_mbar_init();
+    }
+    const uint32_t sb = tc::smem_u32(smem);
+    const TcOperand opU{sb + L::u_hi, sb + L::u_lo, CS, false};
+    const TcOperand opA1{sb + L::a1_hi, sb + L::a1_lo, CS, false};
+    const TcOperand opW1{sb + L::w1_hi, sb + L::w1_lo, 2 * D * 16, false};
+    const TcOperand opW2m{sb + L::w2m_hi, sb + L::w2m_lo, D * 16, false}, opW2x{sb + L::w2x_hi, sb + L::w2x_lo, D * 16, false};
+
+    struct Row {
+        float u[16];
+        int dst;
+    };
+    // one thread per edge row: u, and where the row's finished segmented sum goes (>= 0: agg[node]; -1: head partial;
+    // -2: tail partial; -3: the receiver run continues in the next row)
+    auto gather_load = [&](int tile, Row& g) {
+        const int e0 = tile * 128, nrows = min(128, a.E - e0);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) g.u[k] = 0.f;
+        g.dst = -3;
+        if (tid < nrows) {
+            const int i = a.recv[e0 + tid], j = a.send[e0 + tid];
+            const float rx = a.x[3 * i + 0] - a.x[3 * j + 0];
+            const float ry = a.x[3 * i + 1] - a.x[3 * j + 1];
+            const float rz = a.x[3 * i + 2] - a.x[3 * j + 2];
+            const float nrm = sqrtf(rx * rx + ry * ry + rz * rz);
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                if (k < H) g.u[k] = a.h[(size_t)i * H + k];
+                else if (k < 2 * H) g.u[k] = a.h[(size_t)j * H + (k - H)];
+                else if (k == 2 * H) g.u[k] = nrm * nrm;
+            }
+            const bool last = tid == nrows - 1 || (tid + 1) % TS == 0 || a.recv[e0 + tid + 1] != i;
+            if (last) {
+                const int es = e0 + (tid / TS) * TS;
+                g.dst = a.row_ptr[i] < es ? -1 : (a.row_ptr[i + 1] > es + TS ? -2 : i);
+            }
+        }
+    };
+    auto store_u = [&](const Row& g) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) tc::split2(g.u[8 * j + 2 * p], g.u[8 * j + 2 * p + 1], hi[p], lo[p]);
+            *reinterpret_cast<uint4*>(smem + L::u_hi + tc::chunk_off(128, tid, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(smem + L::u_lo + tc::chunk_off(128, tid, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        }
+    };
+    auto store_dst = [&](int dst) {  // tid < 128: one mask word per 32-row segment marks the rows that flush
+        sDst[tid] = dst;
+        const uint32_t m = __ballot_sync(0xffffffffu, dst != -3);
+        if (lane == 0) sMask[warp] = m;
+    };
+
+    const int nit = blockIdx.x < a.tiles ? (a.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    if (tid < 128 && nit > 0) {
+        Row g;
+        gather_load(blockIdx.x, g);
+        store_u(g);
+        store_dst(g.dst);
     }
     tc::fence_async_smem();
     tc::fence_before_sync();
@@ -273,158 +321,119 @@ __global__ void __launch_bounds__(256, 1) tc_edge_fwd(TcFwdArgs a) {
     tc::fence_after_sync();
     const uint32_t tmem = *slot;
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    if (tid == 0 && nit > 0) {
+        tc_issue_op<NPASS>(tmem, 0, opU, opW1, 16, 2 * D, false);
+        tc::mma_commit(&bars[0]);
+    }
     bool ok = true;
 
-    uint32_t phase = 0;
-    for (int tile = blockIdx.x; tile < a.tiles; tile += gridDim.x, phase ^= 1) {
+    for (int it = 0; it < nit; ++it) {
+        const int tile = blockIdx.x + it * gridDim.x;
         const int e0 = tile * 128;
         const int nrows = min(128, a.E - e0);
-        // ---- gather (one thread per edge row): u -> bf16 hi/lo chunks 0,1 of the U tile
-        if (tid < 128) {
-            float u[16];
-#pragma unroll
-            for (int k = 0; k < 16; ++k) u[k] = 0.f;
-            int i = -1;
-            float rx = 0.f, ry = 0.f, rz = 0.f, dot = 0.f;
-            if (tid < nrows) {
-                i = a.recv[e0 + tid];
-                const int j = a.send[e0 + tid];
-                rx = a.x[3 * i + 0] - a.x[3 * j + 0];
-                ry = a.x[3 * i + 1] - a.x[3 * j + 1];
-                rz = a.x[3 * i + 2] - a.x[3 * j + 2];
-                dot = rx * rx + ry * ry + rz * rz;
-                const float nrm = sqrtf(dot);
-#pragma unroll
-                for (int k = 0; k < 16; ++k) {
-                    if (k < H) u[k] = a.h[(size_t)i * H + k];
-                    else if (k < 2 * H) u[k] = a.h[(size_t)j * H + (k - H)];
-                    else if (k == 2 * H) u[k] = nrm * nrm;
-                }
-            }
-            // segmented-sum bookkeeping: is this row the last of its receiver run inside its TS-row segment, and where
-            // does the finished sum go?  >= 0: agg[node]; -1: head partial; -2: tail partial; -3: keep accumulating
-            int dst = -3;
-            if (tid < nrows) {
-                const bool last = tid == nrows - 1 || (tid + 1) % TS == 0 || a.recv[e0 + tid + 1] != i;
-                if (last) {
-                    const int es = e0 + (tid / TS) * TS;
-                    dst = a.row_ptr[i] < es ? -1 : (a.row_ptr[i + 1] > es + TS ? -2 : i);
-                }
-            }
-            sDst[tid] = dst;
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                uint32_t hi[4], lo[4];
-#pragma unroll
-                for (int p = 0; p < 4; ++p) tc::split2(u[8 * j + 2 * p], u[8 * j + 2 * p + 1], hi[p], lo[p]);
-                *reinterpret_cast<uint4*>(smem + L::u_hi + tc::chunk_off(128, tid, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<uint4*>(smem + L::u_lo + tc::chunk_off(128, tid, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-            }
-        }
-        tc::fence_async_smem();
-        tc::fence_before_sync();
-        __syncthreads();
-        if (tid == 0) {
-            tc::fence_after_sync();
-            tc_issue<NPASS>(tmem, 0, smem + L::u_hi, smem + L::u_lo, smem + L::w1_hi, smem + L::w1_lo, 16, 2 * D);
-            tc::mma_commit(&bars[0]);
-        }
+        const uint32_t phase = it & 1;
+        const bool has_next = it + 1 < nit;
+        Row gnext;
+        gnext.dst = -3;
+        if (tid < 128 && has_next) gather_load(tile + gridDim.x, gnext);
         ok = tc::mbar_wait(&bars[0], phase) && ok;
         tc::fence_after_sync();
-        // ---- layer-1 epilogue of the coordinate branch -> A1, then GEMM2x
+        // ---- layer-1 epilogue of the coordinate branch -> A1; the U tile is free again: store the next tile's rows
         {
             uint32_t hi[16], lo[16];
-#pragma unroll
-            for (int b = 0; b < HALF / 32; ++b) {
-                const int c0 = hf * HALF + 32 * b;
-                tc_epi32<FAST>(trow + D + c0, vec + D + c0, hi, lo);
-                tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, hi, lo, NPASS == 3);
-            }
+            tc_epi32<FAST>(trow + D + c0, vec + D + c0, hi, lo);
+            tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, hi, lo, LO);
         }
+        if (tid < 128 && has_next) store_u(gnext);
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
         if (tid == 0) {
             tc::fence_after_sync();
-            tc_issue<NPASS>(tmem, 3 * D, smem + L::a1_hi, smem + L::a1_lo, smem + L::w2x_hi, smem + L::w2x_lo, D, D);
+            tc_issue_op<NPASS>(tmem, 3 * D, opA1, opW2x, D, D, false);
             tc::mma_commit(&bars[1]);
         }
-        // ---- layer-1 epilogue of the message branch: computed in registers while GEMM2x runs
-        uint32_t mhi[HALF / 32][16], mlo[HALF / 32][16];
-#pragma unroll
-        for (int b = 0; b < HALF / 32; ++b) tc_epi32<FAST>(trow + hf * HALF + 32 * b, vec + hf * HALF + 32 * b, mhi[b], mlo[b]);
+        // ---- layer-1 epilogue of the message branch: in registers while GEMM2x runs
+        uint32_t mhi[16], mlo[16];
+        tc_epi32<FAST>(trow + c0, vec + c0, mhi, mlo);
         ok = tc::mbar_wait(&bars[1], phase) && ok;  // GEMM2x has consumed A1
         tc::fence_after_sync();
-#pragma unroll
-        for (int b = 0; b < HALF / 32; ++b)
-            tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, hf * HALF + 32 * b, mhi[b], mlo[b], NPASS == 3);
+        tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, mhi, mlo, LO);
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
         if (tid == 0) {
             tc::fence_after_sync();
-            tc_issue<NPASS>(tmem, 2 * D, smem + L::a1_hi, smem + L::a1_lo, smem + L::w2m_hi, smem + L::w2m_lo, D, D);
+            tc_issue_op<NPASS>(tmem, 2 * D, opA1, opW2m, D, D, false);
             tc::mma_commit(&bars[2]);
+            if (has_next) {  // z1 of both branches has been consumed: next tile's GEMM1 queues behind GEMM2m
+                tc_issue_op<NPASS>(tmem, 0, opU, opW1, 16, 2 * D, false);
+                tc::mma_commit(&bars[0]);
+            }
         }
         // ---- layer-2 epilogue of the coordinate branch while GEMM2m runs: phi partial over this thread's columns
         {
             float s = 0.f;
+            float v[32];
+            tc::tmem_ld32(trow + 3 * D + c0, v);
 #pragma unroll
-            for (int b = 0; b < HALF / 32; ++b) {
-                const int c0 = hf * HALF + 32 * b;
-                float v[32];
-                tc::tmem_ld32(trow + 3 * D + c0, v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) s = fmaf(vec[5 * D + c0 + i], tc_silu<FAST>(v[i] + vec[3 * D + c0 + i]), s);
-            }
-            phiPart[hf * 128 + r] = s;
+            for (int i = 0; i < 32; ++i) s = fmaf(vec[5 * D + c0 + i], tc_silu<FAST>(v[i] + vec[3 * D + c0 + i]), s);
+            phiPart[cg * 128 + r] = s;
         }
         ok = tc::mbar_wait(&bars[2], phase) && ok;
         tc::fence_after_sync();
         // ---- layer-2 epilogue of the message branch: m in registers, gate partial
-        float m[HALF];
+        float m[32];
         {
             float s = 0.f;
+            float v[32];
+            tc::tmem_ld32(trow + 2 * D + c0, v);
 #pragma unroll
-            for (int b = 0; b < HALF / 32; ++b) {
-                const int c0 = hf * HALF + 32 * b;
-                float v[32];
-                tc::tmem_ld32(trow + 2 * D + c0, v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    m[32 * b + i] = tc_silu<FAST>(v[i] + vec[2 * D + c0 + i]);
-                    s = fmaf(vec[4 * D + c0 + i], m[32 * b + i], s);
-                }
+            for (int i = 0; i < 32; ++i) {
+                m[i] = tc_silu<FAST>(v[i] + vec[2 * D + c0 + i]);
+                s = fmaf(vec[4 * D + c0 + i], m[i], s);
             }
-            gatePart[hf * 128 + r] = s;
+            gatePart[cg * 128 + r] = s;
         }
         tc::fence_before_sync();
-        __syncthreads();  // both column halves of phi / gate are in smem; GEMM2m is done with A1 -> staging may overwrite it
+        __syncthreads();  // all column groups of phi / gate are in smem; GEMM2m is done with A1 -> staging may overwrite it
         {
-            const float g = sigmoid_f(gatePart[r] + gatePart[128 + r] + vec[6 * D]);
-            if (hf == 0 && r < nrows) a.phi_edge[e0 + r] = phiPart[r] + phiPart[128 + r] + vec[6 * D + 1];
+            float gs = vec[6 * D];
 #pragma unroll
-            for (int c = 0; c < HALF; ++c) stage[r * D + ((hf * HALF + c) ^ lane)] = g * m[c];
+            for (int k = 0; k < NG; ++k) gs += gatePart[k * 128 + r];
+            const float g = sigmoid_f(gs);
+            if (cg == 0 && r < nrows) {
+                float ph = vec[6 * D + 1];
+#pragma unroll
+                for (int k = 0; k < NG; ++k) ph += phiPart[k * 128 + r];
+                a.phi_edge[e0 + r] = ph;
+            }
+#pragma unroll
+            for (int c = 0; c < 32; ++c) stage[r * D + ((c0 + c) ^ lane)] = g * m[c];
         }
         __syncthreads();
-        // ---- fixed-order segmented sums over receivers: thread (segment, column) walks its TS rows in edge order
+        // ---- fixed-order segmented sums over receivers: thread (segment, column) walks its 32 rows in edge order and
+        //      flushes at the rows marked in the segment's mask word
         {
             const int seg = tid / D, c = tid % D;
-            const int r0 = seg * TS, r1 = min(r0 + TS, nrows);
-            float* part = a.part + (size_t)(tile * NSEG + seg) * 2 * AGGW;
+            const int r0 = seg * TS;
+            float* part = a.part + (size_t)(tile * 4 + seg) * 2 * AGGW;
+            uint32_t mask = sMask[seg];
             float sum = 0.f;
-#pragma unroll 8
-            for (int rr = r0; rr < r1; ++rr) {
-                sum += stage[rr * D + (c ^ (rr & 31))];
-                const int dst = sDst[rr];
-                if (dst != -3) {
-                    if (dst >= 0) a.agg[(size_t)dst * AGGW + c] = sum;
-                    else part[(dst == -1 ? 0 : AGGW) + c] = sum;
-                    sum = 0.f;
-                }
+            int rr = r0;
+            while (mask) {
+                const int stop = r0 + __ffs(mask) - 1;
+                mask &= mask - 1;
+#pragma unroll 4
+                for (; rr <= stop; ++rr) sum += stage[rr * D + (c ^ (rr & 31))];
+                const int dst = sDst[stop];
+                if (dst >= 0) a.agg[(size_t)dst * AGGW + c] = sum;
+                else part[(dst == -1 ? 0 : AGGW) + c] = sum;
+                sum = 0.f;
             }
         }
-        __syncthreads();
+        __syncthreads();  // staging (aliases A1) and the flush table are free
+        if (tid < 128 && has_next) store_dst(gnext.dst);
     }
     if (!ok) asm volatile("trap;");  // an mbarrier wait timed out: fail loudly instead of returning garbage
     tc::fence_before_sync();
@@ -451,7 +460,7 @@ static int launch_tc_fwd(const TcFwdArgs& a, cudaStream_t st) {
     }
     const int grid = a.tiles < 148 ? a.tiles : 148;
     egnn_prof_begin(EGNN_K_TC_EDGE_FWD, st);
-    tc_edge_fwd<D, NPASS><<<grid, 256, TcLayout<D>::TOTAL, st>>>(a);
+    tc_edge_fwd<D, NPASS><<<grid, 4 * D, TcLayout<D>::TOTAL, st>>>(a);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("tc_edge_fwd");
     return EGNN_OK;
