@@ -262,45 +262,70 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
     const TcOperand opW1{sb + L::w1_hi, sb + L::w1_lo, 2 * D * 16, false};
     const TcOperand opW2m{sb + L::w2m_hi, sb + L::w2m_lo, D * 16, false}, opW2x{sb + L::w2x_hi, sb + L::w2x_lo, D * 16, false};
 
+    // The gather of one edge row is split in three stages so that its two dependent global-load latencies hide under
+    // other work: (1) edge ids, (2) node data of both ends, (3) u -> bf16 tile, and where the row's finished
+    // segmented sum goes (>= 0: agg[node]; -1: head partial; -2: tail partial; -3: the run continues in the next row)
     struct Row {
-        float u[16];
-        int dst;
+        int i, j, inext;          // stage 1
+        float xi[3], xj[3];       // stage 2
+        float hi_[8], hj_[8];
+        int rp0, rp1;
     };
-    // one thread per edge row: u, and where the row's finished segmented sum goes (>= 0: agg[node]; -1: head partial;
-    // -2: tail partial; -3: the receiver run continues in the next row)
-    auto gather_load = [&](int tile, Row& g) {
-        const int e0 = tile * 128, nrows = min(128, a.E - e0);
+    auto gather_ids = [&](int tile, Row& g) {
+        const int e = min(tile * 128 + tid, a.E - 1);
+        g.i = a.recv[e];
+        g.j = a.send[e];
+        g.inext = a.recv[min(e + 1, a.E - 1)];
+    };
+    auto gather_nodes = [&](Row& g) {
 #pragma unroll
-        for (int k = 0; k < 16; ++k) g.u[k] = 0.f;
-        g.dst = -3;
-        if (tid < nrows) {
-            const int i = a.recv[e0 + tid], j = a.send[e0 + tid];
-            const float rx = a.x[3 * i + 0] - a.x[3 * j + 0];
-            const float ry = a.x[3 * i + 1] - a.x[3 * j + 1];
-            const float rz = a.x[3 * i + 2] - a.x[3 * j + 2];
-            const float nrm = sqrtf(rx * rx + ry * ry + rz * rz);
-#pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                if (k < H) g.u[k] = a.h[(size_t)i * H + k];
-                else if (k < 2 * H) g.u[k] = a.h[(size_t)j * H + (k - H)];
-                else if (k == 2 * H) g.u[k] = nrm * nrm;
-            }
-            const bool last = tid == nrows - 1 || (tid + 1) % TS == 0 || a.recv[e0 + tid + 1] != i;
-            if (last) {
-                const int es = e0 + (tid / TS) * TS;
-                g.dst = a.row_ptr[i] < es ? -1 : (a.row_ptr[i + 1] > es + TS ? -2 : i);
-            }
+        for (int k = 0; k < 3; ++k) {
+            g.xi[k] = a.x[3 * g.i + k];
+            g.xj[k] = a.x[3 * g.j + k];
         }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            g.hi_[k] = k < H ? a.h[(size_t)g.i * H + k] : 0.f;
+            g.hj_[k] = k < H ? a.h[(size_t)g.j * H + k] : 0.f;
+        }
+        g.rp0 = a.row_ptr[g.i];
+        g.rp1 = a.row_ptr[g.i + 1];
     };
-    auto store_u = [&](const Row& g) {
+    // returns the flush destination of the row
+    auto store_u = [&](int tile, const Row& g) -> int {
+        const int e0 = tile * 128, nrows = min(128, a.E - e0);
+        const bool valid = tid < nrows;
+        const float rx = g.xi[0] - g.xj[0], ry = g.xi[1] - g.xj[1], rz = g.xi[2] - g.xj[2];
+        const float nrm = sqrtf(rx * rx + ry * ry + rz * rz);
+        float u[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            float v = 0.f;
+#pragma unroll
+            for (int o = 0; o < 8; ++o) {
+                if (k == o && o < H) v = g.hi_[o];
+                if (k == H + o && o < H) v = g.hj_[o];
+            }
+            if (k == 2 * H) v = nrm * nrm;
+            u[k] = valid ? v : 0.f;
+        }
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
             uint32_t hi[4], lo[4];
 #pragma unroll
-            for (int p = 0; p < 4; ++p) tc::split2(g.u[8 * j + 2 * p], g.u[8 * j + 2 * p + 1], hi[p], lo[p]);
+            for (int p = 0; p < 4; ++p) tc::split2(u[8 * j + 2 * p], u[8 * j + 2 * p + 1], hi[p], lo[p]);
             *reinterpret_cast<uint4*>(smem + L::u_hi + tc::chunk_off(128, tid, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             *reinterpret_cast<uint4*>(smem + L::u_lo + tc::chunk_off(128, tid, j)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         }
+        int dst = -3;
+        if (valid) {
+            const bool last = tid == nrows - 1 || (tid + 1) % TS == 0 || g.inext != g.i;
+            if (last) {
+                const int es = e0 + (tid / TS) * TS;
+                dst = g.rp0 < es ? -1 : (g.rp1 > es + TS ? -2 : g.i);
+            }
+        }
+        return dst;
     };
     auto store_dst = [&](int dst) {  // tid < 128: one mask word per 32-row segment marks the rows that flush
         sDst[tid] = dst;
@@ -311,9 +336,9 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
     const int nit = blockIdx.x < a.tiles ? (a.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     if (tid < 128 && nit > 0) {
         Row g;
-        gather_load(blockIdx.x, g);
-        store_u(g);
-        store_dst(g.dst);
+        gather_ids(blockIdx.x, g);
+        gather_nodes(g);
+        store_dst(store_u(blockIdx.x, g));
     }
     tc::fence_async_smem();
     tc::fence_before_sync();
@@ -334,17 +359,18 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
         const uint32_t phase = it & 1;
         const bool has_next = it + 1 < nit;
         Row gnext;
-        gnext.dst = -3;
-        if (tid < 128 && has_next) gather_load(tile + gridDim.x, gnext);
+        int dst_next = -3;
+        if (tid < 128 && has_next) gather_ids(tile + gridDim.x, gnext);   // stage 1: lands during the GEMM1 wait
         ok = tc::mbar_wait(&bars[0], phase) && ok;
         tc::fence_after_sync();
+        if (tid < 128 && has_next) gather_nodes(gnext);                     // stage 2: lands during the epilogue below
         // ---- layer-1 epilogue of the coordinate branch -> A1; the U tile is free again: store the next tile's rows
         {
             uint32_t hi[16], lo[16];
             tc_epi32<FAST>(trow + D + c0, vec + D + c0, hi, lo);
             tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, hi, lo, LO);
         }
-        if (tid < 128 && has_next) store_u(gnext);
+        if (tid < 128 && has_next) dst_next = store_u(tile + gridDim.x, gnext);  // stage 3
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
@@ -433,7 +459,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
             }
         }
         __syncthreads();  // staging (aliases A1) and the flush table are free
-        if (tid < 128 && has_next) store_dst(gnext.dst);
+        if (tid < 128 && has_next) store_dst(dst_next);
     }
     if (!ok) asm volatile("trap;");  // an mbarrier wait timed out: fail loudly instead of returning garbage
     tc::fence_before_sync();
