@@ -203,7 +203,7 @@ def run_product(args, rank, world, local):
     from diffusion_model_b200.data import Data
     from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
     from diffusion_model_b200.distributed import allreduce_gradients, broadcast_parameters
-    from diffusion_model_b200.graph import build_edges_cutoff
+    from diffusion_model_b200.graph import build_edges_cutoff, check_pending
     from diffusion_model_b200.optim import FlatAdam
     from diffusion_model_b200.train_per_iretation import batch_loss
 
@@ -248,7 +248,9 @@ def run_product(args, rank, world, local):
         b = Data(x=oh_p.to(dev, non_blocking=True), pos=pos_p.to(dev, non_blocking=True),
                  edge_index=ei_h.to(dev, non_blocking=True))
         b.node_ptr = np_p.to(dev, non_blocking=True)
-        return train_step(b).item()  # D2H read of the step's loss
+        out = train_step(b).item()  # D2H read of the step's loss
+        check_pending(wait=False)   # deferred edge-list validation of this step's graph (copy already landed)
+        return out
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
@@ -279,6 +281,15 @@ def run_product(args, rank, world, local):
     ms_e2e, _, _ = timed(e2e_step, args.steps, max(args.warmup, 3))
     e2e_value = G_ * world * args.steps / (ms_e2e * 1e-3)
     h2d = pos_p.numel() * 4 + oh_p.numel() * 4 + ei_h.numel() * 8 + np_p.numel() * 4 + G_ * 4
+    # host time to enqueue one step (no sync inside): the floor of the step time when the GPU is not the bottleneck
+    host_ms = []
+    for _ in range(5):
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        train_step(resident)
+        host_ms.append(1e3 * (time.perf_counter() - t0))
+    torch.cuda.synchronize(dev)
+    host_ms = statistics.median(host_ms)
 
     # per-kernel device times (CUDA events on the launching stream, separate short pass after the timed regions)
     import ctypes as C
@@ -328,7 +339,7 @@ def run_product(args, rank, world, local):
                 scaling="weak", vs_baseline=None, dtype=args.precision, data="synthetic",
                 config=dict(workload_config(args.precision), nodes_per_gpu=N, edges_per_gpu=E),
                 e2e=dict(value=e2e_value, unit="graph-steps/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4,
-                         ms_per_step=ms_e2e / args.steps),
+                         ms_per_step=ms_e2e / args.steps, host_enqueue_ms_per_step=host_ms),
                 gpu_launches=int(launches), clocks=clocks, roofline=roofline, kernels=prof,
                 train_flops_per_step=3 * fwd_flops(CFG["L"], d, CFG["H"], N, E))
     if rank == 0 and world == 1:

@@ -26,9 +26,17 @@ __global__ void __launch_bounds__(256) egcl_xupdate_bwd(const float* __restrict_
     const int g = blockIdx.x;
     const int a = node_ptr[g], b = node_ptr[g + 1];
     const int lo = scope == EGNN_NORM_CALL ? 0 : a, hi = scope == EGNN_NORM_CALL ? N : b;
-    float s = 0.f;
-    for (int idx = 3 * lo + threadIdx.x; idx < 3 * hi; idx += 256) s = fmaf(gx_out[idx], dxu[idx], s);
-    const float dot = block_sum_256(s, red);
+    // four independent chains per thread (fixed order): the whole-call dot is latency-bound otherwise
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int idx = 3 * lo + threadIdx.x;
+    for (; idx + 768 < 3 * hi; idx += 1024) {
+        s0 = fmaf(gx_out[idx], dxu[idx], s0);
+        s1 = fmaf(gx_out[idx + 256], dxu[idx + 256], s1);
+        s2 = fmaf(gx_out[idx + 512], dxu[idx + 512], s2);
+        s3 = fmaf(gx_out[idx + 768], dxu[idx + 768], s3);
+    }
+    for (; idx < 3 * hi; idx += 256) s0 = fmaf(gx_out[idx], dxu[idx], s0);
+    const float dot = block_sum_256((s0 + s1) + (s2 + s3), red);
     const float Sg = S[g], den = Sg + 1.f;
     if (threadIdx.x == 0) coefS[g] = Sg > 0.f ? -dot / (den * den) / Sg : 0.f;
     for (int idx = 3 * a + threadIdx.x; idx < 3 * b; idx += 256) gdx[idx] = gx_out[idx] / den;

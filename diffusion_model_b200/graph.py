@@ -104,17 +104,43 @@ class GraphIndex:
         flags = torch.empty(2, dtype=I32, device=dev)
         call("egnn_graph_prepare", ptr(edge_index), N, E, ptr(self.recv), ptr(self.send), ptr(self.row_ptr),
              ptr(self.col_ptr), ptr(self.col_edge), ptr(scratch), ptr(flags), st)
-        if validate:
-            f = flags.tolist()
-            if f[1]:
-                raise _lib.EgnnError("edge_index holds a node id outside [0, num_nodes)")
-            if f[0]:
-                raise _lib.EgnnError(
-                    "edge_index[0] must be non-decreasing (receiver-sorted), as every edge builder of the reference "
-                    "produces; sort the columns by edge_index[0] first")
+        # validation flags: read now (validate=True, one host sync) or copied to pinned memory and checked at the next
+        # natural sync point (validate="deferred": training loops, where a host sync per minibatch stalls the pipeline;
+        # the kernels clamp bad ids, so a malformed list gives wrong numbers but no wild access until it is reported)
+        self._pending = None
+        if validate == "deferred":
+            host = torch.empty(2, dtype=I32, pin_memory=True)
+            host.copy_(flags, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(dev))
+            self._pending = (host, ev)
+            _PENDING.append(self)
+        elif validate:
+            self._raise_on(flags.tolist())
         self.desc = GraphDesc(N, E, self.G, self.recv.data_ptr(), self.send.data_ptr(), self.row_ptr.data_ptr(),
                               self.col_ptr.data_ptr(), self.col_edge.data_ptr(), self.node_ptr.data_ptr(),
                               self.node_graph.data_ptr())
+
+    @staticmethod
+    def _raise_on(f):
+        if f[1]:
+            raise _lib.EgnnError("edge_index holds a node id outside [0, num_nodes)")
+        if f[0]:
+            raise _lib.EgnnError(
+                "edge_index[0] must be non-decreasing (receiver-sorted), as every edge builder of the reference "
+                "produces; sort the columns by edge_index[0] first")
+
+    def check(self, wait=True):
+        """Raise if the deferred validation of this edge list failed (no-op once checked)."""
+        if self._pending is None:
+            return True
+        host, ev = self._pending
+        if not wait and not ev.query():
+            return False
+        ev.synchronize()
+        self._pending = None
+        self._raise_on(host.tolist())
+        return True
 
     def ref(self):
         return C.byref(self.desc)
@@ -122,9 +148,18 @@ class GraphIndex:
 
 _CACHE: dict = {}
 _CACHE_MAX = 16
+_PENDING: list = []  # GraphIndex objects whose deferred validation has not been read yet
 
 
-def graph_index_for(edge_index, num_nodes, batch=None, node_ptr=None):
+def check_pending(wait=True):
+    """Report deferred edge-list validation results; wait=False only looks at copies that have already landed."""
+    for gi in list(_PENDING):
+        if gi.check(wait=wait):
+            _PENDING.remove(gi)
+
+
+
+def graph_index_for(edge_index, num_nodes, batch=None, node_ptr=None, validate=True):
     """Cached GraphIndex keyed on the edge_index storage: generate() builds edge_index once per sample and calls the
     denoiser T+1 times with it (parts/train_per_iretation.py:308-364)."""
     bkey = None
@@ -138,7 +173,9 @@ def graph_index_for(edge_index, num_nodes, batch=None, node_ptr=None):
     if hit is not None and hit[0]() is edge_index:
         return hit[1]
     import weakref
-    gi = GraphIndex(edge_index, num_nodes, batch=batch, node_ptr=node_ptr)
+    if _PENDING:
+        check_pending(wait=False)
+    gi = GraphIndex(edge_index, num_nodes, batch=batch, node_ptr=node_ptr, validate=validate)
     if len(_CACHE) >= _CACHE_MAX:
         _CACHE.pop(next(iter(_CACHE)))
     try:

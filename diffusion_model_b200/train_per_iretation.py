@@ -19,6 +19,7 @@ import random
 import torch
 
 from . import _lib
+from .graph import check_pending, graph_index_for
 from ._lib import call, ptr, stream_ptr
 from .data import Data
 from .diffusion_x_h import _node_ptr_of, remove_mean  # noqa: F401  (re-exported like the reference module)
@@ -145,8 +146,11 @@ def batch_loss(egnn, batch_data, diffusion_process, params, t=None, noise_pos=No
     """One minibatch of train_epoch up to ``loss = loss / num_graph`` (:130-169).  Returns (loss, num_graph, aux)."""
     node_ptr, G = _graph_boundaries(batch_data, graph_index)
     d = _diffuse(batch_data, node_ptr, G, diffusion_process, t, noise_pos, noise_h, cond)
+    # edge-list validation is deferred to the next host sync (graph.check_pending): no pipeline stall per minibatch
+    gi = graph_index_for(batch_data.edge_index.to(d["z_x"].device), d["z_x"].shape[0], node_ptr=node_ptr,
+                         validate="deferred")
     h, x = egnn(batch_data.edge_index, d["h_in"], d["z_x"], node_ptr=node_ptr,
-                norm_scope=params.get("norm_scope", "call"))
+                norm_scope=params.get("norm_scope", "call"), graph=gi)
     A = params.get("atom_type_size", d["A"])
     loss = _EpsLoss.apply(x, h, d["z_x"], d["eps_x"], d["eps_h"], node_ptr, G, A)
     return loss, G, dict(d, h_out=h, x_out=x)
@@ -175,7 +179,9 @@ def _run_epoch(nn_dict, loader, params, diffusion_process, optimizer, train):
             with torch.no_grad():
                 loss, G, _ = batch_loss(egnn, data, diffusion_process, params, cond=cond)
         epoch_loss += loss.detach() * G  # (:178) summed squared error of the batch
-    return epoch_loss.item() / max(total_nodes, 1)  # per-node average (:181)
+    out = epoch_loss.item() / max(total_nodes, 1)  # per-node average (:181); the only host sync of the epoch
+    check_pending()
+    return out
 
 
 def train_epoch(nn_dict, train_loader, params, diffusion_process, optimizer):

@@ -265,3 +265,22 @@ def test_trajectory_matches_reference(lib, golden_dir):
         assert np.array_equal(out["atoms"][0].cpu().numpy(), zt["atoms"])
         for t, (zx, zh) in out["record"].items():
             assert relerr(zx, zt[f"zx_t{t}"]) < tol and relerr(zh, zt[f"zh_t{t}"]) < tol, t
+
+
+def test_deferred_edge_list_validation(lib):
+    """training loops validate the edge list without a host sync per minibatch; the error surfaces at check_pending()"""
+    from diffusion_model_b200 import EgnnError
+    from diffusion_model_b200.graph import GraphIndex, check_pending
+    good = torch.tensor([[0, 0, 1, 2], [1, 2, 0, 0]], device=DEV)
+    bad = torch.tensor([[1, 0, 2, 0], [0, 1, 0, 2]], device=DEV)   # receivers not sorted
+    oob = torch.tensor([[0, 0, 1, 2], [1, 7, 0, 0]], device=DEV)   # sender id out of range
+    GraphIndex(good, 3, validate="deferred")
+    check_pending()
+    for ei in (bad, oob):
+        gi = GraphIndex(ei, 3, validate="deferred")
+        with pytest.raises(EgnnError):
+            check_pending()
+        assert gi._pending is None
+    check_pending()  # nothing left behind
+    with pytest.raises(EgnnError):
+        GraphIndex(bad, 3)
