@@ -18,28 +18,40 @@ namespace {
 
 constexpr int TNB = 32;  // nodes per tile of the node backward kernel
 
+// one CTA per graph.  Whole-call scope: every CTA reduces its own graph's share of sum_i gx'_i . dxu_i, the last CTA to
+// finish (integer ticket, self-resetting) adds the per-graph shares in graph order -> same bits on every run.
 __global__ void __launch_bounds__(256) egcl_xupdate_bwd(const float* __restrict__ gx_out, const float* __restrict__ dxu,
                                                         const float* __restrict__ S, const int32_t* __restrict__ node_ptr,
                                                         int N, int scope, float* __restrict__ gdx,
-                                                        float* __restrict__ coefS) {
+                                                        float* __restrict__ coefS, float* __restrict__ dotp,
+                                                        unsigned int* __restrict__ ticket) {
     __shared__ float red[8];
-    const int g = blockIdx.x;
+    __shared__ bool is_last;
+    const int g = blockIdx.x, G = gridDim.x;
     const int a = node_ptr[g], b = node_ptr[g + 1];
-    const int lo = scope == EGNN_NORM_CALL ? 0 : a, hi = scope == EGNN_NORM_CALL ? N : b;
-    // four independent chains per thread (fixed order): the whole-call dot is latency-bound otherwise
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    int idx = 3 * lo + threadIdx.x;
-    for (; idx + 768 < 3 * hi; idx += 1024) {
-        s0 = fmaf(gx_out[idx], dxu[idx], s0);
-        s1 = fmaf(gx_out[idx + 256], dxu[idx + 256], s1);
-        s2 = fmaf(gx_out[idx + 512], dxu[idx + 512], s2);
-        s3 = fmaf(gx_out[idx + 768], dxu[idx + 768], s3);
-    }
-    for (; idx < 3 * hi; idx += 256) s0 = fmaf(gx_out[idx], dxu[idx], s0);
-    const float dot = block_sum_256((s0 + s1) + (s2 + s3), red);
+    float s = 0.f;
+    for (int idx = 3 * a + threadIdx.x; idx < 3 * b; idx += 256) s = fmaf(gx_out[idx], dxu[idx], s);
+    const float dot = block_sum_256(s, red);
     const float Sg = S[g], den = Sg + 1.f;
-    if (threadIdx.x == 0) coefS[g] = Sg > 0.f ? -dot / (den * den) / Sg : 0.f;
     for (int idx = 3 * a + threadIdx.x; idx < 3 * b; idx += 256) gdx[idx] = gx_out[idx] / den;
+    if (scope != EGNN_NORM_CALL) {
+        if (threadIdx.x == 0) coefS[g] = Sg > 0.f ? -dot / (den * den) / Sg : 0.f;
+        return;
+    }
+    if (threadIdx.x == 0) {
+        dotp[g] = dot;
+        __threadfence();
+        is_last = atomicAdd(ticket, 1u) == (unsigned)G - 1;
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    float t = 0.f;
+    for (int k = threadIdx.x; k < G; k += 256) t += __ldcg(dotp + k);
+    const float tot = block_sum_256(t, red);
+    const float c = Sg > 0.f ? -tot / (den * den) / Sg : 0.f;  // S is the same for every graph in this scope
+    for (int k = threadIdx.x; k < G; k += 256) coefS[k] = c;
+    if (threadIdx.x == 0) *ticket = 0u;
 }
 
 struct NodeBwdArgs {
@@ -402,7 +414,7 @@ namespace {
 constexpr int kNumSM = 148;  // B200
 
 struct BwdWs {
-    int64_t gdx, coefS, gM, gh_node, Gr, Gs, ghb, gxb, part, total;
+    int64_t gdx, coefS, dotp, gM, gh_node, Gr, Gs, ghb, gxb, part, total;
     int gridE, gridN, TEB;
 };
 inline int edge_tile_bwd(const egnn_net_t& n) {
@@ -422,6 +434,7 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     auto take = [&](int64_t cnt) { int64_t o = p; p += round_up64(cnt, 4); return o; };
     w.gdx = take(N * 3);
     w.coefS = take(G);
+    w.dotp = take(G + 4);  // per-graph shares of the whole-call dot, then the CTA ticket
     w.gM = take(N * n.Ms);
     w.gh_node = take(N * n.H);
     w.Gr = take(2 * E * W);  // two slabs: the tensor-core path writes one per branch
@@ -497,6 +510,7 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
     // rows actually used by this call's kernels (the workspace is sized for the larger of the two paths)
     const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : (int)std::min<int64_t>((E + bw.TEB - 1) / bw.TEB, kNumSM)) : 0;
     const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : (int)std::min<int64_t>((N + TNB - 1) / TNB, kNumSM);
+    EGNN_CUDA(cudaMemsetAsync(ws + bw.dotp + g->G, 0, 4 * sizeof(float), st));  // the ticket of egcl_xupdate_bwd
     for (int l = net->L - 1; l >= 0; --l) {
         const float* P = params + (size_t)l * lo.total;
         const float* Pk = packed + (size_t)l * po.total;
@@ -509,7 +523,8 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
 
         egcl_xupdate_bwd<<<g->G, 256, 0, st>>>(gxo, fwd_ws_ptr + fw.dxu + (size_t)l * N * 3,
                                                fwd_ws_ptr + fw.S + (size_t)l * g->G, g->node_ptr, N, norm_scope,
-                                               ws + bw.gdx, ws + bw.coefS);
+                                               ws + bw.gdx, ws + bw.coefS, ws + bw.dotp,
+                                               reinterpret_cast<unsigned int*>(ws + bw.dotp + g->G));
         EGNN_CHECK_LAUNCH("egcl_xupdate_bwd");
         // the tensor-core kernels overwrite exactly the entries the reduction reads; the FFMA kernels accumulate
         if (!use_tc) EGNN_CUDA(cudaMemsetAsync(ws + bw.part, 0, sizeof(float) * (size_t)(rowsE + rowsN) * lo.total, st));
