@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
     tc::fence_after_sync();
     const uint32_t tmem = *slot;
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-    if (tid == 0 && nit > 0) {
+    if (warp == NT / 32 - 1 && nit > 0 && tc::elect_one()) {
         tc_issue_op<NPASS>(tmem, 0, opU, opW1, 16, 2 * D, false);
         tc::mma_commit(&bars[0]);
     }
@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (warp == NT / 32 - 1 && tc::elect_one()) {
             tc::fence_after_sync();
             tc_issue_op<NPASS>(tmem, 3 * D, opA1, opW2x, D, D, false);
             tc::mma_commit(&bars[1]);
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (warp == NT / 32 - 1 && tc::elect_one()) {
             tc::fence_after_sync();
             tc_issue_op<NPASS>(tmem, 2 * D, opA1, opW2m, D, D, false);
             tc::mma_commit(&bars[2]);
@@ -709,7 +709,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
-    if (tid == 0 && nit > 0) {
+    if (warp == NT / 32 - 1 && nit > 0 && tc::elect_one()) {
         tc::fence_after_sync();
         const TcOperand opU0{sb + L::u0_hi, sb + L::u0_lo, TS, false};
         tc_issue_op<NPASS>(tmem, cA, opU0, opW1, 16, D, false);  // z1 of the first tile
@@ -746,7 +746,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (warp == NT / 32 - 1 && tc::elect_one()) {
             tc::fence_after_sync();
             tc_issue_op<NPASS>(tmem, cB, opA1, opW2, D, D, false);  // z2 = a1 . W2^T
             tc::mma_commit(&bars[1]);
@@ -839,7 +839,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (warp == NT / 32 - 1 && tc::elect_one()) {
             tc::fence_after_sync();
             tc_issue_op<NPASS>(tmem, cB, opG, opW2mn, D, D, false);  // ga1 = gz2 . W2
             tc::mma_commit(&bars[2]);
@@ -873,7 +873,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (warp == NT / 32 - 1 && tc::elect_one()) {
             tc::fence_after_sync();
             if (has_next) {  // next tile's z1 first: its epilogue overlaps the two narrow MMAs below
                 const TcOperand opUn{sb + (buf ? L::u0_hi : L::u1_hi), sb + (buf ? L::u0_lo : L::u1_lo), TS, false};

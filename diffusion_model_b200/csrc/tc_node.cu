@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
     const TcOperand opS{sb + L::s_hi, sb + L::s_lo, TS, false}, opSmn{sb + L::s_hi, sb + L::s_lo, TS, true};
     const TcOperand opGHmn{sb + L::gh_hi, sb + L::gh_lo, TS, true};
     bool ok = true;
-    if (tid == 0) {
+    if (warp == NT / 32 - 1 && tc::elect_one()) {
         tc_issue_op<NPASS>(tmem, cZ, opA, opW, KP, D, false);  // z1
         tc::mma_commit(&bars[0]);
     }
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
-    if (tid == 0) {
+    if (warp == NT / 32 - 1 && tc::elect_one()) {
         tc::fence_after_sync();
         tc_issue_op<NPASS>(tmem, cW2T, opSmn, opGHmn, 128, 16, false);  // dWh2^T [k][o] = s1^T . gh'
         tc::mma_commit(&bars[1]);
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
-    if (tid == 0) {
+    if (warp == NT / 32 - 1 && tc::elect_one()) {
         tc::fence_after_sync();
         tc_issue_op<NPASS>(tmem, cG, opS, opWmn, D, KP, false);      // g[h, M] = gz1 . Wh1
         tc_issue_op<NPASS>(tmem, cW1, opSmn, opAmn, 128, KP, false);  // [dWh1 | db1] = gz1^T . [h, M, 0.., 1]
