@@ -83,8 +83,9 @@ class GraphIndex:
         if node_ptr is not None:
             self.node_ptr = node_ptr.to(device=dev, dtype=I32).contiguous()
             self.G = self.node_ptr.numel() - 1
-            counts = (self.node_ptr[1:] - self.node_ptr[:-1]).to(torch.int64)
-            self.node_graph = torch.repeat_interleave(torch.arange(self.G, device=dev, dtype=I32), counts).contiguous()
+            # graph id of node i = number of boundaries <= i (no host sync, unlike repeat_interleave with device counts)
+            self.node_graph = torch.searchsorted(self.node_ptr[1:].contiguous(),
+                                                 torch.arange(N, device=dev, dtype=I32), right=True).to(I32).contiguous()
         elif batch is not None:
             batch = batch.to(device=dev, dtype=torch.int64).contiguous()
             self.G = int(batch[-1].item()) + 1 if N > 0 else 1
