@@ -284,3 +284,50 @@ def test_deferred_edge_list_validation(lib):
     check_pending()  # nothing left behind
     with pytest.raises(EgnnError):
         GraphIndex(bad, 3)
+
+
+def test_xonly_variant_against_oracle(lib, golden_dir):
+    """E3diffusion_new drop-in (train.py / test.py path): posterior mean in x_hat form, COM-free
+    noise, and one train.py-style step (loss + gradients) against the oracle restatement"""
+    from diffusion_model_b200.E3diffusion_new import E3DiffusionProcess, remove_mean
+    z = load(golden_dir, "diffusion_kat")
+    T = int(z["T"])
+    dp = E3DiffusionProcess(s=float(z["s"]), power=float(z["power"]), num_diffusion_timestep=T)
+    sch = D.Schedule(float(z["s"]), float(z["power"]), T)
+    zz, eps = torch.from_numpy(z["z"]), torch.from_numpy(z["eps"])
+    for t in (1000, 500, 1):
+        mu = dp.calculate_mu(zz.to(DEV), eps.to(DEV), t)
+        assert relerr(mu, z[f"t{t}_mu_xonly"]) <= 1e-6
+        torch.manual_seed(t)
+        nxt = dp.reverse_diffuse_one_step(mu, t)
+        step = (nxt - mu).cpu()
+        assert float(step.mean(dim=0).abs().max()) <= 1e-5 * max(1.0, float(step.abs().max()))  # COM-free noise
+    # one training step of train.py:238-288 on a 24-atom fully connected graph
+    zl = load(golden_dir, "loss_cfg1")
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    sd = state_dict_of(zl)
+    net = EquivariantGNN(**egnn_ref.net_sizes(4, 64))
+    net.load_state_dict(sd)
+    net = net.to(DEV)
+    n, t = 24, 400
+    gen = torch.Generator().manual_seed(5)
+    pos = D.remove_mean(torch.randn(n, 3, generator=gen) * 2)
+    onehot = torch.nn.functional.one_hot(torch.randint(0, 2, (n,), generator=gen), 2).float()
+    ei = torch.as_tensor(G.fc_edges(n))
+    torch.manual_seed(7)
+    pos_t, noise = dp.diffuse_zero_to_t(pos.to(DEV), t)
+    assert relerr(pos_t, sch.alpha[t] * pos + sch.sigma[t] * noise.cpu()) <= 1e-6
+    h = torch.cat((onehot.to(DEV), torch.full((n, 1), t / T, device=DEV)), dim=1)
+    _, x = net(ei.to(DEV), h, pos_t)
+    loss = ((remove_mean(x - pos_t) - noise) ** 2).sum()
+    loss.backward()
+    sdg = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    ref = LP.train_loss_xonly(lambda e, hh, xx: egnn_ref.egnn_forward(sdg, 4, e, hh, xx), sch, pos, onehot, ei, t,
+                              noise.cpu())
+    ref.backward()
+    assert abs(loss.item() - ref.item()) <= 2e-5 * abs(ref.item())
+    for k, p in net.named_parameters():
+        if sdg[k].grad is not None:
+            scale = max(float(sdg[k].grad.abs().max()), 1e-3 * max(float(v.grad.abs().max()) for v in sdg.values()
+                                                                   if v.grad is not None))
+            assert float((p.grad.cpu() - sdg[k].grad).abs().max()) <= 1e-3 * scale, k
