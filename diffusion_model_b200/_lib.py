@@ -49,6 +49,8 @@ SIGNATURES = {
     "egnn_cutoff_count": (C.c_int, [_P, _P, _P, _P, _F, _I32, _P, _P]),
     "egnn_cutoff_fill": (C.c_int, [_P, _P, _P, _P, _F, _I32, _P, _I64, _P, _P]),
     "egnn_exclusive_scan_i32": (C.c_int, [_P, _I32, _P, _P]),
+    "egnn_cutoff_fallback": (C.c_int, [_P, _P, _P, _F, _I32, _P, _P, _P]),
+    "egnn_cutoff_fallback_fill": (C.c_int, [_P, _P, _I32, _I64, _P, _P]),
     "egnn_graph_prepare": (C.c_int, [_P, _I32, _I64, _P, _P, _P, _P, _P, _P, _P, _P]),
     "egnn_node_ptr_from_batch": (C.c_int, [_P, _I32, _I32, _P, _P, _P]),
     "egnn_pack_weights": (C.c_int, [_NET, _P, _P, _P]),

@@ -181,6 +181,69 @@ __global__ void __launch_bounds__(256) batch_to_i32_kernel(const int64_t* __rest
 
 inline unsigned blocks_for(int64_t n, int per) { return (unsigned)((n + per - 1) / per > 0 ? (n + per - 1) / per : 1); }
 
+// Fallback of the reference's cutoff loop (something.ipynb:6340-6365): a graph with NO pair inside the cutoff gets the
+// single closest ordered pair (i, j) with r_c < dist < 100 -- the first strict minimum of the row-major scan.
+// One CTA per graph; runs between the count pass and the scan: bumps deg[i*] and records the pair.
+__global__ void __launch_bounds__(256) cutoff_fallback_kernel(const float* __restrict__ pos,
+                                                              const int32_t* __restrict__ node_ptr,
+                                                              const float* __restrict__ box, float r_c,
+                                                              int32_t* __restrict__ deg, int32_t* __restrict__ fb) {
+    __shared__ int s_any;
+    __shared__ float s_d[256];
+    __shared__ long long s_k[256];
+    const int g = blockIdx.x, tid = threadIdx.x;
+    const int a = node_ptr[g], b = node_ptr[g + 1], n = b - a;
+    if (tid == 0) s_any = 0;
+    __syncthreads();
+    int any = 0;
+    for (int i = a + tid; i < b; i += 256) any |= deg[i] != 0;
+    if (any) s_any = 1;
+    __syncthreads();
+    if (tid == 0) fb[2 * g] = fb[2 * g + 1] = -1;
+    if (s_any || n < 2) return;
+    const float* box3 = box ? box + 3 * g : nullptr;
+    float best = 100.f;  // the reference starts from min_norm = 100
+    long long bestk = -1;
+    for (long long k = tid; k < (long long)n * n; k += 256) {  // ascending k per thread: '<' keeps the first minimum
+        const int i = (int)(k / n), j = (int)(k % n);
+        if (i == j) continue;
+        const float d = pair_dist(pos, a + i, a + j, box3);
+        if (d < best && d > r_c) {
+            best = d;
+            bestk = k;
+        }
+    }
+    s_d[tid] = best;
+    s_k[tid] = bestk;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (tid < s) {
+            const float d2 = s_d[tid + s];
+            const long long k2 = s_k[tid + s];
+            if (k2 >= 0 && (s_k[tid] < 0 || d2 < s_d[tid] || (d2 == s_d[tid] && k2 < s_k[tid]))) {
+                s_d[tid] = d2;
+                s_k[tid] = k2;
+            }
+        }
+        __syncthreads();
+    }
+    if (tid == 0 && s_k[0] >= 0) {
+        const int i = a + (int)(s_k[0] / n), j = a + (int)(s_k[0] % n);
+        fb[2 * g] = i;
+        fb[2 * g + 1] = j;
+        deg[i] = 1;
+    }
+}
+
+__global__ void cutoff_fallback_fill_kernel(const int32_t* __restrict__ fb, const int32_t* __restrict__ row_ptr, int G,
+                                            int64_t E, int64_t* __restrict__ out) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G || fb[2 * g] < 0) return;
+    const int64_t e = row_ptr[fb[2 * g]];
+    out[e] = fb[2 * g];
+    out[E + e] = fb[2 * g + 1];
+}
+
 }  // namespace
 
 extern "C" int egnn_build_edges_fc(const int32_t* node_ptr, int32_t G, int32_t N, int64_t E, int64_t* edge_index_out,
@@ -189,6 +252,24 @@ extern "C" int egnn_build_edges_fc(const int32_t* node_ptr, int32_t G, int32_t N
     if (G == 0 || E == 0) return EGNN_OK;
     fc_edges_kernel<<<G, 256, 0, (cudaStream_t)stream>>>(node_ptr, G, E, edge_index_out);
     EGNN_CHECK_LAUNCH("fc_edges_kernel");
+    return EGNN_OK;
+}
+
+extern "C" int egnn_cutoff_fallback(const float* pos, const int32_t* node_ptr, const float* box, float r_c, int32_t G,
+                                    int32_t* deg, int32_t* fb_pairs, void* stream) {
+    EGNN_REQUIRE(pos && node_ptr && deg && fb_pairs, "egnn_cutoff_fallback: NULL pointer");
+    if (G <= 0) return EGNN_OK;
+    cutoff_fallback_kernel<<<G, 256, 0, (cudaStream_t)stream>>>(pos, node_ptr, box, r_c, deg, fb_pairs);
+    EGNN_CHECK_LAUNCH("cutoff_fallback_kernel");
+    return EGNN_OK;
+}
+
+extern "C" int egnn_cutoff_fallback_fill(const int32_t* fb_pairs, const int32_t* row_ptr, int32_t G, int64_t E,
+                                         int64_t* edge_index_out, void* stream) {
+    EGNN_REQUIRE(fb_pairs && row_ptr && (edge_index_out || E == 0), "egnn_cutoff_fallback_fill: NULL pointer");
+    if (G <= 0 || E <= 0) return EGNN_OK;
+    cutoff_fallback_fill_kernel<<<(G + 127) / 128, 128, 0, (cudaStream_t)stream>>>(fb_pairs, row_ptr, G, E, edge_index_out);
+    EGNN_CHECK_LAUNCH("cutoff_fallback_fill_kernel");
     return EGNN_OK;
 }
 

@@ -39,11 +39,12 @@ def build_edges_fc(sizes, device="cuda"):
     return out
 
 
-def build_edges_cutoff(pos, r_c, node_ptr=None, box=None, return_row_ptr=False):
+def build_edges_cutoff(pos, r_c, node_ptr=None, box=None, return_row_ptr=False, fallback=True):
     """Directed edges (i,j), i != j, dist < r_c, lexicographic; int64 [2,E].
 
     pos: fp32 [N,3] CUDA.  node_ptr: int [G+1] graph boundaries (default: one graph).  box: fp32 [G,3] orthorhombic
-    box lengths for periodic minimum image, or None for open boundaries.
+    box lengths for periodic minimum image, or None for open boundaries.  fallback: a graph with no pair inside the
+    cutoff gets its single closest ordered pair, like the reference's loop (something.ipynb:6346-6358).
     """
     pos = pos.contiguous()
     N = pos.shape[0]
@@ -52,8 +53,8 @@ def build_edges_cutoff(pos, r_c, node_ptr=None, box=None, return_row_ptr=False):
         node_ptr = torch.tensor([0, N], dtype=I32, device=dev)
     node_ptr = node_ptr.to(device=dev, dtype=I32).contiguous()
     G = node_ptr.numel() - 1
-    counts = (node_ptr[1:] - node_ptr[:-1]).to(torch.int64)
-    node_graph = torch.repeat_interleave(torch.arange(G, device=dev, dtype=I32), counts).contiguous()
+    node_graph = torch.searchsorted(node_ptr[1:].contiguous(), torch.arange(N, device=dev, dtype=I32),
+                                    right=True).to(I32).contiguous()
     if box is not None:
         box = box.to(device=dev, dtype=torch.float32).reshape(G, 3).contiguous()
     st = stream_ptr(dev)
@@ -61,11 +62,17 @@ def build_edges_cutoff(pos, r_c, node_ptr=None, box=None, return_row_ptr=False):
     row_ptr = torch.empty(N + 1, dtype=I32, device=dev)
     call("egnn_cutoff_count", ptr(pos, torch.float32), ptr(node_ptr), ptr(node_graph), ptr(box, allow_none=True),
          float(r_c), N, ptr(deg), st)
+    fb = None
+    if fallback:
+        fb = torch.empty((G, 2), dtype=I32, device=dev)
+        call("egnn_cutoff_fallback", ptr(pos), ptr(node_ptr), ptr(box, allow_none=True), float(r_c), G, ptr(deg), ptr(fb), st)
     call("egnn_exclusive_scan_i32", ptr(deg), N, ptr(row_ptr), st)
     E = int(row_ptr[-1].item())
     out = torch.empty((2, E), dtype=torch.int64, device=dev)
     call("egnn_cutoff_fill", ptr(pos), ptr(node_ptr), ptr(node_graph), ptr(box, allow_none=True), float(r_c), N,
          ptr(row_ptr), E, ptr(out), st)
+    if fallback:
+        call("egnn_cutoff_fallback_fill", ptr(fb), ptr(row_ptr), G, E, ptr(out), st)
     return (out, row_ptr) if return_row_ptr else out
 
 

@@ -107,6 +107,14 @@ int egnn_cutoff_count(const float* pos, const int32_t* node_ptr, const int32_t* 
 int egnn_cutoff_fill(const float* pos, const int32_t* node_ptr, const int32_t* node_graph, const float* box,
                      float r_c, int32_t N, const int32_t* row_ptr, int64_t E, int64_t* edge_index_out, void* stream);
 int egnn_exclusive_scan_i32(const int32_t* in, int32_t n, int32_t* out /* [n+1] */, void* stream);
+/* fallback of the same loop (something.ipynb:6346-6358): a graph with no pair inside the cutoff gets the single closest
+ * ordered pair with r_c < dist < 100 (first strict minimum of the row-major scan).  Call egnn_cutoff_fallback between
+ * the count pass and the scan (it sets deg[i*] = 1 and records fb_pairs int32 [G][2], -1 when unused), and
+ * egnn_cutoff_fallback_fill after egnn_cutoff_fill. */
+int egnn_cutoff_fallback(const float* pos, const int32_t* node_ptr, const float* box, float r_c, int32_t G,
+                         int32_t* deg, int32_t* fb_pairs, void* stream);
+int egnn_cutoff_fallback_fill(const int32_t* fb_pairs, const int32_t* row_ptr, int32_t G, int64_t E,
+                              int64_t* edge_index_out, void* stream);
 
 /* derived structures from a reference-layout edge_index (int64 [2,E]).  Requires edge_index[0] non-decreasing
  * (every builder of the reference produces that); flags_out[0] is set to 1 on the device if it is not, flags_out[1]

@@ -331,3 +331,34 @@ def test_xonly_variant_against_oracle(lib, golden_dir):
             scale = max(float(sdg[k].grad.abs().max()), 1e-3 * max(float(v.grad.abs().max()) for v in sdg.values()
                                                                    if v.grad is not None))
             assert float((p.grad.cpu() - sdg[k].grad).abs().max()) <= 1e-3 * scale, k
+
+
+def test_cutoff_fallback_closest_pair(lib):
+    """graphs with no pair inside the cutoff get the reference loop's closest ordered pair (something.ipynb:6346-6358):
+    first strict minimum in row-major order, ties and pairs exactly at the cutoff included; batched with normal graphs"""
+    from diffusion_model_b200.graph import build_edges_cutoff
+    rng = np.random.default_rng(11)
+    graphs = [
+        rng.normal(size=(12, 3)).astype(np.float32) * 1.0,                      # normal graph with edges
+        (rng.normal(size=(9, 3)) * 40).astype(np.float32),                      # sparse: no pair inside 2.0
+        np.array([[0, 0, 0], [3, 0, 0], [0, 3, 0], [-3, 0, 0]], np.float32),    # tie: several pairs at distance 3
+        np.array([[0, 0, 0], [2, 0, 0], [7, 0, 0]], np.float32),                # a pair exactly AT the cutoff is skipped
+        np.array([[0, 0, 0], [500, 0, 0]], np.float32),                         # nothing below 100: stays empty
+        np.array([[1, 2, 3]], np.float32),                                      # single atom
+        rng.normal(size=(6, 3)).astype(np.float32) * 0.5,
+    ]
+    ptr_ = np.concatenate([[0], np.cumsum([len(g) for g in graphs])]).astype(np.int32)
+    want = np.concatenate([G.cutoff_edges(g, 2.0, None, offset=int(o)) for g, o in zip(graphs, ptr_[:-1])], axis=1)
+    pos = torch.from_numpy(np.concatenate(graphs)).to(DEV)
+    got = build_edges_cutoff(pos, 2.0, node_ptr=torch.from_numpy(ptr_))
+    assert np.array_equal(got.cpu().numpy(), want)
+    assert want.shape[1] > 0 and np.array_equal(want[:, (want[0] >= 12) & (want[0] < 21)].shape, (2, 1))
+    plain = build_edges_cutoff(pos, 2.0, node_ptr=torch.from_numpy(ptr_), fallback=False)
+    nofb = np.concatenate([G.cutoff_edges(g, 2.0, None, offset=int(o), fallback=False) for g, o in zip(graphs, ptr_[:-1])], axis=1)
+    assert np.array_equal(plain.cpu().numpy(), nofb)
+    # periodic: minimum-image distances decide the fallback pair too
+    box = np.array([[30.0, 30.0, 30.0]], np.float32)
+    p = np.array([[1, 1, 1], [28, 1, 1], [15, 15, 15]], np.float32)   # atoms 0 and 1 are 3 apart through the boundary
+    got = build_edges_cutoff(torch.from_numpy(p).to(DEV), 2.0, node_ptr=torch.tensor([0, 3]), box=torch.from_numpy(box))
+    assert np.array_equal(got.cpu().numpy(), G.cutoff_edges(p, 2.0, box[0]))
+    assert got.cpu().tolist() == [[0], [1]]
