@@ -128,24 +128,24 @@ __global__ void __launch_bounds__(256) egcl_node_bwd(NodeBwdArgs a) {
     }
 }
 
-// grad[p] = sum of the partial rows that hold parameter p, in row order.  branch_rows: the tensor-core edge backward
-// gives even rows to the mlp_m + attention parameters and odd rows to the mlp_x parameters (other entries of a row are
-// never written, so they must not be read); otherwise every edge row holds every edge parameter.
+// grad[p] = sum of the partial rows that hold parameter p, in row order.  rows_m > 0: the tensor-core edge backward
+// gives rows [0, rows_m) to the mlp_m + attention parameters and rows [rows_m, rowsE) to the mlp_x parameters (other
+// entries of a row are never written, so they must not be read); otherwise every edge row holds every edge parameter.
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ part, int rowsE, int rowsN, int n,
-                                                              int x_begin, int h_begin, int h_end, int branch_rows,
+                                                              int x_begin, int h_begin, int h_end, int rows_m,
                                                               float* __restrict__ out) {
     const int p = blockIdx.x * 256 + threadIdx.x;
     if (p >= n) return;
-    int r0 = 0, r1 = rowsE, step = 1;
+    int r0 = 0, r1 = rowsE;
     if (p >= h_begin && p < h_end) {
         r0 = rowsE;
         r1 = rowsE + rowsN;
-    } else if (branch_rows) {
-        step = 2;
-        r0 = (p >= x_begin && p < h_begin) ? 1 : 0;
+    } else if (rows_m > 0) {
+        if (p >= x_begin && p < h_begin) r0 = rows_m;
+        else r1 = rows_m;
     }
     float s = 0.f;
-    for (int r = r0; r < r1; r += step) s += part[(size_t)r * n + p];
+    for (int r = r0; r < r1; ++r) s += part[(size_t)r * n + p];
     out[p] = s;
 }
 
@@ -401,6 +401,7 @@ size_t egnn_edge_fwd_smem(const egnn_net_t& net, int TE);
 int egnn_validate_net(const egnn_net_t* net);
 int egnn_validate_graph(const egnn_graph_t* g, bool need_sender_csr);
 int egnn_tc_bwd_grid(int64_t E);
+void egnn_tc_bwd_split(int64_t E, int* nM, int* nX);
 int egnn_tc_node_bwd_grid(int64_t N);
 int egnn_tc_node_backward(const egnn_net_t& net, int N, const float* params_layer, const float* packed_layer, const float* h,
                           const float* msum, const float* gh_out, float* gh_node, float* gM, float* part, int precision,
@@ -511,6 +512,11 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
     const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : (int)std::min<int64_t>((E + bw.TEB - 1) / bw.TEB, kNumSM)) : 0;
     const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : (int)std::min<int64_t>((N + TNB - 1) / TNB, kNumSM);
     EGNN_CUDA(cudaMemsetAsync(ws + bw.dotp + g->G, 0, 4 * sizeof(float), st));  // the ticket of egcl_xupdate_bwd
+    int rows_m = 0;
+    if (use_tc && E > 0) {
+        int nX;
+        egnn_tc_bwd_split(E, &rows_m, &nX);
+    }
     for (int l = net->L - 1; l >= 0; --l) {
         const float* P = params + (size_t)l * lo.total;
         const float* Pk = packed + (size_t)l * po.total;
@@ -570,7 +576,7 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
             EGNN_CHECK_LAUNCH("egcl_gather_bwd");
         }
         reduce_partials_kernel<<<(lo.total + 255) / 256, 256, 0, st>>>(ws + bw.part, rowsE, rowsN, lo.total, lo.wx1, lo.wh1,
-                                                                      lo.wa, use_tc ? 1 : 0,
+                                                                      lo.wa, rows_m,
                                                                       grad_params + (size_t)l * lo.total);
         EGNN_CHECK_LAUNCH("reduce_partials_kernel");
     }

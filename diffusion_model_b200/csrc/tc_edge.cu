@@ -1,6 +1,8 @@
 // tcgen05 (5th-generation tensor core) path of the edge MLPs: operands staged in shared memory as bf16 hi/lo splits,
 // fp32 accumulators in TMEM, SiLU epilogues out of TMEM.  This file also holds the one-tile GEMM self-test that pins
 // the shared-memory descriptor conventions on real hardware (tests/test_gpu_tc.py).
+#include <cstdlib>
+
 #include "tc_tile.cuh"
 
 namespace {
@@ -506,7 +508,7 @@ int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const flo
 }
 
 // =====================================================================================================================
-// Fused EGCL edge kernel on tcgen05 (backward).  Each CTA owns ONE branch (blockIdx.x & 1: 0 = mlp_m + gate,
+// Fused EGCL edge kernel on tcgen05 (backward).  Each CTA owns ONE branch (blockIdx.x < nM: 0 = mlp_m + gate,
 // 1 = mlp_x) and walks its 128-edge tiles with 4*D threads (thread = edge row x 32-column group); per tile
 //   recompute   z1 = U.W1^T (block A),  a1 = SiLU(z1+b1) -> tile A1,  z2 = a1.W2^T (block B)
 //   upstream    gz2 = dL/dz2 -> tile G            (gate / phi algebra of SURVEY.md Appendix A on the CUDA cores)
@@ -551,7 +553,8 @@ struct TcBwdArgs {
     const uint8_t* blob;
     const float *gM, *gdx, *coefS;
     float *Gr, *Gs;  // [2][E][H+3]: branch-major; the gather kernel adds both branches
-    float* part;     // [gridDim.x][layer param count], zero-initialised
+    float* part;     // [gridDim.x][layer param count]
+    int nM;          // CTAs [0, nM) take the message branch, [nM, gridDim.x) the coordinate branch
 };
 
 struct TcEdgeRow {  // one gathered edge held in registers between its global loads and its shared-memory stores
@@ -575,7 +578,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     const int q = warp & 3, cg = warp >> 2;
     const int r = q * 32 + lane;  // edge row == TMEM lane
     const int c0 = cg * 32;       // this thread's 32 columns
-    const int branch = blockIdx.x & 1;
+    const int branch = (int)blockIdx.x < a.nM ? 0 : 1;
     const int H = a.net.H, K0 = 2 * H + 1, W = H + 3;
     float* vec = reinterpret_cast<float*>(smem + L::vec);
     int* sI = reinterpret_cast<int*>(smem + L::sI);
@@ -666,8 +669,8 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         }
     };
 
-    const int tstride = gridDim.x >> 1;
-    const int tile0 = blockIdx.x >> 1;
+    const int tstride = branch ? (int)gridDim.x - a.nM : a.nM;
+    const int tile0 = branch ? (int)blockIdx.x - a.nM : (int)blockIdx.x;
     const int nit = tile0 < a.tiles ? (a.tiles - tile0 + tstride - 1) / tstride : 0;
     auto edge_outputs = [&](int e0p, int nrowsp, int bufp, float phi) {  // cg == 0 warps: this branch's per-edge outputs
         float gu[32];
@@ -965,11 +968,29 @@ int launch_tc_bwd(const TcBwdArgs& a, int grid, cudaStream_t st) {
 
 }  // namespace
 
-// number of CTAs (= private partial rows) the tensor-core edge backward uses for E edges: even, <= 148, <= 2 * tiles
-int egnn_tc_bwd_grid(int64_t E) {
+// CTAs (= private partial rows) of the tensor-core edge backward for E edges: nM message-branch CTAs followed by nX
+// coordinate-branch CTAs, nM + nX <= 148, each <= tiles.  The message branch does more CUDA-core work per tile (gate,
+// two row dots, the gM gather) but the coordinate branch writes more per edge; measured on B200 the even split is best
+// (EGNN_TC_BWD_MSHARE percent, default 50; 46 and 54 are 1-8 % slower at cfg2).
+void egnn_tc_bwd_split(int64_t E, int* nM, int* nX) {
     const int64_t tiles = (E + 127) / 128;
-    const int64_t g = 2 * tiles < 148 ? 2 * tiles : 148;
-    return (int)g;
+    if (2 * tiles <= 148) {
+        *nM = *nX = (int)tiles;
+        return;
+    }
+    static int share = -1;
+    if (share < 0) {
+        const char* env = getenv("EGNN_TC_BWD_MSHARE");
+        share = env ? atoi(env) : 50;
+        if (share < 10 || share > 90) share = 50;
+    }
+    *nM = (148 * share + 50) / 100;
+    *nX = 148 - *nM;
+}
+int egnn_tc_bwd_grid(int64_t E) {
+    int nM, nX;
+    egnn_tc_bwd_split(E, &nM, &nX);
+    return nM + nX;
 }
 
 // edge phase of one layer's backward on the tensor cores.  Gr / Gs hold [2][E][H+3] (one slab per branch).
@@ -980,8 +1001,10 @@ int egnn_tc_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const fl
                  "use precision fp32", net.Mh, net.Ms, net.Xh, net.H);
     const PackOff po = pack_off(net);
     TcBwdArgs a{net, g.N, g.E, (g.E + 127) / 128, g.recv, g.send, g.node_graph, h, x,
-                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), gM, gdx, coefS, Gr, Gs, part};
-    const int grid = egnn_tc_bwd_grid(g.E);
+                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), gM, gdx, coefS, Gr, Gs, part, 0};
+    int nX;
+    egnn_tc_bwd_split(g.E, &a.nM, &nX);
+    const int grid = a.nM + nX;
     const bool x3 = precision == EGNN_PREC_BF16X3;
     if (net.Mh == 128) return x3 ? launch_tc_bwd<128, 3>(a, grid, st) : launch_tc_bwd<128, 1>(a, grid, st);
     return x3 ? launch_tc_bwd<64, 3>(a, grid, st) : launch_tc_bwd<64, 1>(a, grid, st);
