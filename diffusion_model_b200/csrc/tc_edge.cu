@@ -555,6 +555,7 @@ struct TcBwdArgs {
     float *Gr, *Gs;  // [2][E][H+3]: branch-major; the gather kernel adds both branches
     float* part;     // [gridDim.x][layer param count]
     int nM;          // CTAs [0, nM) take the message branch, [nM, gridDim.x) the coordinate branch
+    int g_lo;        // bit 0 / bit 1: the gradient tile gz2 / gz1 is stored as bf16 hi + lo (else hi only: 2 products per MMA)
 };
 
 struct TcEdgeRow {  // one gathered edge held in registers between its global loads and its shared-memory stores
@@ -568,6 +569,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     using L = TcBwdLayout<D>;
     constexpr bool FAST = NPASS == 1;
     constexpr bool LO = NPASS == 3;
+    const bool GLO2 = LO && (a.g_lo & 1), GLO1 = LO && (a.g_lo & 2);  // lo halves of the gz2 / gz1 tiles
     constexpr int NT = L::NT, NG = L::NG;
     // TMEM columns: z1 -> SiLU'(z1),  z2 | ga1,  db2 (even tiles),  dW2,  db2 (odd tiles),  dW1 + db1,  gu
     constexpr int cA = 0, cB = D, cBias0 = 2 * D, cW2 = 2 * D + 16, cBias1 = 3 * D + 16, cP1 = 3 * D + 32,
@@ -803,7 +805,8 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
                 }
                 rowA[cg * 128 + r] = sdot;
                 rowB[cg * 128 + r] = tdot;
-                __syncthreads();
+                // only the NG warps that share this row quadrant exchange partial dots: named barrier 1 + q
+                asm volatile("bar.sync %0, %1;" ::"r"(1 + q), "r"(NG * 32) : "memory");
                 float ssum = vec[3 * D], tsum = 0.f;
 #pragma unroll
                 for (int k = 0; k < NG; ++k) {
@@ -836,7 +839,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
                     cs[c] = c_row * (z[c] * sg[c]);
                 }
             }
-            tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, gz, LO);
+            tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, gz, GLO2);
             accs += c_row;
         }
         tc::fence_async_smem();
@@ -844,11 +847,11 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         __syncthreads();
         if (warp == NT / 32 - 1 && tc::elect_one()) {
             tc::fence_after_sync();
-            tc_issue_op<NPASS>(tmem, cB, opG, opW2mn, D, D, false);  // ga1 = gz2 . W2
+            tc_issue_op<NPASS>(tmem, cB, opG, opW2mn, D, D, false, GLO2);  // ga1 = gz2 . W2
             tc::mma_commit(&bars[2]);
             // [db2 | dW2] += gz2^T . [u | a1] (even tiles) or [dW2 | db2] += gz2^T . [a1 | u] (odd tiles)
             const TcOperand opB{sb + (buf ? L::a1_hi : L::u0_hi), sb + (buf ? L::a1_lo : L::u0_lo), TS, true};
-            tc_issue_op<NPASS>(tmem, buf ? cW2 : cBias0, opGmn, opB, 128, D + 16, true);
+            tc_issue_op<NPASS>(tmem, buf ? cW2 : cBias0, opGmn, opB, 128, D + 16, true, GLO2);
             tc::mma_commit(&bars[3]);
         }
         // ---- in the shadow of dgrad: column sums for d wa / d wx3; phi_e of this tile for its deferred outputs
@@ -871,7 +874,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             for (int i = 0; i < 32; ++i) ga[i] *= d1[i];
             ok = tc::mbar_wait(&bars[3], phase) && ok;
             tc::fence_after_sync();
-            tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, ga, LO);
+            tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, ga, GLO1);
         }
         tc::fence_async_smem();
         tc::fence_before_sync();
@@ -883,9 +886,9 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
                 tc_issue_op<NPASS>(tmem, cA, opUn, opW1, 16, D, false);
                 tc::mma_commit(&bars[0]);
             }
-            tc_issue_op<NPASS>(tmem, cGU, opG, opW1mn, D, 16, false);  // gu = gz1 . W1   (16 columns)
+            tc_issue_op<NPASS>(tmem, cGU, opG, opW1mn, D, 16, false, GLO1);  // gu = gz1 . W1   (16 columns)
             tc::mma_commit(&bars[4]);
-            tc_issue_op<NPASS>(tmem, cP1, opGmn, opUmn, 128, 16, true);  // [dW1 | db1] += gz1^T . u
+            tc_issue_op<NPASS>(tmem, cP1, opGmn, opUmn, 128, 16, true, GLO1);  // [dW1 | db1] += gz1^T . u
             tc::mma_commit(&bars[5]);
         }
     }
@@ -1001,7 +1004,15 @@ int egnn_tc_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const fl
                  "use precision fp32", net.Mh, net.Ms, net.Xh, net.H);
     const PackOff po = pack_off(net);
     TcBwdArgs a{net, g.N, g.E, (g.E + 127) / 128, g.recv, g.send, g.node_graph, h, x,
-                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), gM, gdx, coefS, Gr, Gs, part, 0};
+                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), gM, gdx, coefS, Gr, Gs, part, 0, 3};
+    {
+        static int glo = -1;
+        if (glo < 0) {
+            const char* env = getenv("EGNN_TC_BWD_GLO");
+            glo = env ? atoi(env) & 3 : 3;
+        }
+        a.g_lo = glo;
+    }
     int nX;
     egnn_tc_bwd_split(g.E, &a.nM, &nX);
     const int grid = a.nM + nX;

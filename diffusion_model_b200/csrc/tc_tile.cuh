@@ -50,13 +50,15 @@ __device__ __forceinline__ uint64_t tc_op_desc(const TcOperand& o, bool use_lo, 
 // one thread: D[128 x N] (+)= A . B^T over K, NPASS split products, into TMEM column dcol.
 // The descriptor of k-step s is the descriptor of step 0 plus s * (step bytes >> 4) in the 14-bit address field (shared
 // memory is < 256 KB, so the field never carries): two integer adds per MMA instead of a rebuilt descriptor.
+// a_has_lo = false: the A tile was stored as bf16 hi only (its lo.hi product is skipped)
 template <int NPASS>
 __device__ __forceinline__ void tc_issue_op(uint32_t tmem, int dcol, const TcOperand& A, const TcOperand& B, int K, int N,
-                                            bool acc) {
+                                            bool acc, bool a_has_lo = true) {
     const uint32_t idesc = tc::make_idesc_bf16(128, N) | (A.mn ? 1u << 15 : 0u) | (B.mn ? 1u << 16 : 0u);
     const uint64_t astep = (A.mn ? 256u : 2u * A.chunk_stride) >> 4, bstep = (B.mn ? 256u : 2u * B.chunk_stride) >> 4;
 #pragma unroll
     for (int p = 0; p < NPASS; ++p) {
+        if (p == 1 && !a_has_lo) continue;
         uint64_t ad = tc_op_desc(A, p == 1, 0), bd = tc_op_desc(B, p == 2, 0);
 #pragma unroll 8
         for (int s = 0; s < K / 16; ++s) {
