@@ -231,7 +231,7 @@ struct TcFwdArgs {
 template <int D, int NPASS>
 __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
     using L = TcLayout<D>;
-    constexpr bool FAST = NPASS == 1;
+    constexpr bool FAST = true;  // one-MUFU SiLU / sigmoid (tanh.approx) in both tensor-core modes, see tc_tile.cuh
     constexpr bool LO = NPASS == 3;
     constexpr int NT = 4 * D, NG = D / 32;
     constexpr int TS = 32;  // edges per segment == partial-buffer granularity (part_tile_for)
@@ -367,11 +367,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
         tc::fence_after_sync();
         if (tid < 128 && has_next) gather_nodes(gnext);                     // stage 2: lands during the epilogue below
         // ---- layer-1 epilogue of the coordinate branch -> A1; the U tile is free again: store the next tile's rows
-        {
-            uint32_t hi[16], lo[16];
-            tc_epi32<FAST>(trow + D + c0, vec + D + c0, hi, lo);
-            tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, hi, lo, LO);
-        }
+        tc_epi_store_chunked<FAST>(trow + D + c0, vec + D + c0, smem + L::a1_hi, smem + L::a1_lo, r, c0, LO);
         if (tid < 128 && has_next) dst_next = store_u(tile + gridDim.x, gnext);  // stage 3
         tc::fence_async_smem();
         tc::fence_before_sync();
@@ -567,7 +563,7 @@ struct TcEdgeRow {  // one gathered edge held in registers between its global lo
 template <int D, int NPASS>
 __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     using L = TcBwdLayout<D>;
-    constexpr bool FAST = NPASS == 1;
+    constexpr bool FAST = true;  // one-MUFU SiLU / sigmoid (tanh.approx) in both tensor-core modes, see tc_tile.cuh
     constexpr bool LO = NPASS == 3;
     const bool GLO2 = LO && (a.g_lo & 1), GLO1 = LO && (a.g_lo & 2);  // lo halves of the gz2 / gz1 tiles
     constexpr int NT = L::NT, NG = L::NG;

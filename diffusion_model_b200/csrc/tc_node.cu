@@ -37,7 +37,7 @@ struct TcNodeBwdArgs {
 template <int D, int NPASS>
 __global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
     using L = TcNodeLayout<D>;
-    constexpr bool FAST = NPASS == 1;
+    constexpr bool FAST = true;  // one-MUFU SiLU / sigmoid (tanh.approx) in both tensor-core modes, see tc_tile.cuh
     constexpr bool LO = NPASS == 3;
     constexpr int NT = L::NT, NG = L::NG, KP = L::KP;
     constexpr int cZ = 0, cG = D, cW1 = 2 * D + 32, cW2T = 3 * D + 48;  // TMEM columns (512 allocated)
