@@ -736,10 +736,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             tc::tmem_ld32(trow + cA + c0, v);
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-                const float zz = v[i] + b1[c0 + i];
-                const float s = tc_sigmoid<FAST>(zz);
-                act[i] = zz * s;
-                v[i] = s * fmaf(zz, 1.f - s, 1.f);
+                tc_silu_and_grad(v[i] + b1[c0 + i], act[i], v[i]);
             }
             tc_split_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, act, LO);
             tc::tmem_st32(trow + cA + c0, v);
@@ -764,18 +761,15 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         if (it > 0) ok = tc::mbar_wait(&bars[5], phase ^ 1) && ok;  // previous tile's dW1 MMA is done with U[buf^1] and tile G
         tc::fence_after_sync();
         if (tid < 128 && has_next) gather_store(buf ^ 1, gnext);
-        // ---- upstream gradient of z2: z, sigmoid(z) of this thread's 32 columns in registers
+        // ---- upstream gradient of z2: out = SiLU(z2 + b2) and SiLU' of this thread's 32 columns
         float cs[32];  // coef_e * out_e[c]: column sums taken after the MMAs below have been issued
         {
-            float z[32], sg[32];
+            float m[32], d2[32];
             {
                 float v[32];
                 tc::tmem_ld32(trow + cB + c0, v);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    z[i] = v[i] + b2[c0 + i];
-                    sg[i] = tc_sigmoid<FAST>(z[i]);
-                }
+                for (int i = 0; i < 32; ++i) tc_silu_and_grad(v[i] + b2[c0 + i], m[i], d2[i]);
             }
             const float4 rr = sR[buf * 128 + r];
             const int i = sI[buf * 128 + r];
@@ -788,16 +782,14 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
 #pragma unroll
                 for (int c4 = 0; c4 < 8; ++c4) {
                     const float4 gm = __ldg(gMi + c4);
-                    const float m0 = z[4 * c4] * sg[4 * c4], m1 = z[4 * c4 + 1] * sg[4 * c4 + 1];
-                    const float m2 = z[4 * c4 + 2] * sg[4 * c4 + 2], m3 = z[4 * c4 + 3] * sg[4 * c4 + 3];
-                    sdot = fmaf(wvh[4 * c4], m0, sdot);
-                    sdot = fmaf(wvh[4 * c4 + 1], m1, sdot);
-                    sdot = fmaf(wvh[4 * c4 + 2], m2, sdot);
-                    sdot = fmaf(wvh[4 * c4 + 3], m3, sdot);
-                    tdot = fmaf(gm.x, m0, tdot);
-                    tdot = fmaf(gm.y, m1, tdot);
-                    tdot = fmaf(gm.z, m2, tdot);
-                    tdot = fmaf(gm.w, m3, tdot);
+                    sdot = fmaf(wvh[4 * c4], m[4 * c4], sdot);
+                    sdot = fmaf(wvh[4 * c4 + 1], m[4 * c4 + 1], sdot);
+                    sdot = fmaf(wvh[4 * c4 + 2], m[4 * c4 + 2], sdot);
+                    sdot = fmaf(wvh[4 * c4 + 3], m[4 * c4 + 3], sdot);
+                    tdot = fmaf(gm.x, m[4 * c4], tdot);
+                    tdot = fmaf(gm.y, m[4 * c4 + 1], tdot);
+                    tdot = fmaf(gm.z, m[4 * c4 + 2], tdot);
+                    tdot = fmaf(gm.w, m[4 * c4 + 3], tdot);
                 }
                 rowA[cg * 128 + r] = sdot;
                 rowB[cg * 128 + r] = tdot;
@@ -816,7 +808,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
                 // phi = wx3.q + bx3 (needed for the coordinate output);  c_row = gphi = gdx[i].r
                 float pdot = 0.f;
 #pragma unroll
-                for (int c = 0; c < 32; ++c) pdot = fmaf(wvh[c], z[c] * sg[c], pdot);
+                for (int c = 0; c < 32; ++c) pdot = fmaf(wvh[c], m[c], pdot);
                 rowA[cg * 128 + r] = pdot;
                 const float* gd = a.gdx + (size_t)i * 3;
                 c_row = rr.w * (gd[0] * rr.x + gd[1] * rr.y + gd[2] * rr.z);
@@ -830,9 +822,8 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const int c = 4 * c4 + k;
-                    const float d2 = sg[c] * fmaf(z[c], 1.f - sg[c], 1.f);
-                    gz[c] = fmaf(c_g, gmv[k], c_row * wvh[c]) * d2;
-                    cs[c] = c_row * (z[c] * sg[c]);
+                    gz[c] = fmaf(c_g, gmv[k], c_row * wvh[c]) * d2[c];
+                    cs[c] = c_row * m[c];
                 }
             }
             tc_split_store32(smem + L::g_hi, smem + L::g_lo, r, c0, gz, GLO2);

@@ -139,14 +139,13 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
         for (int k = 0; k < 8; ++k) gh[k] = sGH[r * 8 + k];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-            const float zz = v[i] + vec[c0 + i];
-            const float s = tc_sigmoid<FAST>(zz);
-            act[i] = zz * s;
+            float dact;
+            tc_silu_and_grad(v[i] + vec[c0 + i], act[i], dact);
             float t = 0.f;
 #pragma unroll
             for (int o = 0; o < 8; ++o)
                 if (o < H) t = fmaf(gh[o], vec[D + o * D + c0 + i], t);
-            gz[i] = t * s * fmaf(zz, 1.f - s, 1.f);
+            gz[i] = t * dact;
         }
         tc_split_store32(smem + L::s_hi, smem + L::s_lo, r, c0, act, LO);
     }
