@@ -10,12 +10,29 @@ The reference is single-process (main.py:125); nothing here replaces reference c
 """
 from __future__ import annotations
 
+import contextlib
 import os
+import sys
 
 import torch
 import torch.distributed as dist
 
 from .optim import flat_grad_of, scatter_flat_grad
+
+
+@contextlib.contextmanager
+def _stdout_to_stderr():
+    """NCCL prints its version banner on file descriptor 1 when the first communicator is created; programs whose
+    stdout is a machine-readable result line (bench.py) create the communicator inside this redirect."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        yield
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(saved)
 
 
 def init_from_env(backend=None):
@@ -30,7 +47,14 @@ def init_from_env(backend=None):
             backend = "nccl" if torch.cuda.is_available() else "gloo"
         if backend == "nccl":
             torch.cuda.set_device(local)
-        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+            with _stdout_to_stderr():
+                dist.init_process_group(backend=backend, rank=rank, world_size=world,
+                                        device_id=torch.device("cuda", local))
+                warm = torch.zeros(1, device=torch.device("cuda", local))
+                dist.all_reduce(warm)  # creates the communicator now (banner, topology search) rather than in a timed step
+                torch.cuda.synchronize()
+        else:
+            dist.init_process_group(backend=backend, rank=rank, world_size=world)
     return rank, world, local
 
 
