@@ -65,13 +65,25 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
         for (int b = 0; b < 3; ++b) tc::mbar_init(&bars[b], 1);
         tc::fence_mbar_init();
     }
+    // ---- the tile's message sums are one contiguous [rows x D] block: coalesced copy into shared memory (the S tile
+    //      region, free until GEMM1 is done), column index XOR-swizzled so that the per-row reads below are conflict-free
+    float* stageF = reinterpret_cast<float*>(smem + L::s_hi);
+    {
+        const int n0 = blockIdx.x * 128, rows = min(128, a.N - n0);
+        const float* src = a.msum + (size_t)n0 * D;
+        for (int idx = tid; idx < rows * D; idx += NT) {
+            const int rr = idx / D, m = idx % D;
+            stageF[rr * D + (m ^ (rr & 31))] = __ldg(src + idx);
+        }
+    }
+    __syncthreads();
     // ---- A tile = [h | M | 0 .. | 1] of this thread's row, 32 columns (+ the 16 trailing columns by column group 0)
     {
         float v[32];
 #pragma unroll
         for (int k = 0; k < 32; ++k) {
             const int c = c0 + k;
-            v[k] = !valid ? 0.f : (c < H ? a.h[(size_t)n * H + c] : a.msum[(size_t)n * D + (c - H)]);
+            v[k] = !valid ? 0.f : (c < H ? a.h[(size_t)n * H + c] : stageF[r * D + ((c - H) ^ (r & 31))]);
         }
         tc_split_store32(smem + L::a_hi, smem + L::a_lo, r, c0, v, true);
         if (cg == 0) {
@@ -79,7 +91,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
 #pragma unroll
             for (int k = 0; k < 16; ++k) {
                 const int c = D + k;
-                t[k] = !valid ? 0.f : (c < KA ? a.msum[(size_t)n * D + (c - H)] : (c == KP - 1 ? 1.f : 0.f));
+                t[k] = !valid ? 0.f : (c < KA ? stageF[r * D + ((c - H) ^ (r & 31))] : (c == KP - 1 ? 1.f : 0.f));
             }
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
@@ -173,38 +185,49 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
     if (!ok) asm volatile("trap;");
     tc::fence_after_sync();
     float* part = a.part + (size_t)blockIdx.x * lo.total;
+    // ---- outputs: every thread owns one row, so direct global stores would hit 32 different lines per instruction.
+    //      Stage through shared memory (all MMAs are done: the A tile and the weight image are dead) with odd row
+    //      strides (conflict-free for row-per-lane writes), then write the contiguous global blocks coalesced.
+    float* stageG = reinterpret_cast<float*>(smem + L::a_hi);  // [128][D+1]   g[M] of the tile's nodes
+    float* stageP = reinterpret_cast<float*>(smem + L::w_hi);  // [D][KA]      dWh1 == its global layout
     {
         float v[32];
         tc::tmem_ld32(trow + cG + c0, v);
-        if (valid) {
 #pragma unroll
-            for (int k = 0; k < 32; ++k) {
-                const int c = c0 + k;
-                if (c < H) a.gh_node[(size_t)n * H + c] = v[k];
-                else a.gM[(size_t)n * D + (c - H)] = v[k];
+        for (int k = 0; k < 32; ++k) {
+            const int c = c0 + k;
+            if (c < H) {
+                if (valid) a.gh_node[(size_t)n * H + c] = v[k];
+            } else {
+                stageG[r * (D + 1) + (c - H)] = v[k];
             }
         }
         tc::tmem_ld32(trow + cW1 + c0, v);
         if (r < D) {
 #pragma unroll
-            for (int k = 0; k < 32; ++k) part[lo.wh1 + r * KA + c0 + k] = v[k];
+            for (int k = 0; k < 32; ++k) stageP[r * KA + c0 + k] = v[k];
         }
     }
     if (cg == 0) {
         float v[32];
         tc::tmem_ld32(trow + cG + D, v);
-        if (valid) {
 #pragma unroll
-            for (int k = 0; k < 16; ++k)
-                if (D + k < KA) a.gM[(size_t)n * D + (D + k - H)] = v[k];
-        }
+        for (int k = 0; k < 16; ++k)
+            if (D + k < KA) stageG[r * (D + 1) + (D + k - H)] = v[k];
         tc::tmem_ld32(trow + cW1 + D, v);
         if (r < D) {
 #pragma unroll
             for (int k = 0; k < 16; ++k)
-                if (D + k < KA) part[lo.wh1 + r * KA + D + k] = v[k];
+                if (D + k < KA) stageP[r * KA + D + k] = v[k];
             part[lo.bh1 + r] = v[15];
         }
+    }
+    __syncthreads();
+    {
+        const int n0 = blockIdx.x * 128, rows = min(128, a.N - n0);
+        float* dst = a.gM + (size_t)n0 * D;
+        for (int idx = tid; idx < rows * D; idx += NT) dst[idx] = stageG[(idx / D) * (D + 1) + idx % D];
+        for (int idx = tid; idx < D * KA; idx += NT) part[lo.wh1 + idx] = stageP[idx];
     }
     if (cg == NG - 1) {
         float v[32];
