@@ -320,8 +320,11 @@ def run_product(args, rank, world, local):
         ach = algo[top] / (prof[top]["ms_per_launch"] * 1e-3) / 1e12
         # tensor-core FLOPs actually issued: the backward recomputes both edge MLPs (3x forward), and bf16x3 issues
         # three bf16 MMAs (hi.hi + lo.hi + hi.lo) per fp32-accurate product
+        # (forward: GEMM1 + GEMM2 of both branches; backward: the same recomputed + dgrad, and the weight-gradient MMAs
+        # with two of the three split products)
         passes = {"fp32": 0, "bf16x3": 3, "bf16": 1}[args.precision] if top.startswith("tc_") else 0
-        issued = passes * (3 if top.endswith("bwd") else 1) * edge_flops
+        wgrad_passes = min(passes, 2)
+        issued = (2 * passes + wgrad_passes if top.endswith("bwd") else passes) * edge_flops
         traffic = None
         try:
             with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
