@@ -5,7 +5,8 @@
 One step = diffuse_as_batch + EGNN forward + loss + backward + optimizer step over one batch (the body of
 train_epoch, parts/train_per_iretation.py:122-179).  metric = denoiser graph-steps/s (graphs trained per second,
 whole job).  `value` is timed with the batch resident in HBM; `e2e` goes through the public API from pinned HOST
-buffers every step (H2D of the batch, edge-index preparation, D2H of the loss).  N > 1: one rank per GPU, each its own
+buffers every step (H2D of the batch through data.DevicePrefetcher -- the copy of step i+1 overlaps step i --, edge-index
+preparation, D2H of the loss every step, read by the host one step later).  N > 1: one rank per GPU, each its own
 64-graph batch (weak scaling), one NCCL all-reduce of the flat gradient per step.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
@@ -17,6 +18,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import random
 import statistics
@@ -200,7 +202,7 @@ def run_product(args, rank, world, local):
     import torch.distributed as dist
     from diffusion_model_b200 import _lib
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
-    from diffusion_model_b200.data import Data
+    from diffusion_model_b200.data import Data, DevicePrefetcher
     from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
     from diffusion_model_b200.distributed import allreduce_gradients, broadcast_parameters
     from diffusion_model_b200.graph import build_edges_cutoff, check_pending
@@ -244,13 +246,34 @@ def run_product(args, rank, world, local):
         opt.step(grad_scale=1.0 / world)
         return loss
 
+    # e2e: the public loader path.  Every step's inputs start in pinned HOST memory; DevicePrefetcher issues step
+    # i+1's H2D copy on a side stream while step i computes (one copy per step inside the timed region), and the
+    # step's loss is copied back to pinned memory every step and read by the host one step later (no stall).
+    host_batch = Data(x=oh_p, pos=pos_p, edge_index=ei_h)
+    host_batch.node_ptr = np_p
+
+    def host_batches():
+        while True:
+            yield host_batch
+
+    feed = iter(DevicePrefetcher(host_batches(), dev))
+    loss_pin = torch.zeros(2, pin_memory=True)
+    loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
+    e2e_state = dict(i=0, last=None)
+
     def e2e_step():
-        b = Data(x=oh_p.to(dev, non_blocking=True), pos=pos_p.to(dev, non_blocking=True),
-                 edge_index=ei_h.to(dev, non_blocking=True))
-        b.node_ptr = np_p.to(dev, non_blocking=True)
-        out = train_step(b).item()  # D2H read of the step's loss
-        check_pending(wait=False)   # deferred edge-list validation of this step's graph (copy already landed)
-        return out
+        b = next(feed)
+        loss = train_step(b)
+        k = e2e_state["i"] & 1
+        loss_pin[k:k + 1].copy_(loss.detach().view(1), non_blocking=True)  # D2H read of the step's loss
+        loss_ev[k].record()
+        if e2e_state["i"] > 0:
+            loss_ev[k ^ 1].synchronize()
+            e2e_state["last"] = float(loss_pin[k ^ 1])
+            if not math.isfinite(e2e_state["last"]):
+                raise SystemExit("bench.py: non-finite loss in the e2e loop")
+        e2e_state["i"] += 1
+        check_pending(wait=False)   # deferred edge-list validation of the graphs whose flags have landed
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
@@ -342,6 +365,7 @@ def run_product(args, rank, world, local):
                 scaling="weak", vs_baseline=None, dtype=args.precision, data="synthetic",
                 config=dict(workload_config(args.precision), nodes_per_gpu=N, edges_per_gpu=E),
                 e2e=dict(value=e2e_value, unit="graph-steps/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4,
+                         pipeline="H2D of step i+1 prefetched on a copy stream during step i; loss D2H every step, read 1 step late",
                          ms_per_step=ms_e2e / args.steps, host_enqueue_ms_per_step=host_ms),
                 gpu_launches=int(launches), clocks=clocks, roofline=roofline, kernels=prof,
                 train_flops_per_step=3 * fwd_flops(CFG["L"], d, CFG["H"], N, E))

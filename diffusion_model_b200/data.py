@@ -83,3 +83,59 @@ class DataLoader:
             if self.drop_last and len(chunk) < self.batch_size:
                 return
             yield Batch.from_data_list([self.dataset[i] for i in chunk])
+
+
+class DevicePrefetcher:
+    """Iterates ``loader`` one batch ahead: batch i+1 is copied host->device on a side stream (from pinned memory when
+    ``pin`` is set or the tensors already are pinned) while the caller's stream still works on batch i; the caller's
+    stream waits on the copy's event before the batch is handed out, so no host synchronisation is involved.  The
+    reference's loop does ``data.to('cuda')`` in line (parts/train_per_iretation.py:123); this is the same copy, moved
+    off the critical path.  CUDA only."""
+
+    def __init__(self, loader, device="cuda", pin=True):
+        self.loader, self.device, self.pin = loader, torch.device(device), pin
+        if self.device.type != "cuda":
+            raise ValueError("DevicePrefetcher copies to a CUDA device")
+        self._stream = None
+
+    def __len__(self):
+        return len(self.loader)
+
+    def _upload(self, batch):
+        if not isinstance(batch, Data):  # foreign containers (real PyG batches): plain in-line copy, no prefetch
+            return batch.to(self.device), None
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(self.device)
+        out = batch.__class__.__new__(batch.__class__)
+        out.__dict__.update(batch.__dict__)
+        with torch.cuda.stream(self._stream):
+            for k, v in batch.__dict__.items():
+                if torch.is_tensor(v) and not v.is_cuda:
+                    if self.pin and not v.is_pinned():
+                        v = v.pin_memory()
+                    out.__dict__[k] = v.to(self.device, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._stream)
+        return out, ev
+
+    def _hand_out(self, item):
+        out, ev = item
+        if ev is None:
+            return out
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ev)
+        for v in out.__dict__.values():
+            if torch.is_tensor(v) and v.is_cuda:
+                v.record_stream(cur)  # allocated on the copy stream, consumed on the caller's
+        return out
+
+    def __iter__(self):
+        it = iter(self.loader)
+        try:
+            nxt = self._upload(next(it))
+        except StopIteration:
+            return
+        for batch in it:
+            cur, nxt = nxt, self._upload(batch)
+            yield self._hand_out(cur)
+        yield self._hand_out(nxt)

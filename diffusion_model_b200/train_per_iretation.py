@@ -21,7 +21,7 @@ import torch
 from . import _lib
 from .graph import check_pending, graph_index_for
 from ._lib import call, ptr, stream_ptr
-from .data import Data
+from .data import Data, DevicePrefetcher
 from .diffusion_x_h import _node_ptr_of, remove_mean  # noqa: F401  (re-exported like the reference module)
 
 I32 = torch.int32
@@ -166,8 +166,7 @@ def _run_epoch(nn_dict, loader, params, diffusion_process, optimizer, train):
         nn_dict["spectrum_compressor"].train(train)
     epoch_loss = torch.zeros((), device="cuda")
     total_nodes = 0
-    for data in loader:
-        data = data.to("cuda")
+    for data in DevicePrefetcher(loader, "cuda"):  # next minibatch's H2D copy overlaps this one's kernels
         total_nodes += data.num_nodes
         cond = _conditioning(data, params, nn_dict)
         if train:
