@@ -128,7 +128,10 @@ struct TcLayout {
     static constexpr int w1_hi = 0, w1_lo = W1_BYTES;
     static constexpr int w2m_hi = 2 * W1_BYTES, w2m_lo = w2m_hi + W2_BYTES;
     static constexpr int w2x_hi = w2m_lo + W2_BYTES, w2x_lo = w2x_hi + W2_BYTES;
-    static constexpr int vec = w2x_lo + W2_BYTES;  // fp32: bm1 [D] | bx1 [D] | bm2 [D] | bx2 [D] | wa [D] | wx3 [D] | ba, bx3, 0, 0
+    // All four matrices and the four bias vectors are stored HALVED (exact in bf16 / fp32): the MMAs then deliver z / 2,
+    // which is what the one-MUFU SiLU (tc_silu_h) consumes -- one multiply per element less in every epilogue.  The
+    // layer-1 biases sit in K slot 15 of W1 (rows of U carry a constant 1 there), so GEMM1 adds them for free.
+    static constexpr int vec = w2x_lo + W2_BYTES;  // fp32: bm1/2 [D] | bx1/2 [D] | bm2/2 [D] | bx2/2 [D] | wa [D] | wx3 [D] | ba, bx3, 0, 0
     static constexpr int BLOB = vec + (6 * D + 4) * 4;
     static constexpr int blob_pad = (BLOB + 15) / 16 * 16;
     // per-tile operands
@@ -156,10 +159,12 @@ __global__ void __launch_bounds__(256) tc_pack_kernel(egnn_net_t net, const floa
     for (int idx = t0; idx < 2 * D * 2; idx += stride) {
         const int n = idx >> 1, j = idx & 1;
         const float* row = n < D ? P + lo.wm1 + n * K0 : P + lo.wx1 + (n - D) * K0;
+        const float bias = n < D ? P[lo.bm1 + n] : P[lo.bx1 + n - D];
         uint32_t hi[4], lw[4];
         for (int q = 0; q < 4; ++q) {
-            const int k = j * 8 + 2 * q;
-            tc::split2(k < K0 ? row[k] : 0.f, k + 1 < K0 ? row[k + 1] : 0.f, hi[q], lw[q]);
+            const int k = j * 8 + 2 * q;  // K slot 15 (always >= K0) carries the bias: u[15] is the constant 1
+            tc::split2(k < K0 ? 0.5f * row[k] : 0.f, k + 1 < K0 ? 0.5f * row[k + 1] : (k + 1 == 15 ? 0.5f * bias : 0.f), hi[q],
+                       lw[q]);
         }
         *reinterpret_cast<uint4*>(blob + tc::chunk_off(2 * D, n, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
         *reinterpret_cast<uint4*>(blob + W1B + tc::chunk_off(2 * D, n, j)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
@@ -170,17 +175,18 @@ __global__ void __launch_bounds__(256) tc_pack_kernel(egnn_net_t net, const floa
         for (int idx = t0; idx < D * (D / 8); idx += stride) {
             const int n = idx / (D / 8), j = idx % (D / 8);
             uint32_t hi[4], lw[4];
-            for (int q = 0; q < 4; ++q) tc::split2(W[n * D + j * 8 + 2 * q], W[n * D + j * 8 + 2 * q + 1], hi[q], lw[q]);
+            for (int q = 0; q < 4; ++q)
+                tc::split2(0.5f * W[n * D + j * 8 + 2 * q], 0.5f * W[n * D + j * 8 + 2 * q + 1], hi[q], lw[q]);
             *reinterpret_cast<uint4*>(dst + tc::chunk_off(D, n, j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             *reinterpret_cast<uint4*>(dst + W2B + tc::chunk_off(D, n, j)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
         }
     }
     float* vec = reinterpret_cast<float*>(blob + 2 * W1B + 4 * W2B);
     for (int c = t0; c < D; c += stride) {
-        vec[c] = P[lo.bm1 + c];
-        vec[D + c] = P[lo.bx1 + c];
-        vec[2 * D + c] = P[lo.bm2 + c];
-        vec[3 * D + c] = P[lo.bx2 + c];
+        vec[c] = 0.5f * P[lo.bm1 + c];  // (layer-1 biases travel in K slot 15 of W1; kept here for reference only)
+        vec[D + c] = 0.5f * P[lo.bx1 + c];
+        vec[2 * D + c] = 0.5f * P[lo.bm2 + c];
+        vec[3 * D + c] = 0.5f * P[lo.bx2 + c];
         vec[4 * D + c] = P[lo.wa + c];
         vec[5 * D + c] = P[lo.wx3 + c];
     }
@@ -309,6 +315,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
                 if (k == H + o && o < H) v = g.hj_[o];
             }
             if (k == 2 * H) v = nrm * nrm;
+            if (k == 15) v = 1.f;  // bias slot
             u[k] = valid ? v : 0.f;
         }
 #pragma unroll
@@ -367,7 +374,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
         tc::fence_after_sync();
         if (tid < 128 && has_next) gather_nodes(gnext);                     // stage 2: lands during the epilogue below
         // ---- layer-1 epilogue of the coordinate branch -> A1; the U tile is free again: store the next tile's rows
-        tc_epi_store_chunked<FAST>(trow + D + c0, vec + D + c0, smem + L::a1_hi, smem + L::a1_lo, r, c0, LO);
+        tc_epi_store_chunked(trow + D + c0, smem + L::a1_hi, smem + L::a1_lo, r, c0, LO);
         if (tid < 128 && has_next) dst_next = store_u(tile + gridDim.x, gnext);  // stage 3
         tc::fence_async_smem();
         tc::fence_before_sync();
@@ -379,7 +386,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
         }
         // ---- layer-1 epilogue of the message branch: in registers while GEMM2x runs
         uint32_t mhi[16], mlo[16];
-        tc_epi32<FAST>(trow + c0, vec + c0, mhi, mlo);
+        tc_epi32(trow + c0, mhi, mlo);
         ok = tc::mbar_wait(&bars[1], phase) && ok;  // GEMM2x has consumed A1
         tc::fence_after_sync();
         tc_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, mhi, mlo, LO);
@@ -401,7 +408,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
             float v[32];
             tc::tmem_ld32(trow + 3 * D + c0, v);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) s = fmaf(vec[5 * D + c0 + i], tc_silu<FAST>(v[i] + vec[3 * D + c0 + i]), s);
+            for (int i = 0; i < 32; ++i) s = fmaf(vec[5 * D + c0 + i], tc_silu_h(v[i] + vec[3 * D + c0 + i]), s);
             phiPart[cg * 128 + r] = s;
         }
         ok = tc::mbar_wait(&bars[2], phase) && ok;
@@ -414,7 +421,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
             tc::tmem_ld32(trow + 2 * D + c0, v);
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-                m[i] = tc_silu<FAST>(v[i] + vec[2 * D + c0 + i]);
+                m[i] = tc_silu_h(v[i] + vec[2 * D + c0 + i]);
                 s = fmaf(vec[4 * D + c0 + i], m[i], s);
             }
             gatePart[cg * 128 + r] = s;
@@ -511,6 +518,9 @@ int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const flo
 //   dgrad       ga1 = gz2 . W2   (block B)        B operand = the SAME W2 image viewed MN-major
 //   wgrad       [dW2 | db2] += gz2^T . [a1 | u]   (persistent TMEM accumulators; slot 15 of u is the constant 1)
 //   gz1 = ga1 * SiLU'(z1+b1) -> tile G;   gu = gz1 . W1 (16 columns),  [dW1 | db1] += gz1^T . u
+// The weight image is stored halved (TcLayout): the MMAs give z / 2, the epilogues produce 2 SiLU' from the same tanh, so
+// the gradient tiles hold 2 gz -- dgrad through the halved weights is then exact (2 gz . W / 2) and the persistent
+// weight-gradient accumulators are halved once when they are written out.
 // Shared-memory tiles are written once by the thread that owns the edge row (16-byte chunks) and serve both as
 // K-major operands (row = edge) and as MN-major operands (K = edge) -- same bytes, two descriptor views.
 // The two wgrad MMAs run behind the CUDA-core work of the next phase (own mbarriers); the U tile is double-buffered and
@@ -623,8 +633,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     const TcOperand opW1{sb + L::w1_hi, sb + L::w1_lo, D * 16, false}, opW1mn{sb + L::w1_hi, sb + L::w1_lo, D * 16, true};
     const TcOperand opW2{sb + L::w2_hi, sb + L::w2_lo, D * 16, false}, opW2mn{sb + L::w2_hi, sb + L::w2_lo, D * 16, true};
 
-    const float* b1 = vec;
-    const float* b2 = vec + D;
+    const float* b2 = vec + D;      // b2 / 2 (the image is stored halved, see TcLayout)
     const float* wv = vec + 2 * D;  // wa (gate) or wx3 (phi head)
     float* Grb = a.Gr + (size_t)branch * a.E * W;
     float* Gsb = a.Gs + (size_t)branch * a.E * W;
@@ -735,9 +744,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             float v[32], act[32];
             tc::tmem_ld32(trow + cA + c0, v);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                tc_silu_and_grad(v[i] + b1[c0 + i], act[i], v[i]);
-            }
+            for (int i = 0; i < 32; ++i) tc_silu_and_grad2_h(v[i], act[i], v[i]);  // TMEM holds z1 / 2 incl. bias
             tc_split_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, act, LO);
             tc::tmem_st32(trow + cA + c0, v);
         }
@@ -769,7 +776,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
                 float v[32];
                 tc::tmem_ld32(trow + cB + c0, v);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) tc_silu_and_grad(v[i] + b2[c0 + i], m[i], d2[i]);
+                for (int i = 0; i < 32; ++i) tc_silu_and_grad2_h(v[i] + b2[c0 + i], m[i], d2[i]);
             }
             const float4 rr = sR[buf * 128 + r];
             const int i = sI[buf * 128 + r];
@@ -906,7 +913,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             if (r < D) {
                 float* dst = part + o_w2 + (size_t)r * D + c0;  // partial rows are not 16-byte aligned in general
 #pragma unroll
-                for (int k = 0; k < 32; ++k) dst[k] = v[k];
+                for (int k = 0; k < 32; ++k) dst[k] = 0.5f * v[k];  // the gz tiles carry 2 * dL/dz (see header)
             }
         }
         if (cg == 0) {
@@ -914,11 +921,11 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             tc::tmem_ld32(trow + cBias0, v0);  // column 15: db2 of the even tiles
             tc::tmem_ld32(trow + cBias1, v1);  // column 15: db2 of the odd tiles; [16,32): dW1, column 31: db1
             if (r < D) {
-                part[o_b2 + r] = v0[15] + v1[15];
-                part[o_b1 + r] = v1[31];
+                part[o_b2 + r] = 0.5f * (v0[15] + v1[15]);
+                part[o_b1 + r] = 0.5f * v1[31];
 #pragma unroll
                 for (int k = 0; k < 15; ++k)
-                    if (k < K0) part[o_w1 + r * K0 + k] = v1[16 + k];
+                    if (k < K0) part[o_w1 + r * K0 + k] = 0.5f * v1[16 + k];
             }
         }
         float* colred = rowA;  // [NT/32][32]

@@ -30,36 +30,39 @@ __device__ __forceinline__ void tc_silu_and_grad(float z, float& act, float& dac
     dact = fmaf(act, fmaf(-0.5f, t, 0.5f), fmaf(0.5f, t, 0.5f));
 }
 
-// this thread's row, columns [c0, c0+32) of a TMEM block: act(acc + bias) packed as bf16 hi/lo pairs
-template <bool FAST>
-__device__ __forceinline__ void tc_epi32(uint32_t taddr, const float* bias, uint32_t (&hi)[16], uint32_t (&lo)[16]) {
+// The edge kernels keep their weight images halved, so the accumulators ARE h = z / 2:
+__device__ __forceinline__ float tc_silu_h(float h) {
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+    return fmaf(h, t, h);
+}
+// SiLU(z) and 2 SiLU'(z) = (1 + t) + SiLU(z) (1 - t) from h = z / 2
+__device__ __forceinline__ void tc_silu_and_grad2_h(float h, float& act, float& dact2) {
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+    act = fmaf(h, t, h);
+    dact2 = fmaf(act, 1.f - t, 1.f + t);
+}
+
+// this thread's row, columns [c0, c0+32) of a TMEM block holding z / 2 (bias included): SiLU packed as bf16 hi/lo pairs
+__device__ __forceinline__ void tc_epi32(uint32_t taddr, uint32_t (&hi)[16], uint32_t (&lo)[16]) {
     float v[32];
     tc::tmem_ld32(taddr, v);
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        const float a = tc_silu<FAST>(v[2 * i] + bias[2 * i]);
-        const float b = tc_silu<FAST>(v[2 * i + 1] + bias[2 * i + 1]);
-        tc::split2(a, b, hi[i], lo[i]);
-    }
+    for (int i = 0; i < 16; ++i) tc::split2(tc_silu_h(v[2 * i]), tc_silu_h(v[2 * i + 1]), hi[i], lo[i]);
 }
-// this thread's row, columns [c0, c0+32) of a TMEM block -> act(acc + bias) -> bf16 hi/lo chunks of a 128-row tile.
+// this thread's row, columns [c0, c0+32) of a TMEM block (z / 2, bias included) -> SiLU -> bf16 hi/lo chunks of a 128-row tile.
 // Walks the 32 columns as four 8-column chunks in a REAL loop: each chunk is a burst of MUFU work (two per element)
 // followed by ALU work (split, pack, store); keeping the chunks apart stops the scheduler from hoisting all 64 MUFU
 // ops to the front, so that across the warps of an SM sub-partition the XU and ALU pipes run concurrently.
-template <bool FAST>
-__device__ __forceinline__ void tc_epi_store_chunked(uint32_t taddr, const float* bias, uint8_t* t_hi, uint8_t* t_lo, int r,
-                                                     int c0, bool with_lo) {
+__device__ __forceinline__ void tc_epi_store_chunked(uint32_t taddr, uint8_t* t_hi, uint8_t* t_lo, int r, int c0, bool with_lo) {
 #pragma unroll 1
     for (int j = 0; j < 4; ++j) {
         float v[8];
         tc::tmem_ld8(taddr + 8 * j, v);
         uint32_t hi[4], lo[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const float a = tc_silu<FAST>(v[2 * i] + bias[8 * j + 2 * i]);
-            const float b = tc_silu<FAST>(v[2 * i + 1] + bias[8 * j + 2 * i + 1]);
-            tc::split2(a, b, hi[i], lo[i]);
-        }
+        for (int i = 0; i < 4; ++i) tc::split2(tc_silu_h(v[2 * i]), tc_silu_h(v[2 * i + 1]), hi[i], lo[i]);
         const uint32_t off = tc::chunk_off(128, r, (c0 >> 3) + j);
         *reinterpret_cast<uint4*>(t_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
         if (with_lo) *reinterpret_cast<uint4*>(t_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
