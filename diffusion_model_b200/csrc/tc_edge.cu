@@ -274,13 +274,14 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
     // other work: (1) edge ids, (2) node data of both ends, (3) u -> bf16 tile, and where the row's finished
     // segmented sum goes (>= 0: agg[node]; -1: head partial; -2: tail partial; -3: the run continues in the next row)
     struct Row {
-        int i, j, inext;          // stage 1
+        int i, inext;             // stage 1 (the sender id is only needed for the addresses of stage 2)
+        int j;
         float xi[3], xj[3];       // stage 2
-        float hi_[8], hj_[8];
+        float u[14];              // h_i | h_j already in their K slots
         int rp0, rp1;
     };
     auto gather_ids = [&](int tile, Row& g) {
-        const int e = min(tile * 128 + tid, a.E - 1);
+        const int e = min(tile * 128 + tid, a.E - 1);  // rows past the end repeat the last edge; they are never flushed
         g.i = a.recv[e];
         g.j = a.send[e];
         g.inext = a.recv[min(e + 1, a.E - 1)];
@@ -291,10 +292,12 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
             g.xi[k] = a.x[3 * g.i + k];
             g.xj[k] = a.x[3 * g.j + k];
         }
+        const float* hi_ = a.h + (size_t)g.i * H;
+        const float* hjm = a.h + (size_t)g.j * H - H;  // slot k in [H, 2H) reads h_j[k - H]
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            g.hi_[k] = k < H ? a.h[(size_t)g.i * H + k] : 0.f;
-            g.hj_[k] = k < H ? a.h[(size_t)g.j * H + k] : 0.f;
+        for (int k = 0; k < 14; ++k) {
+            const float* p = k < H ? hi_ : hjm;
+            g.u[k] = k < 2 * H ? p[k] : 0.f;
         }
         g.rp0 = a.row_ptr[g.i];
         g.rp1 = a.row_ptr[g.i + 1];
@@ -305,19 +308,12 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
         const bool valid = tid < nrows;
         const float rx = g.xi[0] - g.xj[0], ry = g.xi[1] - g.xj[1], rz = g.xi[2] - g.xj[2];
         const float nrm = sqrtf(rx * rx + ry * ry + rz * rz);
+        const float d2 = nrm * nrm;
         float u[16];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            float v = 0.f;
-#pragma unroll
-            for (int o = 0; o < 8; ++o) {
-                if (k == o && o < H) v = g.hi_[o];
-                if (k == H + o && o < H) v = g.hj_[o];
-            }
-            if (k == 2 * H) v = nrm * nrm;
-            if (k == 15) v = 1.f;  // bias slot
-            u[k] = valid ? v : 0.f;
-        }
+        for (int k = 0; k < 14; ++k) u[k] = k == 2 * H ? d2 : g.u[k];
+        u[14] = 2 * H == 14 ? d2 : 0.f;
+        u[15] = 1.f;  // bias slot
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
             uint32_t hi[4], lo[4];
@@ -764,10 +760,14 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             tc::fence_after_sync();
             edge_outputs((tile - tstride) * 128, min(128, a.E - (tile - tstride) * 128), buf ^ 1, phi_prev);
         }
+        if (tid < 128 && has_next) {  // still in the shadow: the next tile's U rows (the previous dW1 MMA has left U[buf^1])
+            if (it > 0) ok = tc::mbar_wait(&bars[5], phase ^ 1) && ok;
+            tc::fence_after_sync();
+            gather_store(buf ^ 1, gnext);
+        }
         ok = tc::mbar_wait(&bars[1], phase) && ok;
-        if (it > 0) ok = tc::mbar_wait(&bars[5], phase ^ 1) && ok;  // previous tile's dW1 MMA is done with U[buf^1] and tile G
+        if (it > 0) ok = tc::mbar_wait(&bars[5], phase ^ 1) && ok;  // previous tile's dW1 MMA is done with tile G as well
         tc::fence_after_sync();
-        if (tid < 128 && has_next) gather_store(buf ^ 1, gnext);
         // ---- upstream gradient of z2: out = SiLU(z2 + b2) and SiLU' of this thread's 32 columns
         float cs[32];  // coef_e * out_e[c]: column sums taken after the MMAs below have been issued
         {
@@ -884,6 +884,8 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             }
             tc_issue_op<NPASS>(tmem, cGU, opG, opW1mn, D, 16, false, GLO1);  // gu = gz1 . W1   (16 columns)
             tc::mma_commit(&bars[4]);
+        } else if (warp == NT / 32 - 2 && tc::elect_one()) {  // independent of the two above: issued by another warp
+            tc::fence_after_sync();
             tc_issue_op<NPASS>(tmem, cP1, opGmn, opUmn, 128, 16, true, false);  // [dW1 | db1] += gz1^T . u
             tc::mma_commit(&bars[5]);
         }
