@@ -336,6 +336,10 @@ int egnn_tc_pack(const egnn_net_t& net, const float* params, float* packed, cuda
 int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
                          const float* x, float* agg, float* part, float* phi_edge, int precision, cudaStream_t st);
 
+int egnn_tc_node_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
+                         const float* h, const float* x, const float* agg, const float* part, const float* phi_edge,
+                         float* h_out, float* msum, float* dxu, float* Dn, int precision, cudaStream_t st);
+
 extern "C" int egnn_pack_weights(const egnn_net_t* net, const float* params, float* packed, void* stream) {
     if (int rc = egnn_validate_net(net)) return rc;
     pack_weights_kernel<<<dim3(32, net->L), 256, 0, (cudaStream_t)stream>>>(*net, params, packed);
@@ -363,7 +367,12 @@ int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const f
         }
         if (rc) return rc;
     }
-    {
+    if (tensor && tc_node_supported(net)) {
+        if (int rc = egnn_tc_node_forward(net, g, P, Pk, h, x, ws + w.agg, ws + w.part, ws + w.phi, h_out,
+                                          ws + w.msum + (size_t)l * g.N * net.Ms, ws + w.dxu + (size_t)l * g.N * 3, ws + w.D,
+                                          precision, st))
+            return rc;
+    } else {
         NodeFwdArgs na{net, g.N, TE, g.row_ptr, h, P, Pk, ws + w.agg, ws + w.part, h_out,
                        ws + w.msum + (size_t)l * g.N * net.Ms, ws + w.dxu + (size_t)l * g.N * 3, ws + w.D,
                        tensor ? ws + w.phi : nullptr, g.send, x};

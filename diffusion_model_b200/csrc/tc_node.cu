@@ -244,6 +244,242 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_bwd(TcNodeBwdArgs a) {
     if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// tcgen05 path of the node FORWARD: one CTA per 128-node tile, 4*D threads.
+//   M_i    = per-receiver message sum: the edge kernel's agg row or, for a node cut by 32-edge segment boundaries (the
+//            usual case), tail partial of its first segment + head partials of the following ones, in segment order
+//   dxu_i  = sum_e r_e phi_e,  D_i = sum_e |r_e|^2      (over the receiver's edges, fixed order)
+//   h'     = Wh2 . SiLU(Wh1 [h, M] + b1) + b2           GEMM1 on the tensor cores (K = D + 16), the H-wide second
+//                                                       layer as per-thread partial dots over 32 columns
+// Reference: EGCL.forward's node update, EquivariantGraphNeuralNetwork.py:26-30, 66-69 (no residual).
+// All global reads of the tile's sums are coalesced (a warp reads 32 consecutive columns of one row); the loads of
+// several rows are issued together so that the dependent chains (row_ptr -> partial rows, send -> x) overlap.
+// ---------------------------------------------------------------------------------------------------------------------
+struct TcNodeFwdArgs {
+    egnn_net_t net;
+    int N, TE;
+    const int32_t *row_ptr, *send;
+    const float *h, *x;
+    const float* P;        // this layer's fp32 parameters
+    const uint8_t* nblob;  // Wh1 image (hi | lo)
+    const float *agg, *part, *phi_edge;
+    float *h_out, *msum, *dxu, *Dn;
+};
+
+template <int D, int NPASS>
+__global__ void __launch_bounds__(4 * D, 1) tc_node_fwd(TcNodeFwdArgs a) {
+    using L = TcNodeLayout<D>;
+    constexpr bool LO = NPASS == 3;
+    constexpr int NT = L::NT, NG = L::NG, KP = L::KP;
+    constexpr int LPN = NT / 128;  // lanes per node of the dxu / D sums
+    constexpr uint32_t TS = 128 * 16;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q = warp & 3, cg = warp >> 2;
+    const int r = q * 32 + lane, c0 = cg * 32;
+    constexpr int TE = 32;  // partial-segment length of the tcgen05 edge kernel (part_tile_for); a shift, not a division
+    const int H = a.net.H, KA = H + D, AGGW = D + 4;
+    const LayerOff lo = layer_off(a.net);
+    float* vec = reinterpret_cast<float*>(smem + L::vec);    // b1 [D] | Wh2 [8][D]
+    float* sPart = reinterpret_cast<float*>(smem + L::s_hi);  // float [NG][128][8] partial dots (after the A tile is built)
+    int* sRow = reinterpret_cast<int*>(smem + L::sGH);        // int [129] row_ptr of the tile's nodes
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::bars);
+    uint32_t* slot = reinterpret_cast<uint32_t*>(smem + L::slot);
+    const int n0 = blockIdx.x * 128, rows = min(128, a.N - n0);
+    const int n = n0 + r;
+    const bool valid = r < rows;
+
+    // weight image: asynchronous copy, waited for just before the MMA
+    {
+        const uint32_t dst = tc::smem_u32(smem + L::w_hi);
+        for (int o = tid * 16; o < 2 * L::NCH * D * 16; o += NT * 16)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + o), "l"(a.nblob + o) : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int c = tid; c < D; c += NT) vec[c] = a.P[lo.bh1 + c];
+    for (int c = tid; c < 8 * D; c += NT) vec[D + c] = c < H * D ? a.P[lo.wh2 + c] : 0.f;
+    if (tid <= 128) sRow[tid] = a.row_ptr[min(n0 + tid, a.N)];
+    if (warp == 0) tc::tmem_alloc(slot, D);
+    if (tid == 0) {
+        tc::mbar_init(&bars[0], 1);
+        tc::fence_mbar_init();
+    }
+    __syncthreads();
+
+    // ---- message sums of the tile: thread -> (row, column) with consecutive threads on consecutive columns.  Per
+    //      element up to three partial rows are read unconditionally-predicated (tail of the first segment or the agg
+    //      row, heads of the next two segments) so that UNR rows are in flight together; longer runs take the loop.
+    float* stageF = reinterpret_cast<float*>(smem + L::s_hi);
+    {
+        constexpr int UNR = 8;
+        constexpr int RPI = NT / D;  // rows covered per iteration
+        const int m = tid % D, rsub = tid / D;
+        for (int rb0 = 0; rb0 < rows; rb0 += UNR * RPI) {
+            float p0[UNR], p1[UNR], p2[UNR];
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                const int rr = rb0 + u * RPI + rsub;
+                p0[u] = p1[u] = p2[u] = 0.f;
+                if (rr < rows) {
+                    const int ea = sRow[rr], eb = sRow[rr + 1];
+                    if (ea < eb) {
+                        const int t0 = ea / TE, t1 = (eb - 1) / TE;
+                        p0[u] = t0 == t1 ? a.agg[(size_t)(n0 + rr) * AGGW + m] : a.part[((size_t)t0 * 2 + 1) * AGGW + m];
+                        if (t0 + 1 <= t1) p1[u] = a.part[((size_t)(t0 + 1) * 2) * AGGW + m];
+                        if (t0 + 2 <= t1) p2[u] = a.part[((size_t)(t0 + 2) * 2) * AGGW + m];
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                const int rr = rb0 + u * RPI + rsub;
+                if (rr < rows) {
+                    float sum = (p0[u] + p1[u]) + p2[u];
+                    const int ea = sRow[rr], eb = sRow[rr + 1];
+                    if (ea < eb) {
+                        const int t1 = (eb - 1) / TE;
+                        for (int t = ea / TE + 3; t <= t1; ++t) sum += a.part[((size_t)t * 2) * AGGW + m];
+                    }
+                    a.msum[(size_t)(n0 + rr) * D + m] = sum;
+                    stageF[rr * D + (m ^ (rr & 31))] = sum;
+                }
+            }
+        }
+    }
+    // ---- coordinate sums: LPN lanes per node walk the receiver's edges with stride LPN, four edges in flight per lane
+    {
+        const int rr = tid / LPN, sub = tid % LPN;
+        float sx = 0.f, sy = 0.f, sz = 0.f, sd = 0.f;
+        if (rr < rows) {
+            const int i = n0 + rr;
+            const float xi = a.x[3 * i], yi = a.x[3 * i + 1], zi = a.x[3 * i + 2];
+            const int eb = sRow[rr + 1];
+            for (int e = sRow[rr] + sub; e < eb; e += 4 * LPN) {
+                int j[4];
+                float ph[4], xs[4][3];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int ee = e + u * LPN;
+                    j[u] = ee < eb ? a.send[ee] : i;
+                    ph[u] = ee < eb ? a.phi_edge[ee] : 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    xs[u][0] = a.x[3 * j[u]];
+                    xs[u][1] = a.x[3 * j[u] + 1];
+                    xs[u][2] = a.x[3 * j[u] + 2];
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {  // padding lanes read x_i itself: r = 0 and phi = 0 add exact zeros
+                    const float rx = xi - xs[u][0], ry = yi - xs[u][1], rz = zi - xs[u][2];
+                    sx = fmaf(rx, ph[u], sx);
+                    sy = fmaf(ry, ph[u], sy);
+                    sz = fmaf(rz, ph[u], sz);
+                    sd += rx * rx + ry * ry + rz * rz;
+                }
+            }
+        }
+#pragma unroll
+        for (int o = LPN / 2; o > 0; o >>= 1) {
+            sx += __shfl_xor_sync(0xffffffffu, sx, o);
+            sy += __shfl_xor_sync(0xffffffffu, sy, o);
+            sz += __shfl_xor_sync(0xffffffffu, sz, o);
+            sd += __shfl_xor_sync(0xffffffffu, sd, o);
+        }
+        if (rr < rows && sub == 0) {
+            const int i = n0 + rr;
+            a.dxu[(size_t)i * 3 + 0] = sx;
+            a.dxu[(size_t)i * 3 + 1] = sy;
+            a.dxu[(size_t)i * 3 + 2] = sz;
+            a.Dn[i] = sd;
+        }
+    }
+    __syncthreads();
+    // ---- A tile = [h | M | 0 .. | 1] of this thread's row, 32 columns (+ the 16 trailing columns by column group 0)
+    {
+        float v[32];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            const int c = c0 + k;
+            v[k] = !valid ? 0.f : (c < H ? a.h[(size_t)n * H + c] : stageF[r * D + ((c - H) ^ (r & 31))]);
+        }
+        tc_split_store32(smem + L::a_hi, smem + L::a_lo, r, c0, v, true);
+        if (cg == 0) {
+            float t[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const int c = D + k;
+                t[k] = !valid ? 0.f : (c < KA ? stageF[r * D + ((c - H) ^ (r & 31))] : 0.f);
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                uint32_t hi[4], lw[4];
+#pragma unroll
+                for (int p = 0; p < 4; ++p) tc::split2(t[8 * j + 2 * p], t[8 * j + 2 * p + 1], hi[p], lw[p]);
+                *reinterpret_cast<uint4*>(smem + L::a_hi + tc::chunk_off(128, r, D / 8 + j)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(smem + L::a_lo + tc::chunk_off(128, r, D / 8 + j)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            }
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = *slot;
+    const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+    const uint32_t sb = tc::smem_u32(smem);
+    const TcOperand opA{sb + L::a_hi, sb + L::a_lo, TS, false};
+    const TcOperand opW{sb + L::w_hi, sb + L::w_lo, D * 16, false};
+    if (warp == NT / 32 - 1 && tc::elect_one()) {
+        tc_issue_op<NPASS>(tmem, 0, opA, opW, KP, D, false);  // z1
+        tc::mma_commit(&bars[0]);
+    }
+    if (!tc::mbar_wait(&bars[0], 0)) asm volatile("trap;");
+    tc::fence_after_sync();
+    // ---- s1 = SiLU(z1 + b1); partial dots with the H rows of Wh2 over this thread's 32 columns
+    {
+        float v[32], pd[8];
+        tc::tmem_ld32(trow + c0, v);
+#pragma unroll
+        for (int o = 0; o < 8; ++o) pd[o] = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const float s1 = tc_silu<true>(v[i] + vec[c0 + i]);
+#pragma unroll
+            for (int o = 0; o < 8; ++o)
+                if (o < H) pd[o] = fmaf(vec[D + o * D + c0 + i], s1, pd[o]);
+        }
+#pragma unroll
+        for (int o = 0; o < 8; ++o) sPart[(cg * 128 + r) * 8 + o] = pd[o];
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    for (int idx = tid; idx < rows * H; idx += NT) {  // h_out block of the tile is contiguous: coalesced
+        const int rr = idx / H, o = idx - rr * H;
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < NG; ++k) s += sPart[(k * 128 + rr) * 8 + o];
+        a.h_out[(size_t)n0 * H + idx] = s + a.P[lo.bh2 + o];
+    }
+    if (warp == 0) tc::tmem_dealloc(tmem, D);
+}
+
+template <int D, int NPASS>
+int launch_tc_node_fwd(const TcNodeFwdArgs& a, int grid, cudaStream_t st) {
+    constexpr int SMEM = TcNodeLayout<D>::TOTAL;
+    static bool configured = false;
+    if (!configured) {
+        EGNN_CUDA(cudaFuncSetAttribute(tc_node_fwd<D, NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        configured = true;
+    }
+    egnn_prof_begin(EGNN_K_NODE_FWD, st);
+    tc_node_fwd<D, NPASS><<<grid, 4 * D, SMEM, st>>>(a);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("tc_node_fwd");
+    return EGNN_OK;
+}
+
 template <int D, int NPASS>
 int launch_tc_node_bwd(const TcNodeBwdArgs& a, int grid, cudaStream_t st) {
     constexpr int SMEM = TcNodeLayout<D>::TOTAL;
@@ -275,4 +511,21 @@ int egnn_tc_node_backward(const egnn_net_t& net, int N, const float* params_laye
     const bool x3 = precision == EGNN_PREC_BF16X3;
     if (net.Mh == 128) return x3 ? launch_tc_node_bwd<128, 3>(a, grid, st) : launch_tc_node_bwd<128, 1>(a, grid, st);
     return x3 ? launch_tc_node_bwd<64, 3>(a, grid, st) : launch_tc_node_bwd<64, 1>(a, grid, st);
+}
+
+// node phase of one layer's forward on the tensor cores (the edge phase must have run on the tcgen05 path: 32-edge
+// partial segments, phi per edge)
+int egnn_tc_node_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
+                         const float* h, const float* x, const float* agg, const float* part, const float* phi_edge,
+                         float* h_out, float* msum, float* dxu, float* Dn, int precision, cudaStream_t st) {
+    EGNN_REQUIRE(tc_node_supported(net), "tcgen05 node path needs Hh = Ms = d in {64,128}");
+    EGNN_REQUIRE(part_tile_for(net) == 32, "tcgen05 node forward expects 32-edge partial segments");
+    (void)precision;  // K = d + 16 only: always three split-bf16 products, in the bf16 mode as well (h feeds every later layer)
+    const PackOff po = pack_off(net);
+    const uint8_t* blob = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    TcNodeFwdArgs a{net, g.N, part_tile_for(net), g.row_ptr, g.send, h, x, params_layer,
+                    blob + (tc_blob_bytes(net.Mh) + 15) / 16 * 16, agg, part, phi_edge, h_out, msum, dxu, Dn};
+    const int grid = (g.N + 127) / 128;
+    if (net.Mh == 128) return launch_tc_node_fwd<128, 3>(a, grid, st);
+    return launch_tc_node_fwd<64, 3>(a, grid, st);
 }
