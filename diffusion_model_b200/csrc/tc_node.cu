@@ -306,42 +306,57 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_fwd(TcNodeFwdArgs a) {
     }
     __syncthreads();
 
-    // ---- message sums of the tile: thread -> (row, column) with consecutive threads on consecutive columns.  Per
-    //      element up to three partial rows are read unconditionally-predicated (tail of the first segment or the agg
-    //      row, heads of the next two segments) so that UNR rows are in flight together; longer runs take the loop.
+    // ---- message sums of the tile: D/4 lanes own one row (a float4 each: rows of agg / part / msum are 16-byte
+    //      aligned).  Per row up to three partial rows are read under predicates (agg row or tail of the first segment,
+    //      heads of the next two) so that the loads of UNR rows are in flight together; longer runs take the loop.
     float* stageF = reinterpret_cast<float*>(smem + L::s_hi);
     {
-        constexpr int UNR = 8;
-        constexpr int RPI = NT / D;  // rows covered per iteration
-        const int m = tid % D, rsub = tid / D;
-        for (int rb0 = 0; rb0 < rows; rb0 += UNR * RPI) {
-            float p0[UNR], p1[UNR], p2[UNR];
+        constexpr int UNR = 4;
+        constexpr int LPR = D / 4, RPW = 32 / LPR;           // lanes per row, rows per warp and pass
+        constexpr int RPP = (NT / 32) * RPW;                  // rows per CTA pass
+        const int m4 = (lane % LPR) * 4;
+        const int rbase = warp * RPW + lane / LPR;
+        const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int rb0 = 0; rb0 < rows; rb0 += UNR * RPP) {
+            float4 p0[UNR], p1[UNR], p2[UNR];
 #pragma unroll
             for (int u = 0; u < UNR; ++u) {
-                const int rr = rb0 + u * RPI + rsub;
-                p0[u] = p1[u] = p2[u] = 0.f;
+                const int rr = rb0 + u * RPP + rbase;
+                p0[u] = p1[u] = p2[u] = zero4;
                 if (rr < rows) {
                     const int ea = sRow[rr], eb = sRow[rr + 1];
                     if (ea < eb) {
                         const int t0 = ea / TE, t1 = (eb - 1) / TE;
-                        p0[u] = t0 == t1 ? a.agg[(size_t)(n0 + rr) * AGGW + m] : a.part[((size_t)t0 * 2 + 1) * AGGW + m];
-                        if (t0 + 1 <= t1) p1[u] = a.part[((size_t)(t0 + 1) * 2) * AGGW + m];
-                        if (t0 + 2 <= t1) p2[u] = a.part[((size_t)(t0 + 2) * 2) * AGGW + m];
+                        const float* src = t0 == t1 ? a.agg + (size_t)(n0 + rr) * AGGW : a.part + ((size_t)t0 * 2 + 1) * AGGW;
+                        p0[u] = *reinterpret_cast<const float4*>(src + m4);
+                        if (t0 + 1 <= t1) p1[u] = *reinterpret_cast<const float4*>(a.part + ((size_t)(t0 + 1) * 2) * AGGW + m4);
+                        if (t0 + 2 <= t1) p2[u] = *reinterpret_cast<const float4*>(a.part + ((size_t)(t0 + 2) * 2) * AGGW + m4);
                     }
                 }
             }
 #pragma unroll
             for (int u = 0; u < UNR; ++u) {
-                const int rr = rb0 + u * RPI + rsub;
+                const int rr = rb0 + u * RPP + rbase;
                 if (rr < rows) {
-                    float sum = (p0[u] + p1[u]) + p2[u];
+                    float4 sum = make_float4((p0[u].x + p1[u].x) + p2[u].x, (p0[u].y + p1[u].y) + p2[u].y,
+                                             (p0[u].z + p1[u].z) + p2[u].z, (p0[u].w + p1[u].w) + p2[u].w);
                     const int ea = sRow[rr], eb = sRow[rr + 1];
                     if (ea < eb) {
                         const int t1 = (eb - 1) / TE;
-                        for (int t = ea / TE + 3; t <= t1; ++t) sum += a.part[((size_t)t * 2) * AGGW + m];
+                        for (int t = ea / TE + 3; t <= t1; ++t) {
+                            const float4 ph = *reinterpret_cast<const float4*>(a.part + ((size_t)t * 2) * AGGW + m4);
+                            sum.x += ph.x;
+                            sum.y += ph.y;
+                            sum.z += ph.z;
+                            sum.w += ph.w;
+                        }
                     }
-                    a.msum[(size_t)(n0 + rr) * D + m] = sum;
-                    stageF[rr * D + (m ^ (rr & 31))] = sum;
+                    *reinterpret_cast<float4*>(a.msum + (size_t)(n0 + rr) * D + m4) = sum;
+                    const int sw = rr & 31;
+                    stageF[rr * D + ((m4 + 0) ^ sw)] = sum.x;
+                    stageF[rr * D + ((m4 + 1) ^ sw)] = sum.y;
+                    stageF[rr * D + ((m4 + 2) ^ sw)] = sum.z;
+                    stageF[rr * D + ((m4 + 3) ^ sw)] = sum.w;
                 }
             }
         }
@@ -520,6 +535,8 @@ int egnn_tc_node_forward(const egnn_net_t& net, const egnn_graph_t& g, const flo
                          float* h_out, float* msum, float* dxu, float* Dn, int precision, cudaStream_t st) {
     EGNN_REQUIRE(tc_node_supported(net), "tcgen05 node path needs Hh = Ms = d in {64,128}");
     EGNN_REQUIRE(part_tile_for(net) == 32, "tcgen05 node forward expects 32-edge partial segments");
+    EGNN_REQUIRE(((reinterpret_cast<uintptr_t>(agg) | reinterpret_cast<uintptr_t>(part) | reinterpret_cast<uintptr_t>(msum)) & 15) == 0,
+                 "workspace must be 16-byte aligned");
     (void)precision;  // K = d + 16 only: always three split-bf16 products, in the bf16 mode as well (h feeds every later layer)
     const PackOff po = pack_off(net);
     const uint8_t* blob = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
