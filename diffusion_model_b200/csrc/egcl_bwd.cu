@@ -131,22 +131,38 @@ __global__ void __launch_bounds__(256) egcl_node_bwd(NodeBwdArgs a) {
 // grad[p] = sum of the partial rows that hold parameter p, in row order.  rows_m > 0: the tensor-core edge backward
 // gives rows [0, rows_m) to the mlp_m + attention parameters and rows [rows_m, rowsE) to the mlp_x parameters (other
 // entries of a row are never written, so they must not be read); otherwise every edge row holds every edge parameter.
+// 64 parameters x 4 row groups per CTA: group g sums rows r0+g, r0+g+4, ... (eight loads in flight), the four group
+// sums are then added in group order -- a fixed order, so reruns are bit-identical.
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ part, int rowsE, int rowsN, int n,
                                                               int x_begin, int h_begin, int h_end, int rows_m,
                                                               float* __restrict__ out) {
-    const int p = blockIdx.x * 256 + threadIdx.x;
-    if (p >= n) return;
-    int r0 = 0, r1 = rowsE;
-    if (p >= h_begin && p < h_end) {
-        r0 = rowsE;
-        r1 = rowsE + rowsN;
-    } else if (rows_m > 0) {
-        if (p >= x_begin && p < h_begin) r0 = rows_m;
-        else r1 = rows_m;
-    }
+    __shared__ float red[4][64];
+    const int pc = threadIdx.x & 63, g = threadIdx.x >> 6;
+    const int p = blockIdx.x * 64 + pc;
     float s = 0.f;
-    for (int r = r0; r < r1; ++r) s += part[(size_t)r * n + p];
-    out[p] = s;
+    if (p < n) {
+        int r0 = 0, r1 = rowsE;
+        if (p >= h_begin && p < h_end) {
+            r0 = rowsE;
+            r1 = rowsE + rowsN;
+        } else if (rows_m > 0) {
+            if (p >= x_begin && p < h_begin) r0 = rows_m;
+            else r1 = rows_m;
+        }
+        const float* src = part + p;
+        int r = r0 + g;
+        for (; r + 28 < r1; r += 32) {
+            float v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = src[(size_t)(r + 4 * k) * n];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s += v[k];
+        }
+        for (; r < r1; r += 4) s += src[(size_t)r * n];
+    }
+    red[g][pc] = s;
+    __syncthreads();
+    if (g == 0 && p < n) out[p] = ((red[0][pc] + red[1][pc]) + red[2][pc]) + red[3][pc];
 }
 
 struct GatherArgs {
@@ -575,7 +591,7 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
             egnn_prof_end(st);
             EGNN_CHECK_LAUNCH("egcl_gather_bwd");
         }
-        reduce_partials_kernel<<<(lo.total + 255) / 256, 256, 0, st>>>(ws + bw.part, rowsE, rowsN, lo.total, lo.wx1, lo.wh1,
+        reduce_partials_kernel<<<(lo.total + 63) / 64, 256, 0, st>>>(ws + bw.part, rowsE, rowsN, lo.total, lo.wx1, lo.wh1,
                                                                       lo.wa, rows_m,
                                                                       grad_params + (size_t)l * lo.total);
         EGNN_CHECK_LAUNCH("reduce_partials_kernel");
