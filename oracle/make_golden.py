@@ -305,6 +305,51 @@ def golden_loops(egnn_mod, dxh):
     print("traj_cfg1: finite =", finite, "|pos|max =", float(pos_f.abs().max()), "fp32-vs-fp64 relerr =", dev)
 
 
+def golden_conditional(egnn_mod):
+    """Conditional model (parameters.yaml: conditional, to_compress_spectrum, give_exO): h = [h_t | compressor(spectrum) |
+    exO | t/T] (parts/train_per_iretation.py:136-145), H = 2 + 32 + 1 + 1 = 36, driven by the UNMODIFIED reference EGNN
+    and DataPreprocessor.SpectrumCompressor; widths reduced so the fixture stays small."""
+    import importlib
+    dpp = importlib.import_module("DataPreprocessor")
+    A, C, S = 2, 32, 200
+    H = A + C + 1 + 1
+    sizes = dict(L=2, m_input=2 * H + 1, m_hidden=96, m_output=64, x_input=2 * H + 1, x_hidden=80, x_output=1,
+                 h_input=H + 64, h_hidden=112, h_output=H)
+    torch.manual_seed(2024)
+    ref = egnn_mod.EquivariantGNN(**sizes)
+    comp = dpp.SpectrumCompressor(S, [64, 48], C)
+    sd = {k: v.detach().clone() for k, v in ref.state_dict().items()}
+    csd = {k: v.detach().clone() for k, v in comp.state_dict().items()}
+    T = 1000
+    sch = D.Schedule(1e-5, 2.0, T)
+    b = G.make_batch(3, 20, seed=41, edges="fc")
+    pos, x1h = torch.from_numpy(b["pos"]), torch.from_numpy(b["x"])
+    ei, batch = torch.from_numpy(b["edge_index"]), torch.from_numpy(b["batch"])
+    N = pos.shape[0]
+    gen = torch.Generator().manual_seed(17)
+    spectrum = torch.rand(N, S, generator=gen)
+    exO = (torch.arange(N) % 20 == 0).float().view(N, 1)  # the excited O is atom 0 of every structure
+    t_g = torch.tensor([3, 512, 1000])
+    n_pos, n_h = torch.randn(N, 3, generator=gen), torch.randn(N, A, generator=gen)
+    cond = torch.cat((comp(spectrum), exO), dim=1)
+    loss, aux = LP.train_loss(lambda e, h, x: ref(e, h, x), sch, pos, x1h, ei, batch, t_g, n_pos, n_h, A=A, cond=cond)
+    loss.backward()
+    out = dict(pos=b["pos"], x=b["x"], edge_index=b["edge_index"], batch=b["batch"], t=t_g.numpy(), noise_pos=n_pos.numpy(),
+               noise_h=n_h.numpy(), spectrum=spectrum.numpy(), exO=exO.numpy(), loss=np.float64(loss.item()),
+               h_in=aux["h_in"].detach().numpy(), h_out=aux["h_out"].detach().numpy(), x_out=aux["x_out"].detach().numpy(),
+               size_keys=np.array(list(sizes.keys())), sizes=np.array(list(sizes.values())))
+    for k, v in sd.items():
+        out["w:" + k] = v.numpy()
+    for k, p_ in ref.named_parameters():
+        out["g:" + k] = p_.grad.numpy()
+    for k, v in csd.items():
+        out["cw:" + k] = v.numpy()
+    for k, p_ in comp.named_parameters():
+        out["cg:" + k] = p_.grad.numpy()
+    np.savez_compressed(os.path.join(GOLD, "loss_cond.npz"), **out)
+    print("loss_cond: H =", H, "loss =", loss.item())
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(4)
@@ -313,6 +358,7 @@ def main():
     golden_edges()
     golden_egnn(egnn_mod)
     golden_loops(egnn_mod, dxh)
+    golden_conditional(egnn_mod)
     print("golden vectors written to", GOLD)
 
 

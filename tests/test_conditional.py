@@ -1,0 +1,149 @@
+"""Conditional model: h = [h_t | SpectrumCompressor(spectrum) | exO | t/T], H = 36
+(parts/train_per_iretation.py:136-145, DataPreprocessor.py:4-22).  Golden 'loss_cond' comes from the UNMODIFIED reference
+EGNN and SpectrumCompressor (oracle/make_golden.py: golden_conditional).
+
+CPU: the oracle restatement reproduces the reference's loss and gradients.  GPU (-m gpu): the CUDA path through
+batch_loss / sample_structures with the conditioning block, against the golden and the oracle sampler loop.
+Bars: loss 1e-5, outputs 1e-4, gradients 1e-3.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import diffusion_ref as D
+from oracle import egnn_ref, graphs_ref as G, loops_ref as LP
+
+torch.set_num_threads(4)
+A, C = 2, 32
+
+
+def load(golden_dir):
+    return np.load(os.path.join(golden_dir, "loss_cond.npz"), allow_pickle=False)
+
+
+def sizes_of(z):
+    return {str(k): int(v) for k, v in zip(z["size_keys"], z["sizes"])}
+
+
+def relerr(a, b):
+    a, b = torch.as_tensor(a).detach().cpu().double(), torch.as_tensor(b).detach().cpu().double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def compressor_ref(z, spectrum, requires_grad=False):
+    """DataPreprocessor.py:4-22 restated as plain tensor ops on the golden's weights: Linear/ReLU x2, Linear."""
+    w = {k[3:]: torch.from_numpy(z[k]).clone().requires_grad_(requires_grad) for k in z.files if k.startswith("cw:")}
+    y = spectrum
+    idx = sorted({int(k.split(".")[1]) for k in w})
+    for n, i in enumerate(idx):
+        y = y @ w[f"mlp.{i}.weight"].t() + w[f"mlp.{i}.bias"]
+        if n + 1 < len(idx):
+            y = torch.relu(y)
+    return y, w
+
+
+def test_oracle_conditional_loss(golden_dir):
+    z = load(golden_dir)
+    sizes = sizes_of(z)
+    sd = {k[2:]: torch.from_numpy(z[k]).clone().requires_grad_(True) for k in z.files if k.startswith("w:")}
+    comp, cw = compressor_ref(z, torch.from_numpy(z["spectrum"]), requires_grad=True)
+    cond = torch.cat((comp, torch.from_numpy(z["exO"])), dim=1)
+    sch = D.Schedule(1e-5, 2.0, 1000)
+    fwd = lambda e, h, x: egnn_ref.egnn_forward(sd, sizes["L"], e, h, x)
+    loss, aux = LP.train_loss(fwd, sch, torch.from_numpy(z["pos"]), torch.from_numpy(z["x"]),
+                              torch.from_numpy(z["edge_index"]), torch.from_numpy(z["batch"]), torch.from_numpy(z["t"]),
+                              torch.from_numpy(z["noise_pos"]), torch.from_numpy(z["noise_h"]), A=A, cond=cond)
+    assert aux["h_in"].shape[1] == 36
+    assert np.array_equal(aux["h_in"].detach().numpy(), z["h_in"])
+    assert abs(loss.item() - float(z["loss"])) <= 1e-5 * float(z["loss"])
+    loss.backward()
+    for k, p in sd.items():
+        assert relerr(p.grad, z["g:" + k]) <= 1e-4, k
+    for k, p in cw.items():
+        assert relerr(p.grad, z["cg:" + k]) <= 1e-4, k
+
+
+def test_spectrum_compressor_state_dict(golden_dir):
+    """drop-in module: same keys, shapes and forward as the reference's (weights from the golden)"""
+    from diffusion_model_b200.DataPreprocessor import SpectrumCompressor
+    z = load(golden_dir)
+    m = SpectrumCompressor(200, [64, 48], C)
+    want = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("cw:")}
+    assert list(m.state_dict().keys()) == list(want.keys())
+    m.load_state_dict(want)
+    spec = torch.from_numpy(z["spectrum"])
+    ref, _ = compressor_ref(z, spec)
+    assert relerr(m(spec), ref) <= 1e-6
+    assert np.array_equal(m(spec).detach().numpy(), z["h_in"][:, A:A + C]) or relerr(m(spec), z["h_in"][:, A:A + C]) <= 1e-6
+
+
+@pytest.mark.gpu
+def test_conditional_training_loss_and_grads(lib, golden_dir):
+    from diffusion_model_b200.data import Data
+    from diffusion_model_b200.DataPreprocessor import SpectrumCompressor
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    from diffusion_model_b200.train_per_iretation import _conditioning, batch_loss
+    z = load(golden_dir)
+    net = EquivariantGNN(**sizes_of(z))
+    net.load_state_dict({k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w:")})
+    net = net.to("cuda")
+    comp = SpectrumCompressor(200, [64, 48], C)
+    comp.load_state_dict({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("cw:")})
+    comp = comp.to("cuda")
+    dp = E3DiffusionProcess(s=1e-5, power=2.0, num_diffusion_timestep=1000)
+    bd = Data(x=torch.from_numpy(z["x"]).cuda(), pos=torch.from_numpy(z["pos"]).cuda(),
+              edge_index=torch.from_numpy(z["edge_index"]).cuda())
+    bd.batch = torch.from_numpy(z["batch"]).cuda()
+    bd.spectrum = torch.from_numpy(z["spectrum"]).cuda()
+    bd.exO = torch.from_numpy(z["exO"]).cuda()
+    params = dict(atom_type_size=A, conditional=True, to_compress_spectrum=True, give_exO=True)
+    cond = _conditioning(bd, params, {"egnn": net, "spectrum_compressor": comp})
+    assert cond.shape == (60, C + 1)
+    loss, G_, aux = batch_loss(net, bd, dp, params, t=z["t"].tolist(), noise_pos=torch.from_numpy(z["noise_pos"]).cuda(),
+                               noise_h=torch.from_numpy(z["noise_h"]).cuda(), cond=cond)
+    assert G_ == 3
+    assert relerr(aux["h_in"], z["h_in"]) <= 1e-6
+    assert abs(loss.item() - float(z["loss"])) <= 1e-5 * float(z["loss"])
+    assert relerr(aux["h_out"], z["h_out"]) <= 1e-4 and relerr(aux["x_out"], z["x_out"]) <= 1e-4
+    loss.backward()
+    for k, p in net.named_parameters():
+        assert relerr(p.grad, z["g:" + k]) <= 1e-3, k
+    for k, p in comp.named_parameters():  # the gradient reaches the conditioning network through gh_in of the EGNN
+        assert relerr(p.grad, z["cg:" + k]) <= 1e-3, k
+    with pytest.raises(Exception):  # H = 36 has no tcgen05 tile: the library must refuse, not fall back silently
+        net.precision = "bf16x3"
+        batch_loss(net, bd, dp, params, t=z["t"].tolist(), cond=cond.detach())
+    net.precision = "fp32"
+
+
+@pytest.mark.gpu
+def test_conditional_sampler_against_oracle(lib, golden_dir):
+    """generate()'s loop with the conditioning block held constant over the T steps (:340-352), injected noise"""
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    from diffusion_model_b200.sampler import sample_structures
+    z = load(golden_dir)
+    sizes = sizes_of(z)
+    sd = egnn_ref.tame_state_dict({k[2:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("w:")}, sizes["L"])
+    net = EquivariantGNN(**sizes)
+    net.load_state_dict(sd)
+    net = net.to("cuda")
+    n, T = 20, 60
+    comp, _ = compressor_ref(z, torch.from_numpy(z["spectrum"][:n]))
+    cond = torch.cat((comp, torch.from_numpy(z["exO"][:n])), dim=1)
+    sch = D.Schedule(0.05, 2.0, T)
+    dp = E3DiffusionProcess(s=0.05, power=2.0, num_diffusion_timestep=T)
+    noises = LP.make_noises(n, T, A, torch.Generator().manual_seed(77))
+    eifc = torch.from_numpy(G.fc_edges(n))
+    with torch.no_grad():
+        pos, hf, atoms, finite = LP.sample_structure(lambda e, h, x: egnn_ref.egnn_forward(sd, sizes["L"], e, h, x), sch,
+                                                     eifc, n, noises, A=A, cond=cond)
+    assert finite
+    for graphs in (False, True):
+        out = sample_structures(net, dp, n, 1, atom_type_size=A, cond=cond.cuda(), noises=noises, use_cuda_graph=graphs)
+        assert bool(out["finite"][0])
+        assert relerr(out["pos"][0], pos) < 5e-4 and relerr(out["h"][0], hf) < 5e-4
+        assert np.array_equal(out["atoms"][0].cpu().numpy(), atoms.numpy())
