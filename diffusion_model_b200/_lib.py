@@ -63,6 +63,9 @@ SIGNATURES = {
                                     _I32, _P, _P, _P]),
     "egnn_counter_add": (C.c_int, [_P, _I32, _P]),
     "egnn_adam_step": (C.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _F, _P]),
+    "egnn_rdf_local": (C.c_int, [_P, _P, _I32, _P, _P, _P, _I32, C.c_double, C.c_double, _P, _I32, _P, _P, _P, _P]),
+    "egnn_cn2_sites": (C.c_int, [_P, _P, _I32, _F, _P, _P, _P, _P, _P]),
+    "egnn_kabsch": (C.c_int, [_P, _P, _P, _I32, _P, _P, _P, _P]),
 }
 
 _lib = None

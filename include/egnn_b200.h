@@ -182,6 +182,32 @@ int egnn_adam_step(float* params, const float* grads, float* exp_avg, float* exp
                    float beta1, float beta2, float eps, float weight_decay, int32_t step, float grad_scale,
                    void* stream);
 
+/* ---- structure analysis ("sample -> evaluate"): one CTA per structure; structures are the node
+ *      ranges node_ptr[s] .. node_ptr[s+1] of pos [N,3]; atom 0 of a structure is its first node ------------------- */
+/* Local RDF around atom 0 (replaces evaluate_RDF.py:39-60, RDF + length_from_exO).
+ *   counts [S,nbins] int32: #{i >= 1 : edge_lo[k] < |p_i - p_0| < edge_hi[k]}, compared in fp32 like the reference
+ *                           (edge_lo/hi = fp32 images of r_k and r_k + dR, r = np.arange(dR, R + dR, dR));
+ *   rdf    [S,nbins] f64  : gaussian_filter1d(counts / (4 pi rho r_k^2 dR)), rho = n_s / vol, correlation weights
+ *                           `weights` [2*radius+1] (host-computed Gaussian, boundary mode 'reflect');
+ *   dists  [N] f32 or NULL: |p_i - p_0| of every atom (0 for atom 0).
+ * r_sq [nbins] f64 = r_k^2.  nbins <= 4096. */
+int egnn_rdf_local(const float* pos, const int32_t* node_ptr, int32_t S, const float* edge_lo, const float* edge_hi,
+                   const double* r_sq, int32_t nbins, double dR, double vol, const double* weights, int32_t radius,
+                   int32_t* counts, double* rdf, float* dists, void* stream);
+/* Two-coordinated site of atom 0 (replaces the selection loop of evaluate_Si-O-Si.py:28-39 and
+ * CN2_evaluate.py:12-21 calculate_angle_for_CN2 / calculate_bond_length_for_CN2).
+ *   radius > 0 : count [S] = atoms i >= 1 with |p_i - p_0| < radius; idx [S,2] = the first two of them in index order;
+ *   radius <= 0: idx = the two atoms nearest to atom 0 (index order), count = min(2, n - 1);
+ *   angle_deg [S] f64 = degrees(acos(cos)) at atom 0, bonds [S,2] f32 = the two bond lengths (NaN when fewer than two
+ *   atoms were selected; -1 in idx). */
+int egnn_cn2_sites(const float* pos, const int32_t* node_ptr, int32_t S, float radius, int32_t* count, int32_t* idx,
+                   double* angle_deg, float* bonds, void* stream);
+/* Kabsch alignment of P onto Q per structure (replaces evaluate_rmsd_for_pos_generate.py:11-51 kabsch_torch):
+ * R [S,3,3], t [S,3] = centroid(Q) - centroid(P), rmsd [S].  Keeps the reference's handedness quirk (:42-45): for a
+ * left-handed V U^T it returns diag(1,1,-1) V U^T. */
+int egnn_kabsch(const float* P, const float* Q, const int32_t* node_ptr, int32_t S, float* R, float* t, float* rmsd,
+                void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,7 +5,8 @@ lengths of atom 0 with two neighbours.  Pinned against the unmodified reference 
 
 Follows: evaluate_RDF.py:39-45 (length_from_exO), :48-60 (RDF), :62-63 (cos_similarity), :13-24 (Wasserstein);
 CN2_evaluate.py:12-21 (calculate_angle_for_CN2, calculate_bond_length_for_CN2);
-evaluate_Si-O-Si.py:28-33 (neighbour selection: atoms within a radius of atom 0).
+evaluate_Si-O-Si.py:28-33 (neighbour selection: atoms within a radius of atom 0);
+evaluate_rmsd_for_pos_generate.py:11-51 (kabsch_torch).
 """
 import numpy as np
 import torch
@@ -19,16 +20,29 @@ def length_from_exO(position):
     return [torch.norm(position[i] - position[0]) for i in range(1, len(position))]
 
 
+def rdf_edges(R=5.0, dR=0.01):
+    """bin edges of evaluate_RDF.py:53-56: r over np.arange(dR, R+dR, dR) (float64) and r + dR.  ``r < d < r + dR``
+    there compares a python/numpy float with a 0-dim fp32 torch tensor, which torch evaluates in FP32 (the scalar is
+    cast to the tensor's dtype): the effective edges are fp32(r) and fp32(r + dR).  Adjacent bins can therefore overlap
+    or leave a gap of one ulp; a distance exactly equal to fp32(r) is in neither bin."""
+    r = np.arange(0 + dR, R + dR, dR)
+    return r, r.astype(np.float32), (r + dR).astype(np.float32)
+
+
+def rdf_counts(position, R=5.0, dR=0.01):
+    """integer histogram of evaluate_RDF.py:55 (the numerator), one count per bin"""
+    lengths = np.array([float(d) for d in length_from_exO(position)], dtype=np.float32)
+    _, lo, hi = rdf_edges(R, dR)
+    return np.array([np.count_nonzero((lo[k] < lengths) & (lengths < hi[k])) for k in range(len(lo))], dtype=np.int64)
+
+
 def rdf(position, sigma=5, R=5.0, dR=0.01, Normalize=False):
     """evaluate_RDF.py:48-60: histogram of the distances from atom 0 with STRICT bin edges r < d < r + dR over
     r = arange(dR, R + dR, dR), normalised by 4 pi rho r^2 dR with rho = n / (4/3 pi R^3), then gaussian_filter1d."""
-    lengths = np.array([float(d) for d in length_from_exO(position)], dtype=np.float64)
     num_atom = len(position)
     ro = num_atom / (4 / 3 * np.pi * R ** 3)
-    edges = np.arange(0 + dR, R + dR, dR)
-    out = np.empty(len(edges))
-    for k, r in enumerate(edges):
-        out[k] = np.count_nonzero((r < lengths) & (lengths < r + dR)) / (4 * np.pi * ro * r ** 2 * dR)
+    edges, _, _ = rdf_edges(R, dR)
+    out = rdf_counts(position, R, dR) / (4 * np.pi * ro * edges ** 2 * dR)
     out = gaussian_filter1d(out, sigma)
     if Normalize:
         out = out / np.max(out)
@@ -85,3 +99,32 @@ def structure_set_stats(positions, R, dR, sigma=5):
         b1, b2 = bond_lengths_cn2(tri)
         bonds.append(0.5 * (b1 + b2))
     return dict(rdf=np.mean(curves, axis=0), dists=np.array(dists), angles=np.array(angles), bonds=np.array(bonds))
+
+
+def kabsch(P, Q):
+    """evaluate_rmsd_for_pos_generate.py:11-51 (kabsch_torch): rotation, translation and RMSD aligning P onto Q.  Kept
+    quirk (:42-45): for a left-handed V U^T the reference negates the last COLUMN of Vt (the commented-out line negates
+    the last row), i.e. R = diag(1,1,-1) V U^T -- an improper matrix times a mirror, not the optimal proper rotation."""
+    P, Q = torch.as_tensor(P, dtype=torch.float32), torch.as_tensor(Q, dtype=torch.float32)
+    cP, cQ = torch.mean(P, dim=0), torch.mean(Q, dim=0)
+    t = cQ - cP
+    p, q = P - cP, Q - cQ
+    H = torch.matmul(p.transpose(0, 1), q)
+    U, S, Vt = torch.linalg.svd(H)
+    if torch.det(torch.matmul(Vt.transpose(0, 1), U.transpose(0, 1))) < 0.0:
+        Vt = Vt.clone()
+        Vt[:, -1] *= -1.0
+    R = torch.matmul(Vt.transpose(0, 1), U.transpose(0, 1))
+    rmsd = torch.sqrt(torch.sum(torch.square(torch.matmul(p, R.transpose(0, 1)) - q)) / P.shape[0])
+    return R, t, rmsd
+
+
+def cn2_site(position, radius=2.0):
+    """evaluate_Si-O-Si.py:28-39 for one structure: neighbours of atom 0 within ``radius``; when there are exactly two,
+    the angle (degrees) and the two bond lengths of CN2_evaluate.py:12-21, else None for those."""
+    position = torch.as_tensor(position, dtype=torch.float32)
+    nb = neighbours_within(position, radius)
+    if len(nb) != 2:
+        return nb, None, None
+    tri = position[[0] + nb]
+    return nb, angle_cn2(tri), bond_lengths_cn2(tri)

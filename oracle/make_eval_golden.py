@@ -34,12 +34,13 @@ def import_reference():
     sys.path.insert(0, REF)
     import evaluate_RDF
     import CN2_evaluate
-    return evaluate_RDF, CN2_evaluate
+    import evaluate_rmsd_for_pos_generate as rmsd_mod
+    return evaluate_RDF, CN2_evaluate, rmsd_mod
 
 
 def main():
     from oracle import eval_ref as E
-    ref_rdf, ref_cn2 = import_reference()
+    ref_rdf, ref_cn2, ref_rmsd = import_reference()
     gen = torch.Generator().manual_seed(2024)
     out = {}
     for k, (n, scale, R, dR) in enumerate([(24, 2.0, 5.0, 0.01), (64, 3.0, 5.0, 0.01), (24, 30.0, 120.0, 0.25)]):
@@ -55,6 +56,32 @@ def main():
         ang, (b1, b2) = ref_cn2.calculate_angle_for_CN2(tri), ref_cn2.calculate_bond_length_for_CN2(tri)
         assert ang == E.angle_cn2(tri) and (b1, b2) == E.bond_lengths_cn2(tri)
         out[f"cn2_{k}"] = np.array([ang, b1, b2])
+        out[f"cnt{k}"] = E.rdf_counts(pos, R=R, dR=dR)
+    # adversarial cloud: distances sitting EXACTLY on the fp32 images of bin edges and one ulp either side -- the
+    # reference's fp32 comparison (see eval_ref.rdf_edges) decides these, a float64 comparison would not
+    _, lo, hi = E.rdf_edges(5.0, 0.01)
+    ds = []
+    for k in (0, 4, 17, 99, 250, 498, 499):
+        for v in (lo[k], hi[k]):
+            ds += [v, np.nextafter(v, np.float32(0)), np.nextafter(v, np.float32(10))]
+    pos = torch.zeros(len(ds) + 1, 3)
+    pos[1:, 0] = torch.tensor(np.array(ds, dtype=np.float32)) * torch.tensor([1.0, -1.0] * (len(ds) // 2))
+    want = ref_rdf.RDF(pos, R=5.0, dR=0.01)
+    assert np.array_equal(np.asarray(want), E.rdf(pos, R=5.0, dR=0.01)), "edge-case cloud"
+    out["pos_edge"], out["rdf_edge"], out["cnt_edge"] = pos.numpy(), np.asarray(want), E.rdf_counts(pos, 5.0, 0.01)
+    # Kabsch alignment (evaluate_rmsd_for_pos_generate.py:11-51): a rotated + noisy copy and a MIRRORED copy (det < 0 branch)
+    for k, (n, mirror) in enumerate([(24, False), (24, True), (192, False), (3, True)]):
+        P = 3.0 * torch.randn(n, 3, generator=gen)
+        A_ = torch.linalg.qr(torch.randn(3, 3, generator=gen))[0]
+        if (torch.det(A_) < 0) != mirror:
+            A_[:, 0] *= -1.0
+        Q = P @ A_.T + 0.1 * torch.randn(n, 3, generator=gen) + torch.tensor([1.0, -2.0, 0.5])
+        Rr, tr, rr = ref_rmsd.kabsch_torch(P, Q)
+        Ro, to, ro = E.kabsch(P, Q)
+        assert torch.equal(Rr, Ro) and torch.equal(tr, to) and torch.equal(rr, ro), k
+        out[f"kab_P{k}"], out[f"kab_Q{k}"] = P.numpy(), Q.numpy()
+        out[f"kab_R{k}"], out[f"kab_t{k}"], out[f"kab_rmsd{k}"] = Rr.numpy(), tr.numpy(), np.array(rr.item())
+        out[f"kab_det{k}"] = np.array(torch.det(Rr).item())
     a, b = out["rdf0"], out["rdf1"][: len(out["rdf0"])]
     assert ref_rdf.cos_similarity(a, b) == E.cos_similarity(a, b)
     assert ref_rdf.calculate_wasserstein_distance(a, b) == E.wasserstein(a, b)
