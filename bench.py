@@ -33,7 +33,11 @@ import torch
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-CFG = dict(L=6, d=128, H=3, A=2, graphs=64, atoms=192, r_c=5.0, T=1000, s=1e-5, power=2.0, lr=1e-5, seed=2024)
+CFG = dict(L=6, d=128, H=3, A=2, graphs=64, atoms=192, r_c=5.0, T=1000, s=1e-5, power=2.0, lr=1e-5, seed=2024, name="cfg2",
+           cpu_graphs=8)
+# --workload cfg4 (BASELINE configs[3]: 1536-atom cells, 9 layers, hidden 256, 8 graphs per GPU); not the contract line.
+# Hidden 256 has no tcgen05 tile yet (one branch's W2 hi/lo image is 256 KB): it runs the fp32 FFMA kernels.
+CFG4 = dict(L=9, d=256, graphs=8, atoms=1536, name="cfg4", cpu_graphs=1)
 DENSITY = 0.0662  # atoms / A^3, a-SiO2
 
 
@@ -167,7 +171,7 @@ def run_reference(args, rank):
     from oracle import egnn_ref, graphs_ref as G
     torch.manual_seed(CFG["seed"])
     sd = egnn_ref.init_state_dict(**net_sizes(CFG["L"], CFG["d"], CFG["H"]))
-    graphs = 8
+    graphs = CFG["cpu_graphs"]
     ei = torch.from_numpy(G.cutoff_edges_batch(pos[: graphs * CFG["atoms"]].numpy(), node_ptr[: graphs + 1].numpy(),
                                                CFG["r_c"], box[:graphs].numpy()))
     p, o, e, b = cpu_sample(pos, onehot, ei, node_ptr, graphs)
@@ -179,7 +183,7 @@ def run_reference(args, rank):
     times = cpu_train_steps(p, o, e, b, sd, args.steps, args.warmup, threads)
     total = sum(times)
     value = graphs * len(times) / total
-    sample = f"{graphs} of the 64 graphs of the batch per step ({p.shape[0]} atoms, {e.shape[1]} edges), fp32, torch CPU"
+    sample = f"{graphs} of the {CFG['graphs']} graphs of the batch per step ({p.shape[0]} atoms, {e.shape[1]} edges), fp32, torch CPU"
     line = dict(impl="reference", metric="denoiser graph-steps/s (training fwd+bwd+optimizer)", value=value,
                 unit="graph-steps/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
                 ms_per_step=1e3 * total / len(times), higher_is_better=True, scaling="weak", vs_baseline=None,
@@ -191,8 +195,8 @@ def run_reference(args, rank):
 
 
 def workload_config(precision):
-    return dict(workload="cfg2: eps-pred training step, 64 x 192-atom periodic cutoff graphs (r_c=5A) per GPU, EGNN L=6 d=128 H=3, "
-                         "T=1000, Adam lr=1e-5", graphs_per_gpu=CFG["graphs"], atoms=CFG["atoms"], r_c=CFG["r_c"], L=CFG["L"],
+    return dict(workload=f"{CFG['name']}: eps-pred training step, {CFG['graphs']} x {CFG['atoms']}-atom periodic cutoff graphs (r_c=5A) "
+                         f"per GPU, EGNN L={CFG['L']} d={CFG['d']} H=3, T=1000, Adam lr=1e-5", graphs_per_gpu=CFG["graphs"], atoms=CFG["atoms"], r_c=CFG["r_c"], L=CFG["L"],
                 hidden=CFG["d"], precision=precision, parallelism="data-parallel, one NCCL all-reduce of the flat gradient per step",
                 l2="256 MB buffer written between timed steps (L2 flush, inside the timed region)")
 
@@ -371,11 +375,11 @@ def run_product(args, rank, world, local):
                 train_flops_per_step=3 * fwd_flops(CFG["L"], d, CFG["H"], N, E))
     if rank == 0 and world == 1:
         threads = os.cpu_count() or 1
-        graphs = 8
+        graphs = CFG["cpu_graphs"]
         p, o, e, b = cpu_sample(pos_h, oh_h, ei_d.cpu(), node_ptr_h.long(), graphs)
         times = cpu_train_steps(p, o, e, b, sd_cpu, 2, 1, threads)
         line["cpu_baseline"] = dict(value=graphs * len(times) / sum(times), unit="graph-steps/s", cores=threads, kind="port",
-                                    sample=f"{graphs} of the 64 graphs per step ({e.shape[1]} edges), 2 timed steps, oracle/ "
+                                    sample=f"{graphs} of the {CFG['graphs']} graphs per step ({e.shape[1]} edges), 2 timed steps, oracle/ "
                                            "restatement with torch CPU autograd + Adam")
     if rank == 0:
         print(json.dumps(line), flush=True)
@@ -390,7 +394,12 @@ def main():
     ap.add_argument("--precision", default="bf16x3", choices=["fp32", "bf16x3", "bf16"],
                     help="bf16x3 (default): tcgen05 split-bf16 products, fp32 accumulate, <=1e-4 per layer vs the fp32 "
                          "reference; fp32: CUDA-core FFMA; bf16: single tcgen05 product (looser, stated bound)")
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4"],
+                    help="cfg2 (default, the contract line) or cfg4 (1536-atom cells, L=9, hidden 256; fp32 kernels)")
     args = ap.parse_args()
+    if args.workload == "cfg4":
+        CFG.update(CFG4)
+        args.precision = "fp32"
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         run_reference(args, int(os.environ.get("RANK", "0")))
