@@ -79,6 +79,11 @@ struct PackOff {
 __host__ __device__ static inline bool tc_supported(const egnn_net_t& n) {
     return n.Mh == n.Ms && n.Ms == n.Xh && (n.Mh == 64 || n.Mh == 128) && 2 * n.H + 1 <= 16;
 }
+// the tcgen05 edge FORWARD additionally covers d = 256 (tc_edge256.cu: one branch per CTA, W2 streamed through shared
+// memory in K slices by bulk-async copies); its backward still runs on the FFMA kernels
+__host__ __device__ static inline bool tc_fwd_supported(const egnn_net_t& n) {
+    return n.Mh == n.Ms && n.Ms == n.Xh && (n.Mh == 64 || n.Mh == 128 || n.Mh == 256) && 2 * n.H + 1 <= 16;
+}
 // bytes of one layer's tcgen05 weight image (see tc_edge.cu: W1 hi/lo [2d x 16], W2m hi/lo, W2x hi/lo [d x d] bf16, fp32 vectors)
 __host__ __device__ static inline int tc_blob_bytes(int d) { return 2 * (2 * d * 32) + 4 * (d * d * 2) + (6 * d + 4) * 4; }
 // the tcgen05 node backward additionally needs Hh = d (mlp_h hidden width) and room for the constant-1 column
@@ -98,7 +103,7 @@ __host__ __device__ static inline PackOff pack_off(const egnn_net_t& n) {
     o.wh1t = p; p += (n.H + n.Ms) * n.Hh;
     p = round4(p);
     o.tc = p;
-    if (tc_supported(n)) p += (tc_blob_bytes(n.Mh) + 15) / 16 * 4;
+    if (tc_fwd_supported(n)) p += (tc_blob_bytes(n.Mh) + 15) / 16 * 4;
     if (tc_node_supported(n)) p += tc_node_blob_bytes(n.Mh) / 4;
     o.total = round4(p);
     return o;
@@ -126,7 +131,7 @@ static inline int edge_tile_for(const egnn_net_t& n) {
     return te;
 }
 // rows of the tile-partial buffer are sized for the finest segmentation any path uses (tcgen05: 32-edge segments)
-static inline int part_tile_for(const egnn_net_t& n) { return tc_supported(n) ? 32 : edge_tile_for(n); }
+static inline int part_tile_for(const egnn_net_t& n) { return tc_fwd_supported(n) ? 32 : edge_tile_for(n); }
 static inline FwdWs fwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     FwdWs w;
     const int64_t AGGW = n.Ms + 4;
@@ -141,7 +146,7 @@ static inline FwdWs fwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G)
     w.msum = take((int64_t)n.L * N * n.Ms);
     w.dxu = take((int64_t)n.L * N * 3);
     w.S = take((int64_t)n.L * G);
-    w.phi = take(tc_supported(n) ? E : 0);
+    w.phi = take(tc_fwd_supported(n) ? E : 0);
     w.total = p;
     return w;
 }

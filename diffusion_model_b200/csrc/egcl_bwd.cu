@@ -501,9 +501,11 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
     EGNN_REQUIRE(norm_scope == EGNN_NORM_CALL || norm_scope == EGNN_NORM_GRAPH, "bad norm_scope %d", norm_scope);
     EGNN_REQUIRE(g->node_graph != nullptr, "egnn_net_backward: node_graph is NULL");
     EGNN_REQUIRE(precision >= EGNN_PREC_FP32 && precision <= EGNN_PREC_BF16, "bad precision %d", precision);
-    const bool use_tc = precision != EGNN_PREC_FP32;  // edge phase on tcgen05 (bf16x3 split products or plain bf16)
-    if (use_tc)
-        EGNN_REQUIRE(tc_supported(*net), "tcgen05 path needs Mh = Ms = Xh in {64,128} and 2H+1 <= 16; use precision fp32");
+    if (precision != EGNN_PREC_FP32)
+        EGNN_REQUIRE(tc_fwd_supported(*net), "tcgen05 path needs Mh = Ms = Xh in {64,128,256} and 2H+1 <= 16; use precision fp32");
+    // edge phase on tcgen05 (bf16x3 split products or plain bf16); d = 256 has a tcgen05 forward only: its backward runs on
+    // the fp32 FFMA kernels (they recompute the edge activations themselves, so the two halves are independent)
+    const bool use_tc = precision != EGNN_PREC_FP32 && tc_supported(*net);
     const FwdWs fw = fwd_ws(*net, g->N, g->E, g->G);
     const BwdWs bw = bwd_ws(*net, g->N, g->E, g->G);
     if (ws_floats < bw.total) {

@@ -412,8 +412,8 @@ extern "C" int egnn_net_forward(const egnn_net_t* net, const egnn_graph_t* g, co
     EGNN_REQUIRE(norm_scope == EGNN_NORM_CALL || norm_scope == EGNN_NORM_GRAPH, "bad norm_scope %d", norm_scope);
     EGNN_REQUIRE(precision == EGNN_PREC_FP32 || precision == EGNN_PREC_BF16X3 || precision == EGNN_PREC_BF16,
                  "bad precision %d", precision);
-    EGNN_REQUIRE(precision == EGNN_PREC_FP32 || tc_supported(*net),
-                 "tcgen05 precisions need Mh = Ms = Xh in {64,128} and 2H+1 <= 16; use precision fp32 for this network");
+    EGNN_REQUIRE(precision == EGNN_PREC_FP32 || tc_fwd_supported(*net),
+                 "tcgen05 precisions need Mh = Ms = Xh in {64,128,256} and 2H+1 <= 16; use precision fp32 for this network");
     const FwdWs w = fwd_ws(*net, g->N, g->E, g->G);
     if (ws_floats < w.total) {
         egnn_set_error("egnn_net_forward: workspace too small (%lld < %lld floats)", (long long)ws_floats,

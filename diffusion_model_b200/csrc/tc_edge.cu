@@ -472,7 +472,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
 
 // ---- host side -------------------------------------------------------------------------------------------------
 int egnn_tc_pack(const egnn_net_t& net, const float* params, float* packed, cudaStream_t st) {
-    if (!tc_supported(net)) return EGNN_OK;
+    if (!tc_fwd_supported(net)) return EGNN_OK;
     tc_pack_kernel<<<dim3(16, net.L), 256, 0, st>>>(net, params, packed);
     EGNN_CHECK_LAUNCH("tc_pack_kernel");
     return EGNN_OK;
@@ -493,11 +493,15 @@ static int launch_tc_fwd(const TcFwdArgs& a, cudaStream_t st) {
     return EGNN_OK;
 }
 
+int egnn_tc_edge_forward256(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
+                            const float* x, float* agg, float* part, float* phi_edge, int precision, cudaStream_t st);
+
 // edge phase of one layer on the tensor cores; fills agg / part exactly like egcl_edge_fwd (segments of d/2 edges)
 int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
                          const float* x, float* agg, float* part, float* phi_edge, int precision, cudaStream_t st) {
-    EGNN_REQUIRE(tc_supported(net), "tcgen05 path needs Mh = Ms = Xh in {64,128} and 2H+1 <= 16 (got Mh=%d Ms=%d Xh=%d H=%d); "
+    EGNN_REQUIRE(tc_fwd_supported(net), "tcgen05 path needs Mh = Ms = Xh in {64,128,256} and 2H+1 <= 16 (got Mh=%d Ms=%d Xh=%d H=%d); "
                  "use precision fp32", net.Mh, net.Ms, net.Xh, net.H);
+    if (net.Mh == 256) return egnn_tc_edge_forward256(net, g, packed_layer, h, x, agg, part, phi_edge, precision, st);
     const PackOff po = pack_off(net);
     TcFwdArgs a{net, g.N, g.E, (g.E + 127) / 128, g.recv, g.send, g.row_ptr, h, x,
                 reinterpret_cast<const uint8_t*>(packed_layer + po.tc), agg, part, phi_edge};

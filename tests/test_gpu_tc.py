@@ -72,7 +72,7 @@ def _relerr(a, b):
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
 
 
-@pytest.mark.parametrize("name", ["cfg1", "cfg2"])
+@pytest.mark.parametrize("name", ["cfg1", "cfg2", "cfg4"])  # cfg4: d = 256, the streamed-W2 kernel (tc_edge256.cu)
 @pytest.mark.parametrize("precision,tol", [("bf16x3", 1e-4), ("bf16", 2e-2)])
 def test_tc_forward_matches_reference_layers(lib, name, precision, tol):
     z = _load("egnn_" + name)
@@ -115,10 +115,22 @@ def test_tc_forward_edge_cases_and_unsupported(lib):
         ho, xo = net(ei.to(DEV), h.to(DEV), x.to(DEV))
         hr, xr = egnn_ref.egnn_forward(sd, 2, ei, h, x)
     assert _relerr(ho, hr) <= 2e-4 and _relerr(xo, xr) <= 2e-4
-    wide = EquivariantGNN(**egnn_ref.net_sizes(1, 256)).to(DEV)
-    wide.precision = "bf16"
+    # d = 256 on the same ragged graph (one receiver cut by several tiles, a 5-edge receiver, isolated nodes), both modes
+    torch.manual_seed(3)
+    wide = EquivariantGNN(**egnn_ref.net_sizes(2, 256)).to(DEV)
+    sdw = {k: v.detach().cpu() for k, v in wide.state_dict().items()}
+    with torch.no_grad():
+        hr, xr = egnn_ref.egnn_forward(sdw, 2, ei, h, x)
+        for prec, tol in (("bf16x3", 2e-4), ("bf16", 3e-2)):
+            wide.precision = prec
+            ho, xo = wide(ei.to(DEV), h.to(DEV), x.to(DEV))
+            assert _relerr(ho, hr) <= tol and _relerr(xo, xr) <= tol, (prec, _relerr(ho, hr), _relerr(xo, xr))
+            ho2, xo2 = wide(ei.to(DEV), h.to(DEV), x.to(DEV))
+            assert torch.equal(ho, ho2) and torch.equal(xo, xo2)
+    odd = EquivariantGNN(**egnn_ref.net_sizes(1, 96)).to(DEV)  # no tcgen05 tile for d = 96: must refuse, not fall back
+    odd.precision = "bf16"
     with pytest.raises(EgnnError):
-        wide(ei.to(DEV), h.to(DEV), x.to(DEV))
+        odd(ei.to(DEV), h.to(DEV), x.to(DEV))
 
 
 # ---------------------------------------------------------------- tensor-core edge BACKWARD vs the reference autograd
@@ -153,6 +165,16 @@ def test_tc_backward_matches_reference_grads(lib, name, precision, tol):
     assert errs[worst] <= tol, errs
     _, g2 = _grad_errors(name, precision)
     assert all(torch.equal(a, b) for a, b in zip(g1, g2))  # deterministic (no atomics)
+
+
+def test_tc_forward_fp32_backward_d256(lib):
+    """d = 256: tcgen05 forward (bf16x3), backward on the fp32 FFMA kernels (they recompute the edge activations)"""
+    errs, g1 = _grad_errors("cfg4", "bf16x3")
+    worst = max(errs, key=errs.get)
+    print(f"d256 mixed backward: worst {worst} {errs[worst]:.2e}")
+    assert errs[worst] <= 1e-3, errs
+    _, g2 = _grad_errors("cfg4", "bf16x3")
+    assert all(torch.equal(a, b) for a, b in zip(g1, g2))
 
 
 def test_tc_backward_edge_cases(lib):
