@@ -6,7 +6,7 @@ forward+backward, with the fraction of the measured B200 bf16 tensor peak and of
 
 One JSON object per line.  FLOPs / bytes are the algorithmic figures of SURVEY.md 8(d):
     F_layer = E (4 K0 d + 4 d^2 + 4 d) + N (2 d^2 + 4 H d),   B_layer = 8 N (H + 3) + 8 E + 4 P_layer.
-Hidden 256 has no tcgen05 path yet (one branch's W2 image, 256 KB of bf16 hi/lo, exceeds shared memory): those lines
+Hidden 256: tcgen05 forward (tc_edge256.cu, W2 streamed through shared memory), FFMA backward: the fwd_bwd columns of those
 run in fp32 only and say so.
 """
 from __future__ import annotations
@@ -57,6 +57,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--hidden", type=int, nargs="*", default=None)
     args = ap.parse_args()
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EGCL
     from diffusion_model_b200.graph import GraphIndex
@@ -68,12 +69,12 @@ def main():
     K0 = 2 * H + 1
     atoms = [256, 4096] if args.quick else [64, 256, 1024, 4096]
     degs = [32] if args.quick else [16, 32, 64, 128]
-    hidden = [128] if args.quick else [64, 128, 256]
+    hidden = args.hidden or ([128] if args.quick else [64, 128, 256])
     for d in hidden:
         torch.manual_seed(0)
         layer = EGCL(K0, d, d, K0, d, 1, H + d, d, H).to(dev)
         P = sum(p.numel() for p in layer.parameters())
-        modes = ["fp32", "bf16x3", "bf16"] if d in (64, 128) else ["fp32"]
+        modes = ["fp32", "bf16x3", "bf16"]  # d = 256: tcgen05 forward (tc_edge256.cu), FFMA backward
         for n in atoms:
             for deg in degs:
                 if deg >= n:
@@ -109,7 +110,7 @@ def main():
                         fwd_bwd_frac_tensor_peak=3 * flops / (ms_fb * 1e-3) / 1e12 / tf_peak,
                         fwd_gbs=nbytes / (ms_f * 1e-3) / 1e9, fwd_frac_hbm_peak=nbytes / (ms_f * 1e-3) / 1e9 / hbm_peak,
                         flops_fwd=flops, bytes_fwd=nbytes, peaks=dict(tflops=tf_peak, hbm_gbs=hbm_peak, source=src),
-                        note=None if d in (64, 128) else "no tcgen05 path for hidden 256 yet: fp32 FFMA only")), flush=True)
+                        note=None if d in (64, 128) or mode == "fp32" else "hidden 256: tcgen05 forward, fp32 FFMA backward")), flush=True)
 
 
 if __name__ == "__main__":
