@@ -327,7 +327,7 @@ def run_product(args, rank, world, local):
         train_step(resident)
     torch.cuda.synchronize(dev)
     names = {0: "egcl_edge_fwd", 1: "egcl_node_fwd", 2: "egcl_xupdate", 3: "egcl_edge_bwd", 4: "egcl_node_bwd",
-             5: "egcl_gather_bwd", 7: "tc_edge_fwd", 8: "tc_edge_bwd"}
+             5: "egcl_gather_bwd", 7: "tc_edge_fwd", 8: "tc_edge_bwd", 9: "tc_wgrad"}
     prof = {}
     for kind, name in names.items():
         tot, cnt = C.c_double(0), C.c_int64(0)

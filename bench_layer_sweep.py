@@ -7,7 +7,7 @@ forward+backward, with the fraction of the measured B200 bf16 tensor peak and of
 One JSON object per line.  FLOPs / bytes are the algorithmic figures of SURVEY.md 8(d):
     F_layer = E (4 K0 d + 4 d^2 + 4 d) + N (2 d^2 + 4 H d),   B_layer = 8 N (H + 3) + 8 E + 4 P_layer.
 Hidden 256: tcgen05 forward (tc_edge256.cu, W2 streamed through shared memory), FFMA backward: the fwd_bwd columns of those
-run in fp32 only and say so.
+lines are dominated by the fp32 backward and say so.
 """
 from __future__ import annotations
 

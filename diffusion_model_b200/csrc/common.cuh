@@ -12,7 +12,7 @@ void egnn_prof_begin(int kind, cudaStream_t st);
 void egnn_prof_end(cudaStream_t st);
 // kernel families the profiler can bracket (egnn_profile_read)
 enum { EGNN_K_EDGE_FWD = 0, EGNN_K_NODE_FWD = 1, EGNN_K_XUPDATE = 2, EGNN_K_EDGE_BWD = 3, EGNN_K_NODE_BWD = 4,
-       EGNN_K_GATHER_BWD = 5, EGNN_K_REDUCE = 6, EGNN_K_TC_EDGE_FWD = 7, EGNN_K_TC_EDGE_BWD = 8 };
+       EGNN_K_GATHER_BWD = 5, EGNN_K_REDUCE = 6, EGNN_K_TC_EDGE_FWD = 7, EGNN_K_TC_EDGE_BWD = 8, EGNN_K_TC_WGRAD = 9 };
 
 #define EGNN_REQUIRE(cond, ...)              \
     do {                                     \
@@ -86,6 +86,10 @@ __host__ __device__ static inline bool tc_fwd_supported(const egnn_net_t& n) {
 }
 // bytes of one layer's tcgen05 weight image (see tc_edge.cu: W1 hi/lo [2d x 16], W2m hi/lo, W2x hi/lo [d x d] bf16, fp32 vectors)
 __host__ __device__ static inline int tc_blob_bytes(int d) { return 2 * (2 * d * 32) + 4 * (d * d * 2) + (6 * d + 4) * 4; }
+// d = 256 only: K-major images of W2^T / 2 (hi | lo per branch), the streamed B operand of the dgrad in tc_edge256_bwd.cu;
+// appended to the edge part of the image (d = 256 has no node part)
+__host__ __device__ static inline int tc_w2t_offset(int d) { return (tc_blob_bytes(d) + 15) / 16 * 16; }
+__host__ __device__ static inline int tc_w2t_bytes(int d) { return d == 256 ? 4 * d * d * 2 : 0; }
 // the tcgen05 node backward additionally needs Hh = d (mlp_h hidden width) and room for the constant-1 column
 __host__ __device__ static inline bool tc_node_supported(const egnn_net_t& n) {
     return tc_supported(n) && n.Hh == n.Ms && n.H + 1 <= 16;
@@ -103,7 +107,7 @@ __host__ __device__ static inline PackOff pack_off(const egnn_net_t& n) {
     o.wh1t = p; p += (n.H + n.Ms) * n.Hh;
     p = round4(p);
     o.tc = p;
-    if (tc_fwd_supported(n)) p += (tc_blob_bytes(n.Mh) + 15) / 16 * 4;
+    if (tc_fwd_supported(n)) p += (tc_blob_bytes(n.Mh) + 15) / 16 * 4 + tc_w2t_bytes(n.Mh) / 4;
     if (tc_node_supported(n)) p += tc_node_blob_bytes(n.Mh) / 4;
     o.total = round4(p);
     return o;

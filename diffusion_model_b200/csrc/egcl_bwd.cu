@@ -417,6 +417,11 @@ size_t egnn_edge_fwd_smem(const egnn_net_t& net, int TE);
 int egnn_validate_net(const egnn_net_t* net);
 int egnn_validate_graph(const egnn_graph_t* g, bool need_sender_csr);
 int egnn_tc_bwd_grid(int64_t E);
+int egnn_tc_bwd256_rows(int64_t E);
+int64_t egnn_tc_bwd256_img_bytes(int64_t E);
+int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
+                             const float* x, const float* gM, const float* gdx, const float* coefS, float* Gr, float* Gs,
+                             float* part, uint8_t* img, int precision, cudaStream_t st);
 void egnn_tc_bwd_split(int64_t E, int* nM, int* nX);
 int egnn_tc_node_bwd_grid(int64_t N);
 int egnn_tc_node_backward(const egnn_net_t& net, int N, const float* params_layer, const float* packed_layer, const float* h,
@@ -430,8 +435,11 @@ namespace {
 
 constexpr int kNumSM = 148;  // B200
 
+// d = 256 has its own tcgen05 backward (tc_edge256_bwd.cu: two kernels, operand tile images in the workspace)
+static inline bool tc_bwd256_supported(const egnn_net_t& n) { return n.Mh == 256 && tc_fwd_supported(n); }
+
 struct BwdWs {
-    int64_t gdx, coefS, dotp, gM, gh_node, Gr, Gs, ghb, gxb, part, total;
+    int64_t gdx, coefS, dotp, gM, gh_node, Gr, Gs, ghb, gxb, part, img, total;
     int gridE, gridN, TEB;
 };
 inline int edge_tile_bwd(const egnn_net_t& n) {
@@ -444,6 +452,7 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     const int64_t tilesE = (E + w.TEB - 1) / w.TEB, tilesN = (N + TNB - 1) / TNB;
     w.gridE = (int)(tilesE < kNumSM ? tilesE : kNumSM);
     if (tc_supported(n) && E > 0 && egnn_tc_bwd_grid(E) > w.gridE) w.gridE = egnn_tc_bwd_grid(E);
+    if (tc_bwd256_supported(n) && egnn_tc_bwd256_rows(E) > w.gridE) w.gridE = egnn_tc_bwd256_rows(E);
     if (tc_node_supported(n) && egnn_tc_node_bwd_grid(N) > w.gridN) w.gridN = egnn_tc_node_bwd_grid(N);
     w.gridN = (int)(tilesN < kNumSM ? tilesN : kNumSM);
     const int64_t W = n.H + 3;
@@ -459,6 +468,7 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     w.ghb = take(2 * N * n.H);
     w.gxb = take(2 * N * 3);
     w.part = take((int64_t)(w.gridE + w.gridN) * layer_off(n).total);
+    w.img = take(tc_bwd256_supported(n) ? egnn_tc_bwd256_img_bytes(E) / 4 : 0);  // 16-byte aligned: every take() is rounded to 4 floats
     w.total = p;
     return w;
 }
@@ -503,9 +513,10 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
     EGNN_REQUIRE(precision >= EGNN_PREC_FP32 && precision <= EGNN_PREC_BF16, "bad precision %d", precision);
     if (precision != EGNN_PREC_FP32)
         EGNN_REQUIRE(tc_fwd_supported(*net), "tcgen05 path needs Mh = Ms = Xh in {64,128,256} and 2H+1 <= 16; use precision fp32");
-    // edge phase on tcgen05 (bf16x3 split products or plain bf16); d = 256 has a tcgen05 forward only: its backward runs on
-    // the fp32 FFMA kernels (they recompute the edge activations themselves, so the two halves are independent)
+    // edge phase on tcgen05 (bf16x3 split products or plain bf16): d <= 128 one fused kernel with the weight gradients
+    // persistent in TMEM, d = 256 the two-kernel form of tc_edge256_bwd.cu
     const bool use_tc = precision != EGNN_PREC_FP32 && tc_supported(*net);
+    const bool use_tc256 = precision != EGNN_PREC_FP32 && tc_bwd256_supported(*net);
     const FwdWs fw = fwd_ws(*net, g->N, g->E, g->G);
     const BwdWs bw = bwd_ws(*net, g->N, g->E, g->G);
     if (ws_floats < bw.total) {
@@ -527,7 +538,8 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
     }
     const bool node_tc = use_tc && tc_node_supported(*net);
     // rows actually used by this call's kernels (the workspace is sized for the larger of the two paths)
-    const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : (int)std::min<int64_t>((E + bw.TEB - 1) / bw.TEB, kNumSM)) : 0;
+    const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : use_tc256 ? egnn_tc_bwd256_rows(E)
+                                                            : (int)std::min<int64_t>((E + bw.TEB - 1) / bw.TEB, kNumSM)) : 0;
     const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : (int)std::min<int64_t>((N + TNB - 1) / TNB, kNumSM);
     EGNN_CUDA(cudaMemsetAsync(ws + bw.dotp + g->G, 0, 4 * sizeof(float), st));  // the ticket of egcl_xupdate_bwd
     int rows_m = 0;
@@ -567,7 +579,12 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
             egnn_prof_end(st);
             EGNN_CHECK_LAUNCH("egcl_node_bwd");
         }
-        if (E > 0 && use_tc) {
+        if (E > 0 && use_tc256) {
+            if (int rc = egnn_tc_edge_backward256(*net, *g, Pk, hl, xl, ws + bw.gM, ws + bw.gdx, ws + bw.coefS, ws + bw.Gr,
+                                                  ws + bw.Gs, ws + bw.part, reinterpret_cast<uint8_t*>(ws + bw.img),
+                                                  precision, st))
+                return rc;
+        } else if (E > 0 && use_tc) {
             if (int rc = egnn_tc_edge_backward(*net, *g, Pk, hl, xl, ws + bw.gM, ws + bw.gdx, ws + bw.coefS, ws + bw.Gr,
                                                ws + bw.Gs, ws + bw.part, precision, st))
                 return rc;
@@ -585,8 +602,8 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
         }
         {
             GatherArgs ga{N, H, g->row_ptr, g->col_ptr, g->col_edge, ws + bw.gh_node, gxo, ws + bw.Gr, ws + bw.Gs,
-                          use_tc ? ws + bw.Gr + (size_t)E * (H + 3) : nullptr,
-                          use_tc ? ws + bw.Gs + (size_t)E * (H + 3) : nullptr, ghi, gxi};
+                          (use_tc || use_tc256) ? ws + bw.Gr + (size_t)E * (H + 3) : nullptr,
+                          (use_tc || use_tc256) ? ws + bw.Gs + (size_t)E * (H + 3) : nullptr, ghi, gxi};
             const long long tot = (long long)N * (H + 3);
             egnn_prof_begin(EGNN_K_GATHER_BWD, st);
             egcl_gather_bwd<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(ga);

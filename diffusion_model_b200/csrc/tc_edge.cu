@@ -181,6 +181,20 @@ __global__ void __launch_bounds__(256) tc_pack_kernel(egnn_net_t net, const floa
             *reinterpret_cast<uint4*>(dst + W2B + tc::chunk_off(D, n, j)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
         }
     }
+    if (tc_w2t_bytes(D) > 0) {  // d = 256: W2^T / 2 as K-major [rows k][K = n] images, per branch hi | lo
+        for (int which = 0; which < 2; ++which) {
+            const float* W = P + (which == 0 ? lo.wm2 : lo.wx2);
+            uint8_t* dst = blob + tc_w2t_offset(D) + which * 2 * W2B;
+            for (int idx = t0; idx < D * (D / 8); idx += stride) {
+                const int k = idx % D, jn = idx / D;  // consecutive threads read consecutive k of one W2 row
+                uint32_t hi[4], lw[4];
+                for (int q = 0; q < 4; ++q)
+                    tc::split2(0.5f * W[(size_t)(jn * 8 + 2 * q) * D + k], 0.5f * W[(size_t)(jn * 8 + 2 * q + 1) * D + k], hi[q], lw[q]);
+                *reinterpret_cast<uint4*>(dst + tc::chunk_off(D, k, jn)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(dst + W2B + tc::chunk_off(D, k, jn)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            }
+        }
+    }
     float* vec = reinterpret_cast<float*>(blob + 2 * W1B + 4 * W2B);
     for (int c = t0; c < D; c += stride) {
         vec[c] = 0.5f * P[lo.bm1 + c];  // (layer-1 biases travel in K slot 15 of W1; kept here for reference only)

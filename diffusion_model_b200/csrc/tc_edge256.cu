@@ -13,6 +13,7 @@
 // Per tile:  GEMM1 (issued one tile ahead) -> SiLU -> A1 -> 16 x (slice wait, NPASS MMAs of K = 16, commit) -> layer-2
 // epilogue: mlp_x: phi_e = wx3 . SiLU(z2 + b2) + bx3;  mlp_m: m = SiLU(z2 + b2), g = sigmoid(wa . m + ba), g * m summed per
 // receiver in edge order (fixed order, no atomics) exactly like the d <= 128 kernel.
+#include "tc_bulk.cuh"
 #include "tc_tile.cuh"
 
 namespace {
@@ -50,15 +51,6 @@ struct Tc256Args {
     float *agg, *part, *phi_edge;
     int nM;
 };
-
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(src), "r"(bytes), "r"(bar)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
 
 template <int NPASS>
 __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
@@ -180,9 +172,9 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
         const int sl = g % NSLICE, st = g % NSLOT;
         const uint32_t full = tc::smem_u32(&bars[2 + st]);
         const uint32_t dst = sb + L::ring + st * 2 * SLICE_B;
-        mbar_expect_tx(full, LO ? 2 * SLICE_B : SLICE_B);
-        bulk_g2s(dst, w2_hi_g + (size_t)sl * SLICE_B, SLICE_B, full);
-        if (LO) bulk_g2s(dst + SLICE_B, w2_lo_g + (size_t)sl * SLICE_B, SLICE_B, full);
+        tc::mbar_expect_tx(full, LO ? 2 * SLICE_B : SLICE_B);
+        tc::bulk_g2s(dst, w2_hi_g + (size_t)sl * SLICE_B, SLICE_B, full);
+        if (LO) tc::bulk_g2s(dst + SLICE_B, w2_lo_g + (size_t)sl * SLICE_B, SLICE_B, full);
     };
 
     if (tid < 128 && nit > 0) {
