@@ -36,7 +36,7 @@ sys.path.insert(0, ROOT)
 CFG = dict(L=6, d=128, H=3, A=2, graphs=64, atoms=192, r_c=5.0, T=1000, s=1e-5, power=2.0, lr=1e-5, seed=2024, name="cfg2",
            cpu_graphs=8)
 # --workload cfg4 (BASELINE configs[3]: 1536-atom cells, 9 layers, hidden 256, 8 graphs per GPU); not the contract line.
-# Hidden 256: tcgen05 forward with W2 streamed through shared memory (tc_edge256.cu); the backward runs the FFMA kernels.
+# Hidden 256 runs the streamed-W2 tcgen05 kernels (tc_edge256.cu, tc_edge256_bwd.cu); --precision fp32 selects the FFMA kernels.
 CFG4 = dict(L=9, d=256, graphs=8, atoms=1536, name="cfg4", cpu_graphs=1)
 DENSITY = 0.0662  # atoms / A^3, a-SiO2
 
@@ -84,13 +84,27 @@ def fwd_flops(L, d, H, N, E):
 
 
 class ClockSampler:
-    """nvidia-smi samples of SM clock and throttle reasons DURING the timed region."""
+    """SM clock and throttle reasons sampled DURING the timed region: NVML polled from a thread every 5 ms (short timed
+    regions still get samples); `nvidia-smi -lms` as the fallback when the NVML binding is missing."""
 
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.rows, self.proc = [], None
+        self.rows, self.proc, self.nvml, self.stop_flag = [], None, None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+            self.nvml = pynvml
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE, text=True)
@@ -99,11 +113,31 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        n = self.nvml
+        masks = {"hw_slowdown": n.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": n.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": n.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": n.nvmlClocksThrottleReasonSwPowerCap}
+        while not self.stop_flag:
+            try:
+                mhz = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+                bits = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                self.rows.append((mhz, [k for k, m in masks.items() if bits & m]))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+            if not self.rows:
+                return dict(sm_mhz=None, sm_max_mhz=self.max_mhz, reasons=["no samples"], source="nvml")
+            return dict(sm_mhz=statistics.median(r[0] for r in self.rows), sm_max_mhz=self.max_mhz,
+                        reasons=sorted({k for r in self.rows for k in r[1]}), samples=len(self.rows), source="nvml")
         if self.proc is None:
             return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
         time.sleep(0.15)
@@ -115,7 +149,7 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[k] for r in rows for k in range(4) if r[2 + k].lower().startswith("active")})
         return dict(sm_mhz=statistics.median(int(r[0]) for r in rows), sm_max_mhz=int(rows[0][1]), reasons=reasons,
-                    samples=len(rows))
+                    samples=len(rows), source="nvidia-smi")
 
 
 def measured_peaks():
@@ -354,6 +388,8 @@ def run_product(args, rank, world, local):
         issued = (2 * passes + wgrad_passes if top.endswith("bwd") else passes) * edge_flops
         traffic = None
         try:
+            if CFG["name"] != "cfg2":
+                raise OSError("the committed ncu traffic figure is for the cfg2 kernels")
             with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
                 traffic = json.load(f).get(top, {}).get("dram_bytes_per_launch")
         except OSError:
@@ -395,10 +431,10 @@ def main():
                     help="bf16x3 (default): tcgen05 split-bf16 products, fp32 accumulate, <=1e-4 per layer vs the fp32 "
                          "reference; fp32: CUDA-core FFMA; bf16: single tcgen05 product (looser, stated bound)")
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4"],
-                    help="cfg2 (default, the contract line) or cfg4 (1536-atom cells, L=9, hidden 256; fp32 kernels)")
+                    help="cfg2 (default, the contract line) or cfg4 (1536-atom cells, L=9, hidden 256)")
     args = ap.parse_args()
     if args.workload == "cfg4":
-        CFG.update(CFG4)  # bf16x3 / bf16: tcgen05 forward (tc_edge256.cu) + fp32 FFMA backward; fp32: FFMA both ways
+        CFG.update(CFG4)
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         run_reference(args, int(os.environ.get("RANK", "0")))

@@ -6,8 +6,8 @@ forward+backward, with the fraction of the measured B200 bf16 tensor peak and of
 
 One JSON object per line.  FLOPs / bytes are the algorithmic figures of SURVEY.md 8(d):
     F_layer = E (4 K0 d + 4 d^2 + 4 d) + N (2 d^2 + 4 H d),   B_layer = 8 N (H + 3) + 8 E + 4 P_layer.
-Hidden 256: tcgen05 forward (tc_edge256.cu, W2 streamed through shared memory), FFMA backward: the fwd_bwd columns of those
-lines are dominated by the fp32 backward and say so.
+Hidden 256 runs the streamed-W2 tcgen05 kernels (tc_edge256.cu forward, tc_edge256_bwd.cu backward + wgrad GEMM); its node
+MLP stays on the FFMA kernels.
 """
 from __future__ import annotations
 
@@ -74,7 +74,7 @@ def main():
         torch.manual_seed(0)
         layer = EGCL(K0, d, d, K0, d, 1, H + d, d, H).to(dev)
         P = sum(p.numel() for p in layer.parameters())
-        modes = ["fp32", "bf16x3", "bf16"]  # d = 256: tcgen05 forward (tc_edge256.cu), FFMA backward
+        modes = ["fp32", "bf16x3", "bf16"]  # d = 256: streamed-W2 kernels (tc_edge256.cu, tc_edge256_bwd.cu)
         for n in atoms:
             for deg in degs:
                 if deg >= n:
@@ -110,7 +110,7 @@ def main():
                         fwd_bwd_frac_tensor_peak=3 * flops / (ms_fb * 1e-3) / 1e12 / tf_peak,
                         fwd_gbs=nbytes / (ms_f * 1e-3) / 1e9, fwd_frac_hbm_peak=nbytes / (ms_f * 1e-3) / 1e9 / hbm_peak,
                         flops_fwd=flops, bytes_fwd=nbytes, peaks=dict(tflops=tf_peak, hbm_gbs=hbm_peak, source=src),
-                        note=None if d in (64, 128) or mode == "fp32" else "hidden 256: tcgen05 forward, fp32 FFMA backward")), flush=True)
+                        note=None if d in (64, 128) or mode == "fp32" else "hidden 256: W2 streamed through shared memory, node MLP on the FFMA kernels")), flush=True)
 
 
 if __name__ == "__main__":

@@ -179,11 +179,12 @@ def test_tc_backward_d256(lib, precision, tol):
     assert all(torch.equal(a, b) for a, b in zip(g1, g2))
 
 
-def test_tc_backward_edge_cases(lib):
-    """d=64 network, a receiver cut by several tiles, isolated nodes, one short tile, no edges"""
+@pytest.mark.parametrize("d", [64, 256])  # 256: the two-kernel backward (tile images + wgrad GEMM), fewer tiles than CTAs
+def test_tc_backward_edge_cases(lib, d):
+    """a receiver cut by several tiles, isolated nodes, one short tile, no edges"""
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
     torch.manual_seed(0)
-    net = EquivariantGNN(**egnn_ref.net_sizes(2, 64)).to(DEV)
+    net = EquivariantGNN(**egnn_ref.net_sizes(2, d)).to(DEV)
     net.precision = "bf16x3"
     sd = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
     gen = torch.Generator().manual_seed(1)
