@@ -12,7 +12,7 @@ LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libegnn_b200.so")
 SOURCES = ["api.cu", "graph.cu", "egcl_fwd.cu", "egcl_bwd.cu", "diffusion.cu", "tc_edge.cu", "tc_edge256.cu", "tc_edge256_bwd.cu", "tc_node.cu", "analysis.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--extended-lambda",
-              "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
+              "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"] + os.environ.get("EGNN_NVCC_EXTRA", "").split()
 
 
 def _nvcc():

@@ -169,6 +169,9 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
     };
     // the elected issuer thread: pull slice number g (tile-independent content: slice g % NSLICE) into ring slot g % NSLOT
     auto load_slice = [&](int g) {
+#ifdef EGNN_DBG_NOSTREAM
+        return;
+#endif
         const int sl = g % NSLICE, st = g % NSLOT;
         const uint32_t full = tc::smem_u32(&bars[2 + st]);
         const uint32_t dst = sb + L::ring + st * 2 * SLICE_B;
@@ -190,12 +193,23 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
     const uint32_t tmem = *slot;
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
     const bool issuer_warp = warp == NT / 32 - 1;
+    // The W2 ring has its own producer thread (lane 0 of the warp before the issuer's): the MMA issuer only ever waits for
+    // "slice landed", never for "slot free", so several slices' MMAs stay queued on the tensor pipe.  (With one thread
+    // doing both, every slice waited for the previous slice's MMAs to drain: the GEMM ran at one commit round trip per slice.)
+    const bool producer = warp == NT / 32 - 2 && lane == 0;
+    int gload = 0;  // producer: next slice to pull
+    bool ok = true;
+    auto produce = [&](int limit) {
+        for (; gload < limit; ++gload) {
+            if (gload >= NSLOT) ok = tc::mbar_wait(&bars[2 + NSLOT + gload % NSLOT], ((gload - NSLOT) / NSLOT) & 1) && ok;
+            load_slice(gload);
+        }
+    };
+    if (producer && nit > 0) produce(min(total_slices, NSLOT));
     if (issuer_warp && nit > 0 && tc::elect_one()) {
-        for (int g = 0; g < NSLOT - 1 && g < total_slices; ++g) load_slice(g);
         tc_issue_op<NPASS>(tmem, 0, opU, opW1, 16, D, false);
         tc::mma_commit(&bars[0]);
     }
-    bool ok = true;
 
     for (int it = 0; it < nit; ++it) {
         const int tile = tile0 + it * tstride;
@@ -221,7 +235,9 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
             const uint32_t idesc = tc::make_idesc_bf16(128, D);
             for (int s = 0; s < NSLICE; ++s) {
                 const int g = it * NSLICE + s, st = g % NSLOT;
+#ifndef EGNN_DBG_NOSTREAM  // timing experiment only (wrong results): MMAs without the W2 stream
                 ok = tc::mbar_wait(&bars[2 + st], (g / NSLOT) & 1) && ok;  // slice s has landed
+#endif
                 const uint32_t wb = sb + L::ring + st * 2 * SLICE_B;
                 const uint64_t a_hi = tc::make_desc(sb + L::a1_hi + s * 2 * CS, CS, 128);
                 const uint64_t a_lo = tc::make_desc(sb + L::a1_lo + s * 2 * CS, CS, 128);
@@ -232,18 +248,14 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
                     tc::mma_bf16(tmem + D, a_hi, b_lo, idesc, true);
                 }
                 tc::mma_commit(&bars[2 + NSLOT + st]);  // slot st is free again once these MMAs have read it
-                // refill the slot of slice g - 1 with slice g + NSLOT - 1 (the ring keeps NSLOT - 1 copies in flight)
-                const int gn = g + NSLOT - 1;
-                if (gn < total_slices) {
-                    if (g >= 1) ok = tc::mbar_wait(&bars[2 + NSLOT + (g - 1) % NSLOT], ((g - 1) / NSLOT) & 1) && ok;
-                    load_slice(gn);
-                }
             }
             tc::mma_commit(&bars[1]);
             if (has_next) {  // z1 has been consumed by every warp (barrier above): next tile's GEMM1 queues behind GEMM2
                 tc_issue_op<NPASS>(tmem, 0, opU, opW1, 16, D, false);
                 tc::mma_commit(&bars[0]);
             }
+        } else if (producer) {
+            produce(min(total_slices, (it + 1) * NSLICE + NSLOT));  // this tile's slices, then the first ones of the next tile
         }
         __syncwarp();
         ok = tc::mbar_wait(&bars[1], phase) && ok;

@@ -158,6 +158,9 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
         sR[tid] = make_float4(g.rx, g.ry, g.rz, g.valid);
     };
     auto load_slice = [&](int g) {
+#ifdef EGNN_DBG_NOSTREAM
+        return;
+#endif
         const int sl = g % (2 * NSLICE), st = g % NSLOT;
         const uint8_t* src = sl < NSLICE ? w2_g + (size_t)sl * SLICE_B : w2t_g + (size_t)(sl - NSLICE) * SLICE_B;
         const uint32_t full = tc::smem_u32(&bars[4 + st]);
@@ -180,8 +183,18 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
     const uint32_t tmem = *slot;
     const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
     const bool issuer_warp = warp == NT / 32 - 1;
+    // ring producer = lane 0 of the warp before the issuer's (see tc_edge256.cu): the MMA issuer never waits for a free slot
+    const bool producer = warp == NT / 32 - 2 && lane == 0;
+    int gload = 0;
+    bool ok = true;
+    auto produce = [&](int limit) {
+        for (; gload < limit; ++gload) {
+            if (gload >= NSLOT) ok = tc::mbar_wait(&bars[4 + NSLOT + gload % NSLOT], ((gload - NSLOT) / NSLOT) & 1) && ok;
+            load_slice(gload);
+        }
+    };
+    if (producer && nit > 0) produce(min(total_slices, NSLOT));
     if (issuer_warp && nit > 0 && tc::elect_one()) {
-        for (int g = 0; g < NSLOT - 1 && g < total_slices; ++g) load_slice(g);
         tc_issue_op<NPASS>(tmem, cA, opU, opW1, 16, D, false);
         tc::mma_commit(&bars[0]);
     }
@@ -190,7 +203,9 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
         const uint32_t idesc = tc::make_idesc_bf16(128, D);
         for (int s = 0; s < NSLICE; ++s) {
             const int g = gbase + s, st = g % NSLOT;
+#ifndef EGNN_DBG_NOSTREAM  // timing experiment only (wrong results): MMAs without the weight stream
             ok = tc::mbar_wait(&bars[4 + st], (g / NSLOT) & 1) && ok;
+#endif
             const uint32_t wb = sb + L::ring + st * 2 * SLICE_B;
             const uint64_t ah = tc::make_desc(sb + L::R_hi + s * 2 * CS, CS, 128), al = tc::make_desc(sb + L::R_lo + s * 2 * CS, CS, 128);
             const uint64_t bh = tc::make_desc(wb, D * 16, 128), bl = tc::make_desc(wb + SLICE_B, D * 16, 128);
@@ -200,17 +215,11 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
                 tc::mma_bf16(tmem + dcol, ah, bl, idesc, true);
             }
             tc::mma_commit(&bars[4 + NSLOT + st]);
-            const int gn = g + NSLOT - 1;
-            if (gn < total_slices) {
-                if (g >= 1) ok = tc::mbar_wait(&bars[4 + NSLOT + (g - 1) % NSLOT], ((g - 1) / NSLOT) & 1) && ok;
-                load_slice(gn);
-            }
         }
     };
 
     float accv0 = 0.f, accv1 = 0.f;  // running column sums of coef_e * out_e (d wa / d wx3): columns c0 + lane, c0 + 32 + lane
     float accs = 0.f;                // running sum of coef_e of this thread's row (d ba / d bx3)
-    bool ok = true;
 
     for (int it = 0; it < nit; ++it) {
         const int tile = tile0 + it * tstride;
@@ -240,6 +249,8 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
             tc::bulk_commit();
             stream_gemm(it * 2 * NSLICE, cB, true, ok);  // z2 = a1 . W2^T
             tc::mma_commit(&bars[1]);
+        } else if (producer) {
+            produce(min(total_slices, it * 2 * NSLICE + NSLICE + NSLOT));
         }
         __syncwarp();
         // ---- in the shadow of GEMM2: next tile's gather loads
@@ -328,6 +339,8 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
             tc::bulk_commit();
             stream_gemm(it * 2 * NSLICE + NSLICE, cB, LO, ok);  // ga1 = gz2 . W2  (over z2)
             tc::mma_commit(&bars[2]);
+        } else if (producer) {
+            produce(min(total_slices, (it + 1) * 2 * NSLICE + NSLOT));
         }
         __syncwarp();
         float phi = 0.f;
