@@ -15,6 +15,8 @@
 //     slot 15 of u is the constant 1, so bias gradients are MMA columns); accumulators persistent in TMEM over the CTA's
 //     tiles, written once to its partial row.  This kernel is HBM-bound by construction (it streams the images).
 // Conventions as in tc_edge.cu: weight images are stored halved, gradient tiles carry 2 dL/dz, results are halved once.
+#include <cstdlib>
+
 #include "tc_bulk.cuh"
 #include "tc_tile.cuh"
 
@@ -460,23 +462,36 @@ struct Wg256Args {
     int row0;
 };
 
+// Software pipeline: the three split products of a tile are issued as separate groups in the order
+//   P_A = gz_hi . a1_lo,   P_B = gz_hi . a1_hi,   P_C = gz_lo . a1_hi      (each with its u-column product)
+// so that every operand buffer is free as early as possible: a producer thread refills a1_lo (+ u) as soon as P_A of the
+// current tile has completed, gz_hi after P_B, a1_hi and gz_lo after P_C, while the issuer thread only waits for "landed".
+// Loads of the next tile therefore overlap the MMAs of this one without a second set of buffers (208 KB in use).
+struct WgSmem {
+    static constexpr int HALF_B = TILE_B / 2;  // 16 chunk columns x 128 rows x 16 B: one half (128 n) of a gz tile
+    static constexpr int gh = 0, gl = HALF_B, ah = 2 * HALF_B, al = ah + TILE_B, u0 = al + TILE_B, u1 = u0 + 2 * U_B;
+    static constexpr int bars = u1 + 2 * U_B;  // F0, F1, DA, DB, DC
+    static constexpr int slot = bars + 64;
+    static constexpr int TOTAL = slot + 16;
+    static_assert(TOTAL <= 227 * 1024, "tc_wgrad256 shared memory");
+};
+
 template <int NPASS>
 __global__ void __launch_bounds__(128, 1) tc_wgrad256(Wg256Args a) {
+    using S = WgSmem;
     constexpr bool LO = NPASS == 3;
-    constexpr int HALF_B = TILE_B / 2;  // 16 chunk columns x 128 rows x 16 B
-    constexpr int o_gh = 0, o_gl = HALF_B, o_a1 = 2 * HALF_B, o_u = o_a1 + 2 * TILE_B, o_bar = o_u + 2 * U_B;
+    constexpr int HALF_B = S::HALF_B;
     constexpr uint32_t CS = 128 * 16;
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + o_bar);  // 0 full, 1 MMAs done
-    uint32_t* slot = reinterpret_cast<uint32_t*>(smem + o_bar + 16);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::bars);
+    uint32_t* slot = reinterpret_cast<uint32_t*>(smem + S::slot);
     const int tid = threadIdx.x, warp = tid >> 5;
     const int role = (int)blockIdx.x < 4 * a.ns0 ? 0 : 1;
     const int id = role ? (int)blockIdx.x - 4 * a.ns0 : (int)blockIdx.x, ns = role ? a.ns1 : a.ns0;
     const int sp = id % ns, mh = (id / ns) & 1, branch = id / (2 * ns);
     if (warp == 0) tc::tmem_alloc(slot, 512);
     if (tid == 0) {
-        tc::mbar_init(&bars[0], 1);
-        tc::mbar_init(&bars[1], 1);
+        for (int b = 0; b < 5; ++b) tc::mbar_init(&bars[b], 1);
         tc::fence_mbar_init();
     }
     tc::fence_before_sync();
@@ -485,31 +500,75 @@ __global__ void __launch_bounds__(128, 1) tc_wgrad256(Wg256Args a) {
     const uint32_t tmem = *slot;
     const uint32_t sb = tc::smem_u32(smem);
     const int nit = sp < a.tiles ? (a.tiles - sp + ns - 1) / ns : 0;
+    const bool has_f1 = role == 0 || LO;  // a1_hi and / or gz_lo exist
+    const int g_off = role ? IMG_G1 : IMG_G2;
+    const uint32_t F0 = tc::smem_u32(&bars[0]), F1 = tc::smem_u32(&bars[1]);
+    auto img_of = [&](int it) { return a.img + ((size_t)branch * a.tiles + sp + it * ns) * IMG_TILE; };
+    const uint32_t f0_bytes = HALF_B + 2 * U_B + (role == 0 && LO ? TILE_B : 0);
+    const uint32_t f1_bytes = (role == 0 ? TILE_B : 0) + (LO ? HALF_B : 0);
+    // producer-side pieces (one thread)
+    auto load_al_u = [&](int it) {  // first load of a tile's F0 group: arms the barrier for the whole group
+        const uint8_t* img = img_of(it);
+        tc::mbar_expect_tx(F0, f0_bytes);
+        if (role == 0 && LO) tc::bulk_g2s(sb + S::al, img + IMG_A1 + TILE_B, TILE_B, F0);
+        tc::bulk_g2s(sb + ((it & 1) ? S::u1 : S::u0), img + IMG_U, 2 * U_B, F0);
+    };
+    auto load_gh = [&](int it) { tc::bulk_g2s(sb + S::gh, img_of(it) + g_off + mh * HALF_B, HALF_B, F0); };
+    auto load_ah_gl = [&](int it) {
+        const uint8_t* img = img_of(it);
+        tc::mbar_expect_tx(F1, f1_bytes);
+        if (role == 0) tc::bulk_g2s(sb + S::ah, img + IMG_A1, TILE_B, F1);
+        if (LO) tc::bulk_g2s(sb + S::gl, img + g_off + TILE_B + mh * HALF_B, HALF_B, F1);
+    };
     bool ok = true;
-    if (tid == 0) {
-        const TcOperand opG{sb + o_gh, sb + o_gl, CS, true};
-        const TcOperand opA1{sb + o_a1, sb + o_a1 + TILE_B, CS, true}, opUm{sb + o_u, sb + o_u + U_B, CS, true};
-        const uint32_t full = tc::smem_u32(&bars[0]);
-        const int g_off = role ? IMG_G1 : IMG_G2;
-        for (int it = 0; it < nit; ++it) {
-            const int tile = sp + it * ns;
-            const uint8_t* img = a.img + ((size_t)branch * a.tiles + tile) * IMG_TILE;
-            if (it > 0) ok = tc::mbar_wait(&bars[1], (it - 1) & 1) && ok;  // the previous tile's MMAs have read the buffers
-            tc::mbar_expect_tx(full, (LO ? 2 : 1) * HALF_B + (role ? 0 : (LO ? 2 : 1) * TILE_B) + 2 * U_B);
-            tc::bulk_g2s(sb + o_gh, img + g_off + mh * HALF_B, HALF_B, full);
-            if (LO) tc::bulk_g2s(sb + o_gl, img + g_off + TILE_B + mh * HALF_B, HALF_B, full);
-            if (role == 0) tc::bulk_g2s(sb + o_a1, img + IMG_A1, (LO ? 2 : 1) * TILE_B, full);
-            tc::bulk_g2s(sb + o_u, img + IMG_U, 2 * U_B, full);
-            ok = tc::mbar_wait(&bars[0], it & 1) && ok;
-            if (role == 0) {
-                tc_issue_op<NPASS>(tmem, 0, opG, opA1, 128, D, it > 0);
-                tc_issue_op<NPASS>(tmem, D, opG, opUm, 128, 16, it > 0);
-            } else {
-                tc_issue_op<NPASS>(tmem, 0, opG, opUm, 128, 16, it > 0);
+    if (tid == 32 && nit > 0) {  // producer
+        load_al_u(0);
+        load_gh(0);
+        if (has_f1) load_ah_gl(0);
+        for (int it = 0; it + 1 < nit; ++it) {
+            const uint32_t ph = it & 1;
+            // F0 may only be re-armed once the issuer has consumed its current phase, i.e. after a commit that follows
+            // the issuer's F0 wait: P_A's (bf16x3) or P_B's (bf16)
+            ok = tc::mbar_wait(&bars[LO ? 2 : 3], ph) && ok;  // P_A(it) done: a1_lo (and the other u buffer) are free
+            load_al_u(it + 1);
+            if (LO) ok = tc::mbar_wait(&bars[3], ph) && ok;   // P_B(it) done: gz_hi is free
+            load_gh(it + 1);
+            if (has_f1) {
+                ok = tc::mbar_wait(&bars[4], ph) && ok;      // P_C(it) done: a1_hi and gz_lo are free
+                load_ah_gl(it + 1);
             }
-            tc::mma_commit(&bars[1]);
         }
-        if (nit > 0) ok = tc::mbar_wait(&bars[1], (nit - 1) & 1) && ok;
+        if (!ok) asm volatile("trap;");
+    }
+    if (tid == 0 && nit > 0) {  // MMA issuer
+        bool accW = false, accU = false;
+        auto product = [&](uint32_t g_addr, uint32_t a_addr, uint32_t u_addr) {
+            const TcOperand G{sb + g_addr, sb + g_addr, CS, true}, U{sb + u_addr, sb + u_addr, CS, true};
+            if (role == 0) {
+                const TcOperand A1{sb + a_addr, sb + a_addr, CS, true};
+                tc_issue_op<1>(tmem, 0, G, A1, 128, D, accW);
+                accW = true;
+                tc_issue_op<1>(tmem, D, G, U, 128, 16, accU);
+            } else {
+                tc_issue_op<1>(tmem, 0, G, U, 128, 16, accU);
+            }
+            accU = true;
+        };
+        for (int it = 0; it < nit; ++it) {
+            const uint32_t ph = it & 1;
+            const uint32_t ub = (it & 1) ? S::u1 : S::u0;
+            ok = tc::mbar_wait(&bars[0], ph) && ok;  // gz_hi, a1_lo, u
+            if (LO) {
+                product(S::gh, S::al, ub + U_B);      // P_A: gz_hi . [a1_lo | u_lo]
+                tc::mma_commit(&bars[2]);
+            }
+            if (has_f1) ok = tc::mbar_wait(&bars[1], ph) && ok;  // a1_hi, gz_lo
+            product(S::gh, S::ah, ub);                // P_B: gz_hi . [a1_hi | u_hi]
+            tc::mma_commit(&bars[3]);
+            if (LO) product(S::gl, S::ah, ub);        // P_C: gz_lo . [a1_hi | u_hi]
+            tc::mma_commit(&bars[4]);
+        }
+        ok = tc::mbar_wait(&bars[4], (nit - 1) & 1) && ok;
         if (!ok) asm volatile("trap;");
     }
     __syncthreads();
@@ -568,7 +627,7 @@ int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const
                  Gr, Gs, part, img, nM};
     const bool x3 = precision == EGNN_PREC_BF16X3;
     static bool configured = false;
-    constexpr int WG_SMEM = TILE_B + 2 * TILE_B + 2 * U_B + 64;
+    constexpr int WG_SMEM = WgSmem::TOTAL;
     if (!configured) {
         EGNN_CUDA(cudaFuncSetAttribute(tc_edge_bwd256<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, LB::TOTAL));
         EGNN_CUDA(cudaFuncSetAttribute(tc_edge_bwd256<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, LB::TOTAL));
@@ -581,7 +640,14 @@ int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const
     else tc_edge_bwd256<1><<<nM + nX, NT, LB::TOTAL, st>>>(a);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("tc_edge_bwd256");
-    const int ns0 = tiles < 30 ? tiles : 30, ns1 = tiles < 7 ? tiles : 7;  // 120 + 28 CTAs: role 1 moves ~1/3 of the bytes per tile
+    // 37 K splits per (branch, half): role 1 moves 72 KB per tile against role 0's 200 KB, but its tiles are latency-bound
+    static int ns1_cfg = -1;
+    if (ns1_cfg < 0) {
+        const char* env = getenv("EGNN_WG_NS1");
+        ns1_cfg = env ? atoi(env) : 13;
+        if (ns1_cfg < 1 || ns1_cfg > 36) ns1_cfg = 13;  // measured best at cfg4 size (7: 0.86 ms, 11: 0.59, 13: 0.51, 16: 0.53)
+    }
+    const int ns0 = tiles < 37 - ns1_cfg ? tiles : 37 - ns1_cfg, ns1 = tiles < ns1_cfg ? tiles : ns1_cfg;
     Wg256Args w{net, tiles, ns0, ns1, img, part, 148};
     egnn_prof_begin(EGNN_K_TC_WGRAD, st);
     if (x3) tc_wgrad256<3><<<4 * (ns0 + ns1), 128, WG_SMEM, st>>>(w);
