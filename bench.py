@@ -388,10 +388,9 @@ def run_product(args, rank, world, local):
         issued = (2 * passes + wgrad_passes if top.endswith("bwd") else passes) * edge_flops
         traffic = None
         try:
-            if CFG["name"] != "cfg2":
-                raise OSError("the committed ncu traffic figure is for the cfg2 kernels")
+            tkey = top + ("256" if CFG["d"] == 256 else "")  # ncu captures: cfg2 for the d=128 kernels, cfg4 for d=256
             with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
-                traffic = json.load(f).get(top, {}).get("dram_bytes_per_launch")
+                traffic = json.load(f).get(tkey, {}).get("dram_bytes_per_launch")
         except OSError:
             pass
         roofline = dict(bound="tensor", kernel=top, achieved=ach, peak=peaks["tflops"], unit="TFLOP/s",
