@@ -13,8 +13,20 @@
 // Per tile:  GEMM1 (issued one tile ahead) -> SiLU -> A1 -> 16 x (slice wait, NPASS MMAs of K = 16, commit) -> layer-2
 // epilogue: mlp_x: phi_e = wx3 . SiLU(z2 + b2) + bx3;  mlp_m: m = SiLU(z2 + b2), g = sigmoid(wa . m + ba), g * m summed per
 // receiver in edge order (fixed order, no atomics) exactly like the d <= 128 kernel.
+#include <cstdlib>
+
 #include "tc_bulk.cuh"
 #include "tc_tile.cuh"
+
+#ifdef EGNN_DBG_TIMING  // phase time stamps of tile #3 of CTA 0 and CTA 147 (timing experiment, scripts/dbg_phases256.py)
+__device__ long long g_dbg_stamp[2][16];
+#define DBG_STAMP(k) do { if (it == 3 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) g_dbg_stamp[blockIdx.x ? 1 : 0][k] = clock64(); } while (0)
+extern "C" int egnn_dbg_read_stamps(long long* host16x2) {
+    return cudaMemcpyFromSymbol(host16x2, g_dbg_stamp, sizeof(g_dbg_stamp)) == cudaSuccess ? 0 : -2;
+}
+#else
+#define DBG_STAMP(k) do { } while (0)
+#endif
 
 namespace {
 
@@ -201,7 +213,10 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
     bool ok = true;
     auto produce = [&](int limit) {
         for (; gload < limit; ++gload) {
-            if (gload >= NSLOT) ok = tc::mbar_wait(&bars[2 + NSLOT + gload % NSLOT], ((gload - NSLOT) / NSLOT) & 1) && ok;
+            // slots are released in PAIRS (one tcgen05.commit per two slices: the commit is the expensive part of an
+            // issue iteration): the pair of slices g, g+1 (g even) waits for the commit that followed slice g - 3
+            if (gload >= NSLOT && (gload & 1) == 0)
+                ok = tc::mbar_wait(&bars[2 + NSLOT + (gload / 2) % 2], ((gload - NSLOT) / NSLOT) & 1) && ok;
             load_slice(gload);
         }
     };
@@ -220,18 +235,23 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
         Row gnext;
         int dst_next = -3;
         if (tid < 128 && has_next) gather_ids(tile + tstride, gnext);
+        if (tid == 0) DBG_STAMP(0);  // tile start
         ok = tc::mbar_wait(&bars[0], phase) && ok;  // z1 = U . W1^T
         tc::fence_after_sync();
+        if (tid == 0) DBG_STAMP(1);  // GEMM1 observed
         if (tid < 128 && has_next) gather_nodes(gnext);
         // ---- layer-1 epilogue: a1 = SiLU(z1) -> tile A1 (bf16 hi / lo), this thread's 64 columns
         tc_epi_store_chunked(trow + c0, smem + L::a1_hi, smem + L::a1_lo, r, c0, LO);
         tc_epi_store_chunked(trow + c0 + 32, smem + L::a1_hi, smem + L::a1_lo, r, c0 + 32, LO);
         if (tid < 128 && has_next) dst_next = store_u(tile + tstride, gnext);  // GEMM1 is done with the U tile
+        if (tid == 0) DBG_STAMP(2);  // warp 0 finished its layer-1 epilogue
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
+        if (tid == 0) DBG_STAMP(3);  // barrier passed
         if (issuer_warp && tc::elect_one()) {
             tc::fence_after_sync();
+            DBG_STAMP(8);  // issuer starts
             const uint32_t idesc = tc::make_idesc_bf16(128, D);
             for (int s = 0; s < NSLICE; ++s) {
                 const int g = it * NSLICE + s, st = g % NSLOT;
@@ -247,9 +267,10 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
                     tc::mma_bf16(tmem + D, a_lo, b_hi, idesc, true);
                     tc::mma_bf16(tmem + D, a_hi, b_lo, idesc, true);
                 }
-                tc::mma_commit(&bars[2 + NSLOT + st]);  // slot st is free again once these MMAs have read it
+                if (g & 1) tc::mma_commit(&bars[2 + NSLOT + (g / 2) % 2]);  // slots of slices g-1, g are free once these MMAs are done
             }
             tc::mma_commit(&bars[1]);
+            DBG_STAMP(9);  // last MMA of GEMM2 issued and committed
             if (has_next) {  // z1 has been consumed by every warp (barrier above): next tile's GEMM1 queues behind GEMM2
                 tc_issue_op<NPASS>(tmem, 0, opU, opW1, 16, D, false);
                 tc::mma_commit(&bars[0]);
@@ -260,6 +281,7 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
         __syncwarp();
         ok = tc::mbar_wait(&bars[1], phase) && ok;
         tc::fence_after_sync();
+        if (tid == 0) DBG_STAMP(4);  // GEMM2 observed
         // ---- layer-2 epilogue
         if (branch == 1) {
             float s = 0.f;
@@ -320,6 +342,7 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
             }
         }
         __syncthreads();  // staging (aliases A1), rowPart and the flush table are free
+        if (tid == 0) DBG_STAMP(5);  // tile end
         if (tid < 128 && has_next) store_dst(dst_next);
     }
     if (!ok) asm volatile("trap;");  // an mbarrier wait timed out: fail loudly instead of returning garbage
@@ -349,8 +372,17 @@ int egnn_tc_edge_forward256(const egnn_net_t& net, const egnn_graph_t& g, const 
     EGNN_REQUIRE(net.Mh == 256 && tc_fwd_supported(net), "egnn_tc_edge_forward256: needs Mh = Ms = Xh = 256 and 2H+1 <= 16");
     const PackOff po = pack_off(net);
     const int tiles = (g.E + 127) / 128;
-    int nM = 74, nX = 74;  // one CTA per SM, half of them per branch
-    if (tiles < 74) nM = nX = tiles;
+    // one CTA per SM; the message branch does more per tile (gate, staging, segmented sums: 19.0 k cycles against 13.7 k for
+    // the coordinate branch, scripts/dbg_phases256.py), so it gets the larger share of the CTAs
+    static int share = -1;
+    if (share < 0) {
+        const char* env = getenv("EGNN_TC256_FWD_MCTAS");
+        share = env ? atoi(env) : 86;
+        if (share < 16 || share > 132) share = 86;
+    }
+    int nM = share, nX = 148 - share;
+    if (tiles < nM) nM = tiles;
+    if (tiles < nX) nX = tiles;
     Tc256Args a{net, g.N, g.E, tiles, g.recv, g.send, g.row_ptr, h, x,
                 reinterpret_cast<const uint8_t*>(packed_layer + po.tc), agg, part, phi_edge, nM};
     return precision == EGNN_PREC_BF16X3 ? launch256<3>(a, nM + nX, st) : launch256<1>(a, nM + nX, st);

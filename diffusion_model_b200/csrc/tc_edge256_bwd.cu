@@ -191,7 +191,9 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
     bool ok = true;
     auto produce = [&](int limit) {
         for (; gload < limit; ++gload) {
-            if (gload >= NSLOT) ok = tc::mbar_wait(&bars[4 + NSLOT + gload % NSLOT], ((gload - NSLOT) / NSLOT) & 1) && ok;
+            // slots are released in pairs (one tcgen05.commit per two slices, see tc_edge256.cu)
+            if (gload >= NSLOT && (gload & 1) == 0)
+                ok = tc::mbar_wait(&bars[4 + NSLOT + (gload / 2) % 2], ((gload - NSLOT) / NSLOT) & 1) && ok;
             load_slice(gload);
         }
     };
@@ -216,7 +218,7 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
                 if (a_lo) tc::mma_bf16(tmem + dcol, al, bh, idesc, true);
                 tc::mma_bf16(tmem + dcol, ah, bl, idesc, true);
             }
-            tc::mma_commit(&bars[4 + NSLOT + st]);
+            if (g & 1) tc::mma_commit(&bars[4 + NSLOT + (g / 2) % 2]);
         }
     };
 
@@ -622,7 +624,13 @@ int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const
     const PackOff po = pack_off(net);
     const uint8_t* blob = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
     const int tiles = (g.E + 127) / 128;
-    const int nM = tiles < 74 ? tiles : 74, nX = nM;
+    static int share = -1;  // CTAs of the message branch (it makes two passes over z2 for the gate)
+    if (share < 0) {
+        const char* env = getenv("EGNN_TC256_BWD_MCTAS");
+        share = env ? atoi(env) : 74;
+        if (share < 16 || share > 132) share = 74;
+    }
+    const int nM = tiles < share ? tiles : share, nX = tiles < 148 - share ? tiles : 148 - share;
     Bwd256Args a{net, g.N, g.E, tiles, g.recv, g.send, g.node_graph, h, x, blob, blob + tc_w2t_offset(net.Mh), gM, gdx, coefS,
                  Gr, Gs, part, img, nM};
     const bool x3 = precision == EGNN_PREC_BF16X3;
