@@ -754,14 +754,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         ok = tc::mbar_wait(&bars[0], phase) && ok;  // z1 = U . W1^T of this tile (issued one phase ahead)
         tc::fence_after_sync();
         // ---- a1 = SiLU(z1 + b1) -> tile A1;  SiLU'(z1 + b1) replaces z1 in TMEM (read back by the gz1 phase)
-        {
-            float v[32], act[32];
-            tc::tmem_ld32(trow + cA + c0, v);
-#pragma unroll
-            for (int i = 0; i < 32; ++i) tc_silu_and_grad2_h(v[i], act[i], v[i]);  // TMEM holds z1 / 2 incl. bias
-            tc_split_store32(smem + L::a1_hi, smem + L::a1_lo, r, c0, act, LO);
-            tc::tmem_st32(trow + cA + c0, v);
-        }
+        tc_epi_bwd_chunked(trow + cA + c0, smem + L::a1_hi, smem + L::a1_lo, r, c0, LO);  // TMEM holds z1 / 2 incl. bias
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();

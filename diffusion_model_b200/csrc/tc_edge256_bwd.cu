@@ -7,18 +7,33 @@
 //     upstream    gz2 = dL/dz2 (gate / phi algebra of SURVEY.md Appendix A on the CUDA cores) -> tile R
 //     dgrad       ga1 = gz2.W2 with the TRANSPOSED image W2T streamed the same way (over z2 in TMEM)
 //     gz1 = ga1 * SiLU'(z1) -> tile R;  gu = gz1.W1 (16 columns) -> per-edge outputs Gr / Gs
-//     every operand tile the weight gradients need -- a1 (hi + lo), gz2 (hi), gz1 (hi), u (hi + lo) -- leaves shared memory
-//     as a ready-made tcgen05 tile image through a bulk async store (no transposition, no second layout);
+//     [dW1 | db1] of the tile = gz1^T.u (two M = 128 halves, 16 columns each, next to gu) is read back and summed over the
+//     CTA's tiles in 8 registers per thread -- the narrow product needs no image;
+//     the operand tiles of the wide product -- a1 (hi + lo), gz2 (hi + lo), u (hi + lo) -- leave shared memory as ready-made
+//     tcgen05 tile images through bulk async stores (no transposition, no second layout): 270 KB per tile and branch, which
+//     makes this kernel HBM-WRITE bound for a third of its time (the stores run at the SM's share of the HBM bandwidth);
 //     d wa / d wx3 / d ba / d bx3 are register column sums written to the CTA's private partial row.
 //   tc_wgrad256 (split-K GEMM over the edge tiles; CTA = branch x half of the output rows x K split)
-//     [dW2 | db2] += gz2^T.[a1 | u],  [dW1 | db1] += gz1^T.u   (tile images viewed MN-major: K = the 128 edges of a tile;
-//     slot 15 of u is the constant 1, so bias gradients are MMA columns); accumulators persistent in TMEM over the CTA's
-//     tiles, written once to its partial row.  This kernel is HBM-bound by construction (it streams the images).
+//     [dW2 | db2] += gz2^T.[a1 | u]   (tile images viewed MN-major: K = the 128 edges of a tile; slot 15 of u is the
+//     constant 1, so the bias gradient is an MMA column); accumulators persistent in TMEM over the CTA's tiles, written
+//     once to its partial row.  This kernel is HBM-bound by construction (it streams the images).
 // Conventions as in tc_edge.cu: weight images are stored halved, gradient tiles carry 2 dL/dz, results are halved once.
 #include <cstdlib>
 
 #include "tc_bulk.cuh"
 #include "tc_tile.cuh"
+
+#ifdef EGNN_DBG_TIMING  // phase time stamps of tile #3 of the first (mlp_m) and last (mlp_x) CTA, scripts/dbg_phases256.py
+__device__ long long g_dbg_stamp_bwd[2][16];
+#define DBG_STAMP_T(k) do { if (it == 3 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) g_dbg_stamp_bwd[blockIdx.x ? 1 : 0][k] = clock64(); } while (0)
+#define DBG_STAMP(k) do { if (it == 3 && tid == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) g_dbg_stamp_bwd[blockIdx.x ? 1 : 0][k] = clock64(); } while (0)
+extern "C" int egnn_dbg_read_stamps_bwd(long long* host16x2) {
+    return cudaMemcpyFromSymbol(host16x2, g_dbg_stamp_bwd, sizeof(g_dbg_stamp_bwd)) == cudaSuccess ? 0 : -2;
+}
+#else
+#define DBG_STAMP(k) do { } while (0)
+#define DBG_STAMP_T(k) do { } while (0)
+#endif
 
 namespace {
 
@@ -27,8 +42,8 @@ constexpr int NSLICE = 16, NSLOT = 4, SLICE_B = D * 16 * 2;
 constexpr int TILE_B = 128 * D * 2;  // one bf16 [128 x 256] tile (hi or lo)
 constexpr int U_B = 128 * 32;
 
-// bytes of tile images per 128-edge tile and branch:  a1 hi | a1 lo | gz2 hi | gz2 lo | gz1 hi | gz1 lo | u hi | u lo
-constexpr int IMG_A1 = 0, IMG_G2 = 2 * TILE_B, IMG_G1 = 4 * TILE_B, IMG_U = 6 * TILE_B, IMG_TILE = 6 * TILE_B + 2 * U_B;
+// bytes of tile images per 128-edge tile and branch:  a1 hi | a1 lo | gz2 hi | gz2 lo | u hi | u lo
+constexpr int IMG_A1 = 0, IMG_G2 = 2 * TILE_B, IMG_U = 4 * TILE_B, IMG_TILE = 4 * TILE_B + 2 * U_B;
 
 struct LB {
     static constexpr int w1_hi = 0, w1_lo = D * 32;
@@ -224,6 +239,7 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
 
     float accv0 = 0.f, accv1 = 0.f;  // running column sums of coef_e * out_e (d wa / d wx3): columns c0 + lane, c0 + 32 + lane
     float accs = 0.f;                // running sum of coef_e of this thread's row (d ba / d bx3)
+    float accW1[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // running [dW1 | db1] entries of this thread (see the tile end)
 
     for (int it = 0; it < nit; ++it) {
         const int tile = tile0 + it * tstride;
@@ -231,28 +247,28 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
         const uint32_t phase = it & 1;
         const bool has_next = it + 1 < nit;
         uint8_t* img = a.img + ((size_t)branch * a.tiles + tile) * IMG_TILE;
+        DBG_STAMP(0);
         ok = tc::mbar_wait(&bars[0], phase) && ok;
         tc::fence_after_sync();
+        DBG_STAMP(1);
         // ---- a1 = SiLU(z1) -> tile R;  2 SiLU'(z1) replaces z1 in TMEM
-#pragma unroll 1
-        for (int hh = 0; hh < 2; ++hh) {
-            float v[32], act[32];
-            tc::tmem_ld32(trow + cA + c0 + 32 * hh, v);
-#pragma unroll
-            for (int i = 0; i < 32; ++i) tc_silu_and_grad2_h(v[i], act[i], v[i]);
-            tc_split_store32(smem + L::R_hi, smem + L::R_lo, r, c0 + 32 * hh, act, LO);
-            tc::tmem_st32(trow + cA + c0 + 32 * hh, v);
-        }
+        tc_epi_bwd_chunked(trow + cA + c0, smem + L::R_hi, smem + L::R_lo, r, c0, LO);
+        tc_epi_bwd_chunked(trow + cA + c0 + 32, smem + L::R_hi, smem + L::R_lo, r, c0 + 32, LO);
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
+        DBG_STAMP(10);  // a1 barrier passed
         if (issuer_warp && tc::elect_one()) {
             tc::fence_after_sync();
             tc::bulk_s2g(img + IMG_A1, sb + L::R_hi, LO ? 2 * TILE_B : TILE_B);
             tc::bulk_s2g(img + IMG_U, sb + L::u_hi, 2 * U_B);
             tc::bulk_commit();
+            // (draining the store before the MMAs start was measured: the store then takes 5.8 k cycles on its own -- 136 KB at
+            //  the SM's share of the HBM write bandwidth -- and the sum stays the same; the overlap is kept)
+            DBG_STAMP_T(11);  // image stores issued
             stream_gemm(it * 2 * NSLICE, cB, true, ok);  // z2 = a1 . W2^T
             tc::mma_commit(&bars[1]);
+            DBG_STAMP_T(12);  // GEMM2 issued
         } else if (producer) {
             produce(min(total_slices, it * 2 * NSLICE + NSLICE + NSLOT));
         }
@@ -260,8 +276,10 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
         // ---- in the shadow of GEMM2: next tile's gather loads
         EdgeRow gnext;
         if (tid < 128 && has_next) gather_load(tile + tstride, gnext);
+        DBG_STAMP(2);  // a1 epilogue + barrier + gather loads done
         ok = tc::mbar_wait(&bars[1], phase) && ok;
         tc::fence_after_sync();
+        DBG_STAMP(3);  // GEMM2 observed
         // ---- upstream gradient of z2.  message branch: two passes over z2 (the gate needs the whole row first)
         const float4 rr = sR[r];
         const int i = sI[r];
@@ -296,7 +314,7 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
         if (issuer_warp && tc::elect_one()) tc::bulk_wait_read();  // the a1 / u images have left shared memory
         __syncwarp();
         __syncthreads();
-        if (tid < 128 && has_next) store_u(gnext);  // GEMM1 of this tile and the u image store are done with the U tile
+        DBG_STAMP(4);  // gate pass + barrier
         if (branch == 0) {
             const float ssum = vec[2 * D] + rowA[r] + rowA[128 + r] + rowA[256 + r] + rowA[384 + r];
             const float tsum = rowB[r] + rowB[128 + r] + rowB[256 + r] + rowB[384 + r];
@@ -349,38 +367,36 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
         __syncwarp();
         float phi = 0.f;
         if (branch == 1 && cg == 0) phi = vec[2 * D] + rowA[r] + rowA[128 + r] + rowA[256 + r] + rowA[384 + r];
+        DBG_STAMP(5);  // gz2 pass + barrier
         ok = tc::mbar_wait(&bars[2], phase) && ok;
         tc::fence_after_sync();
+        DBG_STAMP(6);  // dgrad observed
         if (issuer_warp && tc::elect_one()) tc::bulk_wait_read();  // the gz2 image has left tile R
         __syncwarp();
         __syncthreads();
         // ---- gz1 = ga1 * SiLU'(z1) -> tile R
-#pragma unroll 1
-        for (int hh = 0; hh < 2; ++hh) {
-            float ga[32], d1[32];
-            tc::tmem_ld32(trow + cB + c0 + 32 * hh, ga);
-            tc::tmem_ld32(trow + cA + c0 + 32 * hh, d1);
-#pragma unroll
-            for (int k = 0; k < 32; ++k) ga[k] *= d1[k];
-            tc_split_store32(smem + L::R_hi, smem + L::R_lo, r, c0 + 32 * hh, ga, LO);
-        }
+        tc_gz1_chunked(trow + cB + c0, trow + cA + c0, smem + L::R_hi, smem + L::R_lo, r, c0, LO);
+        tc_gz1_chunked(trow + cB + c0 + 32, trow + cA + c0 + 32, smem + L::R_hi, smem + L::R_lo, r, c0 + 32, LO);
         tc::fence_async_smem();
         tc::fence_before_sync();
         __syncthreads();
         if (issuer_warp && tc::elect_one()) {
             tc::fence_after_sync();
-            tc::bulk_s2g(img + IMG_G1, sb + L::R_hi, LO ? 2 * TILE_B : TILE_B);
-            tc::bulk_commit();
             tc_issue_op<NPASS>(tmem, cB, opR, opW1mn, D, 16, false, LO);  // gu = gz1 . W1  (16 columns, over ga1)
-            tc::mma_commit(&bars[3]);
-            if (has_next) {  // SiLU'(z1) has been consumed; the next U tile was stored two barriers ago
-                tc_issue_op<NPASS>(tmem, cA, opU, opW1, 16, D, false);
-                tc::mma_commit(&bars[0]);
+            // [dW1 | db1] of this tile = gz1^T . u: tile R viewed MN-major (K = the 128 edges), one MMA group per half of n
+            const TcOperand opUmn{sb + L::u_hi, sb + L::u_lo, CS, true};
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+                const TcOperand opRh{sb + L::R_hi + hf * 16 * CS, sb + L::R_lo + hf * 16 * CS, CS, true};
+                tc_issue_op<NPASS>(tmem, cB + 32 + 16 * hf, opRh, opUmn, 128, 16, false, LO);
             }
+            tc::mma_commit(&bars[3]);
         }
         __syncwarp();
+        DBG_STAMP(7);  // gz1 pass + barrier
         ok = tc::mbar_wait(&bars[3], phase) && ok;
         tc::fence_after_sync();
+        DBG_STAMP(8);  // gu observed
         if (cg == 0) {  // this branch's per-edge outputs
             float gu[32];
             tc::tmem_ld32(trow + cB, gu);
@@ -410,11 +426,26 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
                 Gsb[e * W + H + 2] = -g2;
             }
         }
-        if (issuer_warp && tc::elect_one()) tc::bulk_wait_read();  // the gz1 image has left tile R
-        __syncwarp();
+        {   // thread (row r, column group cg): rows n = 128 (cg / 2) + r of [dW1 | db1], columns 8 (cg % 2) .. + 7
+            float w[8];
+            tc::tmem_ld8(trow + cB + 32 + 16 * (cg >> 1) + 8 * (cg & 1), w);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) accW1[k] += w[k];
+        }
         tc::fence_before_sync();
-        __syncthreads();  // sI / sR / tile R / the gu columns are free
-        if (tid < 128 && has_next) store_row(gnext);  // read after the barrier that follows the next a1 epilogue
+        __syncthreads();  // sI / sR / tile R / the U tile / the gu and dW1 columns are free
+        DBG_STAMP(9);  // tile end
+        if (tid < 128 && has_next) {
+            store_u(gnext);
+            store_row(gnext);
+        }
+        tc::fence_async_smem();
+        __syncthreads();
+        if (has_next && issuer_warp && tc::elect_one()) {
+            tc::fence_after_sync();
+            tc_issue_op<NPASS>(tmem, cA, opU, opW1, 16, D, false);  // z1 of the next tile
+            tc::mma_commit(&bars[0]);
+        }
     }
     if (issuer_warp && tc::elect_one()) tc::bulk_wait_all();
     if (!ok) asm volatile("trap;");
@@ -422,6 +453,16 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
         const LayerOff lo = layer_off(a.net);
         float* part = a.part + (size_t)blockIdx.x * lo.total;
         const int o_wv = branch ? lo.wx3 : lo.wa, o_bv = branch ? lo.bx3 : lo.ba;
+        {
+            const int K0 = 2 * H + 1, o_w1 = branch ? lo.wx1 : lo.wm1, o_b1 = branch ? lo.bx1 : lo.bm1;
+            const int n = 128 * (cg >> 1) + r;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int col = 8 * (cg & 1) + k;
+                if (col < K0) part[o_w1 + n * K0 + col] = 0.5f * accW1[k];  // the gz tiles carry 2 dL/dz
+                else if (col == 15) part[o_b1 + n] = 0.5f * accW1[k];
+            }
+        }
         float* colred = rowA;  // [16 warps][2][32] = 1024 floats: rowA and rowB are contiguous
         colred[(warp * 2 + 0) * 32 + lane] = accv0;
         colred[(warp * 2 + 1) * 32 + lane] = accv1;
@@ -449,16 +490,15 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_bwd256(Bwd256Args a) {
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Weight-gradient GEMM over the tile images (split-K over the edge tiles, accumulators persistent in TMEM).
-//   role 0 CTAs (branch, half mh of the output rows n, K split):   cols [0,256)   += gz2[:, n-half]^T . a1
-//                                                                  cols [256,272) += gz2[:, n-half]^T . u    (col 15: db2)
-//   role 1 CTAs (branch, half mh, K split):                        cols [0,16)    += gz1[:, n-half]^T . u    (dW1, col 15: db1)
+//   CTA = (branch, half mh of the output rows n, K split):   cols [0,256)   += gz2[:, n-half]^T . a1
+//                                                            cols [256,272) += gz2[:, n-half]^T . u    (col 15: db2)
 // All three split products (hi.hi + lo.hi + hi.lo): with only the hi part of gz the error of a weight gradient whose
 // per-edge terms have random signs is ~2^-9 of the LARGEST entry (measured 3e-3 on the cfg4 fixture), above the 1e-3 bar.
 // 128 threads; thread t owns TMEM lane t = output row n = 128 mh + t in the epilogue.
 // ---------------------------------------------------------------------------------------------------------------------
 struct Wg256Args {
     egnn_net_t net;
-    int tiles, ns0, ns1;  // K splits of role 0 / role 1
+    int tiles, ns0;  // K splits
     const uint8_t* img;
     float* part;  // rows [row0, row0 + grid)
     int row0;
@@ -488,8 +528,8 @@ __global__ void __launch_bounds__(128, 1) tc_wgrad256(Wg256Args a) {
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::bars);
     uint32_t* slot = reinterpret_cast<uint32_t*>(smem + S::slot);
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int role = (int)blockIdx.x < 4 * a.ns0 ? 0 : 1;
-    const int id = role ? (int)blockIdx.x - 4 * a.ns0 : (int)blockIdx.x, ns = role ? a.ns1 : a.ns0;
+    constexpr int role = 0;  // (a second role, gz1^T . u from a gz1 image, was folded into tc_edge_bwd256)
+    const int id = (int)blockIdx.x, ns = a.ns0;
     const int sp = id % ns, mh = (id / ns) & 1, branch = id / (2 * ns);
     if (warp == 0) tc::tmem_alloc(slot, 512);
     if (tid == 0) {
@@ -503,7 +543,7 @@ __global__ void __launch_bounds__(128, 1) tc_wgrad256(Wg256Args a) {
     const uint32_t sb = tc::smem_u32(smem);
     const int nit = sp < a.tiles ? (a.tiles - sp + ns - 1) / ns : 0;
     const bool has_f1 = role == 0 || LO;  // a1_hi and / or gz_lo exist
-    const int g_off = role ? IMG_G1 : IMG_G2;
+    const int g_off = IMG_G2;
     const uint32_t F0 = tc::smem_u32(&bars[0]), F1 = tc::smem_u32(&bars[1]);
     auto img_of = [&](int it) { return a.img + ((size_t)branch * a.tiles + sp + it * ns) * IMG_TILE; };
     const uint32_t f0_bytes = HALF_B + 2 * U_B + (role == 0 && LO ? TILE_B : 0);
@@ -648,18 +688,11 @@ int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const
     else tc_edge_bwd256<1><<<nM + nX, NT, LB::TOTAL, st>>>(a);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("tc_edge_bwd256");
-    // 37 K splits per (branch, half): role 1 moves 72 KB per tile against role 0's 200 KB, but its tiles are latency-bound
-    static int ns1_cfg = -1;
-    if (ns1_cfg < 0) {
-        const char* env = getenv("EGNN_WG_NS1");
-        ns1_cfg = env ? atoi(env) : 13;
-        if (ns1_cfg < 1 || ns1_cfg > 36) ns1_cfg = 13;  // measured best at cfg4 size (7: 0.86 ms, 11: 0.59, 13: 0.51, 16: 0.53)
-    }
-    const int ns0 = tiles < 37 - ns1_cfg ? tiles : 37 - ns1_cfg, ns1 = tiles < ns1_cfg ? tiles : ns1_cfg;
-    Wg256Args w{net, tiles, ns0, ns1, img, part, 148};
+    const int ns0 = tiles < 37 ? tiles : 37;  // 2 branches x 2 halves x 37 K splits = 148 CTAs
+    Wg256Args w{net, tiles, ns0, img, part, 148};
     egnn_prof_begin(EGNN_K_TC_WGRAD, st);
-    if (x3) tc_wgrad256<3><<<4 * (ns0 + ns1), 128, WG_SMEM, st>>>(w);
-    else tc_wgrad256<1><<<4 * (ns0 + ns1), 128, WG_SMEM, st>>>(w);
+    if (x3) tc_wgrad256<3><<<4 * ns0, 128, WG_SMEM, st>>>(w);
+    else tc_wgrad256<1><<<4 * ns0, 128, WG_SMEM, st>>>(w);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("tc_wgrad256");
     return EGNN_OK;

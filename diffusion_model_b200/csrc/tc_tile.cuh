@@ -69,6 +69,42 @@ __device__ __forceinline__ void tc_epi_store_chunked(uint32_t taddr, uint8_t* t_
     }
 }
 
+// backward layer-1 epilogue of columns [c0, c0+32): a1 = SiLU(z1) -> bf16 hi/lo chunks of a 128-row tile, 2 SiLU'(z1)
+// back into the same TMEM columns; chunked like tc_epi_store_chunked (8 columns per trip of a REAL loop: light on
+// registers, MUFU and ALU work of different warps interleave)
+__device__ __forceinline__ void tc_epi_bwd_chunked(uint32_t taddr, uint8_t* t_hi, uint8_t* t_lo, int r, int c0, bool with_lo) {
+#pragma unroll 1
+    for (int j = 0; j < 4; ++j) {
+        float v[8], act[8];
+        tc::tmem_ld8(taddr + 8 * j, v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) tc_silu_and_grad2_h(v[i], act[i], v[i]);
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) tc::split2(act[2 * i], act[2 * i + 1], hi[i], lo[i]);
+        const uint32_t off = tc::chunk_off(128, r, (c0 >> 3) + j);
+        *reinterpret_cast<uint4*>(t_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        if (with_lo) *reinterpret_cast<uint4*>(t_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        tc::tmem_st8(taddr + 8 * j, v);
+    }
+    tc::tmem_wait_st();
+}
+// gz1 = ga1 * (2 SiLU'(z1)) of columns [c0, c0+32) -> bf16 hi/lo chunks, chunked the same way
+__device__ __forceinline__ void tc_gz1_chunked(uint32_t t_ga, uint32_t t_d1, uint8_t* t_hi, uint8_t* t_lo, int r, int c0, bool with_lo) {
+#pragma unroll 1
+    for (int j = 0; j < 4; ++j) {
+        float ga[8], d1[8];
+        tc::tmem_ld8(t_ga + 8 * j, ga);
+        tc::tmem_ld8(t_d1 + 8 * j, d1);
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) tc::split2(ga[2 * i] * d1[2 * i], ga[2 * i + 1] * d1[2 * i + 1], hi[i], lo[i]);
+        const uint32_t off = tc::chunk_off(128, r, (c0 >> 3) + j);
+        *reinterpret_cast<uint4*>(t_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        if (with_lo) *reinterpret_cast<uint4*>(t_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+}
+
 __device__ __forceinline__ void tc_store32(uint8_t* a_hi, uint8_t* a_lo, int r, int c0, const uint32_t (&hi)[16],
                                            const uint32_t (&lo)[16], bool with_lo) {
 #pragma unroll

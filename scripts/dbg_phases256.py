@@ -34,3 +34,21 @@ for prec in ("bf16x3", "bf16"):
         t0 = st[0]
         print(prec, "CTA", "first (mlp_m)" if cta == 0 else "last (mlp_x)",
               " | ".join(f"{names[k]} +{st[k] - t0}" for k in (1, 2, 3, 8, 9, 4, 5)))
+
+# backward (tc_edge_bwd256): one forward + backward, stamps of tile #3
+bnames = {1: "GEMM1 observed", 10: "a1 barrier passed", 11: "image stores issued", 12: "GEMM2 issued", 2: "gather loads done", 3: "GEMM2 observed", 4: "gate pass+barrier", 5: "gz2 pass+barrier",
+          6: "dgrad observed", 7: "gz1 pass+barrier", 8: "gu observed", 9: "tile end"}
+for prec in ("bf16x3", "bf16"):
+    layer.precision = prec
+    hg, xg = h.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    for _ in range(2):
+        layer.zero_grad(set_to_none=True)
+        ho, xo = layer(ei, hg, xg)
+        (ho.sum() + xo.sum()).backward()
+    torch.cuda.synchronize()
+    buf = (C.c_longlong * 32)()
+    assert lib.egnn_dbg_read_stamps_bwd(buf) == 0
+    for cta in (0, 1):
+        t0 = buf[cta * 16]
+        print(prec, "bwd CTA", "first (mlp_m)" if cta == 0 else "last (mlp_x)",
+              " | ".join(f"{bnames[k]} +{buf[cta * 16 + k] - t0}" for k in (1, 10, 11, 12, 2, 3, 4, 5, 6, 7, 8, 9)))
