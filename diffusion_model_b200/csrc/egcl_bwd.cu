@@ -133,9 +133,14 @@ __global__ void __launch_bounds__(256) egcl_node_bwd(NodeBwdArgs a) {
 // entries of a row are never written, so they must not be read); otherwise every edge row holds every edge parameter.
 // 64 parameters x 4 row groups per CTA: group g sums rows r0+g, r0+g+4, ... (eight loads in flight), the four group
 // sums are then added in group order -- a fixed order, so reruns are bit-identical.
+// d = 256 (tc_edge256_bwd.cu): rows [0, nM) / [nM, nM + nX) hold the layer-1 and row-dot parameters of the two branches,
+// rows 148 + (2 branch + n / 128) ns + [0, ns) the K splits of row n of [W2 | b2]
+struct RowMap256 {
+    int on, nM, nX, ns, wm2, wx2, D;
+};
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ part, int rowsE, int rowsN, int n,
                                                               int x_begin, int h_begin, int h_end, int rows_m,
-                                                              float* __restrict__ out) {
+                                                              RowMap256 m256, float* __restrict__ out) {
     __shared__ float red[4][64];
     const int pc = threadIdx.x & 63, g = threadIdx.x >> 6;
     const int p = blockIdx.x * 64 + pc;
@@ -145,6 +150,17 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __res
         if (p >= h_begin && p < h_end) {
             r0 = rowsE;
             r1 = rowsE + rowsN;
+        } else if (m256.on) {
+            const int branch = p >= x_begin && p < h_begin;
+            const int q = p - (branch ? m256.wx2 : m256.wm2);  // offset inside [W2 | b2]
+            if (q >= 0 && q < m256.D * m256.D + m256.D) {
+                const int row = q < m256.D * m256.D ? q / m256.D : q - m256.D * m256.D;
+                r0 = 148 + (2 * branch + (row >> 7)) * m256.ns;
+                r1 = r0 + m256.ns;
+            } else {
+                r0 = branch ? m256.nM : 0;
+                r1 = branch ? m256.nM + m256.nX : m256.nM;
+            }
         } else if (rows_m > 0) {
             if (p >= x_begin && p < h_begin) r0 = rows_m;
             else r1 = rows_m;
@@ -419,6 +435,7 @@ int egnn_validate_graph(const egnn_graph_t* g, bool need_sender_csr);
 int egnn_tc_bwd_grid(int64_t E);
 int egnn_tc_bwd256_rows(int64_t E);
 int64_t egnn_tc_bwd256_img_bytes(int64_t E);
+void egnn_tc_bwd256_split(int64_t E, int* nM, int* nX, int* ns);
 int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
                              const float* x, const float* gM, const float* gdx, const float* coefS, float* Gr, float* Gs,
                              float* part, uint8_t* img, int precision, cudaStream_t st);
@@ -438,6 +455,16 @@ constexpr int kNumSM = 148;  // B200
 // d = 256 has its own tcgen05 backward (tc_edge256_bwd.cu: two kernels, operand tile images in the workspace)
 static inline bool tc_bwd256_supported(const egnn_net_t& n) { return n.Mh == 256 && tc_fwd_supported(n); }
 
+// FFMA node backward: shared memory of one CTA, and its grid = private partial rows (two CTAs per SM when they fit)
+inline size_t node_bwd_smem(const egnn_net_t& n) {
+    return sizeof(float) * (size_t)TNB * ((round4(n.H + n.Ms) + 4) + 2 * (round4(n.Hh) + 4) + (round4(n.H) + 4));
+}
+inline int node_bwd_rows(const egnn_net_t& n, int64_t N) {
+    const int64_t tilesN = (N + TNB - 1) / TNB;
+    const int cap = 2 * (node_bwd_smem(n) + 1024) <= 227 * 1024 ? 2 * kNumSM : kNumSM;
+    return (int)(tilesN < cap ? tilesN : cap);
+}
+
 struct BwdWs {
     int64_t gdx, coefS, dotp, gM, gh_node, Gr, Gs, ghb, gxb, part, img, total;
     int gridE, gridN, TEB;
@@ -449,12 +476,12 @@ inline int edge_tile_bwd(const egnn_net_t& n) {
 inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     BwdWs w;
     w.TEB = edge_tile_bwd(n);
-    const int64_t tilesE = (E + w.TEB - 1) / w.TEB, tilesN = (N + TNB - 1) / TNB;
+    const int64_t tilesE = (E + w.TEB - 1) / w.TEB;
     w.gridE = (int)(tilesE < kNumSM ? tilesE : kNumSM);
     if (tc_supported(n) && E > 0 && egnn_tc_bwd_grid(E) > w.gridE) w.gridE = egnn_tc_bwd_grid(E);
     if (tc_bwd256_supported(n) && egnn_tc_bwd256_rows(E) > w.gridE) w.gridE = egnn_tc_bwd256_rows(E);
+    w.gridN = node_bwd_rows(n, N);
     if (tc_node_supported(n) && egnn_tc_node_bwd_grid(N) > w.gridN) w.gridN = egnn_tc_node_bwd_grid(N);
-    w.gridN = (int)(tilesN < kNumSM ? tilesN : kNumSM);
     const int64_t W = n.H + 3;
     int64_t p = 0;
     auto take = [&](int64_t cnt) { int64_t o = p; p += round_up64(cnt, 4); return o; };
@@ -529,7 +556,7 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
     const PackOff po = pack_off(*net);
     const int N = g->N, E = g->E, H = net->H;
     const size_t smemE = edge_bwd_smem(*net, bw.TEB);
-    const size_t smemN = sizeof(float) * (size_t)TNB * ((round4(H + net->Ms) + 4) + 2 * (round4(net->Hh) + 4) + (round4(H) + 4));
+    const size_t smemN = node_bwd_smem(*net);
     EGNN_REQUIRE(smemE <= 200 * 1024 && smemN <= 200 * 1024, "network too wide for the shared-memory tiling");
     static bool node_configured = false;
     if (!node_configured) {
@@ -540,7 +567,13 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
     // rows actually used by this call's kernels (the workspace is sized for the larger of the two paths)
     const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : use_tc256 ? egnn_tc_bwd256_rows(E)
                                                             : (int)std::min<int64_t>((E + bw.TEB - 1) / bw.TEB, kNumSM)) : 0;
-    const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : (int)std::min<int64_t>((N + TNB - 1) / TNB, kNumSM);
+    const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : node_bwd_rows(*net, N);
+    RowMap256 m256{};
+    if (use_tc256 && E > 0) {
+        m256.on = 1;
+        egnn_tc_bwd256_split(E, &m256.nM, &m256.nX, &m256.ns);
+        m256.wm2 = lo.wm2, m256.wx2 = lo.wx2, m256.D = net->Mh;
+    }
     EGNN_CUDA(cudaMemsetAsync(ws + bw.dotp + g->G, 0, 4 * sizeof(float), st));  // the ticket of egcl_xupdate_bwd
     int rows_m = 0;
     if (use_tc && E > 0) {
@@ -563,9 +596,12 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
                                                reinterpret_cast<unsigned int*>(ws + bw.dotp + g->G));
         EGNN_CHECK_LAUNCH("egcl_xupdate_bwd");
         // the tensor-core kernels overwrite exactly the entries the reduction reads; the FFMA kernels accumulate
-        if (!use_tc) EGNN_CUDA(cudaMemsetAsync(ws + bw.part, 0, sizeof(float) * (size_t)(rowsE + rowsN) * lo.total, st));
-        else if (!node_tc)
-            EGNN_CUDA(cudaMemsetAsync(ws + bw.part + (size_t)rowsE * lo.total, 0, sizeof(float) * (size_t)rowsN * lo.total, st));
+        // (the FFMA node kernel touches the mlp_h parameters of its rows only: zero just that column range)
+        if (!use_tc && !use_tc256)
+            EGNN_CUDA(cudaMemsetAsync(ws + bw.part, 0, sizeof(float) * (size_t)(rowsE + rowsN) * lo.total, st));
+        else if (!node_tc && rowsN > 0)
+            EGNN_CUDA(cudaMemset2DAsync(ws + bw.part + (size_t)rowsE * lo.total + lo.wh1, sizeof(float) * (size_t)lo.total, 0,
+                                        sizeof(float) * (size_t)(lo.wa - lo.wh1), (size_t)rowsN, st));
         if (node_tc) {
             if (int rc = egnn_tc_node_backward(*net, N, P, Pk, hl, fwd_ws_ptr + fw.msum + (size_t)l * N * net->Ms, gho,
                                                ws + bw.gh_node, ws + bw.gM, ws + bw.part + (size_t)rowsE * lo.total,
@@ -611,7 +647,7 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
             EGNN_CHECK_LAUNCH("egcl_gather_bwd");
         }
         reduce_partials_kernel<<<(lo.total + 63) / 64, 256, 0, st>>>(ws + bw.part, rowsE, rowsN, lo.total, lo.wx1, lo.wh1,
-                                                                      lo.wa, rows_m,
+                                                                      lo.wa, rows_m, m256,
                                                                       grad_params + (size_t)l * lo.total);
         EGNN_CHECK_LAUNCH("reduce_partials_kernel");
     }

@@ -651,9 +651,23 @@ __global__ void __launch_bounds__(128, 1) tc_wgrad256(Wg256Args a) {
 
 }  // namespace
 
-// rows of the partial-gradient buffer the two kernels write: [0, 148) tc_edge_bwd256 (d wa / d wx3 / d ba / d bx3),
-// [148, 296) tc_wgrad256; the caller zero-fills them (every other entry of a row is read as 0 by the reduction)
+// rows of the partial-gradient buffer the two kernels write (reduce_partials_kernel reads exactly these, nothing is
+// zero-filled):  tc_edge_bwd256 CTA b -> row b, [W1 | b1 | row-dot vector and its bias] of its branch: rows [0, nM) the
+// message branch, [nM, nM + nX) the coordinate branch;  tc_wgrad256 CTA id -> row 148 + id, the 128 rows `mh` of
+// [W2 | b2] of its branch: rows 148 + (2 branch + mh) ns + [0, ns)
 int egnn_tc_bwd256_rows(int64_t E) { return E > 0 ? 296 : 0; }
+void egnn_tc_bwd256_split(int64_t E, int* nM, int* nX, int* ns) {
+    static int share = -1;  // CTAs of the message branch (it makes two passes over z2 for the gate)
+    if (share < 0) {
+        const char* env = getenv("EGNN_TC256_BWD_MCTAS");
+        share = env ? atoi(env) : 74;
+        if (share < 16 || share > 132) share = 74;
+    }
+    const int64_t tiles = (E + 127) / 128;
+    *nM = (int)(tiles < share ? tiles : share);
+    *nX = (int)(tiles < 148 - share ? tiles : 148 - share);
+    *ns = (int)(tiles < 37 ? tiles : 37);  // 2 branches x 2 halves x 37 K splits = 148 CTAs
+}
 int64_t egnn_tc_bwd256_img_bytes(int64_t E) { return 2 * ((E + 127) / 128) * (int64_t)IMG_TILE; }
 
 int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
@@ -664,13 +678,8 @@ int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const
     const PackOff po = pack_off(net);
     const uint8_t* blob = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
     const int tiles = (g.E + 127) / 128;
-    static int share = -1;  // CTAs of the message branch (it makes two passes over z2 for the gate)
-    if (share < 0) {
-        const char* env = getenv("EGNN_TC256_BWD_MCTAS");
-        share = env ? atoi(env) : 74;
-        if (share < 16 || share > 132) share = 74;
-    }
-    const int nM = tiles < share ? tiles : share, nX = tiles < 148 - share ? tiles : 148 - share;
+    int nM, nX, ns0;
+    egnn_tc_bwd256_split(g.E, &nM, &nX, &ns0);
     Bwd256Args a{net, g.N, g.E, tiles, g.recv, g.send, g.node_graph, h, x, blob, blob + tc_w2t_offset(net.Mh), gM, gdx, coefS,
                  Gr, Gs, part, img, nM};
     const bool x3 = precision == EGNN_PREC_BF16X3;
@@ -688,7 +697,6 @@ int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const
     else tc_edge_bwd256<1><<<nM + nX, NT, LB::TOTAL, st>>>(a);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("tc_edge_bwd256");
-    const int ns0 = tiles < 37 ? tiles : 37;  // 2 branches x 2 halves x 37 K splits = 148 CTAs
     Wg256Args w{net, tiles, ns0, img, part, 148};
     egnn_prof_begin(EGNN_K_TC_WGRAD, st);
     if (x3) tc_wgrad256<3><<<4 * ns0, 128, WG_SMEM, st>>>(w);
