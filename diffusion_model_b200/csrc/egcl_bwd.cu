@@ -64,7 +64,7 @@ struct NodeBwdArgs {
     float* part;            // [gridDim.x][layer param count] private rows
 };
 
-__global__ void __launch_bounds__(256) egcl_node_bwd(NodeBwdArgs a) {
+__global__ void __launch_bounds__(256, 2) egcl_node_bwd(NodeBwdArgs a) {
     extern __shared__ __align__(16) float smem[];
     const egnn_net_t& net = a.net;
     const int H = net.H, Ms = net.Ms, Hh = net.Hh, K = H + Ms;

@@ -17,6 +17,21 @@ __device__ __forceinline__ void tile_gemm(const float* __restrict__ As, int lda,
     const int r0 = (tid >> 6) * RT;
     const int cg = tid & 63;
     for (int nb = 0; nb < N; nb += 128) {
+        if (nb > 0 && N - nb <= 8) {
+            // a few trailing columns (e.g. N = d + H): a full 128-column pass would run with 3 of 64 lanes active.
+            // 64/RT threads per row, each one whole dot product; the Bt tail is a handful of sectors shared by all warps
+            constexpr int TC = 64 / RT;
+            const int r = tid / TC;
+            const float* arow = As + r * lda;
+            for (int j = tid % TC; j < N - nb; j += TC) {
+                const float* b = Bt + nb + j;
+                float acc = 0.f;
+#pragma unroll 8
+                for (int k = 0; k < K; ++k) acc = fmaf(arow[k], __ldg(b + (size_t)k * ldb), acc);
+                epi(r, nb + j, acc);
+            }
+            break;
+        }
         const int c0 = nb + cg, c1 = c0 + 64;
         const bool v0 = c0 < N, v1 = c1 < N;
         float acc0[RT], acc1[RT];

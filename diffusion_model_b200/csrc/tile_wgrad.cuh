@@ -10,12 +10,51 @@
 __device__ __forceinline__ void tile_wgrad(const float* __restrict__ GZ, int ldg, const float* __restrict__ A, int lda,
                                            int rows, int M, int Kc, float* __restrict__ dst, int ldd) {
     const int lc = threadIdx.x & 15, lm = threadIdx.x >> 4;
+    if (M <= 8) {
+        // a few output rows (mlp_h's second Linear, M = H): one thread per column instead of 16 busy threads
+        for (int c = threadIdx.x; c < Kc; c += 256) {
+            float acc[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+            for (int r = 0; r < rows; ++r) {
+                const float av = A[r * lda + c];
+                const float4 g0 = *reinterpret_cast<const float4*>(GZ + r * ldg);
+                const float4 g1 = *reinterpret_cast<const float4*>(GZ + r * ldg + 4);
+                const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+                for (int i = 0; i < 8; ++i) acc[i] = fmaf(g[i], av, acc[i]);
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (i < M) dst[(size_t)i * ldd + c] += acc[i];
+        }
+        return;
+    }
+    // a few trailing columns (Kc = d + H): one thread per output row m instead of a 128-column block with one lane busy
+    const int Kmain = (Kc > 128 && Kc % 128 != 0 && Kc % 128 <= 8) ? Kc - Kc % 128 : Kc;
+    if (Kmain < Kc) {
+        const int nt = Kc - Kmain;
+        for (int m = threadIdx.x; m < M; m += 256) {
+            float acc[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+            for (int r = 0; r < rows; ++r) {
+                const float gv = GZ[r * ldg + m];
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (j < nt) acc[j] = fmaf(gv, A[r * lda + Kmain + j], acc[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (j < nt) dst[(size_t)m * ldd + Kmain + j] += acc[j];
+        }
+    }
     for (int mb = 0; mb < M; mb += 128) {
         const int m0 = mb + lm * 8;
         if (m0 >= M) continue;
-        for (int cb = 0; cb < Kc; cb += 128) {
+        for (int cb = 0; cb < Kmain; cb += 128) {
             const int c0 = cb + lc * 4, c1 = c0 + 64;
-            const bool v0 = c0 < Kc, v1 = c1 < Kc;
+            const bool v0 = c0 < Kmain, v1 = c1 < Kmain;
             if (!v0) continue;
             float acc[8][8];
 #pragma unroll
@@ -42,7 +81,7 @@ __device__ __forceinline__ void tile_wgrad(const float* __restrict__ GZ, int ldg
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int c = j < 4 ? c0 + j : c1 + j - 4;
-                    if (c < Kc) dst[(size_t)m * ldd + c] += acc[i][j];
+                    if (c < Kmain) dst[(size_t)m * ldd + c] += acc[i][j];
                 }
             }
         }
