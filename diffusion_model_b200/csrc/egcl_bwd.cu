@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(256, 2) egcl_node_bwd(NodeBwdArgs a) {
         zero_pad_cols(GZ, ldz, TNB, Hh);
         __syncthreads();
         const float* b1 = a.P + lo.bh1;
-        tile_gemm<TNB / 4>(A, lda, a.Pk + po.wh1t, Hh, K, Hh, [&](int r, int c, float acc) {
+        tile_gemm<TNB / 4, 4>(A, lda, a.Pk + po.wh1t, Hh, K, Hh, [&](int r, int c, float acc) {
             const float z = acc + __ldg(b1 + c);
             Sz[r * ldz + c] = silu_f(z);
             GZ[r * ldz + c] = dsilu_f(z);
@@ -114,12 +114,13 @@ __global__ void __launch_bounds__(256, 2) egcl_node_bwd(NodeBwdArgs a) {
         }
         __syncthreads();
         // weight gradients of mlp_h (rows beyond `rows` are zero in GH / GZ)
-        tile_wgrad(GH, ldh, Sz, ldz, rows, H, Hh, part + lo.wh2, Hh);
-        tile_colsum(GH, ldh, rows, H, nullptr, part + lo.bh2);
-        tile_wgrad(GZ, ldz, A, lda, rows, Hh, K, part + lo.wh1, K);
-        tile_colsum(GZ, ldz, rows, Hh, nullptr, part + lo.bh1);
+        const bool add = tile != (int)blockIdx.x;  // the first tile stores: the mlp_h entries of the row need no zero-fill
+        tile_wgrad(GH, ldh, Sz, ldz, rows, H, Hh, part + lo.wh2, Hh, add);
+        tile_colsum(GH, ldh, rows, H, nullptr, part + lo.bh2, add);
+        tile_wgrad(GZ, ldz, A, lda, rows, Hh, K, part + lo.wh1, K, add);
+        tile_colsum(GZ, ldz, rows, Hh, nullptr, part + lo.bh1, add);
         // g[h, M] = gz1 . Wh1
-        tile_gemm<TNB / 4>(GZ, ldz, a.P + lo.wh1, K, Hh, K, [&](int r, int c, float acc) {
+        tile_gemm<TNB / 4, 4>(GZ, ldz, a.P + lo.wh1, K, Hh, K, [&](int r, int c, float acc) {
             if (r < rows) {
                 if (c < H) a.gh_node[(size_t)(n0 + r) * H + c] = acc;
                 else a.gM[(size_t)(n0 + r) * Ms + (c - H)] = acc;
@@ -596,12 +597,9 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
                                                reinterpret_cast<unsigned int*>(ws + bw.dotp + g->G));
         EGNN_CHECK_LAUNCH("egcl_xupdate_bwd");
         // the tensor-core kernels overwrite exactly the entries the reduction reads; the FFMA kernels accumulate
-        // (the FFMA node kernel touches the mlp_h parameters of its rows only: zero just that column range)
-        if (!use_tc && !use_tc256)
-            EGNN_CUDA(cudaMemsetAsync(ws + bw.part, 0, sizeof(float) * (size_t)(rowsE + rowsN) * lo.total, st));
-        else if (!node_tc && rowsN > 0)
-            EGNN_CUDA(cudaMemset2DAsync(ws + bw.part + (size_t)rowsE * lo.total + lo.wh1, sizeof(float) * (size_t)lo.total, 0,
-                                        sizeof(float) * (size_t)(lo.wa - lo.wh1), (size_t)rowsN, st));
+        // (the FFMA node kernel stores every mlp_h entry of its row on its first tile: no zero-fill of the node rows)
+        if (!use_tc && !use_tc256 && rowsE > 0)
+            EGNN_CUDA(cudaMemsetAsync(ws + bw.part, 0, sizeof(float) * (size_t)rowsE * lo.total, st));
         if (node_tc) {
             if (int rc = egnn_tc_node_backward(*net, N, P, Pk, hl, fwd_ws_ptr + fw.msum + (size_t)l * N * net->Ms, gho,
                                                ws + bw.gh_node, ws + bw.gM, ws + bw.part + (size_t)rowsE * lo.total,

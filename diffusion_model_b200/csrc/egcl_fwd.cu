@@ -10,6 +10,9 @@
 // No atomics anywhere: reruns are bit-identical.  Within a tile edges are summed in ascending edge id, the order the
 // reference's CPU scatter_add_ uses.
 #include "tile_gemm.cuh"
+#ifndef EGNN_NODE_FWD_KU
+#define EGNN_NODE_FWD_KU 2
+#endif
 
 namespace {
 
@@ -258,18 +261,20 @@ __global__ void __launch_bounds__(256) egcl_node_fwd(NodeFwdArgs a) {
     }
     __syncthreads();
     const float* b1 = a.P + lo.bh1;
-    tile_gemm<TN / 4>(A, lda, a.Pk + po.wh1t, Hh, K, Hh,
+    tile_gemm<TN / 4, EGNN_NODE_FWD_KU>(A, lda, a.Pk + po.wh1t, Hh, K, Hh,
                       [&](int r, int c, float acc) { Z[r * ldz + c] = silu_f(acc + __ldg(b1 + c)); });
     __syncthreads();
     const float* W2 = a.P + lo.wh2;
     const float* b2 = a.P + lo.bh2;
-    for (int idx = tid; idx < TN * H; idx += 256) {
+    // one warp per (node, output) pair, lanes stride over k, fixed shuffle order
+    for (int idx = tid >> 5; idx < TN * H; idx += 8) {
         const int r = idx / H, o = idx - r * H;
         const int i = n0 + r;
         if (i >= a.N) continue;
         float s = 0.f;
-        for (int k = 0; k < Hh; ++k) s = fmaf(__ldg(W2 + o * Hh + k), Z[r * ldz + k], s);
-        a.h_out[(size_t)i * H + o] = s + __ldg(b2 + o);
+        for (int k = tid & 31; k < Hh; k += 32) s = fmaf(__ldg(W2 + o * Hh + k), Z[r * ldz + k], s);
+        s = warp_sum(s);
+        if ((tid & 31) == 0) a.h_out[(size_t)i * H + o] = s + __ldg(b2 + o);
     }
 }
 

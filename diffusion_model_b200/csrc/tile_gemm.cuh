@@ -10,7 +10,7 @@
 #pragma once
 #include "common.cuh"
 
-template <int RT, class Epi>
+template <int RT, int KU = 1, class Epi>
 __device__ __forceinline__ void tile_gemm(const float* __restrict__ As, int lda, const float* __restrict__ Bt, int ldb,
                                           int K, int N, Epi epi) {
     const int tid = threadIdx.x;
@@ -37,25 +37,32 @@ __device__ __forceinline__ void tile_gemm(const float* __restrict__ As, int lda,
         float acc0[RT], acc1[RT];
 #pragma unroll
         for (int r = 0; r < RT; ++r) acc0[r] = acc1[r] = 0.f;
-        for (int k = 0; k < K; k += 4) {
-            float b0[4], b1[4];
+        // KU k-steps of 4 per batch (template argument; 4 in the node backward): all 8 KU loads of Bt (L2 latency) are in flight before the first FMA needs one
+        for (int k = 0; k < K; k += 4 * KU) {
+            float b0[KU][4], b1[KU][4];
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk) {
-                const bool kv = k + kk < K;
-                b0[kk] = (v0 && kv) ? __ldg(Bt + (size_t)(k + kk) * ldb + c0) : 0.f;
-                b1[kk] = (v1 && kv) ? __ldg(Bt + (size_t)(k + kk) * ldb + c1) : 0.f;
-            }
+            for (int u = 0; u < KU; ++u)
 #pragma unroll
-            for (int r = 0; r < RT; ++r) {
-                const float4 a = *reinterpret_cast<const float4*>(As + (r0 + r) * lda + k);
-                acc0[r] = fmaf(a.x, b0[0], acc0[r]);
-                acc0[r] = fmaf(a.y, b0[1], acc0[r]);
-                acc0[r] = fmaf(a.z, b0[2], acc0[r]);
-                acc0[r] = fmaf(a.w, b0[3], acc0[r]);
-                acc1[r] = fmaf(a.x, b1[0], acc1[r]);
-                acc1[r] = fmaf(a.y, b1[1], acc1[r]);
-                acc1[r] = fmaf(a.z, b1[2], acc1[r]);
-                acc1[r] = fmaf(a.w, b1[3], acc1[r]);
+                for (int kk = 0; kk < 4; ++kk) {
+                    const bool kv = k + 4 * u + kk < K;
+                    b0[u][kk] = (v0 && kv) ? __ldg(Bt + (size_t)(k + 4 * u + kk) * ldb + c0) : 0.f;
+                    b1[u][kk] = (v1 && kv) ? __ldg(Bt + (size_t)(k + 4 * u + kk) * ldb + c1) : 0.f;
+                }
+#pragma unroll
+            for (int u = 0; u < KU; ++u) {
+                if (KU > 1 && k + 4 * u >= K) break;  // (the A columns beyond round4(K) are not defined)
+#pragma unroll
+                for (int r = 0; r < RT; ++r) {
+                    const float4 a = *reinterpret_cast<const float4*>(As + (r0 + r) * lda + k + 4 * u);
+                    acc0[r] = fmaf(a.x, b0[u][0], acc0[r]);
+                    acc0[r] = fmaf(a.y, b0[u][1], acc0[r]);
+                    acc0[r] = fmaf(a.z, b0[u][2], acc0[r]);
+                    acc0[r] = fmaf(a.w, b0[u][3], acc0[r]);
+                    acc1[r] = fmaf(a.x, b1[u][0], acc1[r]);
+                    acc1[r] = fmaf(a.y, b1[u][1], acc1[r]);
+                    acc1[r] = fmaf(a.z, b1[u][2], acc1[r]);
+                    acc1[r] = fmaf(a.w, b1[u][3], acc1[r]);
+                }
             }
         }
 #pragma unroll

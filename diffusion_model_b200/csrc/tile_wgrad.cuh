@@ -1,6 +1,6 @@
 // Weight-gradient tile reductions of the fp32 (CUDA-core) backward path.  Every CTA owns a private row of the
 // partial-gradient buffer, walks its tiles in a fixed order and adds into that row; a final kernel sums the rows in
-// CTA order.  No atomics: reruns are bit-identical.
+// CTA order.  No atomics: reruns are bit-identical.  add = false: the CTA's first tile stores (the row needs no zero-fill).
 #pragma once
 #include "common.cuh"
 
@@ -8,7 +8,7 @@
 // 256 threads = 16 (m groups of 8) x 16 (column lanes owning float4 at 4*lc and 64 + 4*lc of a 128-column block).
 // GZ / A are shared-memory tiles whose row strides are >= round4(width) + 4 (over-reads stay inside the row).
 __device__ __forceinline__ void tile_wgrad(const float* __restrict__ GZ, int ldg, const float* __restrict__ A, int lda,
-                                           int rows, int M, int Kc, float* __restrict__ dst, int ldd) {
+                                           int rows, int M, int Kc, float* __restrict__ dst, int ldd, bool add = true) {
     const int lc = threadIdx.x & 15, lm = threadIdx.x >> 4;
     if (M <= 8) {
         // a few output rows (mlp_h's second Linear, M = H): one thread per column instead of 16 busy threads
@@ -26,7 +26,7 @@ __device__ __forceinline__ void tile_wgrad(const float* __restrict__ GZ, int ldg
             }
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-                if (i < M) dst[(size_t)i * ldd + c] += acc[i];
+                if (i < M) dst[(size_t)i * ldd + c] = add ? dst[(size_t)i * ldd + c] + acc[i] : acc[i];
         }
         return;
     }
@@ -46,7 +46,7 @@ __device__ __forceinline__ void tile_wgrad(const float* __restrict__ GZ, int ldg
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-                if (j < nt) dst[(size_t)m * ldd + Kmain + j] += acc[j];
+                if (j < nt) dst[(size_t)m * ldd + Kmain + j] = add ? dst[(size_t)m * ldd + Kmain + j] + acc[j] : acc[j];
         }
     }
     for (int mb = 0; mb < M; mb += 128) {
@@ -81,7 +81,7 @@ __device__ __forceinline__ void tile_wgrad(const float* __restrict__ GZ, int ldg
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int c = j < 4 ? c0 + j : c1 + j - 4;
-                    if (c < Kmain) dst[(size_t)m * ldd + c] += acc[i][j];
+                    if (c < Kmain) dst[(size_t)m * ldd + c] = add ? dst[(size_t)m * ldd + c] + acc[i][j] : acc[i][j];
                 }
             }
         }
@@ -90,10 +90,10 @@ __device__ __forceinline__ void tile_wgrad(const float* __restrict__ GZ, int ldg
 
 // dst[c] += sum_{r<rows} coef[r] * buf[r*ld + c]   (coef == nullptr -> 1)
 __device__ __forceinline__ void tile_colsum(const float* __restrict__ buf, int ld, int rows, int N,
-                                            const float* __restrict__ coef, float* __restrict__ dst) {
+                                            const float* __restrict__ coef, float* __restrict__ dst, bool add = true) {
     for (int c = threadIdx.x; c < N; c += blockDim.x) {
         float s = 0.f;
         for (int r = 0; r < rows; ++r) s = fmaf(coef ? coef[r] : 1.f, buf[r * ld + c], s);
-        dst[c] += s;
+        dst[c] = add ? dst[c] + s : s;
     }
 }
