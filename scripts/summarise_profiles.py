@@ -60,8 +60,9 @@ for cfg in ("cfg2", "cfg4"):
         f.write("kernel,launches,total_us,share,avg_us\n")
         for k, (n, us) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
             f.write(f'"{k}",{n},{us:.1f},{us / tot:.4f},{us / n:.1f}\n')
-    with open(path, "rb") as fi, gzip.open(os.path.join(dst, f"{tag}_launches_{cfg}.csv.gz"), "wb") as fo:
-        shutil.copyfileobj(fi, fo)
+    with open(path, "rb") as fi, open(os.path.join(dst, f"{tag}_launches_{cfg}.csv.gz"), "wb") as raw:
+        with gzip.GzipFile(fileobj=raw, mode="wb", mtime=0) as fo:  # mtime 0: the same input gives the same bytes
+            shutil.copyfileobj(fi, fo)
 
 traffic_path = os.path.join(dst, f"{tag}_traffic.json")
 traffic = json.load(open(traffic_path)) if os.path.exists(traffic_path) else {}
