@@ -21,6 +21,9 @@
 #include <cstdlib>
 
 #include "tc_bulk.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
 #include "tc_tile.cuh"
 
 #ifdef EGNN_DBG_TIMING  // phase time stamps of tile #3 of the first (mlp_m) and last (mlp_x) CTA, scripts/dbg_phases256.py
@@ -657,13 +660,23 @@ __global__ void __launch_bounds__(128, 1) tc_wgrad256(Wg256Args a) {
 // [W2 | b2] of its branch: rows 148 + (2 branch + mh) ns + [0, ns)
 int egnn_tc_bwd256_rows(int64_t E) { return E > 0 ? 296 : 0; }
 void egnn_tc_bwd256_split(int64_t E, int* nM, int* nX, int* ns) {
-    static int share = -1;  // CTAs of the message branch (it makes two passes over z2 for the gate)
-    if (share < 0) {
+    static int fixed = -1;  // CTAs of the message branch (it makes two passes over z2 for the gate); 0 = choose per call
+    if (fixed < 0) {
         const char* env = getenv("EGNN_TC256_BWD_MCTAS");
-        share = env ? atoi(env) : 74;
-        if (share < 16 || share > 132) share = 74;
+        fixed = env ? atoi(env) : 0;
+        if (fixed < 16 || fixed > 132) fixed = 0;
     }
     const int64_t tiles = (E + 127) / 128;
+    int share = fixed;
+    if (!share) {
+        // a message-branch tile costs ~4 % more than a coordinate-branch tile (measured: 74/74 and 76/72 CTAs bracket the
+        // optimum at cfg4); pick the split with the smallest max over branches of (tiles per CTA) x (tile cost)
+        double best = 1e30;
+        for (int m = 60; m <= 88; ++m) {
+            const double c = std::max(1.04 * (double)((tiles + m - 1) / m), (double)((tiles + 147 - m) / (148 - m)));
+            if (c < best - 1e-9 || (c < best + 1e-9 && std::abs(m - 74) < std::abs(share - 74))) best = c, share = m;
+        }
+    }
     *nM = (int)(tiles < share ? tiles : share);
     *nX = (int)(tiles < 148 - share ? tiles : 148 - share);
     *ns = (int)(tiles < 37 ? tiles : 37);  // 2 branches x 2 halves x 37 K splits = 148 CTAs
