@@ -27,6 +27,15 @@ _PARAM_ORDER = ("mlp_m.0.weight", "mlp_m.0.bias", "mlp_m.2.weight", "mlp_m.2.bia
                 "attention.0.weight", "attention.0.bias")
 
 
+_PARAM_EPOCH = [0]
+
+
+def bump_param_epoch():
+    """Tell every kernel-backed module that parameter memory was written outside autograd's version counters (a fused
+    optimizer kernel, an NCCL broadcast, ``p.data`` arithmetic): packed weight images are rebuilt on the next forward."""
+    _PARAM_EPOCH[0] += 1
+
+
 class _FlatParams:
     """Keeps a list of nn.Parameters as views of ONE contiguous fp32 buffer in the C ABI's layout, plus the packed
     (transposed) copy the kernels read.  state_dict / optimizers keep seeing ordinary parameters."""
@@ -78,9 +87,15 @@ class _FlatParams:
         return self.flat
 
     def packed_for(self, net):
+        """The packed copy of the weights (K-major transposes, bf16 hi/lo tcgen05 images), rebuilt when a parameter's
+        autograd version or the global parameter epoch changed -- and ALWAYS for a forward that records a graph for
+        backward: a training step follows an optimizer update, and updates through ``p.data`` (EMA, weight swaps,
+        schedule-free optimizers, foreign kernels) bump no version counter.  The pack is ~1 % of a training step.
+        Inference under no_grad keeps the cache; call ``invalidate_packed()`` after editing ``p.data`` by hand there."""
         flat = self.ensure()
-        key = (flat.data_ptr(), tuple(p._version for p in self.params))
-        if key != self.packed_key:
+        key = (flat.data_ptr(), tuple(p._version for p in self.params), _PARAM_EPOCH[0])
+        training_forward = torch.is_grad_enabled() and any(p.requires_grad for p in self.params)
+        if key != self.packed_key or training_forward:
             n = _lib.load().egnn_packed_count(C.byref(net))
             if self.packed is None or self.packed.numel() != n or self.packed.device != flat.device:
                 self.packed = torch.empty(n, dtype=torch.float32, device=flat.device)
@@ -185,6 +200,11 @@ class _KernelBacked(nn.Module):
         """The contiguous fp32 parameter buffer (C-ABI layout) all parameters are views of."""
         return self._flat.ensure()
 
+    def invalidate_packed(self):
+        """Force a rebuild of the packed weight images on the next forward (needed only after writing parameter memory
+        through ``p.data`` / a foreign kernel while running inference under ``torch.no_grad()``)."""
+        self._flat.packed_key = None
+
     def _run(self, a, b, c, batch=None, node_ptr=None, norm_scope="call", graph=None):
         if torch.is_floating_point(a):  # forward(h, x, edge_index[, edge_attr]) wording of BASELINE.json
             h, x, edge_index = a, b, c
@@ -240,4 +260,4 @@ class EquivariantGNN(_KernelBacked):
         return self._run(edge_index, h, x, **kw)
 
 
-__all__ = ["EGCL", "EquivariantGNN", "GraphIndex"]
+__all__ = ["EGCL", "EquivariantGNN", "GraphIndex", "bump_param_epoch"]

@@ -29,6 +29,10 @@ class EgnnError(RuntimeError):
     pass
 
 
+class UnsortedEdgeIndex(EgnnError):
+    """edge_index[0] is not non-decreasing (found by the deferred validation of a training minibatch; direct calls sort)."""
+
+
 _P, _I32, _I64, _F = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 _NET, _GR = C.POINTER(NetDesc), C.POINTER(GraphDesc)
 
@@ -63,6 +67,8 @@ SIGNATURES = {
                                     _I32, _P, _P, _P]),
     "egnn_counter_add": (C.c_int, [_P, _I32, _P]),
     "egnn_adam_step": (C.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _F, _P]),
+    "egnn_radam_sf_step": (C.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _F, _F, _I32, _F, _P]),
+    "egnn_lerp": (C.c_int, [_P, _P, _I64, _F, _P]),
     "egnn_rdf_local": (C.c_int, [_P, _P, _I32, _P, _P, _P, _I32, C.c_double, C.c_double, _P, _I32, _P, _P, _P, _P]),
     "egnn_cn2_sites": (C.c_int, [_P, _P, _I32, _F, _P, _P, _P, _P, _P]),
     "egnn_kabsch": (C.c_int, [_P, _P, _P, _I32, _P, _P, _P, _P]),

@@ -306,7 +306,7 @@ extern "C" int egnn_rdf_local(const float* pos, const int32_t* node_ptr, int32_t
     EGNN_REQUIRE(S >= 0 && nbins >= 1 && nbins <= 4096 && radius >= 0 && radius <= 4096 && dR > 0 && vol > 0,
                  "egnn_rdf_local: bad sizes (S=%d nbins=%d radius=%d)", S, nbins, radius);
     const size_t smem = (size_t)nbins * 12;
-    EGNN_CUDA(cudaFuncSetAttribute(rdf_local_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 12));
+    EGNN_SMEM_ATTR(rdf_local_kernel, 4096 * 12);
     rdf_local_kernel<<<S, AT, smem, (cudaStream_t)stream>>>(pos, node_ptr, edge_lo, edge_hi, r_sq, nbins, (float)(1.0 / dR),
                                                             4 * 3.141592653589793, vol, dR, weights, radius, counts, rdf,
                                                             dists);

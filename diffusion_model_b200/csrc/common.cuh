@@ -41,6 +41,22 @@ enum { EGNN_K_EDGE_FWD = 0, EGNN_K_NODE_FWD = 1, EGNN_K_XUPDATE = 2, EGNN_K_EDGE
         }                                                                 \
     } while (0)
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE setting: remember it per device ordinal, not per process
+// (a process driving a second GPU would otherwise launch kernels needing > 48 KB of shared memory unconfigured).
+#define EGNN_SMEM_ATTR(kernel, bytes)                                                                          \
+    do {                                                                                                       \
+        static bool done__[64] = {};                                                                           \
+        int dev__ = 0;                                                                                         \
+        EGNN_CUDA(cudaGetDevice(&dev__));                                                                      \
+        if (dev__ < 0 || dev__ >= 64 || !done__[dev__]) {                                                      \
+            EGNN_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            if (dev__ >= 0 && dev__ < 64) done__[dev__] = true;                                                \
+        }                                                                                                      \
+    } while (0)
+// Grids are sized for the 148 SMs of a B200 (one persistent CTA per SM).  This is a tuning constant, not a correctness
+// requirement: no kernel synchronises across CTAs, so a device with another SM count runs the same grids correctly.
+constexpr int kB200SMs = 148;
+
 static inline int64_t round_up64(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 __host__ __device__ static inline int round4(int a) { return (a + 3) & ~3; }
 

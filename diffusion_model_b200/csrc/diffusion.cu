@@ -7,6 +7,7 @@
 //   loss_fwd_bwd                     parts/train_per_iretation.py:161-169 (+ its gradient)
 //   sampler_step                     diffusion_x_h.py:61-90 inside parts/train_per_iretation.py:335-428
 //   adam_step                        torch.optim.Adam as selected by parts/def_for_main.py:133-134
+//   radam_sf_step, lerp              schedulefree.RAdamScheduleFree as selected by parts/def_for_main.py:137-138
 #include "common.cuh"
 
 namespace {
@@ -224,6 +225,35 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
     p[i] = pi - (lr / bc1) * (mi / denom);
 }
 
+// torch.lerp with a scalar weight (ATen's two-sided form, so that weight = 1 returns `end` exactly)
+__device__ __forceinline__ float lerp_f(float a, float b, float w) {
+    const float d = b - a;
+    return w < 0.5f ? fmaf(w, d, a) : b - d * (1.f - w);
+}
+
+// One RAdamScheduleFree update of a flat parameter range (see egnn_radam_sf_step in the header); scalars from the host.
+__global__ void __launch_bounds__(256) radam_sf_kernel(float* __restrict__ y, const float* __restrict__ g, float* __restrict__ z,
+                                                       float* __restrict__ v, long long n, float lr, float b2, float eps,
+                                                       float wd, float ckp1, float y_lr, float bc2, int adam, float gscale) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    float gi = g[i] * gscale;
+    const float vi = fmaf(1.f - b2, gi * gi, b2 * v[i]);
+    v[i] = vi;
+    if (adam) gi = gi / (sqrtf(vi / bc2) + eps);
+    float yi = y[i];
+    if (wd != 0.f) gi = fmaf(wd, yi, gi);  // weight decay evaluated at y
+    const float zi = z[i];
+    yi = lerp_f(yi, zi, ckp1);
+    y[i] = fmaf(y_lr, gi, yi);
+    z[i] = fmaf(-lr, gi, zi);
+}
+
+__global__ void __launch_bounds__(256) lerp_kernel(float* __restrict__ p, const float* __restrict__ end, long long n, float w) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i < n) p[i] = lerp_f(p[i], end[i], w);
+}
+
 }  // namespace
 
 extern "C" int egnn_remove_mean(float* x, int32_t C, const int32_t* node_ptr, int32_t G, void* stream) {
@@ -293,5 +323,25 @@ extern "C" int egnn_adam_step(float* params, const float* grads, float* exp_avg,
                                                                               beta1, beta2, eps, weight_decay, bc1, bc2s,
                                                                               grad_scale);
     EGNN_CHECK_LAUNCH("adam_kernel");
+    return EGNN_OK;
+}
+
+extern "C" int egnn_radam_sf_step(float* y, const float* grads, float* z, float* exp_avg_sq, int64_t n, float lr, float beta2,
+                                  float eps, float weight_decay, float ckp1, float adaptive_y_lr, float bias_correction2,
+                                  int32_t adam_phase, float grad_scale, void* stream) {
+    EGNN_REQUIRE(y && grads && z && exp_avg_sq && n >= 0 && bias_correction2 > 0.f, "egnn_radam_sf_step: bad arguments");
+    if (n == 0) return EGNN_OK;
+    radam_sf_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(y, grads, z, exp_avg_sq, n, lr, beta2, eps,
+                                                                                  weight_decay, ckp1, adaptive_y_lr,
+                                                                                  bias_correction2, adam_phase, grad_scale);
+    EGNN_CHECK_LAUNCH("radam_sf_kernel");
+    return EGNN_OK;
+}
+
+extern "C" int egnn_lerp(float* p, const float* end, int64_t n, float weight, void* stream) {
+    EGNN_REQUIRE(p && end && n >= 0, "egnn_lerp: bad arguments");
+    if (n == 0) return EGNN_OK;
+    lerp_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p, end, n, weight);
+    EGNN_CHECK_LAUNCH("lerp_kernel");
     return EGNN_OK;
 }

@@ -510,11 +510,7 @@ inline size_t edge_bwd_smem(const egnn_net_t& net, int TE) {
 
 template <int RT>
 int launch_edge_bwd(const EdgeBwdArgs& a, int grid, size_t smem, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        EGNN_CUDA(cudaFuncSetAttribute(egcl_edge_bwd<RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = true;
-    }
+    EGNN_SMEM_ATTR(egcl_edge_bwd<RT>, 200 * 1024);
     egnn_prof_begin(EGNN_K_EDGE_BWD, st);
     egcl_edge_bwd<RT><<<grid, 256, smem, st>>>(a);
     egnn_prof_end(st);
@@ -561,7 +557,7 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
     EGNN_REQUIRE(smemE <= 200 * 1024 && smemN <= 200 * 1024, "network too wide for the shared-memory tiling");
     static bool node_configured = false;
     if (!node_configured) {
-        EGNN_CUDA(cudaFuncSetAttribute(egcl_node_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        EGNN_SMEM_ATTR(egcl_node_bwd, 200 * 1024);
         node_configured = true;
     }
     const bool node_tc = use_tc && tc_node_supported(*net);

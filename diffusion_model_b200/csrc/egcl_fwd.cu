@@ -296,11 +296,7 @@ __global__ void __launch_bounds__(256) egcl_xupdate(const float* __restrict__ x,
 
 template <int RT>
 int launch_edge_fwd(const EdgeFwdArgs& a, size_t smem, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        EGNN_CUDA(cudaFuncSetAttribute(egcl_edge_fwd<RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        configured = true;
-    }
+    EGNN_SMEM_ATTR(egcl_edge_fwd<RT>, 200 * 1024);
     const int TE = 4 * RT;
     const int tiles = (a.E + TE - 1) / TE;
     egnn_prof_begin(EGNN_K_EDGE_FWD, st);
@@ -382,11 +378,7 @@ int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const f
                        ws + w.msum + (size_t)l * g.N * net.Ms, ws + w.dxu + (size_t)l * g.N * 3, ws + w.D,
                        tensor ? ws + w.phi : nullptr, g.send, x};
         const size_t smem = sizeof(float) * (size_t)TN * ((round4(net.H + net.Ms) + 4) + (round4(net.Hh) + 4));
-        static bool configured = false;
-        if (!configured) {
-            EGNN_CUDA(cudaFuncSetAttribute(egcl_node_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            configured = true;
-        }
+        EGNN_SMEM_ATTR(egcl_node_fwd, 200 * 1024);
         egnn_prof_begin(EGNN_K_NODE_FWD, st);
         egcl_node_fwd<<<(g.N + TN - 1) / TN, 256, smem, st>>>(na);
         egnn_prof_end(st);

@@ -101,7 +101,7 @@ extern "C" int egnn_tc_selftest(const float* A, const float* B, float* D, int32_
     EGNN_REQUIRE(K >= 16 && K % 16 == 0 && K <= 128 && N >= 16 && N % 16 == 0 && N <= 256 && (npass == 1 || npass == 3),
                  "egnn_tc_selftest: unsupported shape K=%d N=%d npass=%d", K, N, npass);
     const size_t smem = 200 * 1024;  // fixed and ample: the swapped-descriptor probe must stay inside the allocation
-    EGNN_CUDA(cudaFuncSetAttribute(tc_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    EGNN_SMEM_ATTR(tc_selftest_kernel, 200 * 1024);
     tc_selftest_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, D, K, N, npass, flags, status_dev);
     EGNN_CHECK_LAUNCH("tc_selftest_kernel");
     return EGNN_OK;
@@ -494,11 +494,7 @@ int egnn_tc_pack(const egnn_net_t& net, const float* params, float* packed, cuda
 
 template <int D, int NPASS>
 static int launch_tc_fwd(const TcFwdArgs& a, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        EGNN_CUDA(cudaFuncSetAttribute(tc_edge_fwd<D, NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcLayout<D>::TOTAL));
-        configured = true;
-    }
+    EGNN_SMEM_ATTR((tc_edge_fwd<D, NPASS>), TcLayout<D>::TOTAL);
     const int grid = a.tiles < 148 ? a.tiles : 148;
     egnn_prof_begin(EGNN_K_TC_EDGE_FWD, st);
     tc_edge_fwd<D, NPASS><<<grid, 4 * D, TcLayout<D>::TOTAL, st>>>(a);
@@ -966,11 +962,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
 template <int D, int NPASS>
 int launch_tc_bwd(const TcBwdArgs& a, int grid, cudaStream_t st) {
     constexpr int SMEM = TcBwdLayout<D>::TOTAL;
-    static bool configured = false;
-    if (!configured) {
-        EGNN_CUDA(cudaFuncSetAttribute(tc_edge_bwd<D, NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-        configured = true;
-    }
+    EGNN_SMEM_ATTR((tc_edge_bwd<D, NPASS>), SMEM);
     egnn_prof_begin(EGNN_K_TC_EDGE_BWD, st);
     tc_edge_bwd<D, NPASS><<<grid, 4 * D, SMEM, st>>>(a);
     egnn_prof_end(st);
@@ -992,8 +984,12 @@ void egnn_tc_bwd_split(int64_t E, int* nM, int* nX) {
     }
     static int share = -1;
     if (share < 0) {
+#ifdef EGNN_DBG  // tuning knob of debug builds only: a stray environment variable must not change a release library
         const char* env = getenv("EGNN_TC_BWD_MSHARE");
         share = env ? atoi(env) : 50;
+#else
+        share = 50;
+#endif
         if (share < 10 || share > 90) share = 50;
     }
     *nM = (148 * share + 50) / 100;
@@ -1017,8 +1013,12 @@ int egnn_tc_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const fl
     {
         static int glo = -1;
         if (glo < 0) {
+#ifdef EGNN_DBG  // accuracy knob (which lo-split products the backward issues): debug builds only
             const char* env = getenv("EGNN_TC_BWD_GLO");
             glo = env ? atoi(env) & 3 : 3;
+#else
+            glo = 3;
+#endif
         }
         a.g_lo = glo;
     }

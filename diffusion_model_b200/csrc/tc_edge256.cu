@@ -353,11 +353,7 @@ __global__ void __launch_bounds__(NT, 1) tc_edge_fwd256(Tc256Args a) {
 
 template <int NPASS>
 int launch256(const Tc256Args& a, int grid, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        EGNN_CUDA(cudaFuncSetAttribute(tc_edge_fwd256<NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, L256::TOTAL));
-        configured = true;
-    }
+    EGNN_SMEM_ATTR(tc_edge_fwd256<NPASS>, L256::TOTAL);
     egnn_prof_begin(EGNN_K_TC_EDGE_FWD, st);
     tc_edge_fwd256<NPASS><<<grid, NT, L256::TOTAL, st>>>(a);
     egnn_prof_end(st);
@@ -376,8 +372,12 @@ int egnn_tc_edge_forward256(const egnn_net_t& net, const egnn_graph_t& g, const 
     // the coordinate branch, scripts/dbg_phases256.py), so it gets the larger share of the CTAs
     static int share = -1;
     if (share < 0) {
+#ifdef EGNN_DBG  // tuning knob of debug builds only
         const char* env = getenv("EGNN_TC256_FWD_MCTAS");
         share = env ? atoi(env) : 86;
+#else
+        share = 86;
+#endif
         if (share < 16 || share > 132) share = 86;
     }
     int nM = share, nX = 148 - share;

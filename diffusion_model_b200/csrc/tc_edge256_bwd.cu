@@ -662,8 +662,12 @@ int egnn_tc_bwd256_rows(int64_t E) { return E > 0 ? 296 : 0; }
 void egnn_tc_bwd256_split(int64_t E, int* nM, int* nX, int* ns) {
     static int fixed = -1;  // CTAs of the message branch (it makes two passes over z2 for the gate); 0 = choose per call
     if (fixed < 0) {
+#ifdef EGNN_DBG  // tuning knob of debug builds only
         const char* env = getenv("EGNN_TC256_BWD_MCTAS");
         fixed = env ? atoi(env) : 0;
+#else
+        fixed = 0;
+#endif
         if (fixed < 16 || fixed > 132) fixed = 0;
     }
     const int64_t tiles = (E + 127) / 128;
@@ -696,15 +700,11 @@ int egnn_tc_edge_backward256(const egnn_net_t& net, const egnn_graph_t& g, const
     Bwd256Args a{net, g.N, g.E, tiles, g.recv, g.send, g.node_graph, h, x, blob, blob + tc_w2t_offset(net.Mh), gM, gdx, coefS,
                  Gr, Gs, part, img, nM};
     const bool x3 = precision == EGNN_PREC_BF16X3;
-    static bool configured = false;
     constexpr int WG_SMEM = WgSmem::TOTAL;
-    if (!configured) {
-        EGNN_CUDA(cudaFuncSetAttribute(tc_edge_bwd256<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, LB::TOTAL));
-        EGNN_CUDA(cudaFuncSetAttribute(tc_edge_bwd256<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, LB::TOTAL));
-        EGNN_CUDA(cudaFuncSetAttribute(tc_wgrad256<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
-        EGNN_CUDA(cudaFuncSetAttribute(tc_wgrad256<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
-        configured = true;
-    }
+    EGNN_SMEM_ATTR(tc_edge_bwd256<3>, LB::TOTAL);
+    EGNN_SMEM_ATTR(tc_edge_bwd256<1>, LB::TOTAL);
+    EGNN_SMEM_ATTR(tc_wgrad256<3>, WG_SMEM);
+    EGNN_SMEM_ATTR(tc_wgrad256<1>, WG_SMEM);
     egnn_prof_begin(EGNN_K_TC_EDGE_BWD, st);
     if (x3) tc_edge_bwd256<3><<<nM + nX, NT, LB::TOTAL, st>>>(a);
     else tc_edge_bwd256<1><<<nM + nX, NT, LB::TOTAL, st>>>(a);

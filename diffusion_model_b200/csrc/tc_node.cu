@@ -483,11 +483,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_fwd(TcNodeFwdArgs a) {
 template <int D, int NPASS>
 int launch_tc_node_fwd(const TcNodeFwdArgs& a, int grid, cudaStream_t st) {
     constexpr int SMEM = TcNodeLayout<D>::TOTAL;
-    static bool configured = false;
-    if (!configured) {
-        EGNN_CUDA(cudaFuncSetAttribute(tc_node_fwd<D, NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-        configured = true;
-    }
+    EGNN_SMEM_ATTR((tc_node_fwd<D, NPASS>), SMEM);
     egnn_prof_begin(EGNN_K_NODE_FWD, st);
     tc_node_fwd<D, NPASS><<<grid, 4 * D, SMEM, st>>>(a);
     egnn_prof_end(st);
@@ -498,11 +494,7 @@ int launch_tc_node_fwd(const TcNodeFwdArgs& a, int grid, cudaStream_t st) {
 template <int D, int NPASS>
 int launch_tc_node_bwd(const TcNodeBwdArgs& a, int grid, cudaStream_t st) {
     constexpr int SMEM = TcNodeLayout<D>::TOTAL;
-    static bool configured = false;
-    if (!configured) {
-        EGNN_CUDA(cudaFuncSetAttribute(tc_node_bwd<D, NPASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-        configured = true;
-    }
+    EGNN_SMEM_ATTR((tc_node_bwd<D, NPASS>), SMEM);
     egnn_prof_begin(EGNN_K_NODE_BWD, st);
     tc_node_bwd<D, NPASS><<<grid, 4 * D, SMEM, st>>>(a);
     egnn_prof_end(st);

@@ -18,10 +18,17 @@ I32 = torch.int32
 
 
 def _node_ptr_of(batch_index):
-    """int32 [G+1] boundaries of a non-decreasing PyG ``batch`` vector (one host sync for G, as the reference :9)."""
+    """int32 [G+1] boundaries of a non-decreasing PyG ``batch`` vector (one host sync for G, as the reference :9).
+    The reference's masked loop (:10-13) accepts any node order; the kernels need graphs to be contiguous node ranges,
+    which every PyG / data.Batch collate produces -- anything else raises instead of giving wrong graph boundaries."""
     N = batch_index.numel()
-    G = int(batch_index.max().item()) + 1
     b = batch_index.to(torch.int64).contiguous()
+    if N == 0:
+        raise _lib.EgnnError("empty batch vector")
+    gmax, unsorted = torch.stack([b.max(), (b[1:] < b[:-1]).any().to(torch.int64)]).tolist()  # ONE host sync
+    if unsorted:
+        raise _lib.EgnnError("the batch vector must be non-decreasing (nodes of one graph contiguous), as PyG collates it")
+    G = int(gmax) + 1
     node_ptr = torch.empty(G + 1, dtype=I32, device=b.device)
     node_graph = torch.empty(N, dtype=I32, device=b.device)
     call("egnn_node_ptr_from_batch", ptr(b), N, G, ptr(node_ptr), ptr(node_graph), stream_ptr(b.device))

@@ -86,7 +86,8 @@ def broadcast_parameters(module, src=0, group=None):
     """Make every rank start from rank `src`'s weights (one broadcast of the flat parameter buffer)."""
     if dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.broadcast(module.flat_parameters(), src=src, group=group)
-        module._flat.packed_key = None
+        from .EquivariantGraphNeuralNetwork import bump_param_epoch
+        bump_param_epoch()
 
 
 def sample_sharded(egnn, dp, num_atoms, num_structures, seed=2024, gather=True, **kw):

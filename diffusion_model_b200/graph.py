@@ -95,7 +95,12 @@ class GraphIndex:
                                                  torch.arange(N, device=dev, dtype=I32), right=True).to(I32).contiguous()
         elif batch is not None:
             batch = batch.to(device=dev, dtype=torch.int64).contiguous()
-            self.G = int(batch[-1].item()) + 1 if N > 0 else 1
+            self.G = 1
+            if N > 0:  # G from batch.max() like the reference (diffusion_x_h.py:9); unsorted batch vectors raise
+                gmax, unsorted = torch.stack([batch.max(), (batch[1:] < batch[:-1]).any().to(torch.int64)]).tolist()
+                if unsorted:
+                    raise _lib.EgnnError("the batch vector must be non-decreasing (nodes of one graph contiguous)")
+                self.G = int(gmax) + 1
             self.node_ptr = torch.empty(self.G + 1, dtype=I32, device=dev)
             self.node_graph = torch.empty(N, dtype=I32, device=dev)
             call("egnn_node_ptr_from_batch", ptr(batch), N, self.G, ptr(self.node_ptr), ptr(self.node_graph), st)
@@ -110,8 +115,12 @@ class GraphIndex:
         self.col_edge = torch.empty(max(E, 1), dtype=I32, device=dev)
         scratch = torch.empty(N + 1 + E, dtype=I32, device=dev)
         flags = torch.empty(2, dtype=I32, device=dev)
-        call("egnn_graph_prepare", ptr(edge_index), N, E, ptr(self.recv), ptr(self.send), ptr(self.row_ptr),
-             ptr(self.col_ptr), ptr(self.col_edge), ptr(scratch), ptr(flags), st)
+        self.perm = None  # set when the edge list had to be receiver-sorted: kernel edge e == input edge perm[e]
+
+        def prepare(ei):
+            call("egnn_graph_prepare", ptr(ei), N, E, ptr(self.recv), ptr(self.send), ptr(self.row_ptr),
+                 ptr(self.col_ptr), ptr(self.col_edge), ptr(scratch), ptr(flags), st)
+        prepare(edge_index)
         # validation flags: read now (validate=True, one host sync) or copied to pinned memory and checked at the next
         # natural sync point (validate="deferred": training loops, where a host sync per minibatch stalls the pipeline;
         # the kernels clamp bad ids, so a malformed list gives wrong numbers but no wild access until it is reported)
@@ -124,7 +133,15 @@ class GraphIndex:
             self._pending = (host, ev)
             _PENDING.append(self)
         elif validate:
-            self._raise_on(flags.tolist())
+            f = flags.tolist()
+            if f[0] and not f[1]:
+                # PyG's propagate / scatter accept any edge order (EquivariantGraphNeuralNetwork.py:68,70); the kernels
+                # want receiver-contiguous edges.  A stable sort keeps every receiver's senders in their input order, so
+                # the result is the reference's sum up to fp32 summation order; outputs are per node, nothing to un-permute.
+                self.perm = torch.sort(edge_index[0], stable=True).indices
+                prepare(edge_index[:, self.perm].contiguous())
+                f = flags.tolist()
+            self._raise_on(f)
         self.desc = GraphDesc(N, E, self.G, self.recv.data_ptr(), self.send.data_ptr(), self.row_ptr.data_ptr(),
                               self.col_ptr.data_ptr(), self.col_edge.data_ptr(), self.node_ptr.data_ptr(),
                               self.node_graph.data_ptr())
@@ -134,20 +151,27 @@ class GraphIndex:
         if f[1]:
             raise _lib.EgnnError("edge_index holds a node id outside [0, num_nodes)")
         if f[0]:
-            raise _lib.EgnnError(
-                "edge_index[0] must be non-decreasing (receiver-sorted), as every edge builder of the reference "
-                "produces; sort the columns by edge_index[0] first")
+            raise _lib.UnsortedEdgeIndex(
+                "edge_index[0] is not non-decreasing (receiver-sorted).  Direct EquivariantGNN calls sort such lists; the "
+                "deferred validation of a training minibatch cannot (the kernels have already run on it): "
+                "train_epoch re-runs the minibatch with the sorted list before optimizer.step()")
 
     def check(self, wait=True):
         """Raise if the deferred validation of this edge list failed (no-op once checked)."""
         if self._pending is None:
+            if getattr(self, "_bad", None) is not None:
+                raise self._bad  # a malformed list stays malformed (the object may still sit in the cache)
             return True
         host, ev = self._pending
         if not wait and not ev.query():
             return False
         ev.synchronize()
         self._pending = None
-        self._raise_on(host.tolist())
+        try:
+            self._raise_on(host.tolist())
+        except _lib.EgnnError as e:
+            self._bad = e
+            raise
         return True
 
     def ref(self):

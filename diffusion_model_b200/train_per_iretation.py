@@ -153,7 +153,7 @@ def batch_loss(egnn, batch_data, diffusion_process, params, t=None, noise_pos=No
                 norm_scope=params.get("norm_scope", "call"), graph=gi)
     A = params.get("atom_type_size", d["A"])
     loss = _EpsLoss.apply(x, h, d["z_x"], d["eps_x"], d["eps_h"], node_ptr, G, A)
-    return loss, G, dict(d, h_out=h, x_out=x)
+    return loss, G, dict(d, h_out=h, x_out=x, graph=gi)
 
 
 def _run_epoch(nn_dict, loader, params, diffusion_process, optimizer, train):
@@ -171,12 +171,28 @@ def _run_epoch(nn_dict, loader, params, diffusion_process, optimizer, train):
         cond = _conditioning(data, params, nn_dict)
         if train:
             optimizer.zero_grad()
-            loss, G, _ = batch_loss(egnn, data, diffusion_process, params, cond=cond)
+            loss, G, aux = batch_loss(egnn, data, diffusion_process, params, cond=cond)
             loss.backward()
+            # the minibatch's edge-list validation has landed long before the host gets here (it was enqueued ahead of
+            # the forward); reading it BEFORE the update keeps a malformed list from ever reaching optimizer.step()
+            try:
+                aux["graph"].check(wait=True)
+            except _lib.UnsortedEdgeIndex:
+                # any edge order is legal for the reference's scatter-add: sort by receiver (stable) and redo the batch
+                data.edge_index = data.edge_index[:, torch.sort(data.edge_index[0], stable=True).indices].contiguous()
+                optimizer.zero_grad()
+                loss, G, aux = batch_loss(egnn, data, diffusion_process, params, cond=cond)
+                loss.backward()
+                aux["graph"].check(wait=True)
             optimizer.step()
         else:
             with torch.no_grad():
-                loss, G, _ = batch_loss(egnn, data, diffusion_process, params, cond=cond)
+                loss, G, aux = batch_loss(egnn, data, diffusion_process, params, cond=cond)
+                try:
+                    aux["graph"].check(wait=True)
+                except _lib.UnsortedEdgeIndex:
+                    data.edge_index = data.edge_index[:, torch.sort(data.edge_index[0], stable=True).indices].contiguous()
+                    loss, G, aux = batch_loss(egnn, data, diffusion_process, params, cond=cond)
         epoch_loss += loss.detach() * G  # (:178) summed squared error of the batch
     out = epoch_loss.item() / max(total_nodes, 1)  # per-node average (:181); the only host sync of the epoch
     check_pending()

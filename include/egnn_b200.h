@@ -182,6 +182,19 @@ int egnn_adam_step(float* params, const float* grads, float* exp_avg, float* exp
                    float beta1, float beta2, float eps, float weight_decay, int32_t step, float grad_scale,
                    void* stream);
 
+/* schedulefree.RAdamScheduleFree (parts/def_for_main.py:137-138; `optimizer: RAdamScheduleFree` in parameters.yaml) on flat
+ * buffers.  The package is not part of the reference checkout (un-vendored, unpinned dependency): the update is restated
+ * from its published algorithm (facebookresearch/schedule_free, radam_schedulefree.py); oracle/radam_sf_ref.py is the CPU
+ * restatement the tests compare against.  One launch does, per element and with host-computed scalars of step t,
+ *   v <- beta2 v + (1-beta2) g^2;   g^ = adam_phase ? g / (sqrt(v / bias_correction2) + eps) : g;   g^ += weight_decay y
+ *   y <- lerp(y, z, ckp1) + adaptive_y_lr g^;      z <- z - lr g^
+ * (y: the parameters in train mode, z: the base sequence, lr: the rectified learning rate of the step). */
+int egnn_radam_sf_step(float* y, const float* grads, float* z, float* exp_avg_sq, int64_t n, float lr, float beta2,
+                       float eps, float weight_decay, float ckp1, float adaptive_y_lr, float bias_correction2,
+                       int32_t adam_phase, float grad_scale, void* stream);
+/* p <- lerp(p, end, weight) (torch.lerp): the train() / eval() switch of the schedule-free optimizer (y <-> x) */
+int egnn_lerp(float* p, const float* end, int64_t n, float weight, void* stream);
+
 /* ---- structure analysis ("sample -> evaluate"): one CTA per structure; structures are the node
  *      ranges node_ptr[s] .. node_ptr[s+1] of pos [N,3]; atom 0 of a structure is its first node ------------------- */
 /* Local RDF around atom 0 (replaces evaluate_RDF.py:39-60, RDF + length_from_exO).

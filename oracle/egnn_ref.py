@@ -81,8 +81,11 @@ def egcl_forward(p, edge_index, h, x, norm_scope="call", edge_graph=None, num_gr
     return h_new, x_new
 
 
-def egnn_forward(state_dict, L, edge_index, h, x, norm_scope="call", batch=None, return_layers=False):
-    """EquivariantGNN.forward(edge_index, h, x) -> (h, x)  (EquivariantGraphNeuralNetwork.py:85-88)."""
+def egnn_forward(state_dict, L, edge_index, h, x, norm_scope="call", batch=None, return_layers=False, checkpoint=False):
+    """EquivariantGNN.forward(edge_index, h, x) -> (h, x)  (EquivariantGraphNeuralNetwork.py:85-88).
+
+    checkpoint=True recomputes each layer in backward (same arithmetic, ~L times less autograd memory: the full-size
+    parity tests run E = 4e5 edges through 6-9 layers on the host)."""
     edge_graph = num_graphs = None
     if norm_scope == "graph":
         if batch is None:
@@ -91,7 +94,14 @@ def egnn_forward(state_dict, L, edge_index, h, x, norm_scope="call", batch=None,
         num_graphs = int(batch.max()) + 1
     layers = []
     for l in range(L):
-        h, x = egcl_forward(layer_params(state_dict, l), edge_index, h, x, norm_scope, edge_graph, num_graphs)
+        if checkpoint:
+            from torch.utils.checkpoint import checkpoint as _ckpt
+            p = layer_params(state_dict, l)
+            keys = list(p)
+            h, x = _ckpt(lambda hh, xx, *w: egcl_forward(dict(zip(keys, w)), edge_index, hh, xx, norm_scope, edge_graph,
+                                                         num_graphs), h, x, *[p[k] for k in keys], use_reentrant=False)
+        else:
+            h, x = egcl_forward(layer_params(state_dict, l), edge_index, h, x, norm_scope, edge_graph, num_graphs)
         if return_layers:
             layers.append((h, x))
     return (h, x, layers) if return_layers else (h, x)

@@ -171,3 +171,34 @@ def test_batched_oracle_sampler_equals_per_structure_loop():
             assert bool(fin[k]) == f1
             assert float((pos[k] - p1).abs().max()) <= 1e-4 * float(p1.abs().max())
             assert float((hf[k] - h1).abs().max()) <= 1e-4 * max(1.0, float(h1.abs().max()))
+
+
+def test_radam_schedulefree_restatement_invariants():
+    """oracle/radam_sf_ref.py (parity unpinned: the schedulefree package is absent): invariants of the published algorithm --
+    the first steps (rho_t <= 4) are silent, x_t is the c_t-weighted running average of the z sequence with
+    y_t = beta1 x_t + (1 - beta1) z_t, eval()/train() are inverse maps, and it minimises a quadratic."""
+    from oracle.radam_sf_ref import RAdamScheduleFreeRef
+    torch.manual_seed(0)
+    target = torch.randn(32)
+    p = torch.zeros(32)
+    opt = RAdamScheduleFreeRef([p], lr=0.05)
+    opt.train()
+    x_avg = None
+    for it in range(400):
+        p.grad = p - target
+        z_before = None if p not in opt.state else opt.state[p]["z"].clone()
+        ws_before = opt.g["weight_sum"]
+        opt.step()
+        if it < 4:
+            assert torch.equal(p, torch.zeros(32)) and opt.g["scheduled_lr"] == 0.0
+        z = opt.state[p]["z"]
+        w = opt.g["weight_sum"] - ws_before
+        c = w / opt.g["weight_sum"] if opt.g["weight_sum"] > 0 else 0.0
+        x_avg = z.clone() if x_avg is None else (1 - c) * x_avg + c * z
+        if opt.g["weight_sum"] > 0:
+            assert torch.allclose(p, 0.9 * x_avg + 0.1 * z, atol=1e-5), it
+    opt.eval()
+    assert torch.allclose(p, x_avg, atol=1e-5)
+    assert float((p - target).abs().max()) < 0.15 < float(target.abs().max())  # from 2.1 down, 400 Adam-sized steps
+    opt.train(); opt.eval()
+    assert torch.allclose(p, x_avg, atol=1e-5)
