@@ -11,8 +11,11 @@ preparation, D2H of the loss every step, read by the host one step later).  N > 
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
---impl reference times the CPU restatement of the reference path (oracle/, torch CPU with all host threads) on a
-bounded sample of the same workload; the unmodified reference cannot run here (needs torch_geometric, absent).
+After the training measurement the same line gets a `sampling` object: BASELINE.json configs[2], 512 fully connected
+192-atom structures per GPU, T = 1000, through the public batched sampler (structures/s, fraction of the FLOP bound).
+
+--impl reference times the CPU restatement of the reference path (oracle/, torch CPU with all host threads) on the whole
+64-graph batch of the same workload; the unmodified reference cannot run here (needs torch_geometric, absent).
 """
 from __future__ import annotations
 
@@ -39,6 +42,9 @@ CFG = dict(L=6, d=128, H=3, A=2, graphs=64, atoms=192, r_c=5.0, T=1000, s=1e-5, 
 # Hidden 256 runs the streamed-W2 tcgen05 kernels (tc_edge256.cu, tc_edge256_bwd.cu); --precision fp32 selects the FFMA kernels.
 CFG4 = dict(L=9, d=256, graphs=8, atoms=1536, name="cfg4", cpu_graphs=1)
 DENSITY = 0.0662  # atoms / A^3, a-SiO2
+TRAFFIC_FILE = "r2_traffic.json"  # dram bytes per launch of the top kernels from one `ncu --set full` capture (scripts/profile_round.sh)
+# second half of BASELINE.json's metric (configs[2]): x+h ancestral sampling, fully connected 192-atom structures, T = 1000
+SAMPLING = dict(structures=512, atoms=192, T=1000, L=6, d=128, H=3, s=0.05, power=2.0)
 
 
 def synth_batch(num_graphs, n_atoms, seed):
@@ -199,40 +205,171 @@ def cpu_sample(pos, onehot, edge_index, node_ptr, graphs):
 def run_reference(args, rank):
     if rank != 0:
         return
-    threads = os.cpu_count() or 1
     pos, onehot, box = synth_batch(CFG["graphs"], CFG["atoms"], CFG["seed"] + 1)
     node_ptr = torch.arange(CFG["graphs"] + 1) * CFG["atoms"]
     from oracle import egnn_ref, graphs_ref as G
     torch.manual_seed(CFG["seed"])
     sd = egnn_ref.init_state_dict(**net_sizes(CFG["L"], CFG["d"], CFG["H"]))
-    graphs = CFG["cpu_graphs"]
-    ei = torch.from_numpy(G.cutoff_edges_batch(pos[: graphs * CFG["atoms"]].numpy(), node_ptr[: graphs + 1].numpy(),
-                                               CFG["r_c"], box[:graphs].numpy()))
-    p, o, e, b = cpu_sample(pos, onehot, ei, node_ptr, graphs)
-    probe = cpu_train_steps(p, o, e, b, sd, 1, 1, threads)[0]
-    while graphs > 1 and probe * (args.steps + args.warmup) > 240.0:
-        graphs //= 2
-        probe /= 2
-    p, o, e, b = cpu_sample(pos, onehot, ei, node_ptr, graphs)
-    times = cpu_train_steps(p, o, e, b, sd, args.steps, args.warmup, threads)
-    total = sum(times)
-    value = graphs * len(times) / total
-    sample = f"{graphs} of the {CFG['graphs']} graphs of the batch per step ({p.shape[0]} atoms, {e.shape[1]} edges), fp32, torch CPU"
+    ei = torch.from_numpy(G.cutoff_edges_batch(pos.numpy(), node_ptr.numpy(), CFG["r_c"], box.numpy()))
+    cb, total, nsteps = cpu_baseline_block(pos, onehot, ei, node_ptr, sd, args.steps, args.warmup)
+    value = cb["value"]
     line = dict(impl="reference", metric="denoiser graph-steps/s (training fwd+bwd+optimizer)", value=value,
                 unit="graph-steps/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
-                ms_per_step=1e3 * total / len(times), higher_is_better=True, scaling="weak", vs_baseline=None,
-                dtype="fp32", data="synthetic", config=workload_config("fp32"),
-                cpu_baseline=dict(value=value, unit="graph-steps/s", cores=threads, kind="port", sample=sample),
+                ms_per_step=1e3 * total / nsteps, higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="fp32", data="synthetic", config=workload_config(pos.shape[0], ei.shape[1]),
+                cpu_baseline=cb,
                 e2e=dict(value=value, unit="graph-steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 note="CPU restatement of the reference path (oracle/); the unmodified reference needs torch_geometric")
     print(json.dumps(line), flush=True)
 
 
-def workload_config(precision):
+def workload_config(N, E):
+    """The SAME dict in both arms (the driver compares them); arithmetic type is the top-level `dtype`."""
     return dict(workload=f"{CFG['name']}: eps-pred training step, {CFG['graphs']} x {CFG['atoms']}-atom periodic cutoff graphs (r_c=5A) "
                          f"per GPU, EGNN L={CFG['L']} d={CFG['d']} H=3, T=1000, Adam lr=1e-5", graphs_per_gpu=CFG["graphs"], atoms=CFG["atoms"], r_c=CFG["r_c"], L=CFG["L"],
-                hidden=CFG["d"], precision=precision, parallelism="data-parallel, one NCCL all-reduce of the flat gradient per step",
-                l2="256 MB buffer written between timed steps (L2 flush, inside the timed region)")
+                hidden=CFG["d"], parallelism="data-parallel, one NCCL all-reduce of the flat gradient per step",
+                l2="256 MB buffer written between timed steps (L2 flush, inside the timed region)", nodes_per_gpu=int(N),
+                edges_per_gpu=int(E))
+
+
+def host_info():
+    """Host CPU of the box the CPU arm runs on: model name, logical and physical core counts."""
+    model = None
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.lower().startswith("model name"):
+                    model = line.split(":", 1)[1].strip()
+                    break
+    except OSError:
+        pass
+    phys = None
+    try:
+        import psutil
+        phys = psutil.cpu_count(logical=False)
+    except Exception:
+        pass
+    return dict(cpu_model=model, logical_cpus=os.cpu_count() or 1, physical_cores=phys or os.cpu_count() or 1)
+
+
+def cpu_baseline_block(pos, onehot, ei, node_ptr, sd, steps, warmup, budget_s=240.0):
+    """The CPU restatement of the reference path (oracle/) timed on the host cores: the WHOLE batch per step with every
+    host thread (halved only if one step would blow the time budget), plus a 1-thread and a physical-core figure on an
+    8-graph sample.  Returns (cpu_baseline dict, total seconds, timed steps)."""
+    info = host_info()
+    threads = info["logical_cpus"]
+    graphs = CFG["graphs"]
+    small = min(CFG["cpu_graphs"], graphs)
+    p, o, e, b = cpu_sample(pos, onehot, ei, node_ptr, small)
+    probe = cpu_train_steps(p, o, e, b, sd, 1, 1, threads)[0] * graphs / small
+    while graphs > 1 and probe * (steps + warmup) > budget_s:
+        graphs //= 2
+        probe /= 2
+    p, o, e, b = cpu_sample(pos, onehot, ei, node_ptr, graphs)
+    times = cpu_train_steps(p, o, e, b, sd, steps, warmup, threads)
+    value = graphs * len(times) / sum(times)
+    ps, os_, es, bs = cpu_sample(pos, onehot, ei, node_ptr, small)
+    t1 = cpu_train_steps(ps, os_, es, bs, sd, 1, 0, 1)
+    tp = cpu_train_steps(ps, os_, es, bs, sd, 2, 1, info["physical_cores"])
+    torch.set_num_threads(threads)
+    whole = "all" if graphs == CFG["graphs"] else f"{graphs} of the"
+    cb = dict(value=value, unit="graph-steps/s", cores=threads, kind="port",
+              sample=f"{whole} {CFG['graphs']} graphs of the batch per step ({p.shape[0]} atoms, {e.shape[1]} edges), {len(times)} timed "
+                     f"steps, fp32, oracle/ restatement with torch CPU autograd + Adam",
+              cpu_model=info["cpu_model"], logical_cpus=threads, physical_cores=info["physical_cores"],
+              value_1_thread=small * len(t1) / sum(t1), value_physical_cores=small * len(tp) / sum(tp),
+              thread_sweep_sample=f"{small} graphs per step ({es.shape[1]} edges)")
+    return cb, sum(times), len(times)
+
+
+# ------------------------------------------------------------------------------------------- sampling leg (configs[2])
+def tame_(net, L, fx=0.05, fd=0.02):
+    """Scale the coordinate head and the distance columns so that an UNTRAINED net gives bounded T-step trajectories (no
+    trained weights ship with the reference; default init diverges within a few steps).  Shapes and code path unchanged."""
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import bump_param_epoch
+    with torch.no_grad():
+        for l in range(L):
+            e = net.egcl_list[l]
+            e.mlp_x[4].weight.mul_(fx)
+            e.mlp_x[4].bias.mul_(fx)
+            e.mlp_m[0].weight[:, -1].mul_(fd)
+            e.mlp_x[0].weight[:, -1].mul_(fd)
+    bump_param_epoch()
+
+
+def sampling_leg(args, rank, world, dev, lib, peaks):
+    """`structures` x 192-atom fully connected structures per GPU through the public sampler (generate()'s loop batched:
+    T ancestral steps + the t = 0 step, COM projection, finite flags), batch-sharded, no collective.  Structures/s is the
+    whole job; the bound is the measured bf16 peak over the algorithmic FLOPs of T+1 denoiser calls."""
+    import torch.distributed as dist
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.sampler import sample_structures
+    c = SAMPLING
+    S, n, T, L, d, H = args.sampling_structures, c["atoms"], c["T"], c["L"], c["d"], c["H"]
+    torch.manual_seed(CFG["seed"])
+    net = EquivariantGNN(**net_sizes(L, d, H)).to(dev)
+    tame_(net, L)
+    net.precision = args.precision
+    sd_cpu = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
+    dp = E3DiffusionProcess(s=c["s"], power=c["power"], num_diffusion_timestep=T)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(CFG["seed"] + rank)
+    sample_structures(net, dp, n, min(S, 4), generator=gen, device=dev)  # warm-up: packs weights, allocates, captures
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    l0 = lib.egnn_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    out = sample_structures(net, dp, n, S, generator=gen, device=dev)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    ok = out["finite"].sum().to(torch.float32).view(1)
+    if world > 1:
+        dist.barrier()
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ok, op=dist.ReduceOp.SUM)
+    sec = float(ms.item()) * 1e-3
+    flops_structure_step = fwd_flops(L, d, H, n, n * (n - 1))
+    bound = peaks["tflops"] * 1e12 / ((T + 1) * flops_structure_step)
+    res = dict(metric="sampled structures/s (x+h ancestral sampling, T+1 denoiser calls per structure)",
+               value=S * world / sec, unit="structures/s", per_gpu=S / sec, seconds=sec, structures_per_gpu=S,
+               accepted_structures=int(ok.item()), denoiser_graph_steps_per_s=S * world * (T + 1) / sec,
+               algorithmic_tflops_per_gpu=S * (T + 1) * flops_structure_step / sec / 1e12,
+               bound_structures_per_s_per_gpu=bound, frac_of_bound=S / sec / bound, gpu_launches=int(lib.egnn_launch_count() - l0),
+               config=dict(workload=f"cfg3: x+h joint diffusion sampling, fully connected {n}-atom structures "
+                                    f"(E = {n * (n - 1)} per structure), EGNN L={L} d={d} H=3, T={T}, batch-sharded, no collective",
+                           weights="seeded random init, coordinate head x0.05 / distance columns x0.02 (untrained nets diverge)",
+                           noise="torch device generator, drawn inside the timed region"))
+    if rank == 0 and world == 1:
+        # the reference's sampler on the host cores: ONE structure, a bounded number of steps of generate()'s loop
+        # (parts/train_per_iretation.py:335-374) through the CPU restatement, extrapolated to T+1 steps
+        from oracle import diffusion_ref as D, egnn_ref, graphs_ref as G
+        threads = os.cpu_count() or 1
+        torch.set_num_threads(threads)
+        sch = D.Schedule(c["s"], c["power"], T)
+        ei = torch.as_tensor(G.fc_edges(n)).long()
+        g2 = torch.Generator().manual_seed(1)
+        z_x, z_h = D.remove_mean(torch.randn(n, 3, generator=g2)), torch.randn(n, 2, generator=g2)
+        ksteps, times = 12, []
+        with torch.no_grad():
+            for k in range(ksteps + 2):
+                t = T - k
+                t0 = time.perf_counter()
+                h = torch.cat([z_h, torch.full((n, 1), t / T, dtype=torch.float32)], dim=1)
+                nh, nx = egnn_ref.egnn_forward(sd_cpu, L, ei, h, z_x)
+                eps_x = D.remove_mean(nx - z_x)
+                z_x = D.reverse_diffuse_one_step(sch, z_x, eps_x, t, torch.randn(n, 3, generator=g2), "pos")
+                z_h = D.reverse_diffuse_one_step(sch, h[:, :2], nh[:, :2], t, torch.randn(n, 2, generator=g2), "h")
+                if k >= 2:
+                    times.append(time.perf_counter() - t0)
+        per_step = sum(times) / len(times)
+        res["cpu_baseline"] = dict(value=1.0 / ((T + 1) * per_step), unit="structures/s", cores=threads, kind="port",
+                                   sample=f"1 structure, {ksteps} of the {T + 1} sampler steps ({1e3 * per_step:.1f} ms/step), "
+                                          "extrapolated; one structure per call like generate()")
+    return res
 
 
 # ------------------------------------------------------------------------------------------- product arm (B200)
@@ -378,7 +515,12 @@ def run_product(args, rank, world, local):
     top = max(prof, key=lambda k: prof[k]["ms_per_step"]) if prof else None
     roofline = None
     if top in algo:
-        ach = algo[top] / (prof[top]["ms_per_launch"] * 1e-3) / 1e12
+        # d = 256: the edge backward is TWO kernels per layer (tc_edge_bwd256 writes the tile images, tc_wgrad256 turns
+        # them into dW2): the backward FLOPs are divided by the time of the pair
+        pair_ms = prof[top]["ms_per_launch"]
+        if top == "tc_edge_bwd" and "tc_wgrad" in prof:
+            pair_ms += prof["tc_wgrad"]["ms_per_launch"]
+        ach = algo[top] / (pair_ms * 1e-3) / 1e12
         # tensor-core FLOPs actually issued: the backward recomputes both edge MLPs (3x forward), and bf16x3 issues
         # three bf16 MMAs (hi.hi + lo.hi + hi.lo) per fp32-accurate product
         # (forward: GEMM1 + GEMM2 of both branches; backward: the same recomputed + dgrad, and the weight-gradient MMAs
@@ -389,33 +531,34 @@ def run_product(args, rank, world, local):
         traffic = None
         try:
             tkey = top + ("256" if CFG["d"] == 256 else "")  # ncu captures: cfg2 for the d=128 kernels, cfg4 for d=256
-            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", TRAFFIC_FILE)) as f:
                 traffic = json.load(f).get(tkey, {}).get("dram_bytes_per_launch")
         except OSError:
-            pass
+            try:
+                with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+                    traffic = json.load(f).get(tkey, {}).get("dram_bytes_per_launch")
+            except OSError:
+                pass
         roofline = dict(bound="tensor", kernel=top, achieved=ach, peak=peaks["tflops"], unit="TFLOP/s",
                         frac=ach / peaks["tflops"], traffic=traffic, peak_source=peaks["source"] + " bf16 sustained",
-                        share_of_step=prof[top]["ms_per_step"] / (ms / args.steps),
-                        flops_per_launch=algo[top], ms_per_launch=prof[top]["ms_per_launch"],
+                        share_of_step=pair_ms * prof[top]["launches_per_step"] / (ms / args.steps),
+                        flops_per_launch=algo[top], ms_per_launch=pair_ms,
                         issued_tensor_flops_per_launch=issued,
-                        issued_frac=issued / (prof[top]["ms_per_launch"] * 1e-3) / 1e12 / peaks["tflops"])
+                        issued_frac=issued / (pair_ms * 1e-3) / 1e12 / peaks["tflops"])
     line = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer)", value=value, unit="graph-steps/s",
                 n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=ms / args.steps, higher_is_better=True,
                 scaling="weak", vs_baseline=None, dtype=args.precision, data="synthetic",
-                config=dict(workload_config(args.precision), nodes_per_gpu=N, edges_per_gpu=E),
+                config=workload_config(N, E),
                 e2e=dict(value=e2e_value, unit="graph-steps/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4,
                          pipeline="H2D of step i+1 prefetched on a copy stream during step i; loss D2H every step, read 1 step late",
                          ms_per_step=ms_e2e / args.steps, host_enqueue_ms_per_step=host_ms),
                 gpu_launches=int(launches), clocks=clocks, roofline=roofline, kernels=prof,
                 train_flops_per_step=3 * fwd_flops(CFG["L"], d, CFG["H"], N, E))
     if rank == 0 and world == 1:
-        threads = os.cpu_count() or 1
-        graphs = CFG["cpu_graphs"]
-        p, o, e, b = cpu_sample(pos_h, oh_h, ei_d.cpu(), node_ptr_h.long(), graphs)
-        times = cpu_train_steps(p, o, e, b, sd_cpu, 2, 1, threads)
-        line["cpu_baseline"] = dict(value=graphs * len(times) / sum(times), unit="graph-steps/s", cores=threads, kind="port",
-                                    sample=f"{graphs} of the {CFG['graphs']} graphs per step ({e.shape[1]} edges), 2 timed steps, oracle/ "
-                                           "restatement with torch CPU autograd + Adam")
+        cb, _, _ = cpu_baseline_block(pos_h, oh_h, ei_d.cpu(), node_ptr_h.long(), sd_cpu, 6, 1, budget_s=30.0)
+        line["cpu_baseline"] = cb
+    if args.sampling_structures > 0 and CFG["name"] == "cfg2":
+        line["sampling"] = sampling_leg(args, rank, world, dev, lib, peaks)
     if rank == 0:
         print(json.dumps(line), flush=True)
 
@@ -429,6 +572,8 @@ def main():
     ap.add_argument("--precision", default="bf16x3", choices=["fp32", "bf16x3", "bf16"],
                     help="bf16x3 (default): tcgen05 split-bf16 products, fp32 accumulate, <=1e-4 per layer vs the fp32 "
                          "reference; fp32: CUDA-core FFMA; bf16: single tcgen05 product (looser, stated bound)")
+    ap.add_argument("--sampling-structures", type=int, default=SAMPLING["structures"],
+                    help="structures per GPU of the sampling leg (cfg3: 512 x 192 atoms fully connected, T = 1000); 0 skips it")
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4"],
                     help="cfg2 (default, the contract line) or cfg4 (1536-atom cells, L=9, hidden 256)")
     args = ap.parse_args()

@@ -30,7 +30,8 @@ def tame_(net, L, fx=0.05, fd=0.02):
             e.mlp_x[4].bias.mul_(fx)
             e.mlp_m[0].weight[:, -1].mul_(fd)
             e.mlp_x[0].weight[:, -1].mul_(fd)
-    net._flat.packed_key = None
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import bump_param_epoch
+    bump_param_epoch()
 
 
 def main():

@@ -19,7 +19,7 @@ I32 = torch.int32
 
 def sample_structures(egnn, dp, num_atoms, num_structures=1, atom_type_size=2, onehot_scale=1.0, cond=None,
                       edge_index=None, noises=None, generator=None, use_cuda_graph=True, noise_chunk=50,
-                      record_steps=(), device="cuda"):
+                      record_steps=(), device="cuda", norm_scope="graph"):
     """Returns dict(pos [S,n,3], h [S,n,A], atoms [S,n,A] one-hot argmax, finite [S] bool, edge_index_single).
 
     edge_index: int64 [2,e] edges of ONE structure (default: fully connected, row-major, :308-313); it is replicated
@@ -27,6 +27,8 @@ def sample_structures(egnn, dp, num_atoms, num_structures=1, atom_type_size=2, o
     init_x [S*n,3], init_h [S*n,A], step_x [T,S*n,3], step_h [T,S*n,A] (row k is used at t = T-k), final_x, final_h --
     the layout of oracle/loops_ref.make_noises stacked over structures; otherwise torch.randn on the device.
     cond: optional [n,C] conditioning block inserted between the atom-type columns and the time column.
+    norm_scope: 'graph' (default) = the normaliser of EGCL.message per structure, what generate() computes one structure
+    at a time; 'call' = ONE scalar over the whole batch, what a batched reference call would compute (:64).
     """
     dev = torch.device(device)
     S, n, A = int(num_structures), int(num_atoms), int(atom_type_size)
@@ -77,7 +79,7 @@ def sample_structures(egnn, dp, num_atoms, num_structures=1, atom_type_size=2, o
         period = chunk
 
     def one_step():
-        egnn.forward_into(graph, h_in, z_x, h_out, x_out, norm_scope="graph")
+        egnn.forward_into(graph, h_in, z_x, h_out, x_out, norm_scope=norm_scope)
         call("egnn_sampler_step", ptr(z_x), ptr(h_in), ptr(x_out), ptr(h_out), ptr(ring_x), ptr(ring_h), ptr(coef),
              ptr(t_dev), T, N * 3, N * A, period, float(onehot_scale), ptr(node_ptr), S, H, A, 0, None, ptr(finite),
              stream_ptr(dev))
@@ -115,7 +117,7 @@ def sample_structures(egnn, dp, num_atoms, num_structures=1, atom_type_size=2, o
             record[t] = (z_x.clone(), h_in[:, :A].clone() / onehot_scale)
     # final t = 0 step (:391-428)
     h_in[:, H - 1] = 0.0
-    egnn.forward_into(graph, h_in, z_x, h_out, x_out, norm_scope="graph")
+    egnn.forward_into(graph, h_in, z_x, h_out, x_out, norm_scope=norm_scope)
     fx = (noises["final_x"].to(dev).float() if inj else randn(N, 3)).contiguous()
     fh = (noises["final_h"].to(dev).float() if inj else randn(N, A)).contiguous()
     call("egnn_sampler_step", ptr(z_x), ptr(h_in), ptr(x_out), ptr(h_out), ptr(fx), ptr(fh), ptr(coef), None, 0, 0, 0, 0,

@@ -122,7 +122,7 @@ def sample_structure_xonly(egnn, sch, edge_index, x_onehot, noises, s=1.0):
     return pos
 
 
-def sample_structures_batched(sd, L, sch, n, S, noises, A=2, s=1.0):
+def sample_structures_batched(sd, L, sch, n, S, noises, A=2, s=1.0, norm_scope="graph"):
     """S independent runs of sample_structure() evaluated as ONE batch of S graphs (faster on the CPU, same arithmetic
     per structure): per-graph COM removal (diffusion_x_h.py:10-13 with a batch vector) and the per-graph normaliser
     (norm_scope='graph'), which is what calling generate() once per structure (parts/train_per_iretation.py:299-316)
@@ -132,7 +132,8 @@ def sample_structures_batched(sd, L, sch, n, S, noises, A=2, s=1.0):
     T = sch.T
     batch = torch.arange(S).repeat_interleave(n)
     ei = torch.as_tensor(graphs_ref.fc_edges_batch([n] * S))
-    fwd = lambda h, x: egnn_ref.egnn_forward(sd, L, ei, h, x, "graph", batch=batch)
+    # norm_scope='call': ONE normaliser over the whole batch -- what EGCL.message (:64) computes for a batched call
+    fwd = lambda h, x: egnn_ref.egnn_forward(sd, L, ei, h, x, norm_scope, batch=batch)
 
     def rm(x, _b=None):  # per-graph COM removal; equal-size graphs -> one strided mean instead of the mask loop
         v = x.view(S, n, 3)
