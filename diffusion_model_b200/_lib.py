@@ -56,6 +56,7 @@ SIGNATURES = {
     "egnn_cutoff_fallback": (C.c_int, [_P, _P, _P, _F, _I32, _P, _P, _P]),
     "egnn_cutoff_fallback_fill": (C.c_int, [_P, _P, _I32, _I64, _P, _P]),
     "egnn_graph_prepare": (C.c_int, [_P, _I32, _I64, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "egnn_graph_prepare_noalloc": (C.c_int, [_P, _I32, _I64, _P, _P, _P, _P, _P, _P, _P]),
     "egnn_node_ptr_from_batch": (C.c_int, [_P, _I32, _I32, _P, _P, _P]),
     "egnn_pack_weights": (C.c_int, [_NET, _P, _P, _P]),
     "egnn_net_forward": (C.c_int, [_NET, _GR, _P, _P, _P, _P, _P, _P, _P, _I64, _I32, _I32, _P]),

@@ -331,6 +331,36 @@ extern "C" int egnn_graph_prepare(const int64_t* edge_index, int32_t N, int64_t 
     return EGNN_OK;
 }
 
+// ---- allocation-free variant (no counterpart in the reference) -------------
+// Scratch of egnn_graph_prepare in a file-scope device array instead of a caller buffer: for callers that cannot call
+// cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).  Every GPU that loads the library holds
+// these EGNN_GRAPH_PREPARE_NOALLOC_MAX_INTS * 4 bytes (4 MiB) until exit.  In host code `g_prepare_scratch` is only a
+// host-side stand-in for the symbol, NOT a device address: the address is resolved with cudaGetSymbolAddress, once per
+// device with that device current, and that pointer is what the kernels get.
+static __device__ __align__(256) int32_t g_prepare_scratch[EGNN_GRAPH_PREPARE_NOALLOC_MAX_INTS];
+
+extern "C" int egnn_graph_prepare_noalloc(const int64_t* edge_index, int32_t N, int64_t E, int32_t* recv, int32_t* send,
+                                          int32_t* row_ptr, int32_t* col_ptr, int32_t* col_edge, int32_t* flags_out,
+                                          void* stream) {
+    EGNN_REQUIRE(N >= 0 && E >= 0, "egnn_graph_prepare_noalloc: negative size (N=%d E=%lld)", N, (long long)E);
+    EGNN_REQUIRE((int64_t)N + 1 + E <= (int64_t)EGNN_GRAPH_PREPARE_NOALLOC_MAX_INTS,
+                 "egnn_graph_prepare_noalloc: N + 1 + E = %lld exceeds the static scratch of %d int32 "
+                 "(EGNN_GRAPH_PREPARE_NOALLOC_MAX_INTS); use egnn_graph_prepare with a caller-provided scratch buffer",
+                 (long long)((int64_t)N + 1 + E), (int)EGNN_GRAPH_PREPARE_NOALLOC_MAX_INTS);
+    static int32_t* resolved[64] = {};  // device address of the array, per device ordinal (same value from any thread)
+    int dev = 0;
+    EGNN_CUDA(cudaGetDevice(&dev));
+    int32_t* scratch = (dev >= 0 && dev < 64) ? resolved[dev] : nullptr;
+    if (!scratch) {
+        EGNN_CUDA(cudaGetSymbolAddress((void**)&scratch, g_prepare_scratch));
+        EGNN_REQUIRE(scratch != nullptr, "egnn_graph_prepare_noalloc: cudaGetSymbolAddress returned NULL");
+        if (dev >= 0 && dev < 64) resolved[dev] = scratch;
+    }
+    // same launches as egnn_graph_prepare; it clears the counters it needs at zero itself (cudaMemsetAsync on `stream`:
+    // no allocation), so the previous call's leftovers in the shared array are harmless -- for calls that do not overlap
+    return egnn_graph_prepare(edge_index, N, E, recv, send, row_ptr, col_ptr, col_edge, scratch, flags_out, stream);
+}
+
 extern "C" int egnn_node_ptr_from_batch(const int64_t* batch, int32_t N, int32_t G, int32_t* node_ptr,
                                         int32_t* node_graph, void* stream) {
     EGNN_REQUIRE(N >= 0 && G >= 0, "egnn_node_ptr_from_batch: negative size");

@@ -123,6 +123,18 @@ int egnn_cutoff_fallback_fill(const int32_t* fb_pairs, const int32_t* row_ptr, i
 int egnn_graph_prepare(const int64_t* edge_index, int32_t N, int64_t E, int32_t* recv, int32_t* send,
                        int32_t* row_ptr, int32_t* col_ptr, int32_t* col_edge, int32_t* scratch, int32_t* flags_out,
                        void* stream);
+/* Allocation-free variant of egnn_graph_prepare.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and flags as egnn_graph_prepare, but the int32 [N+1+E] scratch lives in a static
+ * __device__ array inside the library (EGNN_GRAPH_PREPARE_NOALLOC_MAX_INTS int32 = 4 MiB, held by every GPU that loads
+ * the library until exit) and the call performs no cudaMalloc / cudaFree / allocating library routine.
+ *   - N + 1 + E > EGNN_GRAPH_PREPARE_NOALLOC_MAX_INTS is rejected with EGNN_ERR_ARG and a message naming the limit;
+ *   - every call on a device shares the ONE array, which keeps the previous call's contents; the counters that must
+ *     start at zero are cleared on `stream` inside the call.  Calls that overlap on the GPU (different streams, or two
+ *     host threads on one device) RACE on it: serialise them, or use egnn_graph_prepare with private scratch buffers. */
+#define EGNN_GRAPH_PREPARE_NOALLOC_MAX_INTS (1 << 20)
+int egnn_graph_prepare_noalloc(const int64_t* edge_index, int32_t N, int64_t E, int32_t* recv, int32_t* send,
+                               int32_t* row_ptr, int32_t* col_ptr, int32_t* col_edge, int32_t* flags_out, void* stream);
 /* node_graph [N] (non-decreasing) -> node_ptr [G+1] */
 int egnn_node_ptr_from_batch(const int64_t* batch, int32_t N, int32_t G, int32_t* node_ptr, int32_t* node_graph,
                              void* stream);
