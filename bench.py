@@ -215,7 +215,7 @@ def run_reference(args, rank):
     value = cb["value"]
     line = dict(impl="reference", metric="denoiser graph-steps/s (training fwd+bwd+optimizer)", value=value,
                 unit="graph-steps/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
-                ms_per_step=1e3 * total / nsteps, higher_is_better=True, scaling="weak", vs_baseline=None,
+                ms_per_step=1e3 * total / nsteps, higher_is_better=True, scaling=CFG.get("scaling", "weak"), vs_baseline=None,
                 dtype="fp32", data="synthetic", config=workload_config(pos.shape[0], ei.shape[1]),
                 cpu_baseline=cb,
                 e2e=dict(value=value, unit="graph-steps/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
@@ -379,10 +379,10 @@ def run_product(args, rank, world, local):
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
     from diffusion_model_b200.data import Data, DevicePrefetcher
     from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
-    from diffusion_model_b200.distributed import allreduce_gradients, broadcast_parameters
+    from diffusion_model_b200.distributed import OverlappedGradSync, broadcast_parameters
     from diffusion_model_b200.graph import build_edges_cutoff, check_pending
     from diffusion_model_b200.optim import FlatAdam
-    from diffusion_model_b200.train_per_iretation import batch_loss
+    from diffusion_model_b200.train_per_iretation import GraphedTrainStep, batch_loss
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
@@ -398,7 +398,9 @@ def run_product(args, rank, world, local):
     net.precision = args.precision
     sd_cpu = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
     broadcast_parameters(net)
-    opt = FlatAdam(net, lr=CFG["lr"])
+    opt = FlatAdam(net, lr=CFG["lr"], capturable=True)
+    if world > 1:
+        OverlappedGradSync(net, buckets=3)  # gradient all-reduce in 3 buckets of layers, overlapped with backward
     dp = E3DiffusionProcess(s=CFG["s"], power=CFG["power"], num_diffusion_timestep=CFG["T"])
     dp.device_tables(dev)
     prm = dict(atom_type_size=CFG["A"], norm_scope="call")
@@ -413,12 +415,11 @@ def run_product(args, rank, world, local):
     pos_p, oh_p, np_p = pos_h.pin_memory(), oh_h.pin_memory(), node_ptr_h.pin_memory()
 
     def train_step(b):
+        """the step enqueued kernel by kernel through Python (what train_epoch does for minibatches of varying shape)"""
         opt.zero_grad()
         loss, _, _ = batch_loss(net, b, dp, prm)
-        loss.backward()
-        if world > 1:
-            allreduce_gradients(net)
-        opt.step(grad_scale=1.0 / world)
+        loss.backward()   # N > 1: the bucketed all-reduce runs on the sync's stream under the rest of backward
+        opt.step(grad_scale=1.0 / world)   # waits for the last bucket
         return loss
 
     # e2e: the public loader path.  Every step's inputs start in pinned HOST memory; DevicePrefetcher issues step
@@ -431,14 +432,23 @@ def run_product(args, rank, world, local):
         while True:
             yield host_batch
 
+    # The product's fast path for fixed-shape minibatches: the whole step captured once in a CUDA graph
+    # (train_per_iretation.GraphedTrainStep); `--eager` times the kernel-by-kernel path instead.
+    graphed = None if args.eager else GraphedTrainStep(net, dp, prm, opt, resident, grad_scale=1.0 / world, device=dev)
     feed = iter(DevicePrefetcher(host_batches(), dev))
     loss_pin = torch.zeros(2, pin_memory=True)
     loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
     e2e_state = dict(i=0, last=None)
 
     def e2e_step():
-        b = next(feed)
-        loss = train_step(b)
+        if graphed is None:
+            b = next(feed)
+            loss = train_step(b)
+        else:
+            if e2e_state["i"] == 0:
+                graphed.prefetch(host_batch)
+            loss = graphed.step()            # moves the staged minibatch into the static buffers, replays
+            graphed.prefetch(host_batch)     # H2D of the NEXT step's inputs on the copy stream, under this replay
         k = e2e_state["i"] & 1
         loss_pin[k:k + 1].copy_(loss.detach().view(1), non_blocking=True)  # D2H read of the step's loss
         loss_ev[k].record()
@@ -474,17 +484,31 @@ def run_product(args, rank, world, local):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item()), lib.egnn_launch_count() - l0, clocks.stop()
 
-    ms, launches, clocks = timed(lambda: train_step(resident), args.steps, args.warmup)
+    # kernels one step launches (the library counts its launches on the host; a graph replay does not pass there)
+    torch.cuda.synchronize(dev)
+    l0 = lib.egnn_launch_count()
+    train_step(resident)
+    torch.cuda.synchronize(dev)
+    launches_per_step = int(lib.egnn_launch_count() - l0)
+    resident_step = (lambda: train_step(resident)) if graphed is None else (lambda: graphed.step())
+    ms, _, clocks = timed(resident_step, args.steps, args.warmup)
+    launches = launches_per_step * args.steps
     value = G_ * world * args.steps / (ms * 1e-3)
+    eager = None
+    if graphed is not None:
+        k_eager = min(args.steps, 10)
+        ms_eager, _, _ = timed(lambda: train_step(resident), k_eager, 3)
+        eager = dict(ms_per_step=ms_eager / k_eager, value=G_ * world * k_eager / (ms_eager * 1e-3),
+                     note="same step enqueued kernel by kernel through Python (no CUDA graph)")
     ms_e2e, _, _ = timed(e2e_step, args.steps, max(args.warmup, 3))
     e2e_value = G_ * world * args.steps / (ms_e2e * 1e-3)
-    h2d = pos_p.numel() * 4 + oh_p.numel() * 4 + ei_h.numel() * 8 + np_p.numel() * 4 + G_ * 4
+    h2d = pos_p.numel() * 4 + oh_p.numel() * 4 + ei_h.numel() * 8 + G_ * 4 + (np_p.numel() * 4 if graphed is None else 0)
     # host time to enqueue one step (no sync inside): the floor of the step time when the GPU is not the bottleneck
     host_ms = []
     for _ in range(5):
         torch.cuda.synchronize(dev)
         t0 = time.perf_counter()
-        train_step(resident)
+        resident_step()
         host_ms.append(1e3 * (time.perf_counter() - t0))
     torch.cuda.synchronize(dev)
     host_ms = statistics.median(host_ms)
@@ -547,12 +571,17 @@ def run_product(args, rank, world, local):
                         issued_frac=issued / (pair_ms * 1e-3) / 1e12 / peaks["tflops"])
     line = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer)", value=value, unit="graph-steps/s",
                 n_gpus=world, steps=args.steps, warmup=args.warmup, ms_per_step=ms / args.steps, higher_is_better=True,
-                scaling="weak", vs_baseline=None, dtype=args.precision, data="synthetic",
+                scaling=CFG.get("scaling", "weak"), vs_baseline=None, dtype=args.precision, data="synthetic",
                 config=workload_config(N, E),
                 e2e=dict(value=e2e_value, unit="graph-steps/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4,
-                         pipeline="H2D of step i+1 prefetched on a copy stream during step i; loss D2H every step, read 1 step late",
+                         pipeline="H2D of step i+1 staged on a copy stream during step i (then one device-to-device move into the "
+                                  "graph's static buffers); loss D2H every step, read 1 step late",
                          ms_per_step=ms_e2e / args.steps, host_enqueue_ms_per_step=host_ms),
-                gpu_launches=int(launches), clocks=clocks, roofline=roofline, kernels=prof,
+                gpu_launches=int(launches), launches_per_step=launches_per_step,
+                step_mode=("eager: kernels enqueued one by one" if graphed is None else
+                           "CUDA graph: the whole step (edge-list preparation, diffusion, forward, loss, backward, all-reduce, "
+                           "Adam) captured once and replayed; gpu_launches = kernels per step x steps"),
+                eager=eager, clocks=clocks, roofline=roofline, kernels=prof,
                 train_flops_per_step=3 * fwd_flops(CFG["L"], d, CFG["H"], N, E))
     if rank == 0 and world == 1:
         cb, _, _ = cpu_baseline_block(pos_h, oh_h, ei_d.cpu(), node_ptr_h.long(), sd_cpu, 6, 1, budget_s=30.0)
@@ -572,6 +601,10 @@ def main():
     ap.add_argument("--precision", default="bf16x3", choices=["fp32", "bf16x3", "bf16"],
                     help="bf16x3 (default): tcgen05 split-bf16 products, fp32 accumulate, <=1e-4 per layer vs the fp32 "
                          "reference; fp32: CUDA-core FFMA; bf16: single tcgen05 product (looser, stated bound)")
+    ap.add_argument("--global-batch", type=int, default=0,
+                    help="strong scaling: this many graphs in total, split evenly over the ranks (default 0: weak scaling, "
+                         "the workload's graph count on EVERY rank)")
+    ap.add_argument("--eager", action="store_true", help="time the kernel-by-kernel step instead of the CUDA-graph replay")
     ap.add_argument("--sampling-structures", type=int, default=SAMPLING["structures"],
                     help="structures per GPU of the sampling leg (cfg3: 512 x 192 atoms fully connected, T = 1000); 0 skips it")
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4"],
@@ -579,6 +612,14 @@ def main():
     args = ap.parse_args()
     if args.workload == "cfg4":
         CFG.update(CFG4)
+    CFG["scaling"] = "weak"
+    if args.global_batch:
+        world_ = int(os.environ.get("WORLD_SIZE", "1"))
+        if args.global_batch % world_:
+            raise SystemExit(f"--global-batch {args.global_batch} is not a multiple of the {world_} ranks")
+        CFG["graphs"] = args.global_batch // world_
+        CFG["cpu_graphs"] = min(CFG["cpu_graphs"], CFG["graphs"])
+        CFG["scaling"] = "strong"
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         run_reference(args, int(os.environ.get("RANK", "0")))

@@ -8,7 +8,9 @@ Extras that default to the reference behaviour:
     normaliser ``torch.norm(coords_i - coords_j)`` (:64) per graph, i.e. what the reference computes when it samples
     one structure per call (parts/train_per_iretation.py:299-316);
   * ``forward(h, x, edge_index, edge_attr=None)`` argument order (BASELINE.json wording) is recognised by dtype;
-  * ``precision`` attribute: 'fp32' (default), 'bf16x3', 'bf16'.
+  * ``precision`` attribute: 'auto' (default) = 'bf16x3' (tcgen05, split-bf16 products with fp32 accumulation, <= 1e-4 per
+    layer against the fp32 reference -- the same bar as the fp32 mode) whenever the tensor-core kernels cover the network
+    shape, else 'fp32' (CUDA-core FFMA); or one of 'fp32', 'bf16x3', 'bf16' (single product, looser stated bound) by hand.
 """
 from __future__ import annotations
 
@@ -141,9 +143,18 @@ class _EGNNFunction(torch.autograd.Function):
         gflat = torch.empty_like(flat)
         gh_in = torch.empty_like(h)
         gx_in = torch.empty_like(x)
-        call("egnn_net_backward", C.byref(net), gi.ref(), ptr(flat), ptr(packed), ptr(h), ptr(x), ptr(ws), ptr(gh),
-             ptr(gx), ptr(gh_in), ptr(gx_in), ptr(gflat), ptr(bws), nbw, NORM[norm_scope], PREC[precision],
-             stream_ptr(h.device))
+        sync = getattr(owner, "_grad_sync", None)
+        if sync is not None and sync.active():
+            # data-parallel training: one CUDA event per bucket of layers, recorded as soon as that bucket's slice of the
+            # flat gradient is final; the sync object all-reduces it on its communication stream under the rest of backward
+            call("egnn_net_backward_events", C.byref(net), gi.ref(), ptr(flat), ptr(packed), ptr(h), ptr(x), ptr(ws), ptr(gh),
+                 ptr(gx), ptr(gh_in), ptr(gx_in), ptr(gflat), ptr(bws), nbw, NORM[norm_scope], PREC[precision],
+                 sync.event_array(), stream_ptr(h.device))
+            sync.launch(gflat)
+        else:
+            call("egnn_net_backward", C.byref(net), gi.ref(), ptr(flat), ptr(packed), ptr(h), ptr(x), ptr(ws), ptr(gh),
+                 ptr(gx), ptr(gh_in), ptr(gx_in), ptr(gflat), ptr(bws), nbw, NORM[norm_scope], PREC[precision],
+                 stream_ptr(h.device))
         owner._last_grad_flat = gflat
         grads, off = [], 0
         for p in owner._flat.params:
@@ -156,7 +167,15 @@ class _EGNNFunction(torch.autograd.Function):
 class _KernelBacked(nn.Module):
     """Shared plumbing of EGCL (one layer) and EquivariantGNN (L layers)."""
 
-    precision = "fp32"
+    precision = "auto"
+
+    def resolved_precision(self):
+        """The arithmetic mode a call will use: 'auto' -> 'bf16x3' where the tcgen05 edge kernels cover the shape
+        (Mh = Ms = Xh in {64, 128, 256} and 2H+1 <= 16, csrc/common.cuh: tc_fwd_supported), else 'fp32'."""
+        if self.precision != "auto":
+            return self.precision
+        n = self._net
+        return "bf16x3" if (n.Mh == n.Ms == n.Xh and n.Mh in (64, 128, 256) and 2 * n.H + 1 <= 16) else "fp32"
 
     def _setup(self, L, layers, sizes):
         m_input, m_hidden, m_output, x_input, x_hidden, x_output, h_input, h_hidden, h_output = sizes
@@ -176,6 +195,7 @@ class _KernelBacked(nn.Module):
         object.__setattr__(self, "_flat", _FlatParams(plist))
         object.__setattr__(self, "_ws", {})
         object.__setattr__(self, "_last_grad_flat", None)
+        object.__setattr__(self, "_grad_sync", None)  # distributed.OverlappedGradSync, when data-parallel
 
     def _workspace(self, n, device):
         w = self._ws.get((n, device))
@@ -192,7 +212,7 @@ class _KernelBacked(nn.Module):
         nws = _lib.load().egnn_forward_workspace_floats(C.byref(net), graph.N, graph.E, graph.G)
         ws = self._workspace(nws, h.device)
         call("egnn_net_forward", C.byref(net), graph.ref(), ptr(flat), ptr(packed), ptr(h, torch.float32),
-             ptr(x, torch.float32), ptr(h_out), ptr(x_out), ptr(ws), nws, NORM[norm_scope], PREC[self.precision],
+             ptr(x, torch.float32), ptr(h_out), ptr(x_out), ptr(ws), nws, NORM[norm_scope], PREC[self.resolved_precision()],
              stream_ptr(h.device))
         return h_out, x_out
 
@@ -217,7 +237,7 @@ class _KernelBacked(nn.Module):
         if graph is None:
             edge_index = edge_index.to(h.device)
             graph = graph_index_for(edge_index, h.shape[0], batch=batch, node_ptr=node_ptr)
-        return _EGNNFunction.apply(h, x, self, graph, norm_scope, self.precision, *self._flat.params)
+        return _EGNNFunction.apply(h, x, self, graph, norm_scope, self.resolved_precision(), *self._flat.params)
 
 
 def _linear_stack(*dims_and_acts):

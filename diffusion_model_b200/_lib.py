@@ -61,6 +61,7 @@ SIGNATURES = {
     "egnn_pack_weights": (C.c_int, [_NET, _P, _P, _P]),
     "egnn_net_forward": (C.c_int, [_NET, _GR, _P, _P, _P, _P, _P, _P, _P, _I64, _I32, _I32, _P]),
     "egnn_net_backward": (C.c_int, [_NET, _GR, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I32, _I32, _P]),
+    "egnn_net_backward_events": (C.c_int, [_NET, _GR, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _I32, _I32, _P, _P]),
     "egnn_remove_mean": (C.c_int, [_P, _I32, _P, _I32, _P]),
     "egnn_diffuse_batch": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _I32, _I32, _I32, _P, _P, _P, _P]),
     "egnn_loss_fwd_bwd": (C.c_int, [_P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _P, _P, _P, _P]),
@@ -68,6 +69,7 @@ SIGNATURES = {
                                     _I32, _P, _P, _P]),
     "egnn_counter_add": (C.c_int, [_P, _I32, _P]),
     "egnn_adam_step": (C.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _F, _P]),
+    "egnn_adam_step_dev": (C.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _P, _F, _P]),
     "egnn_radam_sf_step": (C.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _F, _F, _I32, _F, _P]),
     "egnn_lerp": (C.c_int, [_P, _P, _I64, _F, _P]),
     "egnn_rdf_local": (C.c_int, [_P, _P, _I32, _P, _P, _P, _I32, C.c_double, C.c_double, _P, _I32, _P, _P, _P, _P]),

@@ -57,6 +57,34 @@ enum { EGNN_K_EDGE_FWD = 0, EGNN_K_NODE_FWD = 1, EGNN_K_XUPDATE = 2, EGNN_K_EDGE
 // requirement: no kernel synchronises across CTAs, so a device with another SM count runs the same grids correctly.
 constexpr int kB200SMs = 148;
 
+// ---- programmatic dependent launch (PDL) --------------------------------------------------------------------------------
+// The forward path of a small graph is a chain of ~3 L short kernels (a 24-atom structure is 5 edge tiles): launch latency
+// and each kernel's prologue (weight-image load, TMEM allocation, barrier set-up) cost more than the math.  A kernel
+// launched with egnn_launch(..., pdl = true) may START while its predecessor in the stream is still running; it does its
+// prologue -- which must touch only memory no kernel of the chain writes (packed weights, the graph index) -- and then
+// calls pdl_wait(), which returns once the predecessor has completed and its writes are visible.  Every kernel of the
+// chain calls pdl_launch_dependents() at its top so that its successor can be scheduled early.  A kernel that was
+// launched normally sees pdl_wait() return at once.  Works under CUDA-graph capture (programmatic edges).
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+static inline cudaError_t egnn_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl,
+                                      Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 static inline int64_t round_up64(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 __host__ __device__ static inline int round4(int a) { return (a + 3) & ~3; }
 

@@ -144,6 +144,8 @@ struct StepArgs {
 };
 __global__ void __launch_bounds__(256) sampler_step_kernel(StepArgs p) {
     __shared__ float red[8];
+    pdl_launch_dependents();
+    pdl_wait();  // common.cuh: PDL -- x_out / h_out come from the denoiser's last kernels
     const int g = blockIdx.x;
     const int a = p.node_ptr[g], b = p.node_ptr[g + 1];
     if (a >= b) return;
@@ -207,13 +209,36 @@ __global__ void __launch_bounds__(256) sampler_step_kernel(StepArgs p) {
     if (threadIdx.x == 0 && !all_ok) p.finite_flag[g] = 0;
 }
 
-__global__ void counter_add_kernel(int32_t* ctr, int32_t delta) { *ctr += delta; }
+__global__ void counter_add_kernel(int32_t* ctr, int32_t delta) {
+    pdl_wait();  // the kernel in front (sampler step, or the last backward kernel) may still be reading the counter
+    *ctr += delta;
+}
 
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, long long n, float lr, float b1, float b2,
                                                    float eps, float wd, float bc1, float bc2_sqrt, float gscale) {
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
+    float gi = g[i] * gscale;
+    const float pi = p[i];
+    if (wd != 0.f) gi = fmaf(wd, pi, gi);
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = pi - (lr / bc1) * (mi / denom);
+}
+
+// Adam with the step number in DEVICE memory: a CUDA-graph replay of a training step must not freeze the bias corrections
+// at the step it was captured on.  *step_dev is the 1-based number of THIS update.
+__global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                                       float* __restrict__ v, long long n, float lr, float b1, float b2,
+                                                       float eps, float wd, const int32_t* __restrict__ step_dev, float gscale) {
+    const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const float step = (float)(*step_dev);
+    const float bc1 = 1.f - powf(b1, step), bc2_sqrt = sqrtf(1.f - powf(b2, step));
     float gi = g[i] * gscale;
     const float pi = p[i];
     if (wd != 0.f) gi = fmaf(wd, pi, gi);
@@ -300,14 +325,14 @@ extern "C" int egnn_sampler_step(float* z_x, float* h_in, const float* x_out, co
     EGNN_REQUIRE(G >= 1 && H >= 1 && A >= 1 && A < H, "egnn_sampler_step: bad sizes");
     StepArgs p{z_x, h_in, x_out, h_out, noise_x, noise_h, coef, t_dev, t_base, noise_period, noise_stride_x, noise_stride_h,
                onehot_scale, node_ptr, H, A, final_step, z_h_out, finite_flag};
-    sampler_step_kernel<<<G, 256, 0, (cudaStream_t)stream>>>(p);
+    EGNN_CUDA(egnn_launch(sampler_step_kernel, dim3(G), dim3(256), 0, (cudaStream_t)stream, true, p));
     EGNN_CHECK_LAUNCH("sampler_step_kernel");
     return EGNN_OK;
 }
 
 extern "C" int egnn_counter_add(int32_t* counter, int32_t delta, void* stream) {
     EGNN_REQUIRE(counter, "egnn_counter_add: NULL pointer");
-    counter_add_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(counter, delta);
+    EGNN_CUDA(egnn_launch(counter_add_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, true, counter, delta));
     EGNN_CHECK_LAUNCH("counter_add_kernel");
     return EGNN_OK;
 }
@@ -343,5 +368,17 @@ extern "C" int egnn_lerp(float* p, const float* end, int64_t n, float weight, vo
     if (n == 0) return EGNN_OK;
     lerp_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p, end, n, weight);
     EGNN_CHECK_LAUNCH("lerp_kernel");
+    return EGNN_OK;
+}
+
+extern "C" int egnn_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                                  float beta1, float beta2, float eps, float weight_decay, const int32_t* step_dev,
+                                  float grad_scale, void* stream) {
+    EGNN_REQUIRE(params && grads && exp_avg && exp_avg_sq && step_dev && n >= 0, "egnn_adam_step_dev: bad arguments");
+    if (n == 0) return EGNN_OK;
+    adam_dev_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, lr,
+                                                                                  beta1, beta2, eps, weight_decay, step_dev,
+                                                                                  grad_scale);
+    EGNN_CHECK_LAUNCH("adam_dev_kernel");
     return EGNN_OK;
 }

@@ -524,10 +524,35 @@ extern "C" int64_t egnn_backward_workspace_floats(const egnn_net_t* net, int32_t
     return bwd_ws(*net, N, E, G).total;
 }
 
+static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const float* params, const float* packed,
+                             const float* h_in, const float* x_in, const float* fwd_ws_ptr, const float* gh_out,
+                             const float* gx_out, float* gh_in, float* gx_in, float* grad_params, float* ws,
+                             int64_t ws_floats, int32_t norm_scope, int32_t precision, void* const* layer_events,
+                             void* stream);
+
 extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, const float* params, const float* packed,
                                  const float* h_in, const float* x_in, const float* fwd_ws_ptr, const float* gh_out,
                                  const float* gx_out, float* gh_in, float* gx_in, float* grad_params, float* ws,
                                  int64_t ws_floats, int32_t norm_scope, int32_t precision, void* stream) {
+    return net_backward_impl(net, g, params, packed, h_in, x_in, fwd_ws_ptr, gh_out, gx_out, gh_in, gx_in, grad_params, ws,
+                             ws_floats, norm_scope, precision, nullptr, stream);
+}
+
+extern "C" int egnn_net_backward_events(const egnn_net_t* net, const egnn_graph_t* g, const float* params,
+                                        const float* packed, const float* h_in, const float* x_in, const float* fwd_ws_ptr,
+                                        const float* gh_out, const float* gx_out, float* gh_in, float* gx_in,
+                                        float* grad_params, float* ws, int64_t ws_floats, int32_t norm_scope,
+                                        int32_t precision, void* const* layer_events_host, void* stream) {
+    EGNN_REQUIRE(layer_events_host != nullptr, "egnn_net_backward_events: NULL event array (use egnn_net_backward)");
+    return net_backward_impl(net, g, params, packed, h_in, x_in, fwd_ws_ptr, gh_out, gx_out, gh_in, gx_in, grad_params, ws,
+                             ws_floats, norm_scope, precision, layer_events_host, stream);
+}
+
+static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const float* params, const float* packed,
+                             const float* h_in, const float* x_in, const float* fwd_ws_ptr, const float* gh_out,
+                             const float* gx_out, float* gh_in, float* gx_in, float* grad_params, float* ws,
+                             int64_t ws_floats, int32_t norm_scope, int32_t precision, void* const* layer_events,
+                             void* stream) {
     if (int rc = egnn_validate_net(net)) return rc;
     if (int rc = egnn_validate_graph(g, true)) return rc;
     EGNN_REQUIRE(params && packed && h_in && x_in && fwd_ws_ptr && gh_out && gx_out && gh_in && gx_in && grad_params && ws,
@@ -555,11 +580,7 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
     const size_t smemE = edge_bwd_smem(*net, bw.TEB);
     const size_t smemN = node_bwd_smem(*net);
     EGNN_REQUIRE(smemE <= 200 * 1024 && smemN <= 200 * 1024, "network too wide for the shared-memory tiling");
-    static bool node_configured = false;
-    if (!node_configured) {
-        EGNN_SMEM_ATTR(egcl_node_bwd, 200 * 1024);
-        node_configured = true;
-    }
+    EGNN_SMEM_ATTR(egcl_node_bwd, 200 * 1024);  // per device (the macro keeps its own per-device flag)
     const bool node_tc = use_tc && tc_node_supported(*net);
     // rows actually used by this call's kernels (the workspace is sized for the larger of the two paths)
     const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : use_tc256 ? egnn_tc_bwd256_rows(E)
@@ -644,6 +665,9 @@ extern "C" int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, c
                                                                       lo.wa, rows_m, m256,
                                                                       grad_params + (size_t)l * lo.total);
         EGNN_CHECK_LAUNCH("reduce_partials_kernel");
+        // layer l's slice of grad_params is final: a communication stream waiting on this event can all-reduce it
+        // while the layers below are still in backward
+        if (layer_events && layer_events[l]) EGNN_CUDA(cudaEventRecord((cudaEvent_t)layer_events[l], st));
     }
     return EGNN_OK;
 }

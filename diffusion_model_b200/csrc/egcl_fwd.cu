@@ -283,6 +283,8 @@ __global__ void __launch_bounds__(256) egcl_xupdate(const float* __restrict__ x,
                                                     const float* __restrict__ D, const int32_t* __restrict__ node_ptr,
                                                     int N, int scope, float* __restrict__ x_out, float* __restrict__ S_out) {
     __shared__ float red[8];
+    pdl_launch_dependents();
+    pdl_wait();  // common.cuh: PDL -- D / dxu come from the node kernel
     const int g = blockIdx.x;
     const int a = node_ptr[g], b = node_ptr[g + 1];
     const int lo = scope == EGNN_NORM_CALL ? 0 : a, hi = scope == EGNN_NORM_CALL ? N : b;
@@ -335,7 +337,7 @@ extern "C" int64_t egnn_forward_workspace_floats(const egnn_net_t* net, int32_t 
 
 int egnn_tc_pack(const egnn_net_t& net, const float* params, float* packed, cudaStream_t st);
 int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
-                         const float* x, float* agg, float* part, float* phi_edge, int precision, cudaStream_t st);
+                         const float* x, float* agg, float* part, float* phi_edge, int precision, cudaStream_t st, bool pdl);
 
 int egnn_tc_node_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
                          const float* h, const float* x, const float* agg, const float* part, const float* phi_edge,
@@ -355,7 +357,9 @@ int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const f
     const bool tensor = precision != EGNN_PREC_FP32;
     const int TE = tensor ? part_tile_for(net) : edge_tile_for(net);
     if (g.E > 0 && tensor) {
-        if (int rc = egnn_tc_edge_forward(net, g, Pk, h, x, ws + w.agg, ws + w.part, ws + w.phi, precision, st)) return rc;
+        // layer 0 is launched normally: its prologue reads the packed weights, which the pack kernels right in front of a
+        // training forward write; every later kernel of the chain may overlap its predecessor's tail (common.cuh: PDL)
+        if (int rc = egnn_tc_edge_forward(net, g, Pk, h, x, ws + w.agg, ws + w.part, ws + w.phi, precision, st, l > 0)) return rc;
     } else if (g.E > 0) {
         EdgeFwdArgs ea{net, g.N, g.E, g.recv, g.send, g.row_ptr, h, x, P, Pk, ws + w.agg, ws + w.part};
         const size_t smem = egnn_edge_fwd_smem(net, TE);
@@ -385,8 +389,8 @@ int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const f
         EGNN_CHECK_LAUNCH("egcl_node_fwd");
     }
     egnn_prof_begin(EGNN_K_XUPDATE, st);
-    egcl_xupdate<<<g.G, 256, 0, st>>>(x, ws + w.dxu + (size_t)l * g.N * 3, ws + w.D, g.node_ptr, g.N, norm_scope, x_out,
-                                      ws + w.S + (size_t)l * g.G);
+    EGNN_CUDA(egnn_launch(egcl_xupdate, dim3(g.G), dim3(256), 0, st, true, x, (const float*)(ws + w.dxu + (size_t)l * g.N * 3),
+                          (const float*)(ws + w.D), g.node_ptr, g.N, norm_scope, x_out, ws + w.S + (size_t)l * g.G));
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("egcl_xupdate");
     return EGNN_OK;

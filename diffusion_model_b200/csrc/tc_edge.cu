@@ -271,6 +271,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::bars);  // [0] GEMM1, [1] GEMM2x, [2] GEMM2m
     uint32_t* slot = reinterpret_cast<uint32_t*>(smem + L::slot);
 
+    pdl_launch_dependents();  // the node kernel behind this one may start its own prologue now (common.cuh: PDL)
     for (int o = tid * 16; o < L::blob_pad; o += NT * 16)
         *reinterpret_cast<uint4*>(smem + o) = __ldg(reinterpret_cast<const uint4*>(a.blob + o));
     if (warp == 0) tc::tmem_alloc(slot, 4 * D);
@@ -353,6 +354,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_fwd(TcFwdArgs a) {
     };
 
     const int nit = blockIdx.x < a.tiles ? (a.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    pdl_wait();  // everything above read only the packed weights; h, x (and agg / part, written below) belong to the chain
     if (tid < 128 && nit > 0) {
         Row g;
         gather_ids(blockIdx.x, g);
@@ -493,11 +495,11 @@ int egnn_tc_pack(const egnn_net_t& net, const float* params, float* packed, cuda
 }
 
 template <int D, int NPASS>
-static int launch_tc_fwd(const TcFwdArgs& a, cudaStream_t st) {
+static int launch_tc_fwd(const TcFwdArgs& a, cudaStream_t st, bool pdl) {
     EGNN_SMEM_ATTR((tc_edge_fwd<D, NPASS>), TcLayout<D>::TOTAL);
     const int grid = a.tiles < 148 ? a.tiles : 148;
     egnn_prof_begin(EGNN_K_TC_EDGE_FWD, st);
-    tc_edge_fwd<D, NPASS><<<grid, 4 * D, TcLayout<D>::TOTAL, st>>>(a);
+    EGNN_CUDA(egnn_launch(tc_edge_fwd<D, NPASS>, dim3(grid), dim3(4 * D), TcLayout<D>::TOTAL, st, pdl, a));
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("tc_edge_fwd");
     return EGNN_OK;
@@ -508,7 +510,7 @@ int egnn_tc_edge_forward256(const egnn_net_t& net, const egnn_graph_t& g, const 
 
 // edge phase of one layer on the tensor cores; fills agg / part exactly like egcl_edge_fwd (segments of d/2 edges)
 int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* packed_layer, const float* h,
-                         const float* x, float* agg, float* part, float* phi_edge, int precision, cudaStream_t st) {
+                         const float* x, float* agg, float* part, float* phi_edge, int precision, cudaStream_t st, bool pdl) {
     EGNN_REQUIRE(tc_fwd_supported(net), "tcgen05 path needs Mh = Ms = Xh in {64,128,256} and 2H+1 <= 16 (got Mh=%d Ms=%d Xh=%d H=%d); "
                  "use precision fp32", net.Mh, net.Ms, net.Xh, net.H);
     if (net.Mh == 256) return egnn_tc_edge_forward256(net, g, packed_layer, h, x, agg, part, phi_edge, precision, st);
@@ -516,8 +518,8 @@ int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const flo
     TcFwdArgs a{net, g.N, g.E, (g.E + 127) / 128, g.recv, g.send, g.row_ptr, h, x,
                 reinterpret_cast<const uint8_t*>(packed_layer + po.tc), agg, part, phi_edge};
     const bool x3 = precision == EGNN_PREC_BF16X3;
-    if (net.Mh == 128) return x3 ? launch_tc_fwd<128, 3>(a, st) : launch_tc_fwd<128, 1>(a, st);
-    return x3 ? launch_tc_fwd<64, 3>(a, st) : launch_tc_fwd<64, 1>(a, st);
+    if (net.Mh == 128) return x3 ? launch_tc_fwd<128, 3>(a, st, pdl) : launch_tc_fwd<128, 1>(a, st, pdl);
+    return x3 ? launch_tc_fwd<64, 3>(a, st, pdl) : launch_tc_fwd<64, 1>(a, st, pdl);
 }
 
 // =====================================================================================================================
@@ -572,6 +574,7 @@ struct TcBwdArgs {
     float* part;     // [gridDim.x][layer param count]
     int nM;          // CTAs [0, nM) take the message branch, [nM, gridDim.x) the coordinate branch
     int g_lo;        // bit 0 / bit 1: the gradient tile gz2 / gz1 is stored as bf16 hi + lo (else hi only: 2 products per MMA)
+    int wg_lo;       // weight-gradient MMAs issue all three split products (small edge counts, see egnn_tc_edge_backward)
 };
 
 struct TcEdgeRow {  // one gathered edge held in registers between its global loads and its shared-memory stores
@@ -586,6 +589,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     constexpr bool FAST = true;  // one-MUFU SiLU / sigmoid (tanh.approx) in both tensor-core modes, see tc_tile.cuh
     constexpr bool LO = NPASS == 3;
     const bool GLO2 = LO && (a.g_lo & 1), GLO1 = LO && (a.g_lo & 2);  // lo halves of the gz2 / gz1 tiles
+    const bool WGLO2 = GLO2 && a.wg_lo, WGLO1 = GLO1 && a.wg_lo;      // third product (gz_lo . x_hi) of the wgrad MMAs
     constexpr int NT = L::NT, NG = L::NG;
     // TMEM columns: z1 -> SiLU'(z1),  z2 | ga1,  db2 (even tiles),  dW2,  db2 (odd tiles),  dW1 + db1,  gu
     constexpr int cA = 0, cB = D, cBias0 = 2 * D, cW2 = 2 * D + 16, cBias1 = 3 * D + 16, cP1 = 3 * D + 32,
@@ -853,8 +857,9 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             // [db2 | dW2] += gz2^T . [u | a1] (even tiles) or [dW2 | db2] += gz2^T . [a1 | u] (odd tiles)
             const TcOperand opB{sb + (buf ? L::a1_hi : L::u0_hi), sb + (buf ? L::a1_lo : L::u0_lo), TS, true};
             // weight gradients sum over every edge of the layer: the gz_lo . a1_hi product only carries the bf16 rounding
-            // of gz (2^-9, unbiased), which averages out over ~1e5 terms -> two products instead of three
-            tc_issue_op<NPASS>(tmem, buf ? cW2 : cBias0, opGmn, opB, 128, D + 16, true, false);
+            // of gz (2^-9, unbiased), which averages out over ~1e5 terms -> two products instead of three; on small
+            // edge lists it does not (measured 1.0e-3 on a bias gradient over 834 edges): there all three are issued
+            tc_issue_op<NPASS>(tmem, buf ? cW2 : cBias0, opGmn, opB, 128, D + 16, true, WGLO2);
             tc::mma_commit(&bars[3]);
         }
         // ---- in the shadow of dgrad: column sums for d wa / d wx3; phi_e of this tile for its deferred outputs
@@ -893,7 +898,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
             tc::mma_commit(&bars[4]);
         } else if (warp == NT / 32 - 2 && tc::elect_one()) {  // independent of the two above: issued by another warp
             tc::fence_after_sync();
-            tc_issue_op<NPASS>(tmem, cP1, opGmn, opUmn, 128, 16, true, false);  // [dW1 | db1] += gz1^T . u
+            tc_issue_op<NPASS>(tmem, cP1, opGmn, opUmn, 128, 16, true, WGLO1);  // [dW1 | db1] += gz1^T . u
             tc::mma_commit(&bars[5]);
         }
     }
@@ -1009,7 +1014,11 @@ int egnn_tc_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const fl
                  "use precision fp32", net.Mh, net.Ms, net.Xh, net.H);
     const PackOff po = pack_off(net);
     TcBwdArgs a{net, g.N, g.E, (g.E + 127) / 128, g.recv, g.send, g.node_graph, h, x,
-                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), gM, gdx, coefS, Gr, Gs, part, 0, 3};
+                reinterpret_cast<const uint8_t*>(packed_layer + po.tc), gM, gdx, coefS, Gr, Gs, part, 0, 3, 0};
+    // Dropping the gz_lo . x_hi product of the weight-gradient MMAs leaves a relative error of 2^-9 / sqrt(E) times the
+    // cancellation of the sum: negligible at 1e5 edges, at the 1e-3 bar below ~1e3.  Under 32768 edges (< 2 tiles per
+    // CTA: the extra MMA pass is free) all three products are issued.
+    a.wg_lo = g.E < 32768 ? 1 : 0;
     {
         static int glo = -1;
         if (glo < 0) {

@@ -289,6 +289,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_fwd(TcNodeFwdArgs a) {
     const int n = n0 + r;
     const bool valid = r < rows;
 
+    pdl_launch_dependents();  // common.cuh: PDL -- the x-update kernel behind this one may be scheduled now
     // weight image: asynchronous copy, waited for just before the MMA
     {
         const uint32_t dst = tc::smem_u32(smem + L::w_hi);
@@ -305,6 +306,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_node_fwd(TcNodeFwdArgs a) {
         tc::fence_mbar_init();
     }
     __syncthreads();
+    pdl_wait();  // the prologue read weights, fp32 parameters and row_ptr only; agg / part / phi come from the edge kernel
 
     // ---- message sums of the tile: D/4 lanes own one row (a float4 each: rows of agg / part / msum are 16-byte
     //      aligned).  Per row up to three partial rows are read under predicates (agg row or tail of the first segment,
@@ -485,7 +487,7 @@ int launch_tc_node_fwd(const TcNodeFwdArgs& a, int grid, cudaStream_t st) {
     constexpr int SMEM = TcNodeLayout<D>::TOTAL;
     EGNN_SMEM_ATTR((tc_node_fwd<D, NPASS>), SMEM);
     egnn_prof_begin(EGNN_K_NODE_FWD, st);
-    tc_node_fwd<D, NPASS><<<grid, 4 * D, SMEM, st>>>(a);
+    EGNN_CUDA(egnn_launch(tc_node_fwd<D, NPASS>, dim3(grid), dim3(4 * D), SMEM, st, true, a));
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("tc_node_fwd");
     return EGNN_OK;

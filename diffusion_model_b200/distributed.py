@@ -82,6 +82,73 @@ def allreduce_gradients(module, group=None):
     return g
 
 
+class OverlappedGradSync:
+    """The training step's only collective -- the all-reduce (sum) of the flat fp32 gradient -- split into a few buckets of
+    whole layers and issued on a communication stream WHILE backward is still running.
+
+    Backward walks the layers L-1 .. 0 and finishes layer l's slice of the flat gradient with its partial-row reduction;
+    ``egnn_net_backward_events`` records a CUDA event there.  Bucket b (layers [lo_b, hi_b)) is all-reduced as soon as the
+    event of its lowest layer has fired, so only the last bucket's all-reduce is exposed; ``finish()`` (called by
+    FlatAdam.step, or by hand before any other optimizer) makes the compute stream wait for it.  Everything is stream
+    ordered -- no host synchronisation -- and capturable in a CUDA graph (the side stream joins the capture through the
+    events).  Needs ``zero_grad(set_to_none=True)`` every step: the per-parameter ``.grad`` tensors must be the views of the
+    flat buffer autograd was handed, not accumulated copies."""
+
+    def __init__(self, module, buckets=3, group=None):
+        import ctypes as C
+        self.module, self.group = module, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        L = module._net.L
+        nb = max(1, min(int(buckets), L))
+        # bucket b = layers [bounds[b], bounds[b+1]); backward reaches the HIGHEST bucket first
+        self.bounds = [round(b * L / nb) for b in range(nb + 1)]
+        self.pending = False
+        self._C = C
+        self._arr = (C.c_void_p * L)()
+        if self.world > 1:
+            dev = module.flat_parameters().device
+            self.comm = torch.cuda.Stream(device=dev)
+            self.events = []
+            for b in range(nb):
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(dev))  # torch creates the cudaEvent_t lazily, at the first record
+                self.events.append(ev)
+                h = ev.cuda_event                          # raw cudaEvent_t (int or ctypes.c_void_p, by torch version)
+                self._arr[self.bounds[b]] = int(getattr(h, "value", h) or 0)  # recorded after layer bounds[b], the bucket's last
+                if not self._arr[self.bounds[b]]:
+                    raise RuntimeError("torch.cuda.Event has no native handle after record()")
+            self.done = torch.cuda.Event()
+        module._grad_sync = self
+
+    def active(self):
+        return self.world > 1
+
+    def event_array(self):
+        return self._arr
+
+    def launch(self, gflat):
+        """Called by the autograd backward right after the backward kernels were enqueued."""
+        L = self.module._net.L
+        P = gflat.numel() // L
+        gflat.record_stream(self.comm)
+        with torch.cuda.stream(self.comm):
+            for b in reversed(range(len(self.events))):
+                self.comm.wait_event(self.events[b])
+                dist.all_reduce(gflat[self.bounds[b] * P:self.bounds[b + 1] * P], op=dist.ReduceOp.SUM, group=self.group)
+            self.done.record(self.comm)
+        self.pending = True
+
+    def finish(self):
+        """Make the current stream wait for the reduced gradient (no-op when nothing is in flight)."""
+        if self.pending:
+            torch.cuda.current_stream(self.comm.device).wait_event(self.done)
+            self.pending = False
+            g, zero_copy = flat_grad_of(self.module)
+            if not zero_copy:
+                raise RuntimeError("OverlappedGradSync needs optimizer.zero_grad(set_to_none=True) before every backward: "
+                                   "the parameter .grad tensors are not the views of the reduced flat buffer")
+
+
 def broadcast_parameters(module, src=0, group=None):
     """Make every rank start from rank `src`'s weights (one broadcast of the flat parameter buffer)."""
     if dist.is_initialized() and dist.get_world_size(group) > 1:
@@ -102,7 +169,11 @@ def sample_sharded(egnn, dp, num_atoms, num_structures, seed=2024, gather=True, 
     dev = torch.device(kw.pop("device", "cuda"))
     gen = torch.Generator(device=dev)
     gen.manual_seed(seed + rank)
-    out = sample_structures(egnn, dp, num_atoms, hi - lo, generator=gen, device=dev, **kw)
+    noises = kw.pop("noises", None)
+    if noises is not None:  # injected draws for the WHOLE job (parity runs): this rank takes the rows of its structures
+        n = int(num_atoms)
+        noises = {k: (v[:, lo * n:hi * n] if k.startswith("step") else v[lo * n:hi * n]) for k, v in noises.items()}
+    out = sample_structures(egnn, dp, num_atoms, hi - lo, generator=gen, device=dev, noises=noises, **kw)
     out["range"] = (lo, hi)
     if gather and world > 1:
         sizes = [shard_range(num_structures, r, world) for r in range(world)]

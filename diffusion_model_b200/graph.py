@@ -117,9 +117,10 @@ class GraphIndex:
         flags = torch.empty(2, dtype=I32, device=dev)
         self.perm = None  # set when the edge list had to be receiver-sorted: kernel edge e == input edge perm[e]
 
-        def prepare(ei):
+        def prepare(ei, stream=None):
             call("egnn_graph_prepare", ptr(ei), N, E, ptr(self.recv), ptr(self.send), ptr(self.row_ptr),
-                 ptr(self.col_ptr), ptr(self.col_edge), ptr(scratch), ptr(flags), st)
+                 ptr(self.col_ptr), ptr(self.col_edge), ptr(scratch), ptr(flags), stream or st)
+        self._prepare, self.flags = prepare, flags
         prepare(edge_index)
         # validation flags: read now (validate=True, one host sync) or copied to pinned memory and checked at the next
         # natural sync point (validate="deferred": training loops, where a host sync per minibatch stalls the pipeline;
@@ -160,13 +161,15 @@ class GraphIndex:
         """Raise if the deferred validation of this edge list failed (no-op once checked)."""
         if self._pending is None:
             if getattr(self, "_bad", None) is not None:
-                raise self._bad  # a malformed list stays malformed (the object may still sit in the cache)
+                raise self._bad  # a malformed list stays malformed for ITS owner (the object may still sit in the cache)
             return True
         host, ev = self._pending
         if not wait and not ev.query():
             return False
         ev.synchronize()
         self._pending = None
+        if self in _PENDING:
+            _PENDING.remove(self)  # reported once: it must never resurface from check_pending() in an unrelated caller
         try:
             self._raise_on(host.tolist())
         except _lib.EgnnError as e:
@@ -177,6 +180,14 @@ class GraphIndex:
     def ref(self):
         return C.byref(self.desc)
 
+    def refresh(self, edge_index):
+        """Rebuild every derived structure IN PLACE from a new edge list of the same shape (same N and E): a few kernel
+        launches, no allocation, capturable in a CUDA graph -- the form a graphed training step replays when the content
+        of its static edge_index buffer changes.  Validation flags land in ``self.flags`` ([unsorted, out of range])."""
+        if tuple(edge_index.shape) != (2, self.E) or edge_index.dtype != torch.int64 or not edge_index.is_contiguous():
+            raise _lib.EgnnError(f"GraphIndex.refresh needs a contiguous int64 [2,{self.E}] edge list")
+        self._prepare(edge_index, stream_ptr(edge_index.device))
+
 
 _CACHE: dict = {}
 _CACHE_MAX = 16
@@ -186,8 +197,10 @@ _PENDING: list = []  # GraphIndex objects whose deferred validation has not been
 def check_pending(wait=True):
     """Report deferred edge-list validation results; wait=False only looks at copies that have already landed."""
     for gi in list(_PENDING):
-        if gi.check(wait=wait):
+        if gi._pending is None:  # already read (and reported) by its owner
             _PENDING.remove(gi)
+            continue
+        gi.check(wait=wait)      # removes itself from the list once its flags have been read, whether it raises or not
 
 
 

@@ -47,10 +47,13 @@ def scatter_flat_grad(module, g):
 
 
 class FlatAdam:
-    def __init__(self, module, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+    def __init__(self, module, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, capturable=False):
+        """capturable=True keeps the step counter in device memory (egnn_adam_step_dev), so that ``step()`` can be captured
+        in a CUDA graph and replayed with the right bias corrections (same meaning as torch.optim.Adam(capturable=True))."""
         self.module, self.lr, self.betas, self.eps, self.weight_decay = module, lr, betas, eps, weight_decay
         self.step_count = 0
         self.exp_avg = self.exp_avg_sq = None
+        self.capturable, self.step_dev = capturable, None
 
     def zero_grad(self, set_to_none=True):
         for p in self.module._flat.params:
@@ -69,18 +72,33 @@ class FlatAdam:
         if self.exp_avg is None or self.exp_avg.numel() != flat.numel() or self.exp_avg.device != flat.device:
             self.exp_avg = torch.zeros_like(flat)
             self.exp_avg_sq = torch.zeros_like(flat)
-        self.step_count += 1
-        call("egnn_adam_step", ptr(flat), ptr(g), ptr(self.exp_avg), ptr(self.exp_avg_sq), flat.numel(), float(self.lr),
-             float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay), self.step_count,
-             float(grad_scale), stream_ptr(flat.device))
+        sync = getattr(self.module, "_grad_sync", None)
+        if sync is not None:
+            sync.finish()  # the update waits for the (overlapped) all-reduce of the last bucket
+        if self.capturable:
+            if self.step_dev is None or self.step_dev.device != flat.device:
+                self.step_dev = torch.full((1,), self.step_count, dtype=torch.int32, device=flat.device)
+            call("egnn_counter_add", ptr(self.step_dev), 1, stream_ptr(flat.device))
+            call("egnn_adam_step_dev", ptr(flat), ptr(g), ptr(self.exp_avg), ptr(self.exp_avg_sq), flat.numel(),
+                 float(self.lr), float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay),
+                 ptr(self.step_dev), float(grad_scale), stream_ptr(flat.device))
+        else:
+            self.step_count += 1
+            call("egnn_adam_step", ptr(flat), ptr(g), ptr(self.exp_avg), ptr(self.exp_avg_sq), flat.numel(), float(self.lr),
+                 float(self.betas[0]), float(self.betas[1]), float(self.eps), float(self.weight_decay), self.step_count,
+                 float(grad_scale), stream_ptr(flat.device))
         bump_param_epoch()  # parameters changed behind autograd's back: every packed weight image is stale
 
     def state_dict(self):
+        if self.capturable and self.step_dev is not None:
+            self.step_count = int(self.step_dev.item())
         return dict(step=self.step_count, exp_avg=self.exp_avg, exp_avg_sq=self.exp_avg_sq, lr=self.lr, betas=self.betas,
                     eps=self.eps, weight_decay=self.weight_decay)
 
     def load_state_dict(self, sd):
         self.step_count, self.exp_avg, self.exp_avg_sq = sd["step"], sd["exp_avg"], sd["exp_avg_sq"]
+        if self.step_dev is not None:
+            self.step_dev.fill_(self.step_count)
         self.lr, self.betas, self.eps, self.weight_decay = sd["lr"], sd["betas"], sd["eps"], sd["weight_decay"]
 
 

@@ -154,6 +154,17 @@ int egnn_net_backward(const egnn_net_t* net, const egnn_graph_t* g, const float*
                       const float* gx_out, float* gh_in, float* gx_in, float* grad_params, float* ws,
                       int64_t ws_floats, int32_t norm_scope, int32_t precision, void* stream);
 
+/* egnn_net_backward that also records one CUDA event per layer: layer_events_host is a HOST array of L cudaEvent_t
+ * (entries may be NULL); event l is recorded on `stream` right after layer l's slice of grad_params
+ * ([l * P_layer, (l+1) * P_layer), P_layer = egnn_param_count / L) is final.  Backward walks l = L-1 .. 0, so a
+ * communication stream that waits on event l can all-reduce that slice over NCCL while the layers below are still in
+ * backward (data-parallel training, SURVEY.md 8e: the gradient all-reduce is the path's only collective). */
+int egnn_net_backward_events(const egnn_net_t* net, const egnn_graph_t* g, const float* params, const float* packed,
+                             const float* h_in, const float* x_in, const float* fwd_ws, const float* gh_out,
+                             const float* gx_out, float* gh_in, float* gx_in, float* grad_params, float* ws,
+                             int64_t ws_floats, int32_t norm_scope, int32_t precision, void* const* layer_events_host,
+                             void* stream);
+
 /* ---- diffusion process: replaces remove_mean (diffusion_x_h.py:5-14), diffuse_zero_to_t (:51-59) inside
  *      diffuse_as_batch (parts/train_per_iretation.py:36-92), the loss tail (:161-169),
  *      calculate_mu + reverse_diffuse_one_step (diffusion_x_h.py:61-90) inside generate (:335-428) ------------- */
@@ -193,6 +204,12 @@ int egnn_counter_add(int32_t* counter, int32_t delta, void* stream);
 int egnn_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                    float beta1, float beta2, float eps, float weight_decay, int32_t step, float grad_scale,
                    void* stream);
+
+/* egnn_adam_step with the 1-based step number read from DEVICE memory (*step_dev): the form a captured CUDA graph of a
+ * training step replays (the host-side counter of egnn_adam_step would freeze the bias corrections at capture time). */
+int egnn_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                       float beta1, float beta2, float eps, float weight_decay, const int32_t* step_dev, float grad_scale,
+                       void* stream);
 
 /* schedulefree.RAdamScheduleFree (parts/def_for_main.py:137-138; `optimizer: RAdamScheduleFree` in parameters.yaml) on flat
  * buffers.  The package is not part of the reference checkout (un-vendored, unpinned dependency): the update is restated

@@ -38,6 +38,7 @@ def make_net(sizes, sd):
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
     net = EquivariantGNN(**sizes)
     net.load_state_dict(sd)
+    net.precision = "fp32"  # these tests pin the CUDA-core fp32 mode; the tcgen05 modes are pinned in test_gpu_tc.py
     return net.to(DEV)
 
 
@@ -104,6 +105,7 @@ def test_backward_edge_cases(lib):
     sizes = egnn_ref.net_sizes(2, 32)
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
     net = EquivariantGNN(**sizes).to(DEV)
+    net.precision = "fp32"
     sd = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
     gen = torch.Generator().manual_seed(1)
     n = 320

@@ -56,8 +56,10 @@ def test_generate_matches_oracle_under_identical_noise(lib, precision, tol):
     T, S, seed = 40, 3, 1234
     net, sd, sizes = _tamed_net(3, 64)
     net.precision = precision
-    dp = E3DiffusionProcess(s=1e-3, power=2.0, num_diffusion_timestep=T)
-    sch = D.Schedule(1e-3, 2.0, T)
+    # s = 0.05: an untrained net's trajectory grows by 1 / alpha_T = 20; with s = 1e-3 it would be 1000 x and every sample
+    # would trip generate()'s `pos > 1000` reject (:434), which redraws for ever -- in the reference's loop as well
+    dp = E3DiffusionProcess(s=0.05, power=2.0, num_diffusion_timestep=T)
+    sch = D.Schedule(0.05, 2.0, T)
     test_data = _dataset(2)
     params = dict(atom_type_size=A, onehot_scaling_factor=1.0, conditional=False, give_exO=False)
     torch.manual_seed(seed)
@@ -146,8 +148,12 @@ def test_eval_epoch_and_train_epoch_return_values_match_oracle(lib, precision):
     random.seed(10); torch.manual_seed(10)
     want, p_ref = _replay_epoch(sd, sizes, loader, sch, T, train=True)
     assert abs(got - want) <= 1e-4 * abs(want), (got, want)
-    for k, p in net.named_parameters():
-        assert float((p.detach().cpu() - p_ref[k].detach()).abs().max()) <= 2e-4, k  # 3 steps of lr 1e-3 (sign-like Adam steps)
+    # 3 Adam steps of lr 1e-3.  Adam's first steps are sign-like (update = lr g / (|g| + eps)): an entry whose gradient is
+    # ~0 can land on the other side under a 1e-5 relative change of the gradients, i.e. 2 lr apart per step.  So: the bulk
+    # within 2e-4, stragglers rare (< 0.5 %) and never further than the 3 x 2 lr a sign flip per step can produce
+    diffs = torch.cat([(p.detach().cpu() - p_ref[k].detach()).abs().flatten() for k, p in net.named_parameters()])
+    assert float((diffs > 2e-4).float().mean()) <= 5e-3, float((diffs > 2e-4).float().mean())
+    assert float(diffs.max()) <= 6.1e-3, float(diffs.max())
 
 
 def test_diffusion_process_loss_and_sample_aliases(lib):
@@ -156,8 +162,8 @@ def test_diffusion_process_loss_and_sample_aliases(lib):
     from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
     T = 30
     net, sd, sizes = _tamed_net(2, 64, seed=3)
-    dp = E3DiffusionProcess(s=1e-3, power=2.0, num_diffusion_timestep=T)
-    sch = D.Schedule(1e-3, 2.0, T)
+    dp = E3DiffusionProcess(s=0.05, power=2.0, num_diffusion_timestep=T)
+    sch = D.Schedule(0.05, 2.0, T)
     b = Batch.from_data_list(_dataset(3))
     gen = torch.Generator().manual_seed(4)
     t = torch.randint(1, T + 1, (3,), generator=gen)
@@ -186,3 +192,89 @@ def test_diffusion_process_loss_and_sample_aliases(lib):
         assert finite and bool(out["finite"][q])
         assert relerr(out["pos"][q], pos) <= 2e-4 and relerr(out["h"][q], hf) <= 2e-4
         assert torch.equal(out["atoms"][q].cpu(), atoms)
+
+
+@pytest.mark.parametrize("use_cuda_graph", [True, False])
+def test_sampler_noise_ring_refills_match_oracle(lib, use_cuda_graph):
+    """The sampler draws its own noise into a ring of `noise_chunk` steps that is refilled between CUDA-graph replays.
+    With T = 40 and a 16-step ring the trajectory crosses three refills; replaying the SAME device generator in the same
+    draw order and feeding those draws to the oracle's one-structure loop must reproduce every structure -- a deterministic
+    check of the noise plumbing (ring indexing, refill timing, graph replay), where a distribution test can only hint."""
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.sampler import sample_structures
+    T, n, S, chunk = 40, 10, 3, 16
+    net, sd, sizes = _tamed_net(2, 64, seed=6)
+    dp = E3DiffusionProcess(s=0.05, power=2.0, num_diffusion_timestep=T)
+    sch = D.Schedule(0.05, 2.0, T)
+    g = torch.Generator(device=DEV)
+    g.manual_seed(77)
+    with torch.no_grad():
+        out = sample_structures(net, dp, n, S, generator=g, noise_chunk=chunk, use_cuda_graph=use_cuda_graph)
+    g.manual_seed(77)
+    N = S * n
+    r = lambda *shape: torch.randn(*shape, device=DEV, generator=g)
+    fill = lambda: (torch.empty(chunk, N, 3, device=DEV).normal_(generator=g), torch.empty(chunk, N, A, device=DEV).normal_(generator=g))
+    init_x, init_h = r(N, 3), r(N, A)
+    if use_cuda_graph:
+        fill()  # the warm-up step before capture consumes one fill
+    fills = [fill() for _ in range((T + chunk - 1) // chunk)]
+    step_x = torch.cat([f[0] for f in fills])[:T]
+    step_h = torch.cat([f[1] for f in fills])[:T]
+    final_x, final_h = r(N, 3), r(N, A)
+    ei = torch.as_tensor(G.fc_edges(n)).long()
+    fwd = lambda e, h, x: egnn_ref.egnn_forward(sd, sizes["L"], e, h, x)
+    for q in range(S):
+        sl = slice(q * n, (q + 1) * n)
+        noises = dict(init_x=init_x[sl].cpu(), init_h=init_h[sl].cpu(), step_x=step_x[:, sl].cpu(), step_h=step_h[:, sl].cpu(),
+                      final_x=final_x[sl].cpu(), final_h=final_h[sl].cpu())
+        with torch.no_grad():
+            pos, hf, atoms, finite = LP.sample_structure(fwd, sch, ei, n, noises)
+        assert finite and bool(out["finite"][q])
+        assert relerr(out["pos"][q], pos) <= 2e-4 and relerr(out["h"][q], hf) <= 2e-4, (q, relerr(out["pos"][q], pos))
+        assert torch.equal(out["atoms"][q].cpu(), atoms)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_graphed_train_step_equals_eager_steps(lib, precision):
+    """train_per_iretation.GraphedTrainStep (one CUDA-graph replay per minibatch: edge-list preparation, diffusion, forward,
+    loss, backward, capturable fused Adam with its step counter on the device) against the same minibatches run eagerly,
+    same t and noise: identical losses, weights equal to the rounding of the bias-correction powers; and constructing the
+    graphed step (its warm-up and capture run real steps) must leave weights and optimizer state untouched."""
+    from diffusion_model_b200.data import Batch
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.optim import FlatAdam
+    from diffusion_model_b200.train_per_iretation import GraphedTrainStep, batch_loss
+    T = 1000
+    dp = E3DiffusionProcess(s=1e-5, power=2.0, num_diffusion_timestep=T)
+    prm = dict(atom_type_size=A)
+    net_e, sd, sizes = _tamed_net(3, 64, seed=8)
+    net_g, _, _ = _tamed_net(3, 64, seed=8)
+    net_e.precision = net_g.precision = precision
+    data = _dataset(3, seed=12)
+    other = _dataset(3, seed=13)   # same shapes (sizes depend on the index only), different content
+    b0 = Batch.from_data_list(data)
+    opt_e, opt_g = FlatAdam(net_e, lr=1e-3), FlatAdam(net_g, lr=1e-3, capturable=True)
+    w0 = net_g.flat_parameters().clone()
+    gs = GraphedTrainStep(net_g, dp, prm, opt_g, b0, static_noise=True)
+    assert torch.equal(net_g.flat_parameters(), w0) and float(opt_g.exp_avg.abs().max()) == 0.0
+    gen = torch.Generator().manual_seed(3)
+    N = b0.pos.shape[0]
+    for it in range(4):
+        b = Batch.from_data_list(data if it % 2 == 0 else other)
+        t = torch.randint(1, T + 1, (3,), generator=gen).tolist()
+        n_pos, n_h = torch.randn(N, 3, generator=gen).to(DEV), torch.randn(N, A, generator=gen).to(DEV)
+        opt_e.zero_grad()
+        loss_e, _, _ = batch_loss(net_e, Batch.from_data_list(data if it % 2 == 0 else other).to(DEV), dp, prm, t=t,
+                                  noise_pos=n_pos, noise_h=n_h)
+        loss_e.backward()
+        opt_e.step()
+        gs.noise_pos.copy_(n_pos)
+        gs.noise_h.copy_(n_h)
+        loss_g = gs.step(b, t=t)       # host minibatch -> staged copy -> static buffers -> replay
+        assert float(loss_g) == float(loss_e) or abs(float(loss_g) - float(loss_e)) <= 1e-6 * abs(float(loss_e)), (it, float(loss_g), float(loss_e))
+        gs.check()
+        d = float((net_g.flat_parameters() - net_e.flat_parameters()).abs().max())
+        assert d <= 2e-6, (it, d)      # lr 1e-3 x relative rounding of 1 - beta^t (device powf vs host powf)
+    assert opt_g.state_dict()["step"] == 4
+    with pytest.raises(Exception):     # a minibatch of another shape cannot go through the captured step
+        gs.step(Batch.from_data_list(_dataset(2, seed=1)))

@@ -38,6 +38,7 @@ def make_net(z):
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
     net = EquivariantGNN(**sizes_of(z))
     net.load_state_dict(state_dict_of(z))
+    net.precision = "fp32"  # these tests pin the CUDA-core fp32 mode; the tcgen05 modes are pinned in test_gpu_tc.py
     return net.to(DEV)
 
 
@@ -92,10 +93,18 @@ def test_graph_index_structures(lib):
     assert np.array_equal(gi.col_ptr.cpu().numpy(), col_ptr)
     assert np.array_equal(gi.col_edge[:E].cpu().numpy(), order)
     assert np.array_equal(gi.node_ptr.cpu().numpy(), b["graph_ptr"])
+    # any edge order is legal for the reference's scatter-add (PyG propagate, :68,:70): an unsorted list is stable-sorted
+    # by receiver on the device, the derived structures are those of the sorted list, `perm` maps kernel edges to input edges
+    rev = ei.flip(1).contiguous()
+    gu = GraphIndex(rev, N)
+    perm = torch.sort(rev[0], stable=True).indices
+    assert torch.equal(gu.perm, perm)
+    srt = rev[:, perm].cpu().numpy()
+    assert np.array_equal(gu.recv[:E].cpu().numpy(), srt[0]) and np.array_equal(gu.send[:E].cpu().numpy(), srt[1])
+    assert np.array_equal(gu.row_ptr.cpu().numpy(), row_ptr)
+    assert np.array_equal(gu.col_ptr.cpu().numpy(), col_ptr)
     with pytest.raises(EgnnError):
-        GraphIndex(ei.flip(1).contiguous(), N)
-    with pytest.raises(EgnnError):
-        GraphIndex(ei + 1000, N)
+        GraphIndex(ei + 1000, N)   # ids outside [0, N) still raise
     gi0 = GraphIndex(torch.zeros(2, 0, dtype=torch.int64, device=DEV), 5)  # empty edge list
     assert gi0.row_ptr.tolist() == [0] * 6
 
@@ -133,6 +142,7 @@ def test_egnn_forward_edge_cases(lib):
     torch.manual_seed(0)
     sz = egnn_ref.net_sizes(2, 32)
     net = EquivariantGNN(**sz).to(DEV)
+    net.precision = "fp32"
     sd = {k: v.detach().cpu() for k, v in net.state_dict().items()}
     gen = torch.Generator().manual_seed(1)
     # (a) isolated nodes + a 300-edge receiver crossing tile boundaries; (b) no edges at all
@@ -250,6 +260,7 @@ def test_trajectory_matches_reference(lib, golden_dir):
     net = EquivariantGNN(**egnn_ref.net_sizes(4, 64))
     net.load_state_dict(sd)
     net = net.to(DEV)
+    net.precision = "fp32"
     n, T = int(zt["n"]), int(zt["T"])
     dp = E3DiffusionProcess(s=float(zt["s"]), power=2.0, num_diffusion_timestep=T)
     noises = LP.make_noises(n, T, 2, torch.Generator().manual_seed(int(zt["seed"])))
@@ -281,9 +292,19 @@ def test_deferred_edge_list_validation(lib):
         with pytest.raises(EgnnError):
             check_pending()
         assert gi._pending is None
-    check_pending()  # nothing left behind
+    check_pending()  # nothing left behind: a reported list never resurfaces in an unrelated caller
+    from diffusion_model_b200.graph import _PENDING
+    assert not _PENDING
+    # the owner of a malformed deferred list keeps getting the error; nobody else does
+    gi = GraphIndex(bad, 3, validate="deferred")
     with pytest.raises(EgnnError):
-        GraphIndex(bad, 3)
+        gi.check()
+    with pytest.raises(EgnnError):
+        gi.check()
+    check_pending()
+    assert GraphIndex(bad, 3).perm is not None   # immediate validation sorts an unsorted list instead of raising
+    with pytest.raises(EgnnError):
+        GraphIndex(oob, 3)
 
 
 def test_xonly_variant_against_oracle(lib, golden_dir):
@@ -309,6 +330,7 @@ def test_xonly_variant_against_oracle(lib, golden_dir):
     net = EquivariantGNN(**egnn_ref.net_sizes(4, 64))
     net.load_state_dict(sd)
     net = net.to(DEV)
+    net.precision = "fp32"
     n, t = 24, 400
     gen = torch.Generator().manual_seed(5)
     pos = D.remove_mean(torch.randn(n, 3, generator=gen) * 2)

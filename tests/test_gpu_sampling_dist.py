@@ -3,106 +3,107 @@ CUDA sampler and by the CPU oracle with the SAME weights and schedule but indepe
 under the reference's structure metrics -- the local RDF around atom 0 (evaluate_RDF.py:39-63, restated and pinned in
 oracle/eval_ref.py) and the angle / bond lengths of atom 0 with two neighbours (CN2_evaluate.py:12-21).
 
-No trained weights ship with the reference, so the net is the tamed random init used by the trajectory fixture; its
-structures have no 2-Angstrom shell, hence R/dR are scaled to the sample's extent and the two NEAREST atoms stand in for
-the radius rule of evaluate_Si-O-Si.py:28-33.  Bars: cosine similarity of the mean RDF curves >= 0.99, two-sample
-Kolmogorov-Smirnov p > 0.01 for distances, angles and bond lengths (seeds are fixed, so the outcome is deterministic).
+The oracle side is a frozen fixture: oracle/make_sampling_golden.py sampled 512 x 24-atom structures (EGNN L=4 d=64, T=250)
+and 24 x 192-atom structures (cfg3's shape, L=6 d=128, T=40) on the CPU and stored them under tests/golden/ -- minutes of
+CPU sampling that buy a large oracle sample without costing every test run.  The test rebuilds the same seeded network
+(checked against the fixture's weight checksum), samples on the GPU, and compares.
+
+What is compared, and why (measured on two independent ORACLE sets, i.e. the metrics' own noise floor):
+  * mean local-RDF curve, cosine similarity >= 0.99 (SURVEY's bar).  R is the 99th percentile of the oracle's distances
+    from atom 0 and the curve has 60 bins: with R taken from the largest distance of the pooled sets (heavy tail) and 480
+    bins the SAME sampler scores only 0.93-0.99 against itself at 128-256 structures per side; at 256 per side with
+    these settings it scores 0.9996.
+  * two-sample Kolmogorov-Smirnov on PER-STRUCTURE statistics (mean and smallest distance from atom 0, radius of gyration,
+    CN2 angle and mean bond length of atom 0 with its two nearest atoms): one value per structure, so the samples are
+    independent.  (The 23 distances of one structure are correlated; pooled, they make a KS test reject the oracle
+    against itself.)  Bar p > 0.01; seeds are fixed, so the outcome is deterministic.
+No trained weights ship with the reference, so the nets are tamed random inits; their structures have no 2-Angstrom shell,
+hence the two NEAREST atoms stand in for the radius rule of evaluate_Si-O-Si.py:28-33.
 """
+import os
+
 import numpy as np
 import pytest
 import torch
 from scipy.stats import ks_2samp
 
-from oracle import diffusion_ref as D
-from oracle import egnn_ref, eval_ref as E, loops_ref as LP
+from oracle import eval_ref as E
+from oracle import make_sampling_golden as MG
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
 
 
-_ORACLE = {}
+def _fixture(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, f"sampling_{name}.npz"))
+    c = MG.SETS[name]
+    sizes, sd = MG.weights_of(c)
+    assert np.allclose(MG.weight_checksum(sd), z["wsum"], rtol=1e-12, atol=0), "rebuilt weights differ from the fixture's"
+    return torch.from_numpy(z["pos"]), c, sizes, sd
 
 
-def _oracle_set(sd, L, sch, n, T, S):
-    if "pos" not in _ORACLE:  # one CPU run serves both precisions
-        gen = torch.Generator().manual_seed(11)
-        per = [LP.make_noises(n, T, 2, gen) for _ in range(S)]
-        cat = {k: torch.cat([p[k] for p in per], dim=1 if k.startswith("step") else 0) for k in per[0]}
-        with torch.no_grad():
-            _ORACLE["pos"], _, _ORACLE["fin"] = LP.sample_structures_batched(sd, L, sch, n, S, cat)
-    return _ORACLE["pos"], _ORACLE["fin"]
-
-
-@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
-def test_sampled_structure_distributions_match_oracle(lib, precision):
+def _gpu_set(c, sizes, sd, S, precision, seed):
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
     from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
     from diffusion_model_b200.sampler import sample_structures
-    torch.manual_seed(0)
-    L, d, n, T, S_cpu, S_gpu = 4, 64, 24, 250, 256, 2048
-    sizes = egnn_ref.net_sizes(L, d)
-    sd = egnn_ref.tame_state_dict(egnn_ref.init_state_dict(**sizes), L)
-    sch = D.Schedule(0.05, 2.0, T)
-    pos_c, fin_c = _oracle_set(sd, L, sch, n, T, S_cpu)
     net = EquivariantGNN(**sizes)
     net.load_state_dict(sd)
     net = net.to(DEV)
     net.precision = precision
-    dp = E3DiffusionProcess(s=0.05, power=2.0, num_diffusion_timestep=T)
+    dp = E3DiffusionProcess(s=c["s"], power=2.0, num_diffusion_timestep=c["T"])
     g = torch.Generator(device=DEV)
-    g.manual_seed(12)
-    out = sample_structures(net, dp, n, S_gpu, generator=g)
-    assert bool(fin_c.all()) and bool(out["finite"].all())
-    pos_g = out["pos"].cpu()
-    extent = float(torch.cat([pos_c.reshape(-1, 3), pos_g.reshape(-1, 3)]).norm(dim=1).max())
-    R = 2.0 * extent
-    dR = R / 480
+    g.manual_seed(seed)
+    out = sample_structures(net, dp, c["n"], S, generator=g)
+    assert bool(out["finite"].all())
+    return out["pos"].cpu()
+
+
+def _d0(s):
+    return (s[:, 1:] - s[:, :1]).norm(dim=2)  # [S, n-1] distances from atom 0
+
+
+def _per_structure(s):
+    d = _d0(s)
+    rg = (s - s.mean(dim=1, keepdim=True)).norm(dim=2).pow(2).mean(dim=1).sqrt()
+    angles, bonds = [], []
+    for p in s:
+        tri = p[E.two_nearest(p)]
+        angles.append(E.angle_cn2(tri))
+        b1, b2 = E.bond_lengths_cn2(tri)
+        bonds.append(0.5 * (b1 + b2))
+    return dict(mean_dist=d.mean(dim=1).numpy(), min_dist=d.min(dim=1).values.numpy(), radius_of_gyration=rg.numpy(),
+                cn2_angle=np.array(angles), cn2_bond=np.array(bonds))
+
+
+def _compare(pos_c, pos_g, nbins, tag):
+    R = float(torch.quantile(_d0(pos_c).flatten(), 0.99))
+    dR = R / nbins
     sc = E.structure_set_stats(list(pos_c), R, dR)
     sg = E.structure_set_stats(list(pos_g), R, dR)
     cos = E.cos_similarity(sc["rdf"], sg["rdf"])
     wd = E.wasserstein(sc["rdf"], sg["rdf"])
-    p_d = ks_2samp(sc["dists"], sg["dists"]).pvalue
-    p_a = ks_2samp(sc["angles"], sg["angles"]).pvalue
-    p_b = ks_2samp(sc["bonds"], sg["bonds"]).pvalue
-    print(f"{precision}: RDF cos-sim {cos:.4f} wasserstein {wd:.3e} KS p: dist {p_d:.3f} angle {p_a:.3f} bond {p_b:.3f}")
+    pc, pg = _per_structure(pos_c), _per_structure(pos_g)
+    ps = {k: float(ks_2samp(pc[k], pg[k]).pvalue) for k in pc}
+    print(f"{tag}: {len(pos_c)} oracle vs {len(pos_g)} CUDA structures | RDF cos-sim {cos:.4f} wasserstein {wd:.3e} | KS p "
+          + " ".join(f"{k} {v:.3f}" for k, v in ps.items()))
+    return cos, ps
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_sampled_structure_distributions_match_oracle(lib, golden_dir, precision):
+    pos_c, c, sizes, sd = _fixture(golden_dir, "set24")
+    pos_g = _gpu_set(c, sizes, sd, 2048, precision, seed=12)
+    cos, ps = _compare(pos_c, pos_g, 60, f"24 atoms T={c['T']} {precision}")
     assert cos >= 0.99, cos
-    assert min(p_d, p_a, p_b) > 0.01, (p_d, p_a, p_b)
+    assert min(ps.values()) > 0.01, ps
 
 
-def test_sampled_distributions_at_cfg3_shape(lib):
+def test_sampled_distributions_at_cfg3_shape(lib, golden_dir):
     """The same check on cfg3's shape -- 192-atom fully connected structures, EGNN L=6 d=128 (the sampling bench's net) --
-    with a short schedule (T = 40) so that the CPU oracle finishes 12 structures in about a minute.  191 distances from
-    atom 0 per structure: the local-RDF curves and the distance distributions of the two samplers must agree."""
-    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
-    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
-    from diffusion_model_b200.sampler import sample_structures
-    torch.manual_seed(1)
-    L, d, n, T, S_cpu, S_gpu = 6, 128, 192, 40, 12, 192
-    sizes = egnn_ref.net_sizes(L, d)
-    sd = egnn_ref.tame_state_dict(egnn_ref.init_state_dict(**sizes), L)
-    sch = D.Schedule(0.05, 2.0, T)
-    gen = torch.Generator().manual_seed(21)
-    per = [LP.make_noises(n, T, 2, gen) for _ in range(S_cpu)]
-    cat = {k: torch.cat([p[k] for p in per], dim=1 if k.startswith("step") else 0) for k in per[0]}
-    with torch.no_grad():
-        pos_c, _, fin_c = LP.sample_structures_batched(sd, L, sch, n, S_cpu, cat)
-    net = EquivariantGNN(**sizes)
-    net.load_state_dict(sd)
-    net = net.to(DEV)
-    net.precision = "bf16x3"
-    dp = E3DiffusionProcess(s=0.05, power=2.0, num_diffusion_timestep=T)
-    g = torch.Generator(device=DEV)
-    g.manual_seed(22)
-    out = sample_structures(net, dp, n, S_gpu, generator=g)
-    assert bool(fin_c.all()) and bool(out["finite"].all())
-    pos_g = out["pos"].cpu()
-    extent = float(torch.cat([pos_c.reshape(-1, 3), pos_g.reshape(-1, 3)]).norm(dim=1).max())
-    R = 2.0 * extent
-    dR = R / 240
-    sc = E.structure_set_stats(list(pos_c), R, dR)
-    sg = E.structure_set_stats(list(pos_g), R, dR)
-    cos = E.cos_similarity(sc["rdf"], sg["rdf"])
-    p_d = ks_2samp(sc["dists"], sg["dists"]).pvalue
-    print(f"cfg3 shape (192 atoms, L=6, d=128, T={T}): RDF cos-sim {cos:.4f} KS p dist {p_d:.3f}")
+    with a short schedule (T = 40).  24 oracle structures: 4 584 distances for the RDF curve (30 bins), and per-structure
+    statistics of 24 against 192."""
+    pos_c, c, sizes, sd = _fixture(golden_dir, "set192")
+    pos_g = _gpu_set(c, sizes, sd, 192, "bf16x3", seed=22)
+    cos, ps = _compare(pos_c, pos_g, 30, f"192 atoms T={c['T']} bf16x3")
     assert cos >= 0.99, cos
-    assert p_d > 0.01, p_d
+    assert min(ps.values()) > 0.01, ps

@@ -202,3 +202,19 @@ def test_radam_schedulefree_restatement_invariants():
     assert float((p - target).abs().max()) < 0.15 < float(target.abs().max())  # from 2.1 down, 400 Adam-sized steps
     opt.train(); opt.eval()
     assert torch.allclose(p, x_avg, atol=1e-5)
+
+
+def test_default_precision_resolution():
+    """host logic of the drop-in: swapping the imports alone selects the tcgen05 bf16x3 mode wherever the tensor-core
+    kernels cover the shape (same 1e-4 bar as the fp32 mode), and the CUDA-core fp32 mode otherwise -- never 'bf16'."""
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EGCL, EquivariantGNN
+    for d in (64, 128, 256):
+        assert EquivariantGNN(**egnn_ref.net_sizes(2, d)).resolved_precision() == "bf16x3"
+    assert EquivariantGNN(**egnn_ref.net_sizes(1, 96)).resolved_precision() == "fp32"            # no tile for d = 96
+    assert EquivariantGNN(**egnn_ref.net_sizes(1, 64, H=36)).resolved_precision() == "fp32"      # K0 = 73 > 16
+    sz = egnn_ref.net_sizes(1, 128)
+    sz.pop("L")
+    layer = EGCL(**sz)
+    assert layer.precision == "auto" and layer.resolved_precision() == "bf16x3"
+    layer.precision = "fp32"
+    assert layer.resolved_precision() == "fp32"
