@@ -693,13 +693,14 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     const int tstride = branch ? (int)gridDim.x - a.nM : a.nM;
     const int tile0 = branch ? (int)blockIdx.x - a.nM : (int)blockIdx.x;
     const int nit = tile0 < a.tiles ? (a.tiles - tile0 + tstride - 1) / tstride : 0;
-    auto edge_outputs = [&](int e0p, int nrowsp, int bufp, float phi) {  // cg == 0 warps: this branch's per-edge outputs
+    // this branch's per-edge outputs of a finished tile.  Run by the cg == 1 warps (same TMEM lanes as cg == 0), so that they
+    // proceed NEXT TO the cg == 0 warps' gather of the following tile instead of behind it; the row's record (rr, i) is read
+    // from shared memory by the caller before the gather store may overwrite that buffer
+    auto edge_outputs = [&](int e0p, int nrowsp, const float4 rr, const int i, float phi) {
         float gu[32];
         tc::tmem_ld32(trow + cGU, gu);
         if (r < nrowsp) {
             const size_t e = (size_t)(e0p + r);
-            const float4 rr = sR[bufp * 128 + r];
-            const int i = sI[bufp * 128 + r];
             float gd = 0.f;
 #pragma unroll
             for (int k = 0; k < 15; ++k) {
@@ -766,13 +767,20 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         // ---- in the shadow of GEMM2: next tile's gather loads, previous tile's per-edge outputs
         TcEdgeRow gnext;
         if (tid < 128 && has_next) gather_load(tile + tstride, gnext);
-        if (it > 0 && cg == 0) {
+        if (it > 0 && cg == 1) {
+            const float4 rrp = sR[(buf ^ 1) * 128 + r];
+            const int ip = sI[(buf ^ 1) * 128 + r];
+            // records read: the cg == 0 warp of this row quadrant may now overwrite the buffer (named barrier 5 + q)
+            if (has_next) asm volatile("bar.arrive %0, %1;" ::"r"(5 + q), "r"(64) : "memory");
             ok = tc::mbar_wait(&bars[4], phase ^ 1) && ok;
             tc::fence_after_sync();
-            edge_outputs((tile - tstride) * 128, min(128, a.E - (tile - tstride) * 128), buf ^ 1, phi_prev);
+            edge_outputs((tile - tstride) * 128, min(128, a.E - (tile - tstride) * 128), rrp, ip, phi_prev);
         }
         if (tid < 128 && has_next) {  // still in the shadow: the next tile's U rows (the previous dW1 MMA has left U[buf^1])
-            if (it > 0) ok = tc::mbar_wait(&bars[5], phase ^ 1) && ok;
+            if (it > 0) {
+                ok = tc::mbar_wait(&bars[5], phase ^ 1) && ok;
+                asm volatile("bar.sync %0, %1;" ::"r"(5 + q), "r"(64) : "memory");
+            }
             tc::fence_after_sync();
             gather_store(buf ^ 1, gnext);
         }
@@ -865,7 +873,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         // ---- in the shadow of dgrad: column sums for d wa / d wx3; phi_e of this tile for its deferred outputs
         warp_colsum32(cs, lane);
         accv += cs[0];
-        if (branch == 1 && cg == 0) {
+        if (branch == 1 && cg == 1) {
             float phi = vec[3 * D];
 #pragma unroll
             for (int k = 0; k < NG; ++k) phi += rowA[k * 128 + r];
@@ -905,10 +913,10 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     if (nit > 0) {
         const int lt = tile0 + (nit - 1) * tstride;
         const uint32_t lp = (uint32_t)((nit - 1) & 1);
-        if (cg == 0) {
+        if (cg == 1) {
             ok = tc::mbar_wait(&bars[4], lp) && ok;
             tc::fence_after_sync();
-            edge_outputs(lt * 128, min(128, a.E - lt * 128), (nit - 1) & 1, phi_prev);
+            edge_outputs(lt * 128, min(128, a.E - lt * 128), sR[((nit - 1) & 1) * 128 + r], sI[((nit - 1) & 1) * 128 + r], phi_prev);
         }
         ok = tc::mbar_wait(&bars[5], lp) && ok;
     }
