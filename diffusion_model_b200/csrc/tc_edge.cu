@@ -591,6 +591,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     const bool GLO2 = LO && (a.g_lo & 1), GLO1 = LO && (a.g_lo & 2);  // lo halves of the gz2 / gz1 tiles
     const bool WGLO2 = GLO2 && a.wg_lo, WGLO1 = GLO1 && a.wg_lo;      // third product (gz_lo . x_hi) of the wgrad MMAs
     constexpr int NT = L::NT, NG = L::NG;
+    constexpr int OUTW = NG >= 3 ? 2 : 1;  // warp groups that write the per-edge outputs: cg 1 (Gr) and cg 2 (Gs) at d = 128
     // TMEM columns: z1 -> SiLU'(z1),  z2 | ga1,  db2 (even tiles),  dW2,  db2 (odd tiles),  dW1 + db1,  gu
     constexpr int cA = 0, cB = D, cBias0 = 2 * D, cW2 = 2 * D + 16, cBias1 = 3 * D + 16, cP1 = 3 * D + 32,
                   cGU = 3 * D + 48;
@@ -696,16 +697,18 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     // this branch's per-edge outputs of a finished tile.  Run by the cg == 1 warps (same TMEM lanes as cg == 0), so that they
     // proceed NEXT TO the cg == 0 warps' gather of the following tile instead of behind it; the row's record (rr, i) is read
     // from shared memory by the caller before the gather store may overwrite that buffer
-    auto edge_outputs = [&](int e0p, int nrowsp, const float4 rr, const int i, float phi) {
+    // part: 0 = both slabs, 1 = the receiver slab Gr only, 2 = the sender slab Gs only (d = 128: cg == 1 / cg == 2 warps)
+    auto edge_outputs = [&](int e0p, int nrowsp, const float4 rr, const int i, float phi, int part) {
         float gu[32];
         tc::tmem_ld32(trow + cGU, gu);
+        const bool doR = part != 2, doS = part != 1;
         if (r < nrowsp) {
             const size_t e = (size_t)(e0p + r);
             float gd = 0.f;
 #pragma unroll
             for (int k = 0; k < 15; ++k) {
-                if (k < H) Grb[e * W + k] = gu[k];
-                else if (k < 2 * H) Gsb[e * W + (k - H)] = gu[k];
+                if (k < H) { if (doR) Grb[e * W + k] = gu[k]; }
+                else if (k < 2 * H) { if (doS) Gsb[e * W + (k - H)] = gu[k]; }
                 else if (k == 2 * H) gd = gu[k];
             }
             float cr = 2.f * gd;
@@ -717,12 +720,16 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
                 gx2 = a.gdx[(size_t)i * 3 + 2];
             }
             const float g0 = fmaf(gx0, phi, cr * rr.x), g1 = fmaf(gx1, phi, cr * rr.y), g2 = fmaf(gx2, phi, cr * rr.z);
-            Grb[e * W + H + 0] = g0;
-            Grb[e * W + H + 1] = g1;
-            Grb[e * W + H + 2] = g2;
-            Gsb[e * W + H + 0] = -g0;
-            Gsb[e * W + H + 1] = -g1;
-            Gsb[e * W + H + 2] = -g2;
+            if (doR) {
+                Grb[e * W + H + 0] = g0;
+                Grb[e * W + H + 1] = g1;
+                Grb[e * W + H + 2] = g2;
+            }
+            if (doS) {
+                Gsb[e * W + H + 0] = -g0;
+                Gsb[e * W + H + 1] = -g1;
+                Gsb[e * W + H + 2] = -g2;
+            }
         }
     };
 
@@ -767,19 +774,19 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         // ---- in the shadow of GEMM2: next tile's gather loads, previous tile's per-edge outputs
         TcEdgeRow gnext;
         if (tid < 128 && has_next) gather_load(tile + tstride, gnext);
-        if (it > 0 && cg == 1) {
+        if (it > 0 && cg >= 1 && cg <= OUTW) {
             const float4 rrp = sR[(buf ^ 1) * 128 + r];
             const int ip = sI[(buf ^ 1) * 128 + r];
             // records read: the cg == 0 warp of this row quadrant may now overwrite the buffer (named barrier 5 + q)
-            if (has_next) asm volatile("bar.arrive %0, %1;" ::"r"(5 + q), "r"(64) : "memory");
+            if (has_next) asm volatile("bar.arrive %0, %1;" ::"r"(5 + q), "r"(32 * (1 + OUTW)) : "memory");
             ok = tc::mbar_wait(&bars[4], phase ^ 1) && ok;
             tc::fence_after_sync();
-            edge_outputs((tile - tstride) * 128, min(128, a.E - (tile - tstride) * 128), rrp, ip, phi_prev);
+            edge_outputs((tile - tstride) * 128, min(128, a.E - (tile - tstride) * 128), rrp, ip, phi_prev, OUTW == 1 ? 0 : cg);
         }
         if (tid < 128 && has_next) {  // still in the shadow: the next tile's U rows (the previous dW1 MMA has left U[buf^1])
             if (it > 0) {
                 ok = tc::mbar_wait(&bars[5], phase ^ 1) && ok;
-                asm volatile("bar.sync %0, %1;" ::"r"(5 + q), "r"(64) : "memory");
+                asm volatile("bar.sync %0, %1;" ::"r"(5 + q), "r"(32 * (1 + OUTW)) : "memory");
             }
             tc::fence_after_sync();
             gather_store(buf ^ 1, gnext);
@@ -873,7 +880,7 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
         // ---- in the shadow of dgrad: column sums for d wa / d wx3; phi_e of this tile for its deferred outputs
         warp_colsum32(cs, lane);
         accv += cs[0];
-        if (branch == 1 && cg == 1) {
+        if (branch == 1 && cg >= 1 && cg <= OUTW) {
             float phi = vec[3 * D];
 #pragma unroll
             for (int k = 0; k < NG; ++k) phi += rowA[k * 128 + r];
@@ -913,10 +920,11 @@ __global__ void __launch_bounds__(4 * D, 1) tc_edge_bwd(TcBwdArgs a) {
     if (nit > 0) {
         const int lt = tile0 + (nit - 1) * tstride;
         const uint32_t lp = (uint32_t)((nit - 1) & 1);
-        if (cg == 1) {
+        if (cg >= 1 && cg <= OUTW) {
             ok = tc::mbar_wait(&bars[4], lp) && ok;
             tc::fence_after_sync();
-            edge_outputs(lt * 128, min(128, a.E - lt * 128), sR[((nit - 1) & 1) * 128 + r], sI[((nit - 1) & 1) * 128 + r], phi_prev);
+            edge_outputs(lt * 128, min(128, a.E - lt * 128), sR[((nit - 1) & 1) * 128 + r], sI[((nit - 1) & 1) * 128 + r], phi_prev,
+                         OUTW == 1 ? 0 : cg);
         }
         ok = tc::mbar_wait(&bars[5], lp) && ok;
     }
