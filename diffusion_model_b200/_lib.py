@@ -104,8 +104,22 @@ def check(rc, what=""):
         raise EgnnError(f"{what or 'libegnn_b200'} failed (status {rc}): {msg}")
 
 
+_arg_device = [None]  # CUDA device index of the last tensor handed to ptr(): the device the next call must run on
+
+
 def call(name, *args):
-    check(getattr(load(), name)(*args), name)
+    """Invoke a C-ABI entry point and raise on a non-zero status.  The library launches on the CURRENT device, so when
+    the tensors of this call (seen by ptr() while the arguments were built) live on another GPU of the process, that
+    device is made current for the duration of the call -- per-device kernel attributes and the static scratch address
+    of egnn_graph_prepare_noalloc are resolved per device inside the library."""
+    fn = getattr(load(), name)
+    dev, _arg_device[0] = _arg_device[0], None
+    if dev is not None and dev != torch.cuda.current_device():
+        with torch.cuda.device(dev):
+            rc = fn(*args)
+    else:
+        rc = fn(*args)
+    check(rc, name)
 
 
 def stream_ptr(device=None):
@@ -124,4 +138,5 @@ def ptr(t, dtype=None, allow_none=False):
         raise EgnnError("libegnn_b200 needs contiguous tensors")
     if dtype is not None and t.dtype != dtype:
         raise EgnnError(f"expected dtype {dtype}, got {t.dtype}")
+    _arg_device[0] = t.device.index  # call() makes this device current (ptr() may also be used for raw ctypes calls)
     return C.c_void_p(t.data_ptr())
