@@ -16,7 +16,9 @@
 
 namespace {
 
-constexpr int TNB = 32;  // nodes per tile of the node backward kernel
+// nodes per tile of the FFMA node backward kernel: 32 where its shared memory fits (every BASELINE width), 16 or 8 for wide
+// mlp_h layers (parameters.yaml: h_hidden_size 1024 needs 306 KB at 32 nodes) -- template parameter of egcl_node_bwd
+constexpr int TNB_MAX = 32;
 
 // one CTA per graph.  Whole-call scope: every CTA reduces its own graph's share of sum_i gx'_i . dxu_i, the last CTA to
 // finish (integer ticket, self-resetting) adds the per-graph shares in graph order -> same bits on every run.
@@ -64,6 +66,7 @@ struct NodeBwdArgs {
     float* part;            // [gridDim.x][layer param count] private rows
 };
 
+template <int TNB>
 __global__ void __launch_bounds__(256, 2) egcl_node_bwd(NodeBwdArgs a) {
     extern __shared__ __align__(16) float smem[];
     const egnn_net_t& net = a.net;
@@ -457,11 +460,18 @@ constexpr int kNumSM = 148;  // B200
 static inline bool tc_bwd256_supported(const egnn_net_t& n) { return n.Mh == 256 && tc_fwd_supported(n); }
 
 // FFMA node backward: shared memory of one CTA, and its grid = private partial rows (two CTAs per SM when they fit)
-inline size_t node_bwd_smem(const egnn_net_t& n) {
-    return sizeof(float) * (size_t)TNB * ((round4(n.H + n.Ms) + 4) + 2 * (round4(n.Hh) + 4) + (round4(n.H) + 4));
+inline size_t node_bwd_smem_for(const egnn_net_t& n, int tnb) {
+    return sizeof(float) * (size_t)tnb * ((round4(n.H + n.Ms) + 4) + 2 * (round4(n.Hh) + 4) + (round4(n.H) + 4));
 }
+inline int node_tile_bwd(const egnn_net_t& n) {  // largest node tile whose shared memory fits; 8 even if that does not
+    int tnb = TNB_MAX;
+    while (tnb > 8 && node_bwd_smem_for(n, tnb) > 200 * 1024) tnb >>= 1;
+    return tnb;
+}
+inline size_t node_bwd_smem(const egnn_net_t& n) { return node_bwd_smem_for(n, node_tile_bwd(n)); }
 inline int node_bwd_rows(const egnn_net_t& n, int64_t N) {
-    const int64_t tilesN = (N + TNB - 1) / TNB;
+    const int tnb = node_tile_bwd(n);
+    const int64_t tilesN = (N + tnb - 1) / tnb;
     const int cap = 2 * (node_bwd_smem(n) + 1024) <= 227 * 1024 ? 2 * kNumSM : kNumSM;
     return (int)(tilesN < cap ? tilesN : cap);
 }
@@ -580,7 +590,9 @@ static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const
     const size_t smemE = edge_bwd_smem(*net, bw.TEB);
     const size_t smemN = node_bwd_smem(*net);
     EGNN_REQUIRE(smemE <= 200 * 1024 && smemN <= 200 * 1024, "network too wide for the shared-memory tiling");
-    EGNN_SMEM_ATTR(egcl_node_bwd, 200 * 1024);  // per device (the macro keeps its own per-device flag)
+    EGNN_SMEM_ATTR(egcl_node_bwd<32>, 200 * 1024);  // per device (the macro keeps its own per-device flag)
+    EGNN_SMEM_ATTR(egcl_node_bwd<16>, 200 * 1024);
+    EGNN_SMEM_ATTR(egcl_node_bwd<8>, 200 * 1024);
     const bool node_tc = use_tc && tc_node_supported(*net);
     // rows actually used by this call's kernels (the workspace is sized for the larger of the two paths)
     const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : use_tc256 ? egnn_tc_bwd256_rows(E)
@@ -623,10 +635,13 @@ static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const
                                                precision, st))
                 return rc;
         } else {
-            NodeBwdArgs na{*net, N, (N + TNB - 1) / TNB, hl, fwd_ws_ptr + fw.msum + (size_t)l * N * net->Ms, P, Pk, gho,
+            const int tnb = node_tile_bwd(*net);
+            NodeBwdArgs na{*net, N, (N + tnb - 1) / tnb, hl, fwd_ws_ptr + fw.msum + (size_t)l * N * net->Ms, P, Pk, gho,
                            ws + bw.gh_node, ws + bw.gM, ws + bw.part + (size_t)rowsE * lo.total};
             egnn_prof_begin(EGNN_K_NODE_BWD, st);
-            egcl_node_bwd<<<rowsN, 256, smemN, st>>>(na);
+            if (tnb == 32) egcl_node_bwd<32><<<rowsN, 256, smemN, st>>>(na);
+            else if (tnb == 16) egcl_node_bwd<16><<<rowsN, 256, smemN, st>>>(na);
+            else egcl_node_bwd<8><<<rowsN, 256, smemN, st>>>(na);
             egnn_prof_end(st);
             EGNN_CHECK_LAUNCH("egcl_node_bwd");
         }

@@ -147,3 +147,46 @@ def test_conditional_sampler_against_oracle(lib, golden_dir):
         assert bool(out["finite"][0])
         assert relerr(out["pos"][0], pos) < 5e-4 and relerr(out["h"][0], hf) < 5e-4
         assert np.array_equal(out["atoms"][0].cpu().numpy(), atoms.numpy())
+
+
+@pytest.mark.gpu
+def test_parameters_yaml_widths_forward_and_gradients(lib):
+    """The only configuration the reference ships (parameters.yaml through main.py:102-121): h = [2 atom types | 32
+    compressed spectrum | exO | t] = 36 columns, K0 = 73, m_hidden = x_hidden = h_hidden = 1024, m_size = 256.  These widths
+    have no tcgen05 tile (2H+1 > 16, Mh != Ms), so `precision = 'auto'` must resolve to the CUDA-core fp32 kernels; two layers
+    of that network on two fully connected graphs against the oracle: every layer 1e-4, every gradient tensor 1e-3."""
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    from diffusion_model_b200.graph import build_edges_fc
+    H, L = 2 + 32 + 1 + 1, 2
+    sizes = dict(L=L, m_input=2 * H + 1, m_hidden=1024, m_output=256, x_input=2 * H + 1, x_hidden=1024, x_output=1,
+                 h_input=H + 256, h_hidden=1024, h_output=H)
+    torch.manual_seed(3)
+    sd = egnn_ref.tame_state_dict(egnn_ref.init_state_dict(**sizes), L)
+    net = EquivariantGNN(**sizes)
+    net.load_state_dict(sd)
+    net = net.to("cuda")
+    assert net.precision == "auto" and net.resolved_precision() == "fp32"
+    gen = torch.Generator().manual_seed(4)
+    n = [30, 22]
+    N = sum(n)
+    h0, x0 = torch.randn(N, H, generator=gen), 2.0 * torch.randn(N, 3, generator=gen)
+    ei = build_edges_fc(n, "cuda")
+    sdg = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    hc, xc = h0.clone().requires_grad_(True), x0.clone().requires_grad_(True)
+    hr, xr, layers = egnn_ref.egnn_forward(sdg, L, ei.cpu(), hc, xc, return_layers=True)
+    (hr.square().sum() + (xr - xc).square().sum()).backward()
+    # per layer, on the oracle's own layer input
+    h, x = h0, x0
+    with torch.no_grad():
+        for l, (hl, xl) in enumerate(layers):
+            ho, xo = net.egcl_list[l](ei, h.to("cuda"), x.to("cuda"))
+            assert relerr(ho, hl.detach()) <= 1e-4 and relerr(xo, xl.detach()) <= 1e-4, (l, relerr(ho, hl.detach()), relerr(xo, xl.detach()))
+            h, x = hl.detach(), xl.detach()
+    hd, xd = h0.to("cuda").requires_grad_(True), x0.to("cuda").requires_grad_(True)
+    ho, xo = net(ei, hd, xd)
+    (ho.square().sum() + (xo - xd).square().sum()).backward()
+    errs = {k: relerr(p.grad, sdg[k].grad) for k, p in net.named_parameters()}
+    errs["h_in"], errs["x_in"] = relerr(hd.grad, hc.grad), relerr(xd.grad, xc.grad)
+    worst = max(errs, key=errs.get)
+    print(f"parameters.yaml widths (K0=73, 1024/256), fp32 kernels: worst gradient {worst} {errs[worst]:.2e}")
+    assert errs[worst] <= 1e-3, sorted(errs.items(), key=lambda kv: -kv[1])[:5]

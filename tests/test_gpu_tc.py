@@ -157,7 +157,9 @@ def _grad_errors(name, precision, scope="call"):
 
 
 @pytest.mark.parametrize("name", ["cfg1", "cfg2"])
-@pytest.mark.parametrize("precision,tol", [("bf16x3", 1e-3), ("bf16", 2.5e-1)])  # bf16: stated loose bound
+# bf16 (ONE tcgen05 product per MMA, no lo halves) is the stated looser mode: its gradient bound is what was measured on
+# B200 -- worst tensor 3.1e-2 (cfg1), 9.9e-2 (cfg2), 9.4e-2 (d = 256) -- with 1.5x headroom, not a round number
+@pytest.mark.parametrize("precision,tol", [("bf16x3", 1e-3), ("bf16", 1.5e-1)])
 def test_tc_backward_matches_reference_grads(lib, name, precision, tol):
     errs, g1 = _grad_errors(name, precision)
     worst = max(errs, key=errs.get)
@@ -167,7 +169,7 @@ def test_tc_backward_matches_reference_grads(lib, name, precision, tol):
     assert all(torch.equal(a, b) for a, b in zip(g1, g2))  # deterministic (no atomics)
 
 
-@pytest.mark.parametrize("precision,tol", [("bf16x3", 1e-3), ("bf16", 2.5e-1)])
+@pytest.mark.parametrize("precision,tol", [("bf16x3", 1e-3), ("bf16", 1.5e-1)])
 def test_tc_backward_d256(lib, precision, tol):
     """d = 256 (cfg4 net): the two-kernel tcgen05 backward of tc_edge256_bwd.cu (tile images + split-K wgrad GEMM)"""
     errs, g1 = _grad_errors("cfg4", precision)
