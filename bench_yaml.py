@@ -1,0 +1,145 @@
+#!/usr/bin/env python
+"""Training step of the ONLY configuration the reference ships (parameters.yaml through main.py:102-121): conditional model,
+h = [2 atom types | 32 compressed spectrum | exO | t] (H = 36, K0 = 73), L = 5, m_hidden = x_hidden = h_hidden = 1024,
+m_size = 256, SpectrumCompressor 200 -> 150 -> 100 -> 50 -> 32, batch_size 1, RAdamScheduleFree, lr 1e-5.
+
+These widths have no tcgen05 tile (2H+1 > 16, Mh != Ms, d = 1024): the step runs on the CUDA-core fp32 kernels
+(`precision = 'auto'` resolves to 'fp32').  Prints ONE JSON line: graph-steps/s of the eps-prediction training step on a
+fully connected graph of `--atoms` atoms (the reference's datasets hold clusters of <= ~120 atoms) for the GPU path and for
+the CPU oracle on the same step.  A parity-config timing for profiles/, not the contract bench line (bench.py).
+
+    python bench_yaml.py [--atoms 96] [--batch 1] [--steps 10] [--skip-cpu]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+YAML = dict(L=5, atom_type_size=2, compressed_spectrum_size=32, spectrum_size=200, compressor_hidden_dim=[150, 100, 50], exO_size=1,
+            t_size=1, d_size=1, m_size=256, m_hidden_size=1024, h_hidden_size=1024, x_hidden_size=1024, T=1000, s=1e-5, power=2.0, lr=1e-5)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--atoms", type=int, default=96)
+    ap.add_argument("--batch", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--skip-cpu", action="store_true")
+    args = ap.parse_args()
+    import bench
+    from diffusion_model_b200 import _lib
+    from diffusion_model_b200.DataPreprocessor import SpectrumCompressor
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    from diffusion_model_b200.data import Batch, Data
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.graph import build_edges_fc
+    from diffusion_model_b200.optim import RAdamScheduleFree
+    from diffusion_model_b200.train_per_iretation import _conditioning, batch_loss
+    if not torch.cuda.is_available():
+        raise SystemExit("bench_yaml.py: no CUDA device; the product has no CPU path")
+    dev = torch.device("cuda", 0)
+    lib = _lib.load()
+    y = YAML
+    H = y["atom_type_size"] + y["compressed_spectrum_size"] + y["t_size"] + y["exO_size"]      # main.py:102-110
+    K0 = 2 * H + y["d_size"]
+    sizes = dict(L=y["L"], m_input=K0, m_hidden=y["m_hidden_size"], m_output=y["m_size"], x_input=K0, x_hidden=y["x_hidden_size"],
+                 x_output=1, h_input=H + y["m_size"], h_hidden=y["h_hidden_size"], h_output=H)
+    torch.manual_seed(2024)
+    net = EquivariantGNN(**sizes).to(dev)
+    comp = SpectrumCompressor(y["spectrum_size"], y["compressor_hidden_dim"], y["compressed_spectrum_size"]).to(dev)
+    assert net.resolved_precision() == "fp32"
+    sd = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
+    cw = {k: v.detach().cpu().clone() for k, v in comp.state_dict().items()}
+    params = dict(atom_type_size=2, conditional=True, to_compress_spectrum=True, give_exO=True, optimizer="RAdamScheduleFree")
+    dp = E3DiffusionProcess(s=y["s"], power=y["power"], num_diffusion_timestep=y["T"])
+    gen = torch.Generator().manual_seed(7)
+    n, G = args.atoms, args.batch
+    graphs = []
+    for _ in range(G):
+        pos, onehot, _ = bench.synth_batch(1, n, int(torch.randint(0, 10 ** 6, (1,), generator=gen)))
+        exo = torch.zeros(n, 1)
+        exo[0] = 1.0
+        graphs.append(Data(x=onehot, pos=pos, edge_index=build_edges_fc([n], dev).cpu(), spectrum=torch.rand(n, y["spectrum_size"], generator=gen),
+                           exO=exo))
+    batch = Batch.from_data_list(graphs).to(dev)
+    E = int(batch.edge_index.shape[1])
+    opt = RAdamScheduleFree(list(net.parameters()) + list(comp.parameters()), lr=y["lr"])
+    opt.train()
+    nn_dict = {"egnn": net, "spectrum_compressor": comp}
+
+    def step():
+        opt.zero_grad()
+        loss, _, _ = batch_loss(net, batch, dp, params, cond=_conditioning(batch, params, nn_dict))
+        loss.backward()
+        opt.step()
+        return loss
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize(dev)
+    l0 = lib.egnn_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / args.steps
+    P = sum(p.numel() for p in net.parameters())
+    K = K0
+    flops_fwd = y["L"] * (E * (2 * K * 1024 + 2 * 1024 * 256 + 2 * 256 + 2 * K * 1024 + 2 * 1024 * 1024 + 2 * 1024)
+                          + G * n * (2 * (H + 256) * 1024 + 2 * 1024 * H))          # SURVEY.md 8(d), general widths
+    out = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer), parameters.yaml network", value=G / (ms * 1e-3),
+               unit="graph-steps/s", ms_per_step=ms, dtype="fp32 (CUDA-core FFMA kernels; no tcgen05 tile for K0=73 / d=1024)",
+               gpu_launches=int(lib.egnn_launch_count() - l0), loss=float(loss.detach()), parameters=P, train_tflops=3 * flops_fwd / (ms * 1e-3) / 1e12,
+               config=dict(workload=f"parameters.yaml: conditional EGNN L=5, K0=73, m/x/h hidden 1024, m_size 256, SpectrumCompressor, "
+                                    f"RAdamScheduleFree; {G} fully connected graph(s) of {n} atoms (E = {E}), T=1000", atoms=n, batch=G, edges=E))
+    if not args.skip_cpu:
+        from oracle import diffusion_ref as D, egnn_ref, loops_ref as LP
+        from oracle.radam_sf_ref import RAdamScheduleFreeRef
+        info = bench.host_info()
+        torch.set_num_threads(info["logical_cpus"])
+        p = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+        cwp = {k: v.clone().requires_grad_(True) for k, v in cw.items()}
+        ro = RAdamScheduleFreeRef(list(p.values()) + list(cwp.values()), lr=y["lr"])
+        ro.train()
+        sch = D.Schedule(y["s"], y["power"], y["T"])
+        b = Batch.from_data_list(graphs)
+        idx = sorted({int(k.split(".")[1]) for k in cwp})
+
+        def compress(spec):
+            z = spec
+            for q, i in enumerate(idx):
+                z = z @ cwp[f"mlp.{i}.weight"].t() + cwp[f"mlp.{i}.bias"]
+                if q + 1 < len(idx):
+                    z = torch.relu(z)
+            return z
+        g2 = torch.Generator().manual_seed(1)
+        times = []
+        for k in range(3):
+            t0 = time.perf_counter()
+            ro.zero_grad()
+            cond = torch.cat((compress(b.spectrum), b.exO), dim=1)
+            t = torch.randint(1, y["T"] + 1, (G,), generator=g2)
+            loss_c, _ = LP.train_loss(lambda e, h, x: egnn_ref.egnn_forward(p, y["L"], e, h, x), sch, b.pos, b.x, b.edge_index, b.batch, t,
+                                      torch.randn(G * n, 3, generator=g2), torch.randn(G * n, 2, generator=g2), A=2, cond=cond)
+            loss_c.backward()
+            ro.step()
+            if k:
+                times.append(time.perf_counter() - t0)
+        sec = sum(times) / len(times)
+        out["cpu_baseline"] = dict(value=G / sec, unit="graph-steps/s", ms_per_step=1e3 * sec, cores=info["logical_cpus"], kind="port",
+                                   cpu_model=info["cpu_model"], sample=f"the same step, {len(times)} timed, oracle/ restatement with torch CPU autograd")
+    print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -252,7 +252,7 @@ __device__ __forceinline__ void edge_branch_bwd(const EdgeBwdArgs& a, const Laye
     __syncthreads();
     {   // recompute layer 1: a1 = SiLU(z1), d1 = SiLU'(z1)
         const float* b1 = a.P + b1o;
-        tile_gemm<RT>(U, ldu, a.Pk + w1t, D1, K0, D1, [&](int r, int c, float acc) {
+        tile_gemm<RT, EGNN_EDGE_KU(RT)>(U, ldu, a.Pk + w1t, D1, K0, D1, [&](int r, int c, float acc) {
             const float z = acc + __ldg(b1 + c);
             bufA[r * ld + c] = silu_f(z);
             bufD1[r * ld + c] = dsilu_f(z);
@@ -261,7 +261,7 @@ __device__ __forceinline__ void edge_branch_bwd(const EdgeBwdArgs& a, const Laye
     __syncthreads();
     {   // recompute layer 2: out = SiLU(z2), d2 = SiLU'(z2)
         const float* b2 = a.P + b2o;
-        tile_gemm<RT>(bufA, ld, a.Pk + w2t, D2, D1, D2, [&](int r, int c, float acc) {
+        tile_gemm<RT, EGNN_EDGE_KU(RT)>(bufA, ld, a.Pk + w2t, D2, D1, D2, [&](int r, int c, float acc) {
             const float z = acc + __ldg(b2 + c);
             bufB[r * ld + c] = silu_f(z);
             bufD2[r * ld + c] = dsilu_f(z);
@@ -328,14 +328,14 @@ __device__ __forceinline__ void edge_branch_bwd(const EdgeBwdArgs& a, const Laye
     tile_wgrad(bufD2, ld, bufA, ld, nrows, D2, D1, part + w2, D1);
     tile_colsum(bufD2, ld, nrows, D2, nullptr, part + b2o);
     // ga1 = gz2 . W2 ; gz1 = ga1 * d1   (in place in bufD1; each element is read and written by the same thread)
-    tile_gemm<RT>(bufD2, ld, a.P + w2, D1, D2, D1,
+    tile_gemm<RT, EGNN_EDGE_KU(RT)>(bufD2, ld, a.P + w2, D1, D2, D1,
                   [&](int r, int c, float acc) { bufD1[r * ld + c] = r < nrows ? acc * bufD1[r * ld + c] : 0.f; });
     __syncthreads();
     // first Linear: dW1 += gz1^T u, db1 += colsum gz1
     tile_wgrad(bufD1, ld, U, ldu, nrows, D1, K0, part + w1, K0);
     tile_colsum(bufD1, ld, nrows, D1, nullptr, part + b1o);
     // gu (+)= gz1 . W1
-    tile_gemm<RT>(bufD1, ld, a.P + w1, K0, D1, K0, [&](int r, int c, float acc) {
+    tile_gemm<RT, EGNN_EDGE_KU(RT)>(bufD1, ld, a.P + w1, K0, D1, K0, [&](int r, int c, float acc) {
         if (IS_M) GU[r * ldu + c] += acc;
         else GU[r * ldu + c] = acc;
     });

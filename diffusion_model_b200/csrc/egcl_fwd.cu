@@ -112,11 +112,11 @@ __global__ void __launch_bounds__(256) egcl_edge_fwd(EdgeFwdArgs a) {
     // ---- coordinate branch: phi_e = wx3 . SiLU(Wx2 SiLU(Wx1 u + b) + b) + b        (:19-25, :63-64)
     {
         const float* b1 = a.P + lo.bx1;
-        tile_gemm<RT>(U, ldu, a.Pk + po.wx1t, Xh, K0, Xh,
+        tile_gemm<RT, EGNN_EDGE_KU(RT)>(U, ldu, a.Pk + po.wx1t, Xh, K0, Xh,
                       [&](int r, int c, float acc) { buf1[r * ld + c] = silu_f(acc + __ldg(b1 + c)); });
         __syncthreads();
         const float* b2 = a.P + lo.bx2;
-        tile_gemm<RT>(buf1, ld, a.Pk + po.wx2t, Xh, Xh, Xh,
+        tile_gemm<RT, EGNN_EDGE_KU(RT)>(buf1, ld, a.Pk + po.wx2t, Xh, Xh, Xh,
                       [&](int r, int c, float acc) { buf2[r * ld + c] = silu_f(acc + __ldg(b2 + c)); });
         __syncthreads();
         row_dots(buf2, ld, TE, Xh, a.P + lo.wx3, __ldg(a.P + lo.bx3), [&](int r, float v) { sPhi[r] = v; });
@@ -126,11 +126,11 @@ __global__ void __launch_bounds__(256) egcl_edge_fwd(EdgeFwdArgs a) {
     // ---- message branch: m_e = SiLU(Wm2 SiLU(Wm1 u + b) + b),  gate g_e = sigmoid(wa . m_e + ba)   (:13-18, :31-34, :57-61)
     {
         const float* b1 = a.P + lo.bm1;
-        tile_gemm<RT>(U, ldu, a.Pk + po.wm1t, Mh, K0, Mh,
+        tile_gemm<RT, EGNN_EDGE_KU(RT)>(U, ldu, a.Pk + po.wm1t, Mh, K0, Mh,
                       [&](int r, int c, float acc) { buf1[r * ld + c] = silu_f(acc + __ldg(b1 + c)); });
         __syncthreads();
         const float* b2 = a.P + lo.bm2;
-        tile_gemm<RT>(buf1, ld, a.Pk + po.wm2t, Ms, Mh, Ms,
+        tile_gemm<RT, EGNN_EDGE_KU(RT)>(buf1, ld, a.Pk + po.wm2t, Ms, Mh, Ms,
                       [&](int r, int c, float acc) { buf2[r * ld + c] = silu_f(acc + __ldg(b2 + c)); });
         __syncthreads();
         row_dots(buf2, ld, TE, Ms, a.P + lo.wa, __ldg(a.P + lo.ba), [&](int r, float v) { sGate[r] = sigmoid_f(v); });

@@ -10,6 +10,11 @@
 #pragma once
 #include "common.cuh"
 
+// k-steps of 4 whose weight loads are issued together in the edge kernels: wide layers force small register tiles (d = 1024:
+// 16-edge tiles, RT = 4), where 8 loads per 32 FMAs leave the L2 latency exposed (parameters.yaml network: 196 ms per step);
+// small tiles have the registers to keep 32 loads in flight.  The accumulation order does not change: results are identical.
+#define EGNN_EDGE_KU(RT) ((RT) <= 8 ? 4 : (RT) <= 16 ? 2 : 1)
+
 template <int RT, int KU = 1, class Epi>
 __device__ __forceinline__ void tile_gemm(const float* __restrict__ As, int lda, const float* __restrict__ Bt, int ldb,
                                           int K, int N, Epi epi) {
