@@ -3,12 +3,13 @@
 h = [2 atom types | 32 compressed spectrum | exO | t] (H = 36, K0 = 73), L = 5, m_hidden = x_hidden = h_hidden = 1024,
 m_size = 256, SpectrumCompressor 200 -> 150 -> 100 -> 50 -> 32, batch_size 1, RAdamScheduleFree, lr 1e-5.
 
-These widths have no tcgen05 tile (2H+1 > 16, Mh != Ms, d = 1024): the step runs on the CUDA-core fp32 kernels
-(`precision = 'auto'` resolves to 'fp32').  Prints ONE JSON line: graph-steps/s of the eps-prediction training step on a
+These widths have no fused tcgen05 kernel (2H+1 > 16, Mh != Ms, d = 1024): under `precision = 'auto'` (= bf16x3) the forward
+runs the tile-GEMM tcgen05 path of csrc/tc_wide.cu and the backward the CUDA-core fp32 kernels; `--precision fp32` runs the
+CUDA-core kernels throughout.  Prints ONE JSON line: graph-steps/s of the eps-prediction training step on a
 fully connected graph of `--atoms` atoms (the reference's datasets hold clusters of <= ~120 atoms) for the GPU path and for
 the CPU oracle on the same step.  A parity-config timing for profiles/, not the contract bench line (bench.py).
 
-    python bench_yaml.py [--atoms 96] [--batch 1] [--steps 10] [--skip-cpu]
+    python bench_yaml.py [--atoms 96] [--batch 1] [--steps 10] [--precision auto|fp32|bf16x3|bf16] [--skip-cpu]
 """
 from __future__ import annotations
 
@@ -33,6 +34,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--precision", default="auto")
     args = ap.parse_args()
     import bench
     from diffusion_model_b200 import _lib
@@ -55,7 +57,8 @@ def main():
     torch.manual_seed(2024)
     net = EquivariantGNN(**sizes).to(dev)
     comp = SpectrumCompressor(y["spectrum_size"], y["compressor_hidden_dim"], y["compressed_spectrum_size"]).to(dev)
-    assert net.resolved_precision() == "fp32"
+    net.precision = args.precision
+    prec = net.resolved_precision()
     sd = {k: v.detach().cpu().clone() for k, v in net.state_dict().items()}
     cw = {k: v.detach().cpu().clone() for k, v in comp.state_dict().items()}
     params = dict(atom_type_size=2, conditional=True, to_compress_spectrum=True, give_exO=True, optimizer="RAdamScheduleFree")
@@ -93,13 +96,28 @@ def main():
     e1.record()
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1) / args.steps
+    launches = int(lib.egnn_launch_count() - l0)
+    # one denoiser call alone (what every sampler step costs): the network forward on the batch's own input
+    with torch.no_grad():
+        cond = _conditioning(batch, params, nn_dict)
+        hin = torch.cat((batch.x, cond, torch.full((G * n, 1), 0.5, device=dev)), dim=1)
+        for _ in range(2):
+            net(batch.edge_index, hin, batch.pos, batch=batch.batch, norm_scope="graph")
+        e0.record()
+        for _ in range(args.steps):
+            net(batch.edge_index, hin, batch.pos, batch=batch.batch, norm_scope="graph")
+        e1.record()
+        torch.cuda.synchronize(dev)
+    fwd_ms = e0.elapsed_time(e1) / args.steps
     P = sum(p.numel() for p in net.parameters())
     K = K0
     flops_fwd = y["L"] * (E * (2 * K * 1024 + 2 * 1024 * 256 + 2 * 256 + 2 * K * 1024 + 2 * 1024 * 1024 + 2 * 1024)
                           + G * n * (2 * (H + 256) * 1024 + 2 * 1024 * H))          # SURVEY.md 8(d), general widths
     out = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer), parameters.yaml network", value=G / (ms * 1e-3),
-               unit="graph-steps/s", ms_per_step=ms, dtype="fp32 (CUDA-core FFMA kernels; no tcgen05 tile for K0=73 / d=1024)",
-               gpu_launches=int(lib.egnn_launch_count() - l0), loss=float(loss.detach()), parameters=P, train_tflops=3 * flops_fwd / (ms * 1e-3) / 1e12,
+               unit="graph-steps/s", ms_per_step=ms,
+               dtype="fp32 (CUDA-core FFMA kernels)" if prec == "fp32" else f"{prec} forward (tcgen05 tile GEMMs, csrc/tc_wide.cu), fp32 backward (CUDA-core FFMA)",
+               gpu_launches=launches, loss=float(loss.detach()), parameters=P, train_tflops=3 * flops_fwd / (ms * 1e-3) / 1e12,
+               denoiser_forward_ms=fwd_ms, forward_tflops=flops_fwd / (fwd_ms * 1e-3) / 1e12,
                config=dict(workload=f"parameters.yaml: conditional EGNN L=5, K0=73, m/x/h hidden 1024, m_size 256, SpectrumCompressor, "
                                     f"RAdamScheduleFree; {G} fully connected graph(s) of {n} atoms (E = {E}), T=1000", atoms=n, batch=G, edges=E))
     if not args.skip_cpu:

@@ -170,12 +170,20 @@ class _KernelBacked(nn.Module):
     precision = "auto"
 
     def resolved_precision(self):
-        """The arithmetic mode a call will use: 'auto' -> 'bf16x3' where the tcgen05 edge kernels cover the shape
-        (Mh = Ms = Xh in {64, 128, 256} and 2H+1 <= 16, csrc/common.cuh: tc_fwd_supported), else 'fp32'."""
+        """The arithmetic mode a call will use: 'auto' -> 'bf16x3' where the fused tcgen05 edge kernels cover the shape
+        (Mh = Ms = Xh in {64, 128, 256} and 2H+1 <= 16, csrc/common.cuh: tc_fwd_supported), and for wide networks the
+        tile-GEMM forward covers (Mh, Xh <= 1024 with one of them >= 256, Ms <= 256, 2H+1 <= 128 -- the reference's
+        parameters.yaml shape; csrc/common.cuh: wide_fwd_supported); else 'fp32'.  Narrow ragged networks stay on the fp32
+        kernels under 'auto': the tile-GEMM path pads every width to 256 and would gain nothing there (ask for 'bf16x3' to
+        run it anyway)."""
         if self.precision != "auto":
             return self.precision
         n = self._net
-        return "bf16x3" if (n.Mh == n.Ms == n.Xh and n.Mh in (64, 128, 256) and 2 * n.H + 1 <= 16) else "fp32"
+        if n.Mh == n.Ms == n.Xh and n.Mh in (64, 128, 256) and 2 * n.H + 1 <= 16:
+            return "bf16x3"
+        if max(n.Mh, n.Xh) >= 256 and n.Mh <= 1024 and n.Xh <= 1024 and n.Ms <= 256 and 2 * n.H + 1 <= 128:
+            return "bf16x3"
+        return "fp32"
 
     def _setup(self, L, layers, sizes):
         m_input, m_hidden, m_output, x_input, x_hidden, x_output, h_input, h_hidden, h_output = sizes

@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libegnn_b200.so")
-SOURCES = ["api.cu", "graph.cu", "egcl_fwd.cu", "egcl_bwd.cu", "diffusion.cu", "tc_edge.cu", "tc_edge256.cu", "tc_edge256_bwd.cu", "tc_node.cu", "analysis.cu"]
+SOURCES = ["api.cu", "graph.cu", "egcl_fwd.cu", "egcl_bwd.cu", "diffusion.cu", "tc_edge.cu", "tc_edge256.cu", "tc_edge256_bwd.cu", "tc_node.cu", "tc_wide.cu", "analysis.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--extended-lambda",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"] + os.environ.get("EGNN_NVCC_EXTRA", "").split()
 

@@ -128,6 +128,63 @@ __host__ __device__ static inline bool tc_supported(const egnn_net_t& n) {
 __host__ __device__ static inline bool tc_fwd_supported(const egnn_net_t& n) {
     return n.Mh == n.Ms && n.Ms == n.Xh && (n.Mh == 64 || n.Mh == 128 || n.Mh == 256) && 2 * n.H + 1 <= 16;
 }
+// ---- generic ("wide") tcgen05 forward path: tc_wide.cu -------------------------------------------------------------------------
+// Networks the fused edge kernels do not cover -- the reference's own parameters.yaml shape (K0 = 73, m/x hidden 1024,
+// m_size 256), ragged widths, conditional models -- run their edge MLPs as a chain of tile GEMMs [128 edges x 256 outputs]
+// with K streamed in 64-wide slices.  Operands are bf16 hi + lo "tile images": a [R rows x 64] slice is 8 chunk columns of
+// R x 16 bytes (hi) followed by the same for lo -- exactly the SWIZZLE_NONE K-major layout of tc_common.cuh, so one
+// cp.async.bulk per slice lands it in shared memory ready for tcgen05.mma.  Widths are zero-padded to the tile sizes.
+constexpr int WIDE_TM = 128, WIDE_TN = 256, WIDE_TK = 64;
+constexpr int WIDE_A_SLICE = WIDE_TM * WIDE_TK * 2 * 2;  // bytes of one activation slice (hi | lo): 32 KB
+constexpr int WIDE_B_SLICE = WIDE_TN * WIDE_TK * 2 * 2;  // bytes of one weight slice (hi | lo): 64 KB
+__host__ __device__ static inline int wide_cdiv(int a, int b) { return (a + b - 1) / b; }
+__host__ __device__ static inline bool tc_fwd_supported(const egnn_net_t& n);
+// forward only; the backward of such a network runs the fp32 FFMA kernels
+__host__ __device__ static inline bool wide_fwd_supported(const egnn_net_t& n) {
+    return !tc_fwd_supported(n) && n.Mh <= 1024 && n.Xh <= 1024 && n.Ms <= WIDE_TN && 2 * n.H + 1 <= 128;
+}
+struct WideOff {  // per layer, in units of WIDE_B_SLICE blocks: block (nt, ks) of a matrix sits at first + nt * KS + ks
+    int ks0, ksm, ksx;           // K slices: K0, Mh, Xh
+    int ntm1, ntm2, ntx1, ntx2;  // N tiles: Mh, Ms, Xh, Xh
+    int m1, m2, x1, x2, blocks;  // first block of each matrix, total
+};
+__host__ __device__ static inline WideOff wide_off(const egnn_net_t& n) {
+    WideOff o;
+    o.ks0 = wide_cdiv(2 * n.H + 1, WIDE_TK);
+    o.ksm = wide_cdiv(n.Mh, WIDE_TK);
+    o.ksx = wide_cdiv(n.Xh, WIDE_TK);
+    o.ntm1 = wide_cdiv(n.Mh, WIDE_TN);
+    o.ntm2 = wide_cdiv(n.Ms, WIDE_TN);
+    o.ntx1 = wide_cdiv(n.Xh, WIDE_TN);
+    o.ntx2 = wide_cdiv(n.Xh, WIDE_TN);
+    o.m1 = 0;
+    o.m2 = o.m1 + o.ntm1 * o.ks0;
+    o.x1 = o.m2 + o.ntm2 * o.ksm;
+    o.x2 = o.x1 + o.ntx1 * o.ks0;
+    o.blocks = o.x2 + o.ntx2 * o.ksx;
+    return o;
+}
+// forward workspace of the wide path (bytes, each part 1 KB aligned): U image | A1 image | g*m fp32 [E][256] | phi parts
+struct WideWs {
+    int64_t u, a1, gm, phip, total;
+    int mtiles, a1_ks;  // a1_ks: slices per tile of the A1 image (its row stride)
+};
+static inline WideWs wide_ws(const egnn_net_t& n, int64_t E) {
+    WideWs w;
+    const WideOff o = wide_off(n);
+    w.mtiles = (int)((E + WIDE_TM - 1) / WIDE_TM);
+    const int npm = o.ntm1 > o.ntx1 ? o.ntm1 : o.ntx1;
+    w.a1_ks = npm * (WIDE_TN / WIDE_TK);
+    int64_t p = 0;
+    auto take = [&](int64_t b) { int64_t q = p; p += (b + 1023) / 1024 * 1024; return q; };
+    w.u = take((int64_t)w.mtiles * o.ks0 * WIDE_A_SLICE);
+    w.a1 = take((int64_t)w.mtiles * w.a1_ks * WIDE_A_SLICE);
+    w.gm = take(E * WIDE_TN * 4);
+    w.phip = take((int64_t)o.ntx2 * E * 4);
+    w.total = p;
+    return w;
+}
+
 // bytes of one layer's tcgen05 weight image (see tc_edge.cu: W1 hi/lo [2d x 16], W2m hi/lo, W2x hi/lo [d x d] bf16, fp32 vectors)
 __host__ __device__ static inline int tc_blob_bytes(int d) { return 2 * (2 * d * 32) + 4 * (d * d * 2) + (6 * d + 4) * 4; }
 // d = 256 only: K-major images of W2^T / 2 (hi | lo per branch), the streamed B operand of the dgrad in tc_edge256_bwd.cu;
@@ -153,6 +210,7 @@ __host__ __device__ static inline PackOff pack_off(const egnn_net_t& n) {
     o.tc = p;
     if (tc_fwd_supported(n)) p += (tc_blob_bytes(n.Mh) + 15) / 16 * 4 + tc_w2t_bytes(n.Mh) / 4;
     if (tc_node_supported(n)) p += tc_node_blob_bytes(n.Mh) / 4;
+    if (wide_fwd_supported(n)) p += wide_off(n).blocks * (WIDE_B_SLICE / 4);  // starts at o.tc (the fused image is absent)
     o.total = round4(p);
     return o;
 }
@@ -168,6 +226,7 @@ struct FwdWs {
     int64_t dxu;    // [L][N][3]   un-normalised coordinate sums
     int64_t S;      // [L][G]      normaliser per graph
     int64_t phi;    // [E]         per-edge phi of the current layer (tcgen05 path)
+    int64_t wide;   // wide-path scratch (WideWs, in floats)
     int64_t total;
 };
 static inline int edge_tile_for(const egnn_net_t& n) {
@@ -194,7 +253,8 @@ static inline FwdWs fwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G)
     w.msum = take((int64_t)n.L * N * n.Ms);
     w.dxu = take((int64_t)n.L * N * 3);
     w.S = take((int64_t)n.L * G);
-    w.phi = take(tc_fwd_supported(n) ? E : 0);
+    w.phi = take(tc_fwd_supported(n) || wide_fwd_supported(n) ? E : 0);
+    w.wide = take(wide_fwd_supported(n) ? 256 + wide_ws(n, E).total / 4 : 0);  // + 256 floats: the caller aligns to 1 KB
     w.total = p;
     return w;
 }

@@ -571,7 +571,8 @@ static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const
     EGNN_REQUIRE(g->node_graph != nullptr, "egnn_net_backward: node_graph is NULL");
     EGNN_REQUIRE(precision >= EGNN_PREC_FP32 && precision <= EGNN_PREC_BF16, "bad precision %d", precision);
     if (precision != EGNN_PREC_FP32)
-        EGNN_REQUIRE(tc_fwd_supported(*net), "tcgen05 path needs Mh = Ms = Xh in {64,128,256} and 2H+1 <= 16; use precision fp32");
+        EGNN_REQUIRE(tc_fwd_supported(*net) || wide_fwd_supported(*net),
+                     "tcgen05 path needs Mh = Ms = Xh in {64,128,256} and 2H+1 <= 16, or the tile-GEMM limits; use precision fp32");
     // edge phase on tcgen05 (bf16x3 split products or plain bf16): d <= 128 one fused kernel with the weight gradients
     // persistent in TMEM, d = 256 the two-kernel form of tc_edge256_bwd.cu
     const bool use_tc = precision != EGNN_PREC_FP32 && tc_supported(*net);

@@ -342,11 +342,17 @@ int egnn_tc_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const flo
 int egnn_tc_node_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
                          const float* h, const float* x, const float* agg, const float* part, const float* phi_edge,
                          float* h_out, float* msum, float* dxu, float* Dn, int precision, cudaStream_t st);
+// tc_wide.cu: the generic tcgen05 forward of the networks the fused kernels do not cover
+int egnn_wide_pack(const egnn_net_t& net, const float* params, float* packed, cudaStream_t st);
+int egnn_wide_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
+                           const float* h, const float* x, float* agg, float* phi_edge, float* scratch, int precision,
+                           cudaStream_t st);
 
 extern "C" int egnn_pack_weights(const egnn_net_t* net, const float* params, float* packed, void* stream) {
     if (int rc = egnn_validate_net(net)) return rc;
     pack_weights_kernel<<<dim3(32, net->L), 256, 0, (cudaStream_t)stream>>>(*net, params, packed);
     EGNN_CHECK_LAUNCH("pack_weights_kernel");
+    if (int rc = egnn_wide_pack(*net, params, packed, (cudaStream_t)stream)) return rc;
     return egnn_tc_pack(*net, params, packed, (cudaStream_t)stream);
 }
 
@@ -355,8 +361,12 @@ int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const f
                            const float* x, float* h_out, float* x_out, float* ws, const FwdWs& w, int l, int norm_scope,
                            int precision, cudaStream_t st) {
     const bool tensor = precision != EGNN_PREC_FP32;
-    const int TE = tensor ? part_tile_for(net) : edge_tile_for(net);
-    if (g.E > 0 && tensor) {
+    const bool wide = tensor && wide_fwd_supported(net);
+    // wide path: agg holds complete per-receiver sums (no tile partials): a tile size no edge range can straddle
+    const int TE = wide ? 1 << 30 : tensor ? part_tile_for(net) : edge_tile_for(net);
+    if (g.E > 0 && wide) {
+        if (int rc = egnn_wide_edge_forward(net, g, P, Pk, h, x, ws + w.agg, ws + w.phi, ws + w.wide, precision, st)) return rc;
+    } else if (g.E > 0 && tensor) {
         // layer 0 is launched normally: its prologue reads the packed weights, which the pack kernels right in front of a
         // training forward write; every later kernel of the chain may overlap its predecessor's tail (common.cuh: PDL)
         if (int rc = egnn_tc_edge_forward(net, g, Pk, h, x, ws + w.agg, ws + w.part, ws + w.phi, precision, st, l > 0)) return rc;
@@ -413,8 +423,9 @@ extern "C" int egnn_net_forward(const egnn_net_t* net, const egnn_graph_t* g, co
     EGNN_REQUIRE(norm_scope == EGNN_NORM_CALL || norm_scope == EGNN_NORM_GRAPH, "bad norm_scope %d", norm_scope);
     EGNN_REQUIRE(precision == EGNN_PREC_FP32 || precision == EGNN_PREC_BF16X3 || precision == EGNN_PREC_BF16,
                  "bad precision %d", precision);
-    EGNN_REQUIRE(precision == EGNN_PREC_FP32 || tc_fwd_supported(*net),
-                 "tcgen05 precisions need Mh = Ms = Xh in {64,128,256} and 2H+1 <= 16; use precision fp32 for this network");
+    EGNN_REQUIRE(precision == EGNN_PREC_FP32 || tc_fwd_supported(*net) || wide_fwd_supported(*net),
+                 "tcgen05 precisions need Mh = Ms = Xh in {64,128,256} and 2H+1 <= 16 (fused kernels) or Mh, Xh <= 1024, Ms <= 256, "
+                 "2H+1 <= 128 (tile-GEMM path); use precision fp32 for this network");
     const FwdWs w = fwd_ws(*net, g->N, g->E, g->G);
     if (ws_floats < w.total) {
         egnn_set_error("egnn_net_forward: workspace too small (%lld < %lld floats)", (long long)ws_floats,

@@ -211,7 +211,12 @@ def test_default_precision_resolution():
     for d in (64, 128, 256):
         assert EquivariantGNN(**egnn_ref.net_sizes(2, d)).resolved_precision() == "bf16x3"
     assert EquivariantGNN(**egnn_ref.net_sizes(1, 96)).resolved_precision() == "fp32"            # no tile for d = 96
-    assert EquivariantGNN(**egnn_ref.net_sizes(1, 64, H=36)).resolved_precision() == "fp32"      # K0 = 73 > 16
+    assert EquivariantGNN(**egnn_ref.net_sizes(1, 64, H=36)).resolved_precision() == "fp32"      # K0 = 73 > 16, narrow
+    # the reference's parameters.yaml widths: the tile-GEMM forward (csrc/tc_wide.cu)
+    yaml = dict(L=1, m_input=73, m_hidden=1024, m_output=256, x_input=73, x_hidden=1024, x_output=1, h_input=36 + 256,
+                h_hidden=1024, h_output=36)
+    assert EquivariantGNN(**yaml).resolved_precision() == "bf16x3"
+    assert EquivariantGNN(**egnn_ref.net_sizes(1, 512, H=70)).resolved_precision() == "fp32"     # K0 = 141 > 128
     sz = egnn_ref.net_sizes(1, 128)
     sz.pop("L")
     layer = EGCL(**sz)
