@@ -4,8 +4,8 @@ h = [2 atom types | 32 compressed spectrum | exO | t] (H = 36, K0 = 73), L = 5, 
 m_size = 256, SpectrumCompressor 200 -> 150 -> 100 -> 50 -> 32, batch_size 1, RAdamScheduleFree, lr 1e-5.
 
 These widths have no fused tcgen05 kernel (2H+1 > 16, Mh != Ms, d = 1024): under `precision = 'auto'` (= bf16x3) the forward
-runs the tile-GEMM tcgen05 path of csrc/tc_wide.cu and the backward the CUDA-core fp32 kernels; `--precision fp32` runs the
-CUDA-core kernels throughout.  Prints ONE JSON line: graph-steps/s of the eps-prediction training step on a
+and the backward of the edge MLPs run the tile-GEMM tcgen05 path of csrc/tc_wide.cu; `--precision fp32` runs the CUDA-core
+kernels throughout.  Prints ONE JSON line: graph-steps/s of the eps-prediction training step on a
 fully connected graph of `--atoms` atoms (the reference's datasets hold clusters of <= ~120 atoms) for the GPU path and for
 the CPU oracle on the same step.  A parity-config timing for profiles/, not the contract bench line (bench.py).
 
@@ -115,7 +115,7 @@ def main():
                           + G * n * (2 * (H + 256) * 1024 + 2 * 1024 * H))          # SURVEY.md 8(d), general widths
     out = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer), parameters.yaml network", value=G / (ms * 1e-3),
                unit="graph-steps/s", ms_per_step=ms,
-               dtype="fp32 (CUDA-core FFMA kernels)" if prec == "fp32" else f"{prec} forward (tcgen05 tile GEMMs, csrc/tc_wide.cu), fp32 backward (CUDA-core FFMA)",
+               dtype="fp32 (CUDA-core FFMA kernels)" if prec == "fp32" else f"{prec} (tcgen05 tile GEMMs for the edge MLPs forward and backward, csrc/tc_wide.cu; node MLP on CUDA-core FFMA)",
                gpu_launches=launches, loss=float(loss.detach()), parameters=P, train_tflops=3 * flops_fwd / (ms * 1e-3) / 1e12,
                denoiser_forward_ms=fwd_ms, forward_tflops=flops_fwd / (fwd_ms * 1e-3) / 1e12,
                config=dict(workload=f"parameters.yaml: conditional EGNN L=5, K0=73, m/x/h hidden 1024, m_size 256, SpectrumCompressor, "

@@ -144,15 +144,18 @@ __host__ __device__ static inline bool wide_fwd_supported(const egnn_net_t& n) {
     return !tc_fwd_supported(n) && n.Mh <= 1024 && n.Xh <= 1024 && n.Ms <= WIDE_TN && 2 * n.H + 1 <= 128;
 }
 struct WideOff {  // per layer, in units of WIDE_B_SLICE blocks: block (nt, ks) of a matrix sits at first + nt * KS + ks
-    int ks0, ksm, ksx;           // K slices: K0, Mh, Xh
+    int ks0, ksm, ksx, kss;      // K slices: K0, Mh, Xh, Ms
     int ntm1, ntm2, ntx1, ntx2;  // N tiles: Mh, Ms, Xh, Xh
-    int m1, m2, x1, x2, blocks;  // first block of each matrix, total
+    int m1, m2, x1, x2;          // forward: first block of each matrix
+    // backward (dgrad) images, rows = INPUT features: Wm2^T [Mh x Ms], Wx2^T [Xh x Xh], [Wm1^T | Wx1^T] [K0 x (Mh + Xh)]
+    int m2t, x2t, w1t, blocks;
 };
 __host__ __device__ static inline WideOff wide_off(const egnn_net_t& n) {
     WideOff o;
     o.ks0 = wide_cdiv(2 * n.H + 1, WIDE_TK);
     o.ksm = wide_cdiv(n.Mh, WIDE_TK);
     o.ksx = wide_cdiv(n.Xh, WIDE_TK);
+    o.kss = wide_cdiv(n.Ms, WIDE_TK);
     o.ntm1 = wide_cdiv(n.Mh, WIDE_TN);
     o.ntm2 = wide_cdiv(n.Ms, WIDE_TN);
     o.ntx1 = wide_cdiv(n.Xh, WIDE_TN);
@@ -161,7 +164,10 @@ __host__ __device__ static inline WideOff wide_off(const egnn_net_t& n) {
     o.m2 = o.m1 + o.ntm1 * o.ks0;
     o.x1 = o.m2 + o.ntm2 * o.ksm;
     o.x2 = o.x1 + o.ntx1 * o.ks0;
-    o.blocks = o.x2 + o.ntx2 * o.ksx;
+    o.m2t = o.x2 + o.ntx2 * o.ksx;
+    o.x2t = o.m2t + o.ntm1 * o.kss;
+    o.w1t = o.x2t + o.ntx2 * o.ksx;
+    o.blocks = o.w1t + 1 * (o.ksm + o.ksx);
     return o;
 }
 // forward workspace of the wide path (bytes, each part 1 KB aligned): U image | A1 image | g*m fp32 [E][256] | phi parts
@@ -181,6 +187,47 @@ static inline WideWs wide_ws(const egnn_net_t& n, int64_t E) {
     w.a1 = take((int64_t)w.mtiles * w.a1_ks * WIDE_A_SLICE);
     w.gm = take(E * WIDE_TN * 4);
     w.phip = take((int64_t)o.ntx2 * E * 4);
+    w.total = p;
+    return w;
+}
+// backward workspace of the wide path (tc_wide.cu: egnn_wide_edge_backward).  "T" images hold the transpose (rows = features,
+// K = edges in 64-edge slices), the operands of the weight-gradient GEMMs.  Ep = edges padded to the 128-edge tile.
+struct WideBwdWs {
+    int64_t u, ut, a1, a1t, d1, g2, g2t, g1m, g1x, g1t, rows, q, gphi, phip, phi, gu, total;
+    int mtiles, kst, np, w_ks;  // kst: 64-edge slices; np: padded hidden width; w_ks: slices per tile row of the np-wide images
+    int splits, per;            // split-K of the weight gradients over the edge slices = private rows of the partial buffer
+};
+static inline WideBwdWs wide_bwd_ws(const egnn_net_t& n, int64_t E) {
+    WideBwdWs w;
+    w.mtiles = (int)((E + WIDE_TM - 1) / WIDE_TM);
+    w.kst = 2 * w.mtiles;
+    const WideOff o = wide_off(n);
+    const int npm = o.ntm1 > o.ntx1 ? o.ntm1 : o.ntx1;
+    w.np = npm * WIDE_TN;
+    w.w_ks = w.np / WIDE_TK;
+    w.splits = w.kst < 16 ? (w.kst > 0 ? w.kst : 1) : 16;
+    w.per = wide_cdiv(w.kst > 0 ? w.kst : 1, w.splits);
+    w.splits = wide_cdiv(w.kst > 0 ? w.kst : 1, w.per);
+    const int64_t Ep = (int64_t)w.mtiles * WIDE_TM;
+    const int64_t img = (int64_t)w.mtiles * w.w_ks * WIDE_A_SLICE;  // [Ep x np] hi | lo = the same bytes in either orientation
+    int64_t p = 0;
+    auto take = [&](int64_t b) { int64_t q = p; p += (b + 1023) / 1024 * 1024; return q; };
+    w.u = take((int64_t)w.mtiles * o.ks0 * WIDE_A_SLICE);
+    w.ut = take((int64_t)w.kst * WIDE_B_SLICE);
+    w.a1 = take(img);
+    w.a1t = take(img);
+    w.d1 = take(Ep * w.np * 4);
+    w.g2 = take(img);
+    w.g2t = take(img);
+    w.g1m = take(img);
+    w.g1x = take(img);
+    w.g1t = take(img);
+    w.rows = take(Ep * w.np * 4);
+    w.q = take(Ep * 4);
+    w.gphi = take(Ep * 4);
+    w.phip = take((int64_t)o.ntx2 * Ep * 4);
+    w.phi = take(Ep * 4);
+    w.gu = take(Ep * 128 * 4);
     w.total = p;
     return w;
 }

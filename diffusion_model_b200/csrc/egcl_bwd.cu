@@ -452,6 +452,13 @@ int egnn_tc_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const fl
                           const float* x, const float* gM, const float* gdx, const float* coefS, float* Gr, float* Gs,
                           float* part, int precision, cudaStream_t st);
 
+// tc_wide.cu: tile-GEMM backward of the edge phase for the networks the fused kernels do not cover
+int egnn_wide_bwd_rows(const egnn_net_t& net, int64_t E);
+int64_t egnn_wide_bwd_bytes(const egnn_net_t& net, int64_t E);
+int egnn_wide_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
+                            const float* h, const float* x, const float* gM, const float* gdx, const float* coefS, float* Gr,
+                            float* Gs, float* part, float* scratch, int precision, cudaStream_t st);
+
 namespace {
 
 constexpr int kNumSM = 148;  // B200
@@ -491,6 +498,7 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     w.gridE = (int)(tilesE < kNumSM ? tilesE : kNumSM);
     if (tc_supported(n) && E > 0 && egnn_tc_bwd_grid(E) > w.gridE) w.gridE = egnn_tc_bwd_grid(E);
     if (tc_bwd256_supported(n) && egnn_tc_bwd256_rows(E) > w.gridE) w.gridE = egnn_tc_bwd256_rows(E);
+    if (wide_fwd_supported(n) && egnn_wide_bwd_rows(n, E) > w.gridE) w.gridE = egnn_wide_bwd_rows(n, E);
     w.gridN = node_bwd_rows(n, N);
     if (tc_node_supported(n) && egnn_tc_node_bwd_grid(N) > w.gridN) w.gridN = egnn_tc_node_bwd_grid(N);
     const int64_t W = n.H + 3;
@@ -506,7 +514,8 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     w.ghb = take(2 * N * n.H);
     w.gxb = take(2 * N * 3);
     w.part = take((int64_t)(w.gridE + w.gridN) * layer_off(n).total);
-    w.img = take(tc_bwd256_supported(n) ? egnn_tc_bwd256_img_bytes(E) / 4 : 0);  // 16-byte aligned: every take() is rounded to 4 floats
+    w.img = take(tc_bwd256_supported(n) ? egnn_tc_bwd256_img_bytes(E) / 4      // 16-byte aligned: every take() is rounded to 4 floats
+                 : wide_fwd_supported(n) && E > 0 ? egnn_wide_bwd_bytes(n, E) / 4 : 0);
     w.total = p;
     return w;
 }
@@ -577,6 +586,7 @@ static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const
     // persistent in TMEM, d = 256 the two-kernel form of tc_edge256_bwd.cu
     const bool use_tc = precision != EGNN_PREC_FP32 && tc_supported(*net);
     const bool use_tc256 = precision != EGNN_PREC_FP32 && tc_bwd256_supported(*net);
+    const bool use_wide = precision != EGNN_PREC_FP32 && wide_fwd_supported(*net);
     const FwdWs fw = fwd_ws(*net, g->N, g->E, g->G);
     const BwdWs bw = bwd_ws(*net, g->N, g->E, g->G);
     if (ws_floats < bw.total) {
@@ -596,7 +606,7 @@ static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const
     EGNN_SMEM_ATTR(egcl_node_bwd<8>, 200 * 1024);
     const bool node_tc = use_tc && tc_node_supported(*net);
     // rows actually used by this call's kernels (the workspace is sized for the larger of the two paths)
-    const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : use_tc256 ? egnn_tc_bwd256_rows(E)
+    const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : use_tc256 ? egnn_tc_bwd256_rows(E) : use_wide ? egnn_wide_bwd_rows(*net, E)
                                                             : (int)std::min<int64_t>((E + bw.TEB - 1) / bw.TEB, kNumSM)) : 0;
     const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : node_bwd_rows(*net, N);
     RowMap256 m256{};
@@ -650,6 +660,10 @@ static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const
             if (int rc = egnn_tc_edge_backward256(*net, *g, Pk, hl, xl, ws + bw.gM, ws + bw.gdx, ws + bw.coefS, ws + bw.Gr,
                                                   ws + bw.Gs, ws + bw.part, reinterpret_cast<uint8_t*>(ws + bw.img),
                                                   precision, st))
+                return rc;
+        } else if (E > 0 && use_wide) {
+            if (int rc = egnn_wide_edge_backward(*net, *g, P, Pk, hl, xl, ws + bw.gM, ws + bw.gdx, ws + bw.coefS, ws + bw.Gr,
+                                                 ws + bw.Gs, ws + bw.part, ws + bw.img, precision, st))
                 return rc;
         } else if (E > 0 && use_tc) {
             if (int rc = egnn_tc_edge_backward(*net, *g, Pk, hl, xl, ws + bw.gM, ws + bw.gdx, ws + bw.coefS, ws + bw.Gr,

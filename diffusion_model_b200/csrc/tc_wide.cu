@@ -21,10 +21,13 @@
 namespace {
 
 // ---- weights -> tile images ---------------------------------------------------------------------------------------------------
-// W [N x K] (nn.Linear: out x in) -> for N tile nt and K slice ks the block (nt * KS + ks): hi chunks (n, j) at j * 4096 + n * 16,
-// lo at 32768 + the same; rows >= N and columns >= K are zero
-__device__ void wide_pack_matrix(const float* __restrict__ W, int N, int K, int NT, int KS, uint8_t* __restrict__ dst, int t0, int stride) {
+// Image of a matrix B [N rows x K] for N tile nt and K slice ks: block (nt * KSstride + ks_off + ks): hi chunks (n, j) at
+// j * 4096 + n * 16, lo at 32768 + the same; rows >= N and columns >= K are zero.  B(n, k) = W[n * ld + k] (forward: nn.Linear
+// stores out x in) or, transposed = true, W[k * ld + n] (dgrad images: rows = input features)
+__device__ void wide_pack_matrix(const float* __restrict__ W, int N, int K, int ld, bool transposed, int KSstride, int ks_off,
+                                 uint8_t* __restrict__ dst, int t0, int stride) {
     const int per_block = WIDE_TN * (WIDE_TK / 8);
+    const int NT = wide_cdiv(N, WIDE_TN), KS = wide_cdiv(K, WIDE_TK);
     for (int idx = t0; idx < NT * KS * per_block; idx += stride) {
         const int blk = idx / per_block, rem = idx - blk * per_block;
         const int j = rem / WIDE_TN, nl = rem - j * WIDE_TN;
@@ -34,11 +37,11 @@ __device__ void wide_pack_matrix(const float* __restrict__ W, int N, int K, int 
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const int k = k0 + 2 * q;
-            const float v0 = (n < N && k < K) ? W[(size_t)n * K + k] : 0.f;
-            const float v1 = (n < N && k + 1 < K) ? W[(size_t)n * K + k + 1] : 0.f;
+            const float v0 = (n < N && k < K) ? (transposed ? W[(size_t)k * ld + n] : W[(size_t)n * ld + k]) : 0.f;
+            const float v1 = (n < N && k + 1 < K) ? (transposed ? W[(size_t)(k + 1) * ld + n] : W[(size_t)n * ld + k + 1]) : 0.f;
             tc::split2(v0, v1, hi[q], lo[q]);
         }
-        uint8_t* b = dst + (size_t)blk * WIDE_B_SLICE + j * (WIDE_TN * 16) + nl * 16;
+        uint8_t* b = dst + (size_t)(nt * KSstride + ks_off + ks) * WIDE_B_SLICE + j * (WIDE_TN * 16) + nl * 16;
         *reinterpret_cast<uint4*>(b) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
         *reinterpret_cast<uint4*>(b + WIDE_B_SLICE / 2) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
     }
@@ -51,16 +54,24 @@ __global__ void __launch_bounds__(256) wide_pack_kernel(egnn_net_t net, const fl
     const float* P = params + (size_t)blockIdx.y * lo.total;
     uint8_t* img = reinterpret_cast<uint8_t*>(packed + (size_t)blockIdx.y * po.total + po.tc);
     const int K0 = 2 * net.H + 1, t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
-    wide_pack_matrix(P + lo.wm1, net.Mh, K0, wo.ntm1, wo.ks0, img + (size_t)wo.m1 * WIDE_B_SLICE, t0, stride);
-    wide_pack_matrix(P + lo.wm2, net.Ms, net.Mh, wo.ntm2, wo.ksm, img + (size_t)wo.m2 * WIDE_B_SLICE, t0, stride);
-    wide_pack_matrix(P + lo.wx1, net.Xh, K0, wo.ntx1, wo.ks0, img + (size_t)wo.x1 * WIDE_B_SLICE, t0, stride);
-    wide_pack_matrix(P + lo.wx2, net.Xh, net.Xh, wo.ntx2, wo.ksx, img + (size_t)wo.x2 * WIDE_B_SLICE, t0, stride);
+    auto at = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
+    wide_pack_matrix(P + lo.wm1, net.Mh, K0, K0, false, wo.ks0, 0, at(wo.m1), t0, stride);
+    wide_pack_matrix(P + lo.wm2, net.Ms, net.Mh, net.Mh, false, wo.ksm, 0, at(wo.m2), t0, stride);
+    wide_pack_matrix(P + lo.wx1, net.Xh, K0, K0, false, wo.ks0, 0, at(wo.x1), t0, stride);
+    wide_pack_matrix(P + lo.wx2, net.Xh, net.Xh, net.Xh, false, wo.ksx, 0, at(wo.x2), t0, stride);
+    // dgrad images: ga1 = gz2 . W2 -> rows = columns of W2;  gu = [gz1m | gz1x] . [Wm1 ; Wx1] -> rows = the K0 input columns
+    wide_pack_matrix(P + lo.wm2, net.Mh, net.Ms, net.Mh, true, wo.kss, 0, at(wo.m2t), t0, stride);
+    wide_pack_matrix(P + lo.wx2, net.Xh, net.Xh, net.Xh, true, wo.ksx, 0, at(wo.x2t), t0, stride);
+    wide_pack_matrix(P + lo.wm1, K0, net.Mh, K0, true, wo.ksm + wo.ksx, 0, at(wo.w1t), t0, stride);
+    wide_pack_matrix(P + lo.wx1, K0, net.Xh, K0, true, wo.ksm + wo.ksx, wo.ksm, at(wo.w1t), t0, stride);
 }
 
 // ---- gather: one thread per (edge row, 8-column chunk) of the U image; rows >= E are zero -----------------------------------------
+// UT != nullptr (backward): also the transposed image (rows = the K0 input columns, K = edges), the B operand of dW1 = gz1^T u
 __global__ void __launch_bounds__(256) wide_gather_kernel(int E, int mtiles, int H, int KS0, const int32_t* __restrict__ recv,
                                                           const int32_t* __restrict__ send, const float* __restrict__ h,
-                                                          const float* __restrict__ x, uint8_t* __restrict__ Uimg) {
+                                                          const float* __restrict__ x, uint8_t* __restrict__ Uimg,
+                                                          uint8_t* __restrict__ UT) {
     const int nchunk = KS0 * (WIDE_TK / 8);
     const long long total = (long long)mtiles * WIDE_TM * nchunk;
     for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
@@ -94,6 +105,16 @@ __global__ void __launch_bounds__(256) wide_gather_kernel(int E, int mtiles, int
         uint8_t* b = Uimg + ((size_t)t * KS0 + j / 8) * WIDE_A_SLICE + (j % 8) * (WIDE_TM * 16) + row_in_tile * 16;
         *reinterpret_cast<uint4*>(b) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
         *reinterpret_cast<uint4*>(b + WIDE_A_SLICE / 2) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        if (UT) {
+            uint8_t* tb = UT + (size_t)(e / WIDE_TK) * WIDE_B_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TN * 16) + (e % 8) * 2;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const uint32_t hw = hi[q >> 1], lw = lo[q >> 1];
+                uint8_t* d = tb + (j * 8 + q) * 16;
+                *reinterpret_cast<uint16_t*>(d) = (uint16_t)(q & 1 ? hw >> 16 : hw & 0xffffu);
+                *reinterpret_cast<uint16_t*>(d + WIDE_B_SLICE / 2) = (uint16_t)(q & 1 ? lw >> 16 : lw & 0xffffu);
+            }
+        }
     }
 }
 
@@ -108,37 +129,159 @@ __global__ void __launch_bounds__(WIDE_TN) wide_segsum_kernel(int Ms, const int3
 }
 
 // ---- phi_e = bx3 + sum of the per-N-tile parts (tile order) ---------------------------------------------------------------------
-__global__ void __launch_bounds__(256) wide_phi_kernel(int E, int NT, const float* __restrict__ part, const float* __restrict__ bx3,
-                                                       float* __restrict__ phi) {
+__global__ void __launch_bounds__(256) wide_phi_kernel(int E, int NT, int64_t part_stride, const float* __restrict__ part,
+                                                       const float* __restrict__ bx3, float* __restrict__ phi) {
     const int e = blockIdx.x * 256 + threadIdx.x;
     if (e >= E) return;
     float s = bx3[0];
-    for (int t = 0; t < NT; ++t) s += part[(size_t)t * E + e];
+    for (int t = 0; t < NT; ++t) s += part[(size_t)t * part_stride + e];
     phi[e] = s;
 }
 
+// ---- backward helpers ---------------------------------------------------------------------------------------------------------
+// gphi_e = gdx[i] . r_e  (egcl_bwd.cu: the coordinate branch's row coefficient); rows >= E are zero
+__global__ void __launch_bounds__(256) wide_gphi_kernel(int E, int Ep, const int32_t* __restrict__ recv, const int32_t* __restrict__ send,
+                                                        const float* __restrict__ x, const float* __restrict__ gdx,
+                                                        float* __restrict__ gphi) {
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    if (e >= Ep) return;
+    float v = 0.f;
+    if (e < E) {
+        const int i = recv[e], j = send[e];
+        v = gdx[3 * i] * (x[3 * i] - x[3 * j]) + gdx[3 * i + 1] * (x[3 * i + 1] - x[3 * j + 1]) + gdx[3 * i + 2] * (x[3 * i + 2] - x[3 * j + 2]);
+    }
+    gphi[e] = v;
+}
+
+// column sums of a transposed (rows = features) hi | lo image over the 64-edge slices of split blockIdx.y: bias gradients.
+// 128 threads = the 128 feature rows of tile blockIdx.x; fixed order inside a split, the splits are summed by reduce_partials_kernel
+__global__ void __launch_bounds__(128) wide_colsum_T_kernel(const uint8_t* __restrict__ T, int kst, int per, int N, float* __restrict__ part,
+                                                            int64_t part_stride) {
+    const int n = blockIdx.x * 128 + threadIdx.x, s = blockIdx.y;
+    const int k0 = s * per, k1 = min(k0 + per, kst);
+    float sum = 0.f;
+    for (int ks = k0; ks < k1; ++ks) {
+        const uint8_t* b = T + ((size_t)blockIdx.x * kst + ks) * WIDE_A_SLICE + threadIdx.x * 16;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint4 h = *reinterpret_cast<const uint4*>(b + j * (WIDE_TM * 16));
+            const uint4 l = *reinterpret_cast<const uint4*>(b + j * (WIDE_TM * 16) + WIDE_A_SLICE / 2);
+            const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                sum += __uint_as_float(hw[q] << 16) + __uint_as_float(lw[q] << 16);
+                sum += __uint_as_float(hw[q] & 0xffff0000u) + __uint_as_float(lw[q] & 0xffff0000u);
+            }
+        }
+    }
+    if (n < N) part[(size_t)s * part_stride + n] = sum;
+}
+
+// column sums of fp32 rows [E x ld] over the edges of split blockIdx.y (32 columns x 8 row lanes per CTA, fixed order)
+__global__ void __launch_bounds__(256) wide_colsum_rows_kernel(const float* __restrict__ rows, int ld, int ncols, int E, int per_edges,
+                                                               float* __restrict__ part, int64_t part_stride) {
+    __shared__ float red[8][32];
+    const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5, c = blockIdx.x * 32 + cl, s = blockIdx.y;
+    const int e0 = s * per_edges, e1 = min(e0 + per_edges, E);
+    float sum = 0.f;
+    if (c < ncols)
+        for (int e = e0 + rl; e < e1; e += 8) sum += rows[(size_t)e * ld + c];
+    red[rl][cl] = sum;
+    __syncthreads();
+    if (rl == 0 && c < ncols) {
+        float t = red[0][cl];
+#pragma unroll
+        for (int k = 1; k < 8; ++k) t += red[k][cl];
+        part[(size_t)s * part_stride + c] = t;
+    }
+}
+
+// per-edge outputs of the layer backward (egcl_bwd.cu: egcl_edge_bwd, "per-edge outputs"): receiver / sender contributions
+__global__ void __launch_bounds__(256) wide_edge_out_kernel(int E, int H, const int32_t* __restrict__ recv, const int32_t* __restrict__ send,
+                                                            const int32_t* __restrict__ node_graph, const float* __restrict__ x,
+                                                            const float* __restrict__ gu, const float* __restrict__ gdx,
+                                                            const float* __restrict__ coefS, const float* __restrict__ phi,
+                                                            float* __restrict__ Gr, float* __restrict__ Gs) {
+    const int W = H + 3;
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= (long long)E * W) return;
+    const int e = (int)(idx / W), c = (int)(idx - (long long)e * W);
+    if (c < H) {
+        Gr[idx] = gu[(size_t)e * 128 + c];
+        Gs[idx] = gu[(size_t)e * 128 + H + c];
+    } else {
+        const int k = c - H, i = recv[e], j = send[e];
+        const float gd = gu[(size_t)e * 128 + 2 * H];  // grad of d_e = |r_e|^2
+        const float rk = x[3 * i + k] - x[3 * j + k];
+        const float gr = gdx[(size_t)i * 3 + k] * phi[e] + (coefS[node_graph[i]] + 2.f * gd) * rk;
+        Gr[idx] = gr;
+        Gs[idx] = -gr;
+    }
+}
+
 // ---- the tile GEMM ------------------------------------------------------------------------------------------------------------
-enum { WIDE_IMG = 0, WIDE_GATE = 1, WIDE_ROWDOT = 2 };
+// forward epilogues:  IMG (SiLU -> next operand image), GATE (gated messages), ROWDOT (phi parts)
+// backward epilogues: IMG_BWD (IMG + transposed image + SiLU' rows), GATE_BWD / ROWDOT_BWD (recompute the second Linear and
+//                     turn it into gz2: operand image + transposed image + the rows whose column sums are d wa / d wx3),
+//                     DGRAD (gz1 = acc * SiLU'(z1): image + transposed image), F32 (plain rows: gu), WGRAD (split-K partial
+//                     tile of a weight gradient, stored in the parameter layout of one row of the partial buffer)
+enum { WIDE_IMG = 0, WIDE_GATE = 1, WIDE_ROWDOT = 2, WIDE_IMG_BWD = 3, WIDE_GATE_BWD = 4, WIDE_ROWDOT_BWD = 5, WIDE_DGRAD = 6,
+       WIDE_F32 = 7, WIDE_WGRAD = 8 };
 struct WideGemmArgs {
-    const uint8_t* A;  // activation image: slice (mt, ks) at (mt * a_ks + ks) * WIDE_A_SLICE
-    const uint8_t* B;  // weight image of this matrix: block (nt, ks) at (nt * KS + ks) * WIDE_B_SLICE
-    int a_ks, KS, NT, mtiles, E, N;
-    const float* bias;  // [N]
-    uint8_t* out_img;   // WIDE_IMG: the next GEMM's activation image, out_ks slices per tile
+    const uint8_t *A, *A2;  // A operand images (rows x K slices): slice (mt, ks) at (mt * a_ks + ks) * WIDE_A_SLICE; K slices >= ks_split
+    int a_ks, a2_ks, ks_split;  // come from A2 (slice ks - ks_split, row stride a2_ks)
+    const uint8_t* B;       // B operand image: block (nt, ks) at (nt * b_ks + ks) * WIDE_B_SLICE
+    int b_ks;
+    int KS, KS_total;       // K slices per tile, and in all: split s of a WGRAD tile covers [s * KS, min((s + 1) * KS, KS_total))
+    int NT, mtiles, splits;
+    int E, N;               // valid rows, valid output columns (WGRAD: valid feature rows n, valid input columns k)
+    const float* bias;      // [N]
+    uint8_t* out_img;       // operand image written by IMG / IMG_BWD / GATE_BWD / ROWDOT_BWD / DGRAD, out_ks slices per row tile
     int out_ks;
-    const float *vec, *scalar;  // WIDE_GATE: wa [N], ba;  WIDE_ROWDOT: wx3 [N]
-    float* out;                 // WIDE_GATE: g*m [E][WIDE_TN];  WIDE_ROWDOT: parts [NT][E]
+    uint8_t* out_T;         // transposed image (kst = 64-edge slices): IMG_BWD rows = 256-row B tiles, the others 128-row A tiles
+    int kst;
+    const float *vec, *scalar;  // GATE*: wa [N], ba;  ROWDOT*: wx3 [N]
+    float* out;                 // GATE: g*m [E][WIDE_TN]; ROWDOT*: phi parts [NT][out_ld]; F32: rows [E][out_ld]; WGRAD: partial rows
+    int64_t out_ld;             // WGRAD: row stride of the weight matrix; its split stride is out_split
+    int64_t out_split;
+    float* rows;                // IMG_BWD: SiLU' rows;  GATE_BWD: gs * m;  ROWDOT_BWD: gphi * a2;  DGRAD (in): SiLU' rows
+    int rows_ld;
+    float* q;                   // GATE_BWD: gs per edge
+    const float* gM;            // GATE_BWD: [N nodes][Ms] gradient of the message sums
+    const int32_t* recv;
+    const float* gphi;          // ROWDOT_BWD: per edge
 };
 constexpr int WIDE_THREADS = 512, WIDE_STAGES = 2, WIDE_STAGE_BYTES = WIDE_A_SLICE + WIDE_B_SLICE;
-constexpr int WIDE_SMEM = WIDE_STAGES * WIDE_STAGE_BYTES + 1024 /*bias, vec*/ * 2 + 4 * WIDE_TM * 4 /*row partials*/ + 64;
+constexpr int WIDE_SMEM = WIDE_STAGES * WIDE_STAGE_BYTES + 1024 /*bias, vec*/ * 2 + 2 * 4 * WIDE_TM * 4 /*row partials*/ + 64;
+
+// 8 consecutive columns of row r -> chunk j of a [128-row] operand slice (hi | lo)
+__device__ __forceinline__ void wide_store_chunk(uint8_t* slice_row, int j, const float (&v)[8]) {
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) tc::split2(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+    *reinterpret_cast<uint4*>(slice_row + j * (WIDE_TM * 16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(slice_row + j * (WIDE_TM * 16) + WIDE_A_SLICE / 2) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+}
+// the same 8 values into the transposed image: element (feature row row0 + i, this thread's edge); tbase points at the
+// edge's 2-byte lane of feature row 0 of the slice, lo_off = half the slice
+__device__ __forceinline__ void wide_store_T(uint8_t* tbase, int row0, int lo_off, const float (&v)[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const __nv_bfloat16 h = __float2bfloat16_rn(v[i]);
+        const __nv_bfloat16 l = __float2bfloat16_rn(v[i] - __bfloat162float(h));
+        *reinterpret_cast<__nv_bfloat16*>(tbase + (row0 + i) * 16) = h;
+        *reinterpret_cast<__nv_bfloat16*>(tbase + (row0 + i) * 16 + lo_off) = l;
+    }
+}
 
 template <int MODE, int NPASS>
 __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
     float* sBias = reinterpret_cast<float*>(smem + WIDE_STAGES * WIDE_STAGE_BYTES);
     float* sVec = sBias + WIDE_TN;
-    float* sDot = sVec + WIDE_TN;  // [4][128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sDot + 4 * WIDE_TM);  // full[2], empty[2], acc
+    float* sDot = sVec + WIDE_TN;      // [4][128]
+    float* sDot2 = sDot + 4 * WIDE_TM;  // [4][128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sDot2 + 4 * WIDE_TM);  // full[2], empty[2], acc
     uint32_t* slot = reinterpret_cast<uint32_t*>(bars + 5);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, q = warp & 3, cg = warp >> 2;
     if (warp == 0) tc::tmem_alloc(slot, 256);
@@ -151,36 +294,53 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
     tc::fence_after_sync();
     const uint32_t tmem = *slot;
     const uint32_t sb = tc::smem_u32(smem);
-    const int tiles = a.mtiles * a.NT;
+    const int tiles = a.mtiles * a.NT * a.splits;
     const int nit = (int)blockIdx.x < tiles ? (tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-    const int total = nit * a.KS;
     bool ok = true;
-    int gl = 0;  // producer: slices requested so far (global over this CTA's tiles)
+    // tile number -> (N tile, row tile, K range).  The NT tiles of one row tile run side by side: its A slices are shared in L2
+    auto decode = [&](int it, int& nt, int& mt, int& kb, int& kc) {
+        const int tile = blockIdx.x + it * gridDim.x;
+        nt = tile % a.NT;
+        const int rest = tile / a.NT;
+        mt = rest % a.mtiles;
+        const int s = rest / a.mtiles;
+        kb = s * a.KS;
+        kc = min(a.KS, a.KS_total - kb);
+    };
+    int p_it = 0, p_ks = 0, p_g = 0;  // producer: next slice to request = slice p_ks of this CTA's tile p_it; p_g counts requests
+    int m_g = 0;                      // issuer: slices consumed
     pdl_launch_dependents();
     pdl_wait();  // the A image comes from the kernel in front
 
     for (int it = 0; it < nit; ++it) {
-        const int tile = blockIdx.x + it * gridDim.x;
-        const int nt = tile % a.NT, mt = tile / a.NT;  // the NT tiles of one edge tile run side by side: its A slices are shared in L2
+        int nt, mt, kb, kc;
+        decode(it, nt, mt, kb, kc);
         if (tid == 0) {
             // this tile's slices plus the first two of the next tile (they land while the epilogue runs)
-            int target = (it + 1) * a.KS + WIDE_STAGES;
-            if (target > total) target = total;
-            for (; gl < target; ++gl) {
-                const int s = gl % WIDE_STAGES, u = gl / WIDE_STAGES;
+            while (p_it < nit && (p_it <= it || (p_it == it + 1 && p_ks < WIDE_STAGES))) {
+                int lnt, lmt, lkb, lkc;
+                decode(p_it, lnt, lmt, lkb, lkc);
+                if (p_ks >= lkc) {
+                    ++p_it;
+                    p_ks = 0;
+                    continue;
+                }
+                const int s = p_g % WIDE_STAGES, u = p_g / WIDE_STAGES;
                 if (u > 0) ok = tc::mbar_wait(&bars[2 + s], (u - 1) & 1) && ok;
-                const int lit = gl / a.KS, ks = gl - lit * a.KS;
-                const int lt = blockIdx.x + lit * gridDim.x;
-                const int lnt = lt % a.NT, lmt = lt / a.NT;
+                const int ks = lkb + p_ks;
+                const uint8_t* srcA = ks < a.ks_split ? a.A + ((size_t)lmt * a.a_ks + ks) * WIDE_A_SLICE
+                                                      : a.A2 + ((size_t)lmt * a.a2_ks + (ks - a.ks_split)) * WIDE_A_SLICE;
                 const uint32_t full = tc::smem_u32(&bars[s]), dst = sb + s * WIDE_STAGE_BYTES;
                 tc::mbar_expect_tx(full, WIDE_STAGE_BYTES);
-                tc::bulk_g2s(dst, a.A + ((size_t)lmt * a.a_ks + ks) * WIDE_A_SLICE, WIDE_A_SLICE, full);
-                tc::bulk_g2s(dst + WIDE_A_SLICE, a.B + ((size_t)lnt * a.KS + ks) * WIDE_B_SLICE, WIDE_B_SLICE, full);
+                tc::bulk_g2s(dst, srcA, WIDE_A_SLICE, full);
+                tc::bulk_g2s(dst + WIDE_A_SLICE, a.B + ((size_t)lnt * a.b_ks + ks) * WIDE_B_SLICE, WIDE_B_SLICE, full);
+                ++p_ks;
+                ++p_g;
             }
         } else if (tid == 32) {
-            for (int ks = 0; ks < a.KS; ++ks) {
-                const int g = it * a.KS + ks, s = g % WIDE_STAGES;
-                ok = tc::mbar_wait(&bars[s], (g / WIDE_STAGES) & 1) && ok;
+            for (int ks = 0; ks < kc; ++ks, ++m_g) {
+                const int s = m_g % WIDE_STAGES;
+                ok = tc::mbar_wait(&bars[s], (m_g / WIDE_STAGES) & 1) && ok;
                 tc::fence_after_sync();
                 const uint32_t base = sb + s * WIDE_STAGE_BYTES;
                 const TcOperand opA{base, base + WIDE_A_SLICE / 2, WIDE_TM * 16, false};
@@ -191,10 +351,11 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
             tc::mma_commit(&bars[4]);
         }
         // bias / vector of this N tile (columns past N are zero: their accumulators are zero too, SiLU(0) = 0)
-        if (tid >= 64 && tid < 64 + WIDE_TN) {
+        if (MODE != WIDE_DGRAD && MODE != WIDE_F32 && MODE != WIDE_WGRAD && tid >= 64 && tid < 64 + WIDE_TN) {
             const int c = tid - 64, n = nt * WIDE_TN + c;
             sBias[c] = n < a.N ? a.bias[n] : 0.f;
-            if (MODE != WIDE_IMG) sVec[c] = n < a.N ? a.vec[n] : 0.f;
+            if (MODE == WIDE_GATE || MODE == WIDE_ROWDOT || MODE == WIDE_GATE_BWD || MODE == WIDE_ROWDOT_BWD)
+                sVec[c] = n < a.N ? a.vec[n] : 0.f;
         }
         __syncthreads();
         ok = tc::mbar_wait(&bars[4], it & 1) && ok;
@@ -202,50 +363,164 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
         __syncwarp();
 
         const int r = q * 32 + lane, e = mt * WIDE_TM + r;
-        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + cg * 64;
-        if (MODE == WIDE_IMG) {
-            uint8_t* o = a.out_img + ((size_t)mt * a.out_ks + nt * (WIDE_TN / WIDE_TK) + cg) * WIDE_A_SLICE + r * 16;
-#pragma unroll 1
-            for (int j = 0; j < 8; ++j) {
-                float v[8];
-                tc::tmem_ld8(taddr + 8 * j, v);
-                uint32_t hi[4], lo[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    tc::split2(tc_silu<true>(v[2 * i] + sBias[cg * 64 + 8 * j + 2 * i]),
-                               tc_silu<true>(v[2 * i + 1] + sBias[cg * 64 + 8 * j + 2 * i + 1]), hi[i], lo[i]);
-                *reinterpret_cast<uint4*>(o + j * (WIDE_TM * 16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<uint4*>(o + j * (WIDE_TM * 16) + WIDE_A_SLICE / 2) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        const bool live = e < a.E;
+        const int c0 = cg * 64;                // this thread's 64 columns of the tile
+        const int n0 = nt * WIDE_TN + c0;      // ... of the matrix
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + c0;
+        if (MODE == WIDE_IMG || MODE == WIDE_IMG_BWD) {
+            uint8_t* o = a.out_img + ((size_t)mt * a.out_ks + n0 / WIDE_TK) * WIDE_A_SLICE + r * 16;
+            uint8_t* t = nullptr;
+            float* d1 = nullptr;
+            if (MODE == WIDE_IMG_BWD) {
+                t = a.out_T + ((size_t)nt * a.kst + e / WIDE_TK) * WIDE_B_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TN * 16) + (e % 8) * 2;
+                d1 = a.rows + (size_t)e * a.rows_ld + n0;
             }
-        } else {
-            // row dot of the activated outputs with vec: 64 columns per thread, then the four column groups in fixed order
-            float dot = 0.f;
 #pragma unroll 1
             for (int j = 0; j < 8; ++j) {
                 float v[8];
                 tc::tmem_ld8(taddr + 8 * j, v);
+                if (MODE == WIDE_IMG) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) dot = fmaf(tc_silu<true>(v[i] + sBias[cg * 64 + 8 * j + i]), sVec[cg * 64 + 8 * j + i], dot);
+                    for (int i = 0; i < 8; ++i) v[i] = tc_silu<true>(v[i] + sBias[c0 + 8 * j + i]);
+                } else {
+                    float d[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        tc_silu_and_grad(v[i] + sBias[c0 + 8 * j + i], v[i], d[i]);
+                        if (!live) v[i] = 0.f, d[i] = 0.f;
+                    }
+                    *reinterpret_cast<float4*>(d1 + 8 * j) = make_float4(d[0], d[1], d[2], d[3]);
+                    *reinterpret_cast<float4*>(d1 + 8 * j + 4) = make_float4(d[4], d[5], d[6], d[7]);
+                    wide_store_T(t, c0 + 8 * j, WIDE_B_SLICE / 2, v);
+                }
+                wide_store_chunk(o, j, v);
+            }
+        } else if (MODE == WIDE_GATE || MODE == WIDE_ROWDOT || MODE == WIDE_GATE_BWD || MODE == WIDE_ROWDOT_BWD) {
+            // row dot of the activated outputs with vec: 64 columns per thread, then the four column groups in fixed order
+            const float* gMi = nullptr;
+            float gph = 0.f;
+            uint8_t *o = nullptr, *t = nullptr;
+            if (MODE == WIDE_GATE_BWD) gMi = a.gM + (size_t)(live ? a.recv[e] : 0) * a.N;
+            if (MODE == WIDE_ROWDOT_BWD) gph = live ? a.gphi[e] : 0.f;
+            if (MODE == WIDE_GATE_BWD || MODE == WIDE_ROWDOT_BWD) {
+                o = a.out_img + ((size_t)mt * a.out_ks + n0 / WIDE_TK) * WIDE_A_SLICE + r * 16;
+                t = a.out_T + ((size_t)(n0 / WIDE_TM) * a.kst + e / WIDE_TK) * WIDE_A_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TM * 16) + (e % 8) * 2;
+            }
+            float dot = 0.f, dot2 = 0.f;
+#pragma unroll 1
+            for (int j = 0; j < 8; ++j) {
+                float v[8];
+                tc::tmem_ld8(taddr + 8 * j, v);
+                if (MODE == WIDE_ROWDOT_BWD) {
+                    // a2 = SiLU(z2), phi part += wx3 . a2;  gz2 = gphi wx3 SiLU'(z2);  rows = gphi a2 (column sums = d wx3)
+                    float g2[8], ga[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float act, dact;
+                        tc_silu_and_grad(v[i] + sBias[c0 + 8 * j + i], act, dact);
+                        const float w = sVec[c0 + 8 * j + i];
+                        dot = fmaf(act, w, dot);
+                        g2[i] = gph * w * dact;
+                        ga[i] = gph * act;
+                    }
+                    float* ro = a.rows + (size_t)e * a.rows_ld + n0 + 8 * j;
+                    *reinterpret_cast<float4*>(ro) = make_float4(ga[0], ga[1], ga[2], ga[3]);
+                    *reinterpret_cast<float4*>(ro + 4) = make_float4(ga[4], ga[5], ga[6], ga[7]);
+                    wide_store_chunk(o, j, g2);
+                    wide_store_T(t, (c0 % WIDE_TM) + 8 * j, WIDE_A_SLICE / 2, g2);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float m = tc_silu<true>(v[i] + sBias[c0 + 8 * j + i]);
+                        dot = fmaf(m, sVec[c0 + 8 * j + i], dot);
+                        if (MODE == WIDE_GATE_BWD) dot2 = fmaf(m, c0 + 8 * j + i < a.N ? gMi[c0 + 8 * j + i] : 0.f, dot2);
+                    }
+                }
             }
             sDot[cg * WIDE_TM + r] = dot;
+            if (MODE == WIDE_GATE_BWD) sDot2[cg * WIDE_TM + r] = dot2;
             __syncthreads();
             const float full = ((sDot[r] + sDot[WIDE_TM + r]) + sDot[2 * WIDE_TM + r]) + sDot[3 * WIDE_TM + r];
-            if (MODE == WIDE_ROWDOT) {
-                if (cg == 0 && e < a.E) a.out[(size_t)nt * a.E + e] = full;
-            } else {
+            if (MODE == WIDE_ROWDOT || MODE == WIDE_ROWDOT_BWD) {
+                if (cg == 0 && live) a.out[(size_t)nt * a.out_ld + e] = full;
+            } else if (MODE == WIDE_GATE) {
                 // second pass over the accumulator (tcgen05.ld is warp-collective: every lane runs it, rows past E only skip the store)
                 const float gate = tc_sigmoid<false>(full + a.scalar[0]);
-                float* o = a.out + (size_t)e * WIDE_TN + cg * 64;
+                float* o2 = a.out + (size_t)e * WIDE_TN + c0;
 #pragma unroll 1
                 for (int j = 0; j < 8; ++j) {
                     float v[8];
                     tc::tmem_ld8(taddr + 8 * j, v);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) v[i] = gate * tc_silu<true>(v[i] + sBias[cg * 64 + 8 * j + i]);
-                    if (e < a.E) {
-                        *reinterpret_cast<float4*>(o + 8 * j) = make_float4(v[0], v[1], v[2], v[3]);
-                        *reinterpret_cast<float4*>(o + 8 * j + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                    for (int i = 0; i < 8; ++i) v[i] = gate * tc_silu<true>(v[i] + sBias[c0 + 8 * j + i]);
+                    if (live) {
+                        *reinterpret_cast<float4*>(o2 + 8 * j) = make_float4(v[0], v[1], v[2], v[3]);
+                        *reinterpret_cast<float4*>(o2 + 8 * j + 4) = make_float4(v[4], v[5], v[6], v[7]);
                     }
+                }
+            } else {
+                // GATE_BWD: g = sigmoid(wa.m + ba); t = gM[i].m; gs = t g (1-g); gz2 = (gM[i] g + gs wa) SiLU'(z2); rows = gs m
+                const float tt = ((sDot2[r] + sDot2[WIDE_TM + r]) + sDot2[2 * WIDE_TM + r]) + sDot2[3 * WIDE_TM + r];
+                const float gate = tc_sigmoid<false>(full + a.scalar[0]);
+                const float gs = live ? tt * gate * (1.f - gate) : 0.f;
+                if (cg == 0) a.q[e] = gs;
+                float* ro = a.rows + (size_t)e * a.rows_ld + c0;
+#pragma unroll 1
+                for (int j = 0; j < 8; ++j) {
+                    float v[8], g2[8];
+                    tc::tmem_ld8(taddr + 8 * j, v);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float m, dm;
+                        tc_silu_and_grad(v[i] + sBias[c0 + 8 * j + i], m, dm);
+                        const int c = c0 + 8 * j + i;
+                        const float gm = c < a.N && live ? gMi[c] : 0.f;
+                        g2[i] = fmaf(gm, gate, gs * sVec[c]) * dm;
+                        v[i] = gs * m;
+                    }
+                    *reinterpret_cast<float4*>(ro + 8 * j) = make_float4(v[0], v[1], v[2], v[3]);
+                    *reinterpret_cast<float4*>(ro + 8 * j + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                    wide_store_chunk(o, j, g2);
+                    wide_store_T(t, (c0 % WIDE_TM) + 8 * j, WIDE_A_SLICE / 2, g2);
+                }
+            }
+        } else if (MODE == WIDE_DGRAD) {
+            uint8_t* o = a.out_img + ((size_t)mt * a.out_ks + n0 / WIDE_TK) * WIDE_A_SLICE + r * 16;
+            uint8_t* t = a.out_T + ((size_t)(n0 / WIDE_TM) * a.kst + e / WIDE_TK) * WIDE_A_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TM * 16) + (e % 8) * 2;
+            const float* d1 = a.rows + (size_t)e * a.rows_ld + n0;
+#pragma unroll 1
+            for (int j = 0; j < 8; ++j) {
+                float v[8];
+                tc::tmem_ld8(taddr + 8 * j, v);
+                const float4 da = *reinterpret_cast<const float4*>(d1 + 8 * j), db = *reinterpret_cast<const float4*>(d1 + 8 * j + 4);
+                const float d[8] = {da.x, da.y, da.z, da.w, db.x, db.y, db.z, db.w};
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * d[i] : 0.f;
+                wide_store_chunk(o, j, v);
+                wide_store_T(t, (c0 % WIDE_TM) + 8 * j, WIDE_A_SLICE / 2, v);
+            }
+        } else if (MODE == WIDE_F32) {
+            float* o = a.out + (size_t)e * a.out_ld + n0;
+#pragma unroll 1
+            for (int j = 0; j < 8; ++j) {
+                float v[8];
+                tc::tmem_ld8(taddr + 8 * j, v);
+                if (live && n0 + 8 * j < a.out_ld) {
+                    *reinterpret_cast<float4*>(o + 8 * j) = make_float4(v[0], v[1], v[2], v[3]);
+                    *reinterpret_cast<float4*>(o + 8 * j + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                }
+            }
+        } else {  // WIDE_WGRAD: row e = feature n of the weight matrix, columns = its input features
+            const int s = (blockIdx.x + it * gridDim.x) / (a.NT * a.mtiles);
+            float* o = a.out + (size_t)s * a.out_split + (size_t)e * a.out_ld + n0;
+#pragma unroll 1
+            for (int j = 0; j < 8; ++j) {
+                float v[8];
+                tc::tmem_ld8(taddr + 8 * j, v);
+                if (live) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        if (n0 + 8 * j + i < a.N) o[8 * j + i] = v[i];
                 }
             }
         }
@@ -258,15 +533,12 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
 }
 
 template <int MODE>
-int launch_wide(const WideGemmArgs& a, int precision, cudaStream_t st, const char* what) {
-    const int tiles = a.mtiles * a.NT;
-    // persistent: one CTA per SM at most; the tile count is rounded so that every CTA runs the same number of tiles when it can
+int launch_wide(const WideGemmArgs& a, int precision, cudaStream_t st, const char* what, int prof_kind) {
+    const int tiles = a.mtiles * a.NT * a.splits;
+    // persistent: one CTA per SM at most; the grid is rounded so that every CTA runs the same number of tiles when it can
     int grid = tiles < kB200SMs ? tiles : kB200SMs;
-    if (tiles > kB200SMs) {
-        const int per = wide_cdiv(tiles, kB200SMs);
-        grid = wide_cdiv(tiles, per);
-    }
-    egnn_prof_begin(EGNN_K_TC_EDGE_FWD, st);
+    if (tiles > kB200SMs) grid = wide_cdiv(tiles, wide_cdiv(tiles, kB200SMs));
+    egnn_prof_begin(prof_kind, st);
     if (precision == EGNN_PREC_BF16X3) {
         EGNN_SMEM_ATTR((tc_wide_gemm<MODE, 3>), WIDE_SMEM);
         tc_wide_gemm<MODE, 3><<<grid, WIDE_THREADS, WIDE_SMEM, st>>>(a);
@@ -278,6 +550,38 @@ int launch_wide(const WideGemmArgs& a, int precision, cudaStream_t st, const cha
     EGNN_CHECK_LAUNCH(what);
     return EGNN_OK;
 }
+
+WideGemmArgs wide_args(int mtiles, int E) {
+    WideGemmArgs a{};
+    a.mtiles = mtiles;
+    a.E = E;
+    a.splits = 1;
+    a.ks_split = 1 << 30;
+    return a;
+}
+// A image with KS slices per row tile, all of them used; B = KS slices per N tile
+void wide_operands(WideGemmArgs& a, const uint8_t* A, int a_ks, const uint8_t* B, int KS, int NT, int N) {
+    a.A = A;
+    a.a_ks = a_ks;
+    a.B = B;
+    a.b_ks = KS;
+    a.KS = a.KS_total = KS;
+    a.NT = NT;
+    a.N = N;
+}
+
+int wide_gather(const egnn_net_t& net, const egnn_graph_t& g, int mtiles, int ks0, const float* h, const float* x, uint8_t* U,
+                uint8_t* UT, cudaStream_t st, int prof_kind) {
+    const long long total = (long long)mtiles * WIDE_TM * ks0 * (WIDE_TK / 8);
+    const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    egnn_prof_begin(prof_kind, st);
+    wide_gather_kernel<<<blocks, 256, 0, st>>>(g.E, mtiles, net.H, ks0, g.recv, g.send, h, x, U, UT);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("wide_gather_kernel");
+    return EGNN_OK;
+}
+
+uint8_t* wide_align(float* scratch) { return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(scratch) + 1023) / 1024 * 1024); }
 
 }  // namespace
 
@@ -297,45 +601,146 @@ int egnn_wide_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const f
     const PackOff po = pack_off(net);
     const WideOff wo = wide_off(net);
     const WideWs ww = wide_ws(net, g.E);
-    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(scratch) + 1023) / 1024 * 1024);
+    uint8_t* base = wide_align(scratch);
     uint8_t* U = base + ww.u;
     uint8_t* A1 = base + ww.a1;
     float* gm = reinterpret_cast<float*>(base + ww.gm);
     float* phip = reinterpret_cast<float*>(base + ww.phip);
     const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    auto blk = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
     const float* P = params_layer;
-    {
-        const long long total = (long long)ww.mtiles * WIDE_TM * wo.ks0 * (WIDE_TK / 8);
-        const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-        egnn_prof_begin(EGNN_K_TC_EDGE_FWD, st);
-        wide_gather_kernel<<<blocks, 256, 0, st>>>(g.E, ww.mtiles, net.H, wo.ks0, g.recv, g.send, h, x, U);
-        egnn_prof_end(st);
-        EGNN_CHECK_LAUNCH("wide_gather_kernel");
-    }
-    WideGemmArgs a{};
-    a.mtiles = ww.mtiles;
-    a.E = g.E;
+    const int K = EGNN_K_TC_EDGE_FWD;
+    if (int rc = wide_gather(net, g, ww.mtiles, wo.ks0, h, x, U, nullptr, st, K)) return rc;
+    WideGemmArgs a = wide_args(ww.mtiles, g.E);
     // message branch
-    a.A = U; a.a_ks = wo.ks0; a.KS = wo.ks0; a.B = img + (size_t)wo.m1 * WIDE_B_SLICE; a.NT = wo.ntm1; a.N = net.Mh;
+    wide_operands(a, U, wo.ks0, blk(wo.m1), wo.ks0, wo.ntm1, net.Mh);
     a.bias = P + lo.bm1; a.out_img = A1; a.out_ks = ww.a1_ks;
-    if (int rc = launch_wide<WIDE_IMG>(a, precision, st, "tc_wide_gemm m1")) return rc;
-    a.A = A1; a.a_ks = ww.a1_ks; a.KS = wo.ksm; a.B = img + (size_t)wo.m2 * WIDE_B_SLICE; a.NT = wo.ntm2; a.N = net.Ms;
+    if (int rc = launch_wide<WIDE_IMG>(a, precision, st, "tc_wide_gemm m1", K)) return rc;
+    wide_operands(a, A1, ww.a1_ks, blk(wo.m2), wo.ksm, wo.ntm2, net.Ms);
     a.bias = P + lo.bm2; a.vec = P + lo.wa; a.scalar = P + lo.ba; a.out = gm;
-    if (int rc = launch_wide<WIDE_GATE>(a, precision, st, "tc_wide_gemm m2")) return rc;
-    egnn_prof_begin(EGNN_K_TC_EDGE_FWD, st);
+    if (int rc = launch_wide<WIDE_GATE>(a, precision, st, "tc_wide_gemm m2", K)) return rc;
+    egnn_prof_begin(K, st);
     wide_segsum_kernel<<<g.N, WIDE_TN, 0, st>>>(net.Ms, g.row_ptr, gm, agg, net.Ms + 4);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("wide_segsum_kernel");
     // coordinate branch
-    a.A = U; a.a_ks = wo.ks0; a.KS = wo.ks0; a.B = img + (size_t)wo.x1 * WIDE_B_SLICE; a.NT = wo.ntx1; a.N = net.Xh;
+    wide_operands(a, U, wo.ks0, blk(wo.x1), wo.ks0, wo.ntx1, net.Xh);
     a.bias = P + lo.bx1; a.out_img = A1; a.out_ks = ww.a1_ks;
-    if (int rc = launch_wide<WIDE_IMG>(a, precision, st, "tc_wide_gemm x1")) return rc;
-    a.A = A1; a.a_ks = ww.a1_ks; a.KS = wo.ksx; a.B = img + (size_t)wo.x2 * WIDE_B_SLICE; a.NT = wo.ntx2; a.N = net.Xh;
-    a.bias = P + lo.bx2; a.vec = P + lo.wx3; a.scalar = nullptr; a.out = phip;
-    if (int rc = launch_wide<WIDE_ROWDOT>(a, precision, st, "tc_wide_gemm x2")) return rc;
-    egnn_prof_begin(EGNN_K_TC_EDGE_FWD, st);
-    wide_phi_kernel<<<(g.E + 255) / 256, 256, 0, st>>>(g.E, wo.ntx2, phip, P + lo.bx3, phi_edge);
+    if (int rc = launch_wide<WIDE_IMG>(a, precision, st, "tc_wide_gemm x1", K)) return rc;
+    wide_operands(a, A1, ww.a1_ks, blk(wo.x2), wo.ksx, wo.ntx2, net.Xh);
+    a.bias = P + lo.bx2; a.vec = P + lo.wx3; a.scalar = nullptr; a.out = phip; a.out_ld = g.E;
+    if (int rc = launch_wide<WIDE_ROWDOT>(a, precision, st, "tc_wide_gemm x2", K)) return rc;
+    egnn_prof_begin(K, st);
+    wide_phi_kernel<<<(g.E + 255) / 256, 256, 0, st>>>(g.E, wo.ntx2, g.E, phip, P + lo.bx3, phi_edge);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("wide_phi_kernel");
+    return EGNN_OK;
+}
+
+int egnn_wide_bwd_rows(const egnn_net_t& net, int64_t E) { return wide_bwd_ws(net, E).splits; }
+int64_t egnn_wide_bwd_bytes(const egnn_net_t& net, int64_t E) { return wide_bwd_ws(net, E).total + 1024; }
+
+// Edge phase of one layer's backward on the tile GEMMs: recompute both branches (keeping SiLU' and the transposed images),
+// gz2 from the gate / phi gradients, dgrad and wgrad GEMMs, bias gradients as column sums.  Weight-gradient partials go to
+// rows [0, egnn_wide_bwd_rows) of `part` in the parameter layout (summed by reduce_partials_kernel); per-edge receiver /
+// sender contributions to Gr / Gs as the FFMA kernel leaves them (egcl_gather_bwd sums them per node).
+int egnn_wide_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
+                            const float* h, const float* x, const float* gM, const float* gdx, const float* coefS, float* Gr,
+                            float* Gs, float* part, float* scratch, int precision, cudaStream_t st) {
+    EGNN_REQUIRE(wide_fwd_supported(net), "egnn_wide_edge_backward: network outside the wide path's limits");
+    const LayerOff lo = layer_off(net);
+    const PackOff po = pack_off(net);
+    const WideOff wo = wide_off(net);
+    const WideBwdWs w = wide_bwd_ws(net, g.E);
+    uint8_t* base = wide_align(scratch);
+    auto f32 = [&](int64_t off) { return reinterpret_cast<float*>(base + off); };
+    uint8_t *U = base + w.u, *UT = base + w.ut, *A1 = base + w.a1, *A1T = base + w.a1t, *G2 = base + w.g2, *G2T = base + w.g2t;
+    uint8_t *G1m = base + w.g1m, *G1x = base + w.g1x, *G1T = base + w.g1t;
+    float *D1 = f32(w.d1), *rows = f32(w.rows), *q = f32(w.q), *gphi = f32(w.gphi), *phip = f32(w.phip), *phi = f32(w.phi), *gu = f32(w.gu);
+    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    auto blk = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
+    const float* P = params_layer;
+    const int K = EGNN_K_TC_EDGE_BWD, K0 = 2 * net.H + 1;
+    const int Ep = w.mtiles * WIDE_TM, S = w.splits, per_edges = w.per * WIDE_TK;
+    const int64_t pstride = lo.total;
+
+    auto colsum_T = [&](const uint8_t* T, int N, int off) {
+        egnn_prof_begin(K, st);
+        wide_colsum_T_kernel<<<dim3(wide_cdiv(N, WIDE_TM), S), 128, 0, st>>>(T, w.kst, w.per, N, part + off, pstride);
+        egnn_prof_end(st);
+    };
+    auto colsum_rows = [&](const float* r, int ld, int ncols, int off) {
+        egnn_prof_begin(K, st);
+        wide_colsum_rows_kernel<<<dim3(wide_cdiv(ncols, 32), S), 256, 0, st>>>(r, ld, ncols, g.E, per_edges, part + off, pstride);
+        egnn_prof_end(st);
+    };
+    // dW [Nout x Kin] = G^T X: A = transposed G image (128-row feature tiles), B = transposed X image (256-row feature tiles)
+    auto wgrad = [&](const uint8_t* GT, int Nout, const uint8_t* XT, int Kin, int off, const char* what) {
+        WideGemmArgs a = wide_args(wide_cdiv(Nout, WIDE_TM), Nout);
+        a.A = GT; a.a_ks = w.kst; a.B = XT; a.b_ks = w.kst;
+        a.KS = w.per; a.KS_total = w.kst; a.splits = S;
+        a.NT = wide_cdiv(Kin, WIDE_TN); a.N = Kin;
+        a.out = part + off; a.out_ld = Kin; a.out_split = pstride;
+        return launch_wide<WIDE_WGRAD>(a, precision, st, what, EGNN_K_TC_WGRAD);
+    };
+
+    if (int rc = wide_gather(net, g, w.mtiles, wo.ks0, h, x, U, UT, st, K)) return rc;
+    egnn_prof_begin(K, st);
+    wide_gphi_kernel<<<wide_cdiv(Ep, 256), 256, 0, st>>>(g.E, Ep, g.recv, g.send, x, gdx, gphi);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("wide_gphi_kernel");
+
+    for (int branch = 0; branch < 2; ++branch) {  // 0: message, 1: coordinate
+        const bool M = branch == 0;
+        const int D1w = M ? net.Mh : net.Xh, D2w = M ? net.Ms : net.Xh;
+        const int ks1 = M ? wo.ksm : wo.ksx, ks2 = M ? wo.kss : wo.ksx;
+        uint8_t* G1 = M ? G1m : G1x;
+        // recompute the first Linear: a1 image, its transpose, SiLU'(z1) rows
+        WideGemmArgs a = wide_args(w.mtiles, g.E);
+        wide_operands(a, U, wo.ks0, blk(M ? wo.m1 : wo.x1), wo.ks0, wide_cdiv(D1w, WIDE_TN), D1w);
+        a.bias = P + (M ? lo.bm1 : lo.bx1); a.out_img = A1; a.out_ks = w.w_ks; a.out_T = A1T; a.kst = w.kst; a.rows = D1; a.rows_ld = w.np;
+        if (int rc = launch_wide<WIDE_IMG_BWD>(a, precision, st, "tc_wide_gemm bwd 1", K)) return rc;
+        // recompute the second Linear and turn it into gz2 (image + transpose); rows = the row-dot vector's gradient terms
+        wide_operands(a, A1, w.w_ks, blk(M ? wo.m2 : wo.x2), ks1, wide_cdiv(D2w, WIDE_TN), D2w);
+        a.bias = P + (M ? lo.bm2 : lo.bx2); a.vec = P + (M ? lo.wa : lo.wx3); a.scalar = M ? P + lo.ba : nullptr;
+        a.out_img = G2; a.out_ks = w.w_ks; a.out_T = G2T; a.rows = rows; a.rows_ld = w.np;
+        a.q = q; a.gM = gM; a.recv = g.recv; a.gphi = gphi; a.out = phip; a.out_ld = Ep;
+        if (M) {
+            if (int rc = launch_wide<WIDE_GATE_BWD>(a, precision, st, "tc_wide_gemm bwd gate", K)) return rc;
+        } else {
+            if (int rc = launch_wide<WIDE_ROWDOT_BWD>(a, precision, st, "tc_wide_gemm bwd phi", K)) return rc;
+            egnn_prof_begin(K, st);
+            wide_phi_kernel<<<wide_cdiv(g.E, 256), 256, 0, st>>>(g.E, wo.ntx2, Ep, phip, P + lo.bx3, phi);
+            egnn_prof_end(st);
+            EGNN_CHECK_LAUNCH("wide_phi_kernel");
+        }
+        // d vec = column sums of the rows; d (its bias) = sum of the row coefficients
+        colsum_rows(rows, w.np, D2w, M ? lo.wa : lo.wx3);
+        colsum_rows(M ? q : gphi, 1, 1, M ? lo.ba : lo.bx3);
+        // second Linear: dW2 = gz2^T a1, db2 = column sums of gz2
+        if (int rc = wgrad(G2T, D2w, A1T, D1w, M ? lo.wm2 : lo.wx2, "tc_wide_gemm wgrad 2")) return rc;
+        colsum_T(G2T, D2w, M ? lo.bm2 : lo.bx2);
+        // ga1 = gz2 . W2;  gz1 = ga1 * SiLU'(z1): image (for gu) + transpose (for dW1)
+        WideGemmArgs d = wide_args(w.mtiles, g.E);
+        wide_operands(d, G2, w.w_ks, blk(M ? wo.m2t : wo.x2t), ks2, wide_cdiv(D1w, WIDE_TN), D1w);
+        d.out_img = G1; d.out_ks = w.w_ks; d.out_T = G1T; d.kst = w.kst; d.rows = D1; d.rows_ld = w.np;
+        if (int rc = launch_wide<WIDE_DGRAD>(d, precision, st, "tc_wide_gemm dgrad 2", K)) return rc;
+        // first Linear: dW1 = gz1^T u, db1 = column sums of gz1
+        if (int rc = wgrad(G1T, D1w, UT, K0, M ? lo.wm1 : lo.wx1, "tc_wide_gemm wgrad 1")) return rc;
+        colsum_T(G1T, D1w, M ? lo.bm1 : lo.bx1);
+    }
+    EGNN_CHECK_LAUNCH("wide colsum kernels");
+    {   // gu = gz1m . Wm1 + gz1x . Wx1: one GEMM over the concatenated K
+        WideGemmArgs a = wide_args(w.mtiles, g.E);
+        a.A = G1m; a.a_ks = w.w_ks; a.A2 = G1x; a.a2_ks = w.w_ks; a.ks_split = wo.ksm;
+        a.B = blk(wo.w1t); a.b_ks = wo.ksm + wo.ksx; a.KS = a.KS_total = wo.ksm + wo.ksx; a.NT = 1; a.N = K0;
+        a.out = gu; a.out_ld = 128;
+        if (int rc = launch_wide<WIDE_F32>(a, precision, st, "tc_wide_gemm dgrad 1", K)) return rc;
+    }
+    const long long tot = (long long)g.E * (net.H + 3);
+    egnn_prof_begin(K, st);
+    wide_edge_out_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(g.E, net.H, g.recv, g.send, g.node_graph, x, gu, gdx, coefS, phi, Gr, Gs);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("wide_edge_out_kernel");
     return EGNN_OK;
 }

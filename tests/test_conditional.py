@@ -114,7 +114,7 @@ def test_conditional_training_loss_and_grads(lib, golden_dir):
     for k, p in comp.named_parameters():  # the gradient reaches the conditioning network through gh_in of the EGNN
         assert relerr(p.grad, z["cg:" + k]) <= 1e-3, k
     # H = 36 has no fused tcgen05 kernel; asked for explicitly, bf16x3 runs the tile-GEMM forward (csrc/tc_wide.cu) with
-    # the fp32 backward: same bars
+    # and backward: same bars
     net.precision = "bf16x3"
     net.zero_grad()
     loss3, _, aux3 = batch_loss(net, bd, dp, params, t=z["t"].tolist(), noise_pos=torch.from_numpy(z["noise_pos"]).cuda(),
@@ -163,7 +163,7 @@ def test_parameters_yaml_widths_forward_and_gradients(lib, precision):
     """The only configuration the reference ships (parameters.yaml through main.py:102-121): h = [2 atom types | 32
     compressed spectrum | exO | t] = 36 columns, K0 = 73, m_hidden = x_hidden = h_hidden = 1024, m_size = 256.  These widths
     have no fused tcgen05 kernel (2H+1 > 16, Mh != Ms): `precision = 'auto'` resolves to bf16x3 on the tile-GEMM forward
-    (csrc/tc_wide.cu; the backward runs the fp32 kernels), 'fp32' runs the CUDA-core kernels throughout.  Two layers of that
+    (csrc/tc_wide.cu, forward and backward of the edge MLPs), 'fp32' runs the CUDA-core kernels throughout.  Two layers of that
     network on two fully connected graphs against the oracle: every layer 1e-4, every gradient tensor 1e-3."""
     from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
     from diffusion_model_b200.graph import build_edges_fc
