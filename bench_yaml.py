@@ -115,7 +115,7 @@ def main():
                           + G * n * (2 * (H + 256) * 1024 + 2 * 1024 * H))          # SURVEY.md 8(d), general widths
     out = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer), parameters.yaml network", value=G / (ms * 1e-3),
                unit="graph-steps/s", ms_per_step=ms,
-               dtype="fp32 (CUDA-core FFMA kernels)" if prec == "fp32" else f"{prec} (tcgen05 tile GEMMs for the edge MLPs forward and backward, csrc/tc_wide.cu; node MLP on CUDA-core FFMA)",
+               dtype="fp32 (CUDA-core FFMA kernels)" if prec == "fp32" else f"{prec} (tcgen05 tile GEMMs, csrc/tc_wide.cu: edge and node MLPs, forward and backward)",
                gpu_launches=launches, loss=float(loss.detach()), parameters=P, train_tflops=3 * flops_fwd / (ms * 1e-3) / 1e12,
                denoiser_forward_ms=fwd_ms, forward_tflops=flops_fwd / (fwd_ms * 1e-3) / 1e12,
                config=dict(workload=f"parameters.yaml: conditional EGNN L=5, K0=73, m/x/h hidden 1024, m_size 256, SpectrumCompressor, "

@@ -148,7 +148,10 @@ struct WideOff {  // per layer, in units of WIDE_B_SLICE blocks: block (nt, ks) 
     int ntm1, ntm2, ntx1, ntx2;  // N tiles: Mh, Ms, Xh, Xh
     int m1, m2, x1, x2;          // forward: first block of each matrix
     // backward (dgrad) images, rows = INPUT features: Wm2^T [Mh x Ms], Wx2^T [Xh x Xh], [Wm1^T | Wx1^T] [K0 x (Mh + Xh)]
-    int m2t, x2t, w1t, blocks;
+    int m2t, x2t, w1t;
+    // node MLP (mlp_h): Wh1 [Hh x (H + Ms)], Wh2 [H x Hh] and their transposes
+    int ksn, ksh, ksH, nth, ntn;  // K slices: H + Ms, Hh, H;  N tiles: Hh, H + Ms
+    int h1, h2, h2t, h1t, blocks;
 };
 __host__ __device__ static inline WideOff wide_off(const egnn_net_t& n) {
     WideOff o;
@@ -167,15 +170,27 @@ __host__ __device__ static inline WideOff wide_off(const egnn_net_t& n) {
     o.m2t = o.x2 + o.ntx2 * o.ksx;
     o.x2t = o.m2t + o.ntm1 * o.kss;
     o.w1t = o.x2t + o.ntx2 * o.ksx;
-    o.blocks = o.w1t + 1 * (o.ksm + o.ksx);
+    o.ksn = wide_cdiv(n.H + n.Ms, WIDE_TK);
+    o.ksh = wide_cdiv(n.Hh, WIDE_TK);
+    o.ksH = wide_cdiv(n.H, WIDE_TK);
+    o.nth = wide_cdiv(n.Hh, WIDE_TN);
+    o.ntn = wide_cdiv(n.H + n.Ms, WIDE_TN);
+    o.h1 = o.w1t + 1 * (o.ksm + o.ksx);
+    o.h2 = o.h1 + o.nth * o.ksn;
+    o.h2t = o.h2 + 1 * o.ksh;
+    o.h1t = o.h2t + o.nth * o.ksH;
+    o.blocks = o.h1t + o.ntn * o.ksh;
     return o;
 }
 // forward workspace of the wide path (bytes, each part 1 KB aligned): U image | A1 image | g*m fp32 [E][256] | phi parts
 struct WideWs {
-    int64_t u, a1, gm, phip, total;
+    int64_t u, a1, gm, phip, ni, a1n, total;
     int mtiles, a1_ks;  // a1_ks: slices per tile of the A1 image (its row stride)
+    int mtiles_n;       // node phase: row tiles of the [h | M] image (ni) and of the hidden image (a1n, nth * 4 slices per tile)
 };
-static inline WideWs wide_ws(const egnn_net_t& n, int64_t E) {
+// the node MLP runs on the tile GEMMs too when its hidden width fits the same limit (else the FFMA node kernels)
+__host__ __device__ static inline bool wide_node_supported(const egnn_net_t& n) { return wide_fwd_supported(n) && n.Hh <= 1024; }
+static inline WideWs wide_ws(const egnn_net_t& n, int64_t E, int64_t N) {
     WideWs w;
     const WideOff o = wide_off(n);
     w.mtiles = (int)((E + WIDE_TM - 1) / WIDE_TM);
@@ -187,6 +202,9 @@ static inline WideWs wide_ws(const egnn_net_t& n, int64_t E) {
     w.a1 = take((int64_t)w.mtiles * w.a1_ks * WIDE_A_SLICE);
     w.gm = take(E * WIDE_TN * 4);
     w.phip = take((int64_t)o.ntx2 * E * 4);
+    w.mtiles_n = (int)((N + WIDE_TM - 1) / WIDE_TM);
+    w.ni = take(wide_node_supported(n) ? (int64_t)w.mtiles_n * o.ksn * WIDE_A_SLICE : 0);
+    w.a1n = take(wide_node_supported(n) ? (int64_t)w.mtiles_n * o.nth * (WIDE_TN / WIDE_TK) * WIDE_A_SLICE : 0);
     w.total = p;
     return w;
 }
@@ -197,6 +215,40 @@ struct WideBwdWs {
     int mtiles, kst, np, w_ks;  // kst: 64-edge slices; np: padded hidden width; w_ks: slices per tile row of the np-wide images
     int splits, per;            // split-K of the weight gradients over the edge slices = private rows of the partial buffer
 };
+// node phase of the backward (rows = nodes): [h | M] image + transpose, hidden image + transpose, SiLU' rows, gh_out image +
+// transpose, gz1 image + transpose, g[h | M] rows
+struct WideNodeBwdWs {
+    int64_t ni, nit, a1, a1t, d1, go, got, g1, g1t, gin, total;
+    int mtiles, kst, hp, h_ks, gin_ld, splits, per;
+};
+static inline WideNodeBwdWs wide_node_bwd_ws(const egnn_net_t& n, int64_t N) {
+    WideNodeBwdWs w;
+    const WideOff o = wide_off(n);
+    w.mtiles = (int)((N + WIDE_TM - 1) / WIDE_TM);
+    w.kst = 2 * w.mtiles;
+    w.hp = o.nth * WIDE_TN;
+    w.h_ks = w.hp / WIDE_TK;
+    w.gin_ld = o.ntn * WIDE_TN;
+    w.splits = w.kst < 16 ? (w.kst > 0 ? w.kst : 1) : 16;
+    w.per = wide_cdiv(w.kst > 0 ? w.kst : 1, w.splits);
+    w.splits = wide_cdiv(w.kst > 0 ? w.kst : 1, w.per);
+    const int64_t Np = (int64_t)w.mtiles * WIDE_TM;
+    const int64_t img = (int64_t)w.mtiles * w.h_ks * WIDE_A_SLICE;
+    int64_t p = 0;
+    auto take = [&](int64_t b) { int64_t q = p; p += (b + 1023) / 1024 * 1024; return q; };
+    w.ni = take((int64_t)w.mtiles * o.ksn * WIDE_A_SLICE);
+    w.nit = take((int64_t)o.ntn * w.kst * WIDE_B_SLICE);
+    w.a1 = take(img);
+    w.a1t = take(img);
+    w.d1 = take(Np * w.hp * 4);
+    w.go = take((int64_t)w.mtiles * o.ksH * WIDE_A_SLICE);
+    w.got = take((int64_t)wide_cdiv(n.H, WIDE_TM) * w.kst * WIDE_A_SLICE);
+    w.g1 = take(img);
+    w.g1t = take(img);
+    w.gin = take(Np * w.gin_ld * 4);
+    w.total = p;
+    return w;
+}
 static inline WideBwdWs wide_bwd_ws(const egnn_net_t& n, int64_t E) {
     WideBwdWs w;
     w.mtiles = (int)((E + WIDE_TM - 1) / WIDE_TM);
@@ -301,7 +353,7 @@ static inline FwdWs fwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G)
     w.dxu = take((int64_t)n.L * N * 3);
     w.S = take((int64_t)n.L * G);
     w.phi = take(tc_fwd_supported(n) || wide_fwd_supported(n) ? E : 0);
-    w.wide = take(wide_fwd_supported(n) ? 256 + wide_ws(n, E).total / 4 : 0);  // + 256 floats: the caller aligns to 1 KB
+    w.wide = take(wide_fwd_supported(n) ? 256 + wide_ws(n, E, N).total / 4 : 0);  // + 256 floats: the caller aligns to 1 KB
     w.total = p;
     return w;
 }

@@ -458,6 +458,11 @@ int64_t egnn_wide_bwd_bytes(const egnn_net_t& net, int64_t E);
 int egnn_wide_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
                             const float* h, const float* x, const float* gM, const float* gdx, const float* coefS, float* Gr,
                             float* Gs, float* part, float* scratch, int precision, cudaStream_t st);
+int egnn_wide_node_bwd_rows(const egnn_net_t& net, int64_t N);
+int64_t egnn_wide_node_bwd_bytes(const egnn_net_t& net, int64_t N);
+int egnn_wide_node_backward(const egnn_net_t& net, int N, const float* params_layer, const float* packed_layer, const float* h,
+                            const float* msum, const float* gh_out, float* gh_node, float* gM, float* part, float* scratch,
+                            int precision, cudaStream_t st);
 
 namespace {
 
@@ -484,7 +489,7 @@ inline int node_bwd_rows(const egnn_net_t& n, int64_t N) {
 }
 
 struct BwdWs {
-    int64_t gdx, coefS, dotp, gM, gh_node, Gr, Gs, ghb, gxb, part, img, total;
+    int64_t gdx, coefS, dotp, gM, gh_node, Gr, Gs, ghb, gxb, part, img, img_node, total;
     int gridE, gridN, TEB;
 };
 inline int edge_tile_bwd(const egnn_net_t& n) {
@@ -501,6 +506,7 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     if (wide_fwd_supported(n) && egnn_wide_bwd_rows(n, E) > w.gridE) w.gridE = egnn_wide_bwd_rows(n, E);
     w.gridN = node_bwd_rows(n, N);
     if (tc_node_supported(n) && egnn_tc_node_bwd_grid(N) > w.gridN) w.gridN = egnn_tc_node_bwd_grid(N);
+    if (wide_node_supported(n) && egnn_wide_node_bwd_rows(n, N) > w.gridN) w.gridN = egnn_wide_node_bwd_rows(n, N);
     const int64_t W = n.H + 3;
     int64_t p = 0;
     auto take = [&](int64_t cnt) { int64_t o = p; p += round_up64(cnt, 4); return o; };
@@ -516,6 +522,7 @@ inline BwdWs bwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G) {
     w.part = take((int64_t)(w.gridE + w.gridN) * layer_off(n).total);
     w.img = take(tc_bwd256_supported(n) ? egnn_tc_bwd256_img_bytes(E) / 4      // 16-byte aligned: every take() is rounded to 4 floats
                  : wide_fwd_supported(n) && E > 0 ? egnn_wide_bwd_bytes(n, E) / 4 : 0);
+    w.img_node = take(wide_node_supported(n) ? egnn_wide_node_bwd_bytes(n, N) / 4 : 0);
     w.total = p;
     return w;
 }
@@ -608,7 +615,8 @@ static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const
     // rows actually used by this call's kernels (the workspace is sized for the larger of the two paths)
     const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : use_tc256 ? egnn_tc_bwd256_rows(E) : use_wide ? egnn_wide_bwd_rows(*net, E)
                                                             : (int)std::min<int64_t>((E + bw.TEB - 1) / bw.TEB, kNumSM)) : 0;
-    const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : node_bwd_rows(*net, N);
+    const bool node_wide = use_wide && wide_node_supported(*net);
+    const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : node_wide ? egnn_wide_node_bwd_rows(*net, N) : node_bwd_rows(*net, N);
     RowMap256 m256{};
     if (use_tc256 && E > 0) {
         m256.on = 1;
@@ -640,7 +648,12 @@ static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const
         // (the FFMA node kernel stores every mlp_h entry of its row on its first tile: no zero-fill of the node rows)
         if (!use_tc && !use_tc256 && rowsE > 0)
             EGNN_CUDA(cudaMemsetAsync(ws + bw.part, 0, sizeof(float) * (size_t)rowsE * lo.total, st));
-        if (node_tc) {
+        if (node_wide) {
+            if (int rc = egnn_wide_node_backward(*net, N, P, Pk, hl, fwd_ws_ptr + fw.msum + (size_t)l * N * net->Ms, gho,
+                                                 ws + bw.gh_node, ws + bw.gM, ws + bw.part + (size_t)rowsE * lo.total,
+                                                 ws + bw.img_node, precision, st))
+                return rc;
+        } else if (node_tc) {
             if (int rc = egnn_tc_node_backward(*net, N, P, Pk, hl, fwd_ws_ptr + fw.msum + (size_t)l * N * net->Ms, gho,
                                                ws + bw.gh_node, ws + bw.gM, ws + bw.part + (size_t)rowsE * lo.total,
                                                precision, st))

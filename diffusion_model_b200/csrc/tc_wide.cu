@@ -64,6 +64,13 @@ __global__ void __launch_bounds__(256) wide_pack_kernel(egnn_net_t net, const fl
     wide_pack_matrix(P + lo.wx2, net.Xh, net.Xh, net.Xh, true, wo.ksx, 0, at(wo.x2t), t0, stride);
     wide_pack_matrix(P + lo.wm1, K0, net.Mh, K0, true, wo.ksm + wo.ksx, 0, at(wo.w1t), t0, stride);
     wide_pack_matrix(P + lo.wx1, K0, net.Xh, K0, true, wo.ksm + wo.ksx, wo.ksm, at(wo.w1t), t0, stride);
+    if (wide_node_supported(net)) {  // mlp_h: forward images, then the dgrad images (rows = input features)
+        const int Kn = net.H + net.Ms;
+        wide_pack_matrix(P + lo.wh1, net.Hh, Kn, Kn, false, wo.ksn, 0, at(wo.h1), t0, stride);
+        wide_pack_matrix(P + lo.wh2, net.H, net.Hh, net.Hh, false, wo.ksh, 0, at(wo.h2), t0, stride);
+        wide_pack_matrix(P + lo.wh2, net.Hh, net.H, net.Hh, true, wo.ksH, 0, at(wo.h2t), t0, stride);
+        wide_pack_matrix(P + lo.wh1, Kn, net.Hh, Kn, true, wo.ksh, 0, at(wo.h1t), t0, stride);
+    }
 }
 
 // ---- gather: one thread per (edge row, 8-column chunk) of the U image; rows >= E are zero -----------------------------------------
@@ -154,27 +161,34 @@ __global__ void __launch_bounds__(256) wide_gphi_kernel(int E, int Ep, const int
 }
 
 // column sums of a transposed (rows = features) hi | lo image over the 64-edge slices of split blockIdx.y: bias gradients.
-// 128 threads = the 128 feature rows of tile blockIdx.x; fixed order inside a split, the splits are summed by reduce_partials_kernel
-__global__ void __launch_bounds__(128) wide_colsum_T_kernel(const uint8_t* __restrict__ T, int kst, int per, int N, float* __restrict__ part,
-                                                            int64_t part_stride) {
-    const int n = blockIdx.x * 128 + threadIdx.x, s = blockIdx.y;
+// 1024 threads = the 128 feature rows of tile blockIdx.x x the 8 chunk columns of a slice; fixed order inside a split, the
+// splits are summed by reduce_partials_kernel
+__global__ void __launch_bounds__(1024) wide_colsum_T_kernel(const uint8_t* __restrict__ T, int kst, int per, int N, float* __restrict__ part,
+                                                             int64_t part_stride) {
+    __shared__ float red[8][128];
+    const int nl = threadIdx.x & 127, j = threadIdx.x >> 7, n = blockIdx.x * 128 + nl, s = blockIdx.y;
     const int k0 = s * per, k1 = min(k0 + per, kst);
     float sum = 0.f;
+#pragma unroll 4
     for (int ks = k0; ks < k1; ++ks) {
-        const uint8_t* b = T + ((size_t)blockIdx.x * kst + ks) * WIDE_A_SLICE + threadIdx.x * 16;
+        const uint8_t* b = T + ((size_t)blockIdx.x * kst + ks) * WIDE_A_SLICE + j * (WIDE_TM * 16) + nl * 16;
+        const uint4 h = *reinterpret_cast<const uint4*>(b);
+        const uint4 l = *reinterpret_cast<const uint4*>(b + WIDE_A_SLICE / 2);
+        const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const uint4 h = *reinterpret_cast<const uint4*>(b + j * (WIDE_TM * 16));
-            const uint4 l = *reinterpret_cast<const uint4*>(b + j * (WIDE_TM * 16) + WIDE_A_SLICE / 2);
-            const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                sum += __uint_as_float(hw[q] << 16) + __uint_as_float(lw[q] << 16);
-                sum += __uint_as_float(hw[q] & 0xffff0000u) + __uint_as_float(lw[q] & 0xffff0000u);
-            }
+        for (int q = 0; q < 4; ++q) {
+            sum += __uint_as_float(hw[q] << 16) + __uint_as_float(lw[q] << 16);
+            sum += __uint_as_float(hw[q] & 0xffff0000u) + __uint_as_float(lw[q] & 0xffff0000u);
         }
     }
-    if (n < N) part[(size_t)s * part_stride + n] = sum;
+    red[j][nl] = sum;
+    __syncthreads();
+    if (j == 0 && n < N) {
+        float t = red[0][nl];
+#pragma unroll
+        for (int k = 1; k < 8; ++k) t += red[k][nl];
+        part[(size_t)s * part_stride + n] = t;
+    }
 }
 
 // column sums of fp32 rows [E x ld] over the edges of split blockIdx.y (32 columns x 8 row lanes per CTA, fixed order)
@@ -184,8 +198,10 @@ __global__ void __launch_bounds__(256) wide_colsum_rows_kernel(const float* __re
     const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5, c = blockIdx.x * 32 + cl, s = blockIdx.y;
     const int e0 = s * per_edges, e1 = min(e0 + per_edges, E);
     float sum = 0.f;
-    if (c < ncols)
+    if (c < ncols) {
+#pragma unroll 4
         for (int e = e0 + rl; e < e1; e += 8) sum += rows[(size_t)e * ld + c];
+    }
     red[rl][cl] = sum;
     __syncthreads();
     if (rl == 0 && c < ncols) {
@@ -217,6 +233,102 @@ __global__ void __launch_bounds__(256) wide_edge_out_kernel(int E, int H, const 
         Gr[idx] = gr;
         Gs[idx] = -gr;
     }
+}
+
+// ---- node phase (mlp_h on the tile GEMMs) ---------------------------------------------------------------------------------------
+// fp32 rows -> operand image (+ transposed image): value(i, k) = k < W1 ? src1[i * W1 + k] : src2[i * ld2 + (k - W1)] for k < W1 + W2.
+// The node MLP's input [h | M] (W1 = H, W2 = Ms; forward: src2 = the per-receiver sums, copied to copy2 = msum), and with
+// W2 = 0 any row matrix (gh_out).  t_rows = 256: transposed image in the B layout (weight-gradient B operand), 128: A layout
+__global__ void __launch_bounds__(256) wide_rows_to_img_kernel(int N, int mtiles, int W1, int W2, int KS, const float* __restrict__ src1,
+                                                               const float* __restrict__ src2, int ld2, float* __restrict__ copy2,
+                                                               uint8_t* __restrict__ img, uint8_t* __restrict__ T, int t_rows, int kst) {
+    const int nchunk = KS * (WIDE_TK / 8);
+    const long long total = (long long)mtiles * WIDE_TM * nchunk;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const int row_in_tile = (int)(idx % WIDE_TM);
+        const long long rest = idx / WIDE_TM;
+        const int j = (int)(rest % nchunk);
+        const int t = (int)(rest / nchunk);
+        const int i = t * WIDE_TM + row_in_tile;
+        float v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int k = j * 8 + q;
+            float val = 0.f;
+            if (i < N) {
+                if (k < W1) val = src1[(size_t)i * W1 + k];
+                else if (k < W1 + W2) {
+                    val = src2[(size_t)i * ld2 + (k - W1)];
+                    if (copy2) copy2[(size_t)i * W2 + (k - W1)] = val;
+                }
+            }
+            v[q] = val;
+        }
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) tc::split2(v[2 * q], v[2 * q + 1], hi[q], lo[q]);
+        uint8_t* b = img + ((size_t)t * KS + j / 8) * WIDE_A_SLICE + (j % 8) * (WIDE_TM * 16) + row_in_tile * 16;
+        *reinterpret_cast<uint4*>(b) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(b + WIDE_A_SLICE / 2) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        if (T) {
+            const int slice_bytes = t_rows * WIDE_TK * 4;  // hi | lo
+            const int k0 = j * 8;
+            uint8_t* tb = T + ((size_t)(k0 / t_rows) * kst + i / WIDE_TK) * slice_bytes + ((i % WIDE_TK) / 8) * (t_rows * 16) + (i % 8) * 2;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const uint32_t hw = hi[q >> 1], lw = lo[q >> 1];
+                uint8_t* d = tb + (k0 % t_rows + q) * 16;
+                *reinterpret_cast<uint16_t*>(d) = (uint16_t)(q & 1 ? hw >> 16 : hw & 0xffffu);
+                *reinterpret_cast<uint16_t*>(d + slice_bytes / 2) = (uint16_t)(q & 1 ? lw >> 16 : lw & 0xffffu);
+            }
+        }
+    }
+}
+
+// un-normalised coordinate sums and sum of |r_e|^2 per receiver from phi_e (egcl_fwd.cu: egcl_node_fwd, the phi_edge branch):
+// 8 lanes per node over its edges, fixed order
+__global__ void __launch_bounds__(256) wide_node_geom_kernel(int N, const int32_t* __restrict__ row_ptr, const int32_t* __restrict__ send,
+                                                             const float* __restrict__ x, const float* __restrict__ phi_edge,
+                                                             float* __restrict__ dxu, float* __restrict__ D) {
+    const int i = blockIdx.x * 32 + (threadIdx.x >> 3), sub = threadIdx.x & 7;
+    float sx = 0.f, sy = 0.f, sz = 0.f, sd = 0.f;
+    if (i < N) {
+        const float xi = x[3 * i], yi = x[3 * i + 1], zi = x[3 * i + 2];
+        for (int e = row_ptr[i] + sub; e < row_ptr[i + 1]; e += 8) {
+            const int j = send[e];
+            const float rx = xi - x[3 * j], ry = yi - x[3 * j + 1], rz = zi - x[3 * j + 2];
+            const float ph = phi_edge[e];
+            sx = fmaf(rx, ph, sx);
+            sy = fmaf(ry, ph, sy);
+            sz = fmaf(rz, ph, sz);
+            sd += rx * rx + ry * ry + rz * rz;
+        }
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+        sx += __shfl_xor_sync(0xffffffffu, sx, o);
+        sy += __shfl_xor_sync(0xffffffffu, sy, o);
+        sz += __shfl_xor_sync(0xffffffffu, sz, o);
+        sd += __shfl_xor_sync(0xffffffffu, sd, o);
+    }
+    if (i < N && sub == 0) {
+        dxu[(size_t)i * 3 + 0] = sx;
+        dxu[(size_t)i * 3 + 1] = sy;
+        dxu[(size_t)i * 3 + 2] = sz;
+        D[i] = sd;
+    }
+}
+
+// g[h | M] rows -> gh_node [N x H], gM [N x Ms]
+__global__ void __launch_bounds__(256) wide_split_gin_kernel(int N, int H, int Ms, const float* __restrict__ gin, int ld,
+                                                             float* __restrict__ gh_node, float* __restrict__ gM) {
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    const int W = H + Ms;
+    if (idx >= (long long)N * W) return;
+    const int i = (int)(idx / W), c = (int)(idx - (long long)i * W);
+    const float v = gin[(size_t)i * ld + c];
+    if (c < H) gh_node[(size_t)i * H + c] = v;
+    else gM[(size_t)i * Ms + (c - H)] = v;
 }
 
 // ---- the tile GEMM ------------------------------------------------------------------------------------------------------------
@@ -505,9 +617,12 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
             for (int j = 0; j < 8; ++j) {
                 float v[8];
                 tc::tmem_ld8(taddr + 8 * j, v);
-                if (live && n0 + 8 * j < a.out_ld) {
-                    *reinterpret_cast<float4*>(o + 8 * j) = make_float4(v[0], v[1], v[2], v[3]);
-                    *reinterpret_cast<float4*>(o + 8 * j + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                if (live) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int n = n0 + 8 * j + i;
+                        if (n < a.N) o[8 * j + i] = v[i] + (a.bias ? a.bias[n] : 0.f);
+                    }
                 }
             }
         } else {  // WIDE_WGRAD: row e = feature n of the weight matrix, columns = its input features
@@ -583,6 +698,46 @@ int wide_gather(const egnn_net_t& net, const egnn_graph_t& g, int mtiles, int ks
 
 uint8_t* wide_align(float* scratch) { return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(scratch) + 1023) / 1024 * 1024); }
 
+// split-K weight gradients / bias column sums of one phase (edges or nodes): rows [0, S) of `part`, parameter layout
+struct WideGrad {
+    int kst, per, S;   // 64-row slices, slices per split, splits
+    float* part;
+    int64_t pstride;
+    int precision;
+    cudaStream_t st;
+    int prof;
+    void colsum_T(const uint8_t* T, int N, int off) const {
+        egnn_prof_begin(prof, st);
+        wide_colsum_T_kernel<<<dim3(wide_cdiv(N, WIDE_TM), S), 1024, 0, st>>>(T, kst, per, N, part + off, pstride);
+        egnn_prof_end(st);
+    }
+    void colsum_rows(const float* r, int ld, int ncols, int nrows, int off) const {
+        egnn_prof_begin(prof, st);
+        wide_colsum_rows_kernel<<<dim3(wide_cdiv(ncols, 32), S), 256, 0, st>>>(r, ld, ncols, nrows, per * WIDE_TK, part + off, pstride);
+        egnn_prof_end(st);
+    }
+    // dW [Nout x Kin] = G^T X: A = transposed G image (128-row feature tiles), B = transposed X image (256-row feature tiles)
+    int wgrad(const uint8_t* GT, int Nout, const uint8_t* XT, int Kin, int off, const char* what) const {
+        WideGemmArgs a = wide_args(wide_cdiv(Nout, WIDE_TM), Nout);
+        a.A = GT; a.a_ks = kst; a.B = XT; a.b_ks = kst;
+        a.KS = per; a.KS_total = kst; a.splits = S;
+        a.NT = wide_cdiv(Kin, WIDE_TN); a.N = Kin;
+        a.out = part + off; a.out_ld = Kin; a.out_split = pstride;
+        return launch_wide<WIDE_WGRAD>(a, precision, st, what, EGNN_K_TC_WGRAD);
+    }
+};
+
+int wide_rows_to_img(int N, int mtiles, int W1, int W2, int KS, const float* src1, const float* src2, int ld2, float* copy2, uint8_t* img,
+                     uint8_t* T, int t_rows, int kst, cudaStream_t st, int prof) {
+    const long long total = (long long)mtiles * WIDE_TM * KS * (WIDE_TK / 8);
+    const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+    egnn_prof_begin(prof, st);
+    wide_rows_to_img_kernel<<<blocks, 256, 0, st>>>(N, mtiles, W1, W2, KS, src1, src2, ld2, copy2, img, T, t_rows, kst);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("wide_rows_to_img_kernel");
+    return EGNN_OK;
+}
+
 }  // namespace
 
 int egnn_wide_pack(const egnn_net_t& net, const float* params, float* packed, cudaStream_t st) {
@@ -600,7 +755,7 @@ int egnn_wide_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const f
     const LayerOff lo = layer_off(net);
     const PackOff po = pack_off(net);
     const WideOff wo = wide_off(net);
-    const WideWs ww = wide_ws(net, g.E);
+    const WideWs ww = wide_ws(net, g.E, g.N);
     uint8_t* base = wide_align(scratch);
     uint8_t* U = base + ww.u;
     uint8_t* A1 = base + ww.a1;
@@ -661,28 +816,10 @@ int egnn_wide_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const 
     auto blk = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
     const float* P = params_layer;
     const int K = EGNN_K_TC_EDGE_BWD, K0 = 2 * net.H + 1;
-    const int Ep = w.mtiles * WIDE_TM, S = w.splits, per_edges = w.per * WIDE_TK;
+    const int Ep = w.mtiles * WIDE_TM, S = w.splits;
     const int64_t pstride = lo.total;
 
-    auto colsum_T = [&](const uint8_t* T, int N, int off) {
-        egnn_prof_begin(K, st);
-        wide_colsum_T_kernel<<<dim3(wide_cdiv(N, WIDE_TM), S), 128, 0, st>>>(T, w.kst, w.per, N, part + off, pstride);
-        egnn_prof_end(st);
-    };
-    auto colsum_rows = [&](const float* r, int ld, int ncols, int off) {
-        egnn_prof_begin(K, st);
-        wide_colsum_rows_kernel<<<dim3(wide_cdiv(ncols, 32), S), 256, 0, st>>>(r, ld, ncols, g.E, per_edges, part + off, pstride);
-        egnn_prof_end(st);
-    };
-    // dW [Nout x Kin] = G^T X: A = transposed G image (128-row feature tiles), B = transposed X image (256-row feature tiles)
-    auto wgrad = [&](const uint8_t* GT, int Nout, const uint8_t* XT, int Kin, int off, const char* what) {
-        WideGemmArgs a = wide_args(wide_cdiv(Nout, WIDE_TM), Nout);
-        a.A = GT; a.a_ks = w.kst; a.B = XT; a.b_ks = w.kst;
-        a.KS = w.per; a.KS_total = w.kst; a.splits = S;
-        a.NT = wide_cdiv(Kin, WIDE_TN); a.N = Kin;
-        a.out = part + off; a.out_ld = Kin; a.out_split = pstride;
-        return launch_wide<WIDE_WGRAD>(a, precision, st, what, EGNN_K_TC_WGRAD);
-    };
+    const WideGrad G{w.kst, w.per, S, part, pstride, precision, st, K};
 
     if (int rc = wide_gather(net, g, w.mtiles, wo.ks0, h, x, U, UT, st, K)) return rc;
     egnn_prof_begin(K, st);
@@ -715,19 +852,19 @@ int egnn_wide_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const 
             EGNN_CHECK_LAUNCH("wide_phi_kernel");
         }
         // d vec = column sums of the rows; d (its bias) = sum of the row coefficients
-        colsum_rows(rows, w.np, D2w, M ? lo.wa : lo.wx3);
-        colsum_rows(M ? q : gphi, 1, 1, M ? lo.ba : lo.bx3);
+        G.colsum_rows(rows, w.np, D2w, g.E, M ? lo.wa : lo.wx3);
+        G.colsum_rows(M ? q : gphi, 1, 1, g.E, M ? lo.ba : lo.bx3);
         // second Linear: dW2 = gz2^T a1, db2 = column sums of gz2
-        if (int rc = wgrad(G2T, D2w, A1T, D1w, M ? lo.wm2 : lo.wx2, "tc_wide_gemm wgrad 2")) return rc;
-        colsum_T(G2T, D2w, M ? lo.bm2 : lo.bx2);
+        if (int rc = G.wgrad(G2T, D2w, A1T, D1w, M ? lo.wm2 : lo.wx2, "tc_wide_gemm wgrad 2")) return rc;
+        G.colsum_T(G2T, D2w, M ? lo.bm2 : lo.bx2);
         // ga1 = gz2 . W2;  gz1 = ga1 * SiLU'(z1): image (for gu) + transpose (for dW1)
         WideGemmArgs d = wide_args(w.mtiles, g.E);
         wide_operands(d, G2, w.w_ks, blk(M ? wo.m2t : wo.x2t), ks2, wide_cdiv(D1w, WIDE_TN), D1w);
         d.out_img = G1; d.out_ks = w.w_ks; d.out_T = G1T; d.kst = w.kst; d.rows = D1; d.rows_ld = w.np;
         if (int rc = launch_wide<WIDE_DGRAD>(d, precision, st, "tc_wide_gemm dgrad 2", K)) return rc;
         // first Linear: dW1 = gz1^T u, db1 = column sums of gz1
-        if (int rc = wgrad(G1T, D1w, UT, K0, M ? lo.wm1 : lo.wx1, "tc_wide_gemm wgrad 1")) return rc;
-        colsum_T(G1T, D1w, M ? lo.bm1 : lo.bx1);
+        if (int rc = G.wgrad(G1T, D1w, UT, K0, M ? lo.wm1 : lo.wx1, "tc_wide_gemm wgrad 1")) return rc;
+        G.colsum_T(G1T, D1w, M ? lo.bm1 : lo.bx1);
     }
     EGNN_CHECK_LAUNCH("wide colsum kernels");
     {   // gu = gz1m . Wm1 + gz1x . Wx1: one GEMM over the concatenated K
@@ -742,5 +879,87 @@ int egnn_wide_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const 
     wide_edge_out_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(g.E, net.H, g.recv, g.send, g.node_graph, x, gu, gdx, coefS, phi, Gr, Gs);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("wide_edge_out_kernel");
+    return EGNN_OK;
+}
+
+// ---- node phase ---------------------------------------------------------------------------------------------------------------
+// h' = mlp_h([h, M]) (EquivariantGraphNeuralNetwork.py:69, no residual) on the tile GEMMs, plus the coordinate sums from phi_e.
+// agg holds complete per-receiver sums (row stride Ms + 4, written by egnn_wide_edge_forward); they are saved to msum.
+int egnn_wide_node_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
+                           const float* h, const float* x, const float* agg, const float* phi_edge, float* h_out, float* msum,
+                           float* dxu, float* Dn, float* scratch, int precision, cudaStream_t st) {
+    EGNN_REQUIRE(wide_node_supported(net), "egnn_wide_node_forward: network outside the wide path's limits");
+    const LayerOff lo = layer_off(net);
+    const PackOff po = pack_off(net);
+    const WideOff wo = wide_off(net);
+    const WideWs ww = wide_ws(net, g.E, g.N);
+    uint8_t* base = wide_align(scratch);
+    uint8_t *NI = base + ww.ni, *A1 = base + ww.a1n;
+    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    auto blk = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
+    const int K = EGNN_K_NODE_FWD, a1_ks = wo.nth * (WIDE_TN / WIDE_TK);
+    egnn_prof_begin(K, st);
+    wide_node_geom_kernel<<<wide_cdiv(g.N, 32), 256, 0, st>>>(g.N, g.row_ptr, g.send, x, phi_edge, dxu, Dn);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("wide_node_geom_kernel");
+    if (int rc = wide_rows_to_img(g.N, ww.mtiles_n, net.H, net.Ms, wo.ksn, h, agg, net.Ms + 4, msum, NI, nullptr, 0, 0, st, K)) return rc;
+    WideGemmArgs a = wide_args(ww.mtiles_n, g.N);
+    wide_operands(a, NI, wo.ksn, blk(wo.h1), wo.ksn, wo.nth, net.Hh);
+    a.bias = params_layer + lo.bh1; a.out_img = A1; a.out_ks = a1_ks;
+    if (int rc = launch_wide<WIDE_IMG>(a, precision, st, "tc_wide_gemm h1", K)) return rc;
+    wide_operands(a, A1, a1_ks, blk(wo.h2), wo.ksh, 1, net.H);
+    a.bias = params_layer + lo.bh2; a.out = h_out; a.out_ld = net.H;
+    return launch_wide<WIDE_F32>(a, precision, st, "tc_wide_gemm h2", K);
+}
+
+int egnn_wide_node_bwd_rows(const egnn_net_t& net, int64_t N) { return wide_node_bwd_ws(net, N).splits; }
+int64_t egnn_wide_node_bwd_bytes(const egnn_net_t& net, int64_t N) { return wide_node_bwd_ws(net, N).total + 1024; }
+
+// backward of mlp_h (egcl_bwd.cu: egcl_node_bwd): gh_node = d/dh, gM = d/dM, weight-gradient partials in rows [0, rows) of part
+int egnn_wide_node_backward(const egnn_net_t& net, int N, const float* params_layer, const float* packed_layer, const float* h,
+                            const float* msum, const float* gh_out, float* gh_node, float* gM, float* part, float* scratch,
+                            int precision, cudaStream_t st) {
+    EGNN_REQUIRE(wide_node_supported(net), "egnn_wide_node_backward: network outside the wide path's limits");
+    const LayerOff lo = layer_off(net);
+    const PackOff po = pack_off(net);
+    const WideOff wo = wide_off(net);
+    const WideNodeBwdWs w = wide_node_bwd_ws(net, N);
+    uint8_t* base = wide_align(scratch);
+    uint8_t *NI = base + w.ni, *NIT = base + w.nit, *A1 = base + w.a1, *A1T = base + w.a1t, *GO = base + w.go, *GOT = base + w.got;
+    uint8_t *G1 = base + w.g1, *G1T = base + w.g1t;
+    float *D1 = reinterpret_cast<float*>(base + w.d1), *gin = reinterpret_cast<float*>(base + w.gin);
+    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    auto blk = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
+    const int K = EGNN_K_NODE_BWD, Kn = net.H + net.Ms;
+    const WideGrad G{w.kst, w.per, w.splits, part, (int64_t)lo.total, precision, st, K};
+    // [h | M] image + transpose; gh_out image + transpose (gz2 = gh_out: the second Linear has no activation)
+    if (int rc = wide_rows_to_img(N, w.mtiles, net.H, net.Ms, wo.ksn, h, msum, net.Ms, nullptr, NI, NIT, WIDE_TN, w.kst, st, K)) return rc;
+    if (int rc = wide_rows_to_img(N, w.mtiles, net.H, 0, wo.ksH, gh_out, nullptr, 0, nullptr, GO, GOT, WIDE_TM, w.kst, st, K)) return rc;
+    // recompute the first Linear: a1 image + transpose + SiLU' rows
+    WideGemmArgs a = wide_args(w.mtiles, N);
+    wide_operands(a, NI, wo.ksn, blk(wo.h1), wo.ksn, wo.nth, net.Hh);
+    a.bias = params_layer + lo.bh1; a.out_img = A1; a.out_ks = w.h_ks; a.out_T = A1T; a.kst = w.kst; a.rows = D1; a.rows_ld = w.hp;
+    if (int rc = launch_wide<WIDE_IMG_BWD>(a, precision, st, "tc_wide_gemm node bwd 1", K)) return rc;
+    // dWh2 = gh_out^T a1, dbh2 = column sums of gh_out
+    if (int rc = G.wgrad(GOT, net.H, A1T, net.Hh, lo.wh2, "tc_wide_gemm node wgrad 2")) return rc;
+    G.colsum_T(GOT, net.H, lo.bh2);
+    // ga1 = gh_out . Wh2;  gz1 = ga1 * SiLU'(z1)
+    WideGemmArgs d = wide_args(w.mtiles, N);
+    wide_operands(d, GO, wo.ksH, blk(wo.h2t), wo.ksH, wo.nth, net.Hh);
+    d.out_img = G1; d.out_ks = w.h_ks; d.out_T = G1T; d.kst = w.kst; d.rows = D1; d.rows_ld = w.hp;
+    if (int rc = launch_wide<WIDE_DGRAD>(d, precision, st, "tc_wide_gemm node dgrad 2", K)) return rc;
+    // dWh1 = gz1^T [h | M], dbh1 = column sums of gz1
+    if (int rc = G.wgrad(G1T, net.Hh, NIT, Kn, lo.wh1, "tc_wide_gemm node wgrad 1")) return rc;
+    G.colsum_T(G1T, net.Hh, lo.bh1);
+    // g[h | M] = gz1 . Wh1
+    WideGemmArgs f = wide_args(w.mtiles, N);
+    wide_operands(f, G1, w.h_ks, blk(wo.h1t), wo.ksh, wo.ntn, Kn);
+    f.out = gin; f.out_ld = w.gin_ld;
+    if (int rc = launch_wide<WIDE_F32>(f, precision, st, "tc_wide_gemm node dgrad 1", K)) return rc;
+    const long long tot = (long long)N * Kn;
+    egnn_prof_begin(K, st);
+    wide_split_gin_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(N, net.H, net.Ms, gin, w.gin_ld, gh_node, gM);
+    egnn_prof_end(st);
+    EGNN_CHECK_LAUNCH("wide_split_gin_kernel");
     return EGNN_OK;
 }
