@@ -607,9 +607,14 @@ def main():
     ap.add_argument("--eager", action="store_true", help="time the kernel-by-kernel step instead of the CUDA-graph replay")
     ap.add_argument("--sampling-structures", type=int, default=SAMPLING["structures"],
                     help="structures per GPU of the sampling leg (cfg3: 512 x 192 atoms fully connected, T = 1000); 0 skips it")
-    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4"],
-                    help="cfg2 (default, the contract line) or cfg4 (1536-atom cells, L=9, hidden 256)")
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg4", "yaml"],
+                    help="cfg2 (default, the contract line), cfg4 (1536-atom cells, L=9, hidden 256) or yaml (the reference's own "
+                         "parameters.yaml network, one GPU: bench_yaml.py; --global-batch = graphs per step, default 1)")
     args = ap.parse_args()
+    if args.workload == "yaml":
+        import bench_yaml
+        bench_yaml.main(["--steps", str(args.steps), "--batch", str(args.global_batch or 1)] + (["--skip-cpu"] if args.impl != "b200" else []))
+        return
     if args.workload == "cfg4":
         CFG.update(CFG4)
     CFG["scaling"] = "weak"

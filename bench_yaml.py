@@ -28,14 +28,17 @@ YAML = dict(L=5, atom_type_size=2, compressed_spectrum_size=32, spectrum_size=20
             t_size=1, d_size=1, m_size=256, m_hidden_size=1024, h_hidden_size=1024, x_hidden_size=1024, T=1000, s=1e-5, power=2.0, lr=1e-5)
 
 
-def main():
+def main(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--atoms", type=int, default=96)
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--precision", default="auto")
-    args = ap.parse_args()
+    ap.add_argument("--sample-structures", type=int, default=0,
+                    help="also sample this many structures in one batch through the public sampler (T = 1000 + the t = 0 step, "
+                         "conditioning held constant): BASELINE.md's published figure is this loop at ONE structure per call")
+    args = ap.parse_args(argv)
     import bench
     from diffusion_model_b200 import _lib
     from diffusion_model_b200.DataPreprocessor import SpectrumCompressor
@@ -120,6 +123,33 @@ def main():
                denoiser_forward_ms=fwd_ms, forward_tflops=flops_fwd / (fwd_ms * 1e-3) / 1e12,
                config=dict(workload=f"parameters.yaml: conditional EGNN L=5, K0=73, m/x/h hidden 1024, m_size 256, SpectrumCompressor, "
                                     f"RAdamScheduleFree; {G} fully connected graph(s) of {n} atoms (E = {E}), T=1000", atoms=n, batch=G, edges=E))
+    if args.sample_structures > 0:
+        # generate()'s loop (parts/train_per_iretation.py:299-442) batched: the reference's published run is this, one structure
+        # per call (~6.9 ms per denoiser graph-step, ~0.144 structures/s on the author's GPU, hidden sizes not recorded)
+        import copy
+        from diffusion_model_b200.sampler import sample_structures
+        S = args.sample_structures
+        snet = copy.deepcopy(net)
+        bench.tame_(snet, y["L"], fx=0.002, fd=0.001)
+        snet.precision = args.precision
+        with torch.no_grad():
+            cond1 = _conditioning(batch, params, nn_dict)[:n]
+        gen_d = torch.Generator(device=dev)
+        gen_d.manual_seed(11)
+        l1 = lib.egnn_launch_count()
+        e0.record()
+        res = sample_structures(snet, dp, n, S, atom_type_size=2, cond=cond1, generator=gen_d, device=dev)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        sec_s = e0.elapsed_time(e1) * 1e-3
+        T1 = y["T"] + 1
+        out["sampling"] = dict(metric="sampled structures/s (conditional x+h ancestral sampling, T+1 denoiser calls per structure)",
+                               value=S / sec_s, unit="structures/s", seconds=sec_s, structures=S, accepted=int(res["finite"].sum()),
+                               denoiser_graph_steps_per_s=S * T1 / sec_s, ms_per_denoiser_call=1e3 * sec_s / T1,
+                               gpu_launches=int(lib.egnn_launch_count() - l1),
+                               published_reference="~144 denoiser graph-steps/s, ~0.144 structures/s, one structure per call (BASELINE.md, author's GPU, "
+                                                   "hidden sizes of that run not recorded)",
+                               weights="seeded random init, coordinate head x0.002 / distance columns x0.001 (untrained nets diverge)")
     if not args.skip_cpu:
         from oracle import diffusion_ref as D, egnn_ref, loops_ref as LP
         from oracle.radam_sf_ref import RAdamScheduleFreeRef

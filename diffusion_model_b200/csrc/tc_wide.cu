@@ -374,16 +374,29 @@ __device__ __forceinline__ void wide_store_chunk(uint8_t* slice_row, int j, cons
     *reinterpret_cast<uint4*>(slice_row + j * (WIDE_TM * 16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
     *reinterpret_cast<uint4*>(slice_row + j * (WIDE_TM * 16) + WIDE_A_SLICE / 2) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }
-// the same 8 values into the transposed image: element (feature row row0 + i, this thread's edge); tbase points at the
-// edge's 2-byte lane of feature row 0 of the slice, lo_off = half the slice
-__device__ __forceinline__ void wide_store_T(uint8_t* tbase, int row0, int lo_off, const float (&v)[8]) {
+// the same 8 values into the transposed image (rows = features, 16-byte chunks of 8 consecutive edges).  The 8 lanes of a
+// group hold 8 consecutive edges: an 8 x 8 transpose through the shuffle network (3 butterfly steps) leaves lane s of the
+// group with feature row0 + s of all 8 edges, i.e. one whole chunk -- a 16-byte store per lane, 128 contiguous bytes per
+// group, instead of sixteen 2-byte stores.  tchunk = the slice's chunk column of this edge group; v is consumed.
+__device__ __forceinline__ void wide_store_T(uint8_t* tchunk, int row0, int lo_off, float (&v)[8], int lane) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const __nv_bfloat16 h = __float2bfloat16_rn(v[i]);
-        const __nv_bfloat16 l = __float2bfloat16_rn(v[i] - __bfloat162float(h));
-        *reinterpret_cast<__nv_bfloat16*>(tbase + (row0 + i) * 16) = h;
-        *reinterpret_cast<__nv_bfloat16*>(tbase + (row0 + i) * 16 + lo_off) = l;
+    for (int d = 4; d > 0; d >>= 1) {
+        const bool up = lane & d;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (i & d) continue;
+            const float send = up ? v[i] : v[i + d];
+            const float recv = __shfl_xor_sync(0xffffffffu, send, d);
+            if (up) v[i] = recv;
+            else v[i + d] = recv;
+        }
     }
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) tc::split2(v[2 * i], v[2 * i + 1], hi[i], lo[i]);
+    uint8_t* d = tchunk + (row0 + (lane & 7)) * 16;
+    *reinterpret_cast<uint4*>(d) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(d + lo_off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }
 
 template <int MODE, int NPASS>
@@ -484,7 +497,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
             uint8_t* t = nullptr;
             float* d1 = nullptr;
             if (MODE == WIDE_IMG_BWD) {
-                t = a.out_T + ((size_t)nt * a.kst + e / WIDE_TK) * WIDE_B_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TN * 16) + (e % 8) * 2;
+                t = a.out_T + ((size_t)nt * a.kst + e / WIDE_TK) * WIDE_B_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TN * 16);
                 d1 = a.rows + (size_t)e * a.rows_ld + n0;
             }
 #pragma unroll 1
@@ -503,9 +516,9 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
                     }
                     *reinterpret_cast<float4*>(d1 + 8 * j) = make_float4(d[0], d[1], d[2], d[3]);
                     *reinterpret_cast<float4*>(d1 + 8 * j + 4) = make_float4(d[4], d[5], d[6], d[7]);
-                    wide_store_T(t, c0 + 8 * j, WIDE_B_SLICE / 2, v);
                 }
                 wide_store_chunk(o, j, v);
+                if (MODE == WIDE_IMG_BWD) wide_store_T(t, c0 + 8 * j, WIDE_B_SLICE / 2, v, lane);
             }
         } else if (MODE == WIDE_GATE || MODE == WIDE_ROWDOT || MODE == WIDE_GATE_BWD || MODE == WIDE_ROWDOT_BWD) {
             // row dot of the activated outputs with vec: 64 columns per thread, then the four column groups in fixed order
@@ -516,7 +529,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
             if (MODE == WIDE_ROWDOT_BWD) gph = live ? a.gphi[e] : 0.f;
             if (MODE == WIDE_GATE_BWD || MODE == WIDE_ROWDOT_BWD) {
                 o = a.out_img + ((size_t)mt * a.out_ks + n0 / WIDE_TK) * WIDE_A_SLICE + r * 16;
-                t = a.out_T + ((size_t)(n0 / WIDE_TM) * a.kst + e / WIDE_TK) * WIDE_A_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TM * 16) + (e % 8) * 2;
+                t = a.out_T + ((size_t)(n0 / WIDE_TM) * a.kst + e / WIDE_TK) * WIDE_A_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TM * 16);
             }
             float dot = 0.f, dot2 = 0.f;
 #pragma unroll 1
@@ -539,7 +552,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
                     *reinterpret_cast<float4*>(ro) = make_float4(ga[0], ga[1], ga[2], ga[3]);
                     *reinterpret_cast<float4*>(ro + 4) = make_float4(ga[4], ga[5], ga[6], ga[7]);
                     wide_store_chunk(o, j, g2);
-                    wide_store_T(t, (c0 % WIDE_TM) + 8 * j, WIDE_A_SLICE / 2, g2);
+                    wide_store_T(t, (c0 % WIDE_TM) + 8 * j, WIDE_A_SLICE / 2, g2, lane);
                 } else {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -593,12 +606,12 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
                     *reinterpret_cast<float4*>(ro + 8 * j) = make_float4(v[0], v[1], v[2], v[3]);
                     *reinterpret_cast<float4*>(ro + 8 * j + 4) = make_float4(v[4], v[5], v[6], v[7]);
                     wide_store_chunk(o, j, g2);
-                    wide_store_T(t, (c0 % WIDE_TM) + 8 * j, WIDE_A_SLICE / 2, g2);
+                    wide_store_T(t, (c0 % WIDE_TM) + 8 * j, WIDE_A_SLICE / 2, g2, lane);
                 }
             }
         } else if (MODE == WIDE_DGRAD) {
             uint8_t* o = a.out_img + ((size_t)mt * a.out_ks + n0 / WIDE_TK) * WIDE_A_SLICE + r * 16;
-            uint8_t* t = a.out_T + ((size_t)(n0 / WIDE_TM) * a.kst + e / WIDE_TK) * WIDE_A_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TM * 16) + (e % 8) * 2;
+            uint8_t* t = a.out_T + ((size_t)(n0 / WIDE_TM) * a.kst + e / WIDE_TK) * WIDE_A_SLICE + ((e % WIDE_TK) / 8) * (WIDE_TM * 16);
             const float* d1 = a.rows + (size_t)e * a.rows_ld + n0;
 #pragma unroll 1
             for (int j = 0; j < 8; ++j) {
@@ -609,7 +622,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[i] = live ? v[i] * d[i] : 0.f;
                 wide_store_chunk(o, j, v);
-                wide_store_T(t, (c0 % WIDE_TM) + 8 * j, WIDE_A_SLICE / 2, v);
+                wide_store_T(t, (c0 % WIDE_TM) + 8 * j, WIDE_A_SLICE / 2, v, lane);
             }
         } else if (MODE == WIDE_F32) {
             float* o = a.out + (size_t)e * a.out_ld + n0;

@@ -350,6 +350,59 @@ def golden_conditional(egnn_mod):
     print("loss_cond: H =", H, "loss =", loss.item())
 
 
+YAML_SIZES = dict(L=2, m_input=73, m_hidden=1024, m_output=256, x_input=73, x_hidden=1024, x_output=1, h_input=36 + 256,
+                  h_hidden=1024, h_output=36)
+YAML_SEED = 2024
+YAML_SUB = 8  # gradients of matrices with more than 50 000 entries are stored as g[::8, ::8] (and their full norm)
+
+
+def yaml_modules(egnn_cls, compressor_cls):
+    """The seeded network of the 'loss_yaml' golden: parameters.yaml widths (main.py:102-121), two layers, default init.
+    The fixture stores a checksum instead of 3.6 M weights; the test rebuilds them with the same seed and class order."""
+    torch.manual_seed(YAML_SEED)
+    net = egnn_cls(**YAML_SIZES)
+    comp = compressor_cls(200, [150, 100, 50], 32)
+    return net, comp
+
+
+def weight_checksum(sd):
+    return np.array([float(v.double().sum()) for v in sd.values()] + [float(v.double().square().sum()) for v in sd.values()])
+
+
+def golden_yaml(egnn_mod):
+    """The reference's own configuration (parameters.yaml: conditional, compressed spectrum 200 -> 150 -> 100 -> 50 -> 32, exO,
+    m/x/h hidden 1024, m_size 256; H = 36, K0 = 73) at L = 2 on two fully connected 14-atom structures: loss, outputs and
+    gradients of the eps-prediction training loss from the UNMODIFIED reference EGNN and SpectrumCompressor."""
+    import importlib
+    dpp = importlib.import_module("DataPreprocessor")
+    A, S = 2, 200
+    ref, comp = yaml_modules(egnn_mod.EquivariantGNN, dpp.SpectrumCompressor)
+    sch = D.Schedule(1e-5, 2.0, 1000)
+    b = G.make_batch(2, 14, seed=43, edges="fc")
+    pos, x1h = torch.from_numpy(b["pos"]), torch.from_numpy(b["x"])
+    ei, batch = torch.from_numpy(b["edge_index"]), torch.from_numpy(b["batch"])
+    N = pos.shape[0]
+    gen = torch.Generator().manual_seed(19)
+    spectrum = torch.rand(N, S, generator=gen)
+    exO = (torch.arange(N) % 14 == 0).float().view(N, 1)
+    t_g = torch.tensor([40, 870])
+    n_pos, n_h = torch.randn(N, 3, generator=gen), torch.randn(N, A, generator=gen)
+    cond = torch.cat((comp(spectrum), exO), dim=1)
+    loss, aux = LP.train_loss(lambda e, h, x: ref(e, h, x), sch, pos, x1h, ei, batch, t_g, n_pos, n_h, A=A, cond=cond)
+    loss.backward()
+    out = dict(pos=b["pos"], x=b["x"], edge_index=b["edge_index"], batch=b["batch"], t=t_g.numpy(), noise_pos=n_pos.numpy(),
+               noise_h=n_h.numpy(), spectrum=spectrum.numpy(), exO=exO.numpy(), loss=np.float64(loss.item()),
+               h_in=aux["h_in"].detach().numpy(), h_out=aux["h_out"].detach().numpy(), x_out=aux["x_out"].detach().numpy(),
+               wsum=weight_checksum(ref.state_dict()), cwsum=weight_checksum(comp.state_dict()))
+    for mod, tag in ((ref, "g:"), (comp, "cg:")):
+        for k, p_ in mod.named_parameters():
+            g = p_.grad
+            out[tag + "norm:" + k] = np.float64(g.double().norm().item())
+            out[tag + k] = (g[::YAML_SUB, ::YAML_SUB] if g.numel() > 50000 else g).numpy()
+    np.savez_compressed(os.path.join(GOLD, "loss_yaml.npz"), **out)
+    print("loss_yaml: loss =", loss.item(), "|h_out| max", float(aux["h_out"].abs().max()))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(4)
@@ -359,6 +412,7 @@ def main():
     golden_egnn(egnn_mod)
     golden_loops(egnn_mod, dxh)
     golden_conditional(egnn_mod)
+    golden_yaml(egnn_mod)
     print("golden vectors written to", GOLD)
 
 

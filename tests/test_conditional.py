@@ -201,3 +201,97 @@ def test_parameters_yaml_widths_forward_and_gradients(lib, precision):
     worst = max(errs, key=errs.get)
     print(f"parameters.yaml widths (K0=73, 1024/256), {net.resolved_precision()}: worst gradient {worst} {errs[worst]:.2e}")
     assert errs[worst] <= 1e-3, sorted(errs.items(), key=lambda kv: -kv[1])[:5]
+
+
+# ---- the reference's own widths (parameters.yaml), golden from the UNMODIFIED reference: oracle/make_golden.py: golden_yaml ----
+def _yaml_golden(golden_dir):
+    from oracle import make_golden as MG
+    z = np.load(os.path.join(golden_dir, "loss_yaml.npz"), allow_pickle=False)
+    return z, MG
+
+
+def _same_weights(a, b):
+    # float64 sums and sums of squares per tensor; the summation order depends on the thread count, hence not bit-equal
+    return np.allclose(a, b, rtol=1e-9, atol=1e-9)
+
+
+def _check_yaml_grads(z, named_grads, tag, bar):
+    from oracle.make_golden import YAML_SUB
+    worst = ("", 0.0)
+    for k, g in named_grads:
+        g = g.detach().cpu()
+        want = torch.from_numpy(z[tag + k])
+        got = g[::YAML_SUB, ::YAML_SUB] if g.numel() > 50000 else g
+        # sub-sampled entries are judged against the tensor's largest stored entry; the full norm pins the rest
+        e = relerr(got, want)
+        ne = abs(float(g.double().norm()) - float(z[tag + "norm:" + k])) / float(z[tag + "norm:" + k])
+        assert e <= bar and ne <= bar, (k, e, ne)
+        if e > worst[1]:
+            worst = (k, e)
+    return worst
+
+
+def test_oracle_yaml_widths_loss(golden_dir):
+    """the CPU restatement against the reference at the reference's own widths (K0 = 73, hidden 1024, m_size 256)"""
+    from diffusion_model_b200.DataPreprocessor import SpectrumCompressor
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    z, MG = _yaml_golden(golden_dir)
+    net, comp = MG.yaml_modules(EquivariantGNN, SpectrumCompressor)  # CPU modules: parameters only (no CPU forward exists)
+    assert _same_weights(MG.weight_checksum(net.state_dict()), z["wsum"]), "seeded weights differ from the fixture's"
+    sd = {k: v.detach().clone().requires_grad_(True) for k, v in net.state_dict().items()}
+    with torch.no_grad():
+        y = torch.from_numpy(z["spectrum"])
+        lin = [m for m in comp.mlp if isinstance(m, torch.nn.Linear)]
+        for n, m in enumerate(lin):
+            y = y @ m.weight.t() + m.bias
+            if n + 1 < len(lin):
+                y = torch.relu(y)
+    cond = torch.cat((y, torch.from_numpy(z["exO"])), dim=1)
+    sch = D.Schedule(1e-5, 2.0, 1000)
+    loss, aux = LP.train_loss(lambda e, h, x: egnn_ref.egnn_forward(sd, MG.YAML_SIZES["L"], e, h, x), sch, torch.from_numpy(z["pos"]),
+                              torch.from_numpy(z["x"]), torch.from_numpy(z["edge_index"]), torch.from_numpy(z["batch"]),
+                              torch.from_numpy(z["t"]), torch.from_numpy(z["noise_pos"]), torch.from_numpy(z["noise_h"]), A=A, cond=cond)
+    assert relerr(aux["h_in"], z["h_in"]) <= 1e-6
+    assert abs(loss.item() - float(z["loss"])) <= 1e-5 * float(z["loss"])
+    loss.backward()
+    _check_yaml_grads(z, [(k, p.grad) for k, p in sd.items()], "g:", 1e-4)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["auto", "fp32"])
+def test_yaml_widths_training_loss_against_reference_golden(lib, golden_dir, precision):
+    """The reference's configuration through the product's entry points (batch_loss, SpectrumCompressor, conditioning):
+    loss 1e-5 (fp32) / 1e-4 (bf16x3), outputs 1e-4, every gradient -- EGNN and compressor -- 1e-3, in the default mode
+    ('auto' = bf16x3 on the tile-GEMM tcgen05 path) and on the fp32 CUDA-core kernels."""
+    from diffusion_model_b200.data import Data
+    from diffusion_model_b200.DataPreprocessor import SpectrumCompressor
+    from diffusion_model_b200.diffusion_x_h import E3DiffusionProcess
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    from diffusion_model_b200.train_per_iretation import _conditioning, batch_loss
+    z, MG = _yaml_golden(golden_dir)
+    net, comp = MG.yaml_modules(EquivariantGNN, SpectrumCompressor)
+    assert _same_weights(MG.weight_checksum(net.state_dict()), z["wsum"]), "seeded weights differ from the fixture's"
+    assert _same_weights(MG.weight_checksum(comp.state_dict()), z["cwsum"])
+    net, comp = net.to("cuda"), comp.to("cuda")
+    assert net.resolved_precision() == "bf16x3"
+    net.precision = precision
+    dp = E3DiffusionProcess(s=1e-5, power=2.0, num_diffusion_timestep=1000)
+    bd = Data(x=torch.from_numpy(z["x"]).cuda(), pos=torch.from_numpy(z["pos"]).cuda(),
+              edge_index=torch.from_numpy(z["edge_index"]).cuda())
+    bd.batch = torch.from_numpy(z["batch"]).cuda()
+    bd.spectrum = torch.from_numpy(z["spectrum"]).cuda()
+    bd.exO = torch.from_numpy(z["exO"]).cuda()
+    params = dict(atom_type_size=A, conditional=True, to_compress_spectrum=True, give_exO=True)
+    cond = _conditioning(bd, params, {"egnn": net, "spectrum_compressor": comp})
+    loss, _, aux = batch_loss(net, bd, dp, params, t=z["t"].tolist(), noise_pos=torch.from_numpy(z["noise_pos"]).cuda(),
+                              noise_h=torch.from_numpy(z["noise_h"]).cuda(), cond=cond)
+    assert relerr(aux["h_in"], z["h_in"]) <= 1e-6
+    lbar = 1e-5 if precision == "fp32" else 1e-4
+    assert abs(loss.item() - float(z["loss"])) <= lbar * float(z["loss"]), (loss.item(), float(z["loss"]))
+    eh, ex = relerr(aux["h_out"], z["h_out"]), relerr(aux["x_out"], z["x_out"])
+    assert eh <= 1e-4 and ex <= 1e-4, (eh, ex)
+    loss.backward()
+    w1 = _check_yaml_grads(z, [(k, p.grad) for k, p in net.named_parameters()], "g:", 1e-3)
+    w2 = _check_yaml_grads(z, [(k, p.grad) for k, p in comp.named_parameters()], "cg:", 1e-3)
+    print(f"parameters.yaml golden, {net.resolved_precision()}: loss rel {abs(loss.item() - float(z['loss'])) / float(z['loss']):.1e} "
+          f"h_out {eh:.1e} x_out {ex:.1e} worst gradient {w1[0]} {w1[1]:.1e} (compressor {w2[1]:.1e})")
