@@ -363,8 +363,8 @@ struct WideGemmArgs {
     const int32_t* recv;
     const float* gphi;          // ROWDOT_BWD: per edge
 };
-constexpr int WIDE_THREADS = 512, WIDE_STAGES = 2, WIDE_STAGE_BYTES = WIDE_A_SLICE + WIDE_B_SLICE;
-constexpr int WIDE_SMEM = WIDE_STAGES * WIDE_STAGE_BYTES + 1024 /*bias, vec*/ * 2 + 2 * 4 * WIDE_TM * 4 /*row partials*/ + 64;
+constexpr int WIDE_EPI_THREADS = 512, WIDE_THREADS = WIDE_EPI_THREADS + 64, WIDE_STAGES = 2, WIDE_STAGE_BYTES = WIDE_A_SLICE + WIDE_B_SLICE;
+constexpr int WIDE_SMEM = WIDE_STAGES * WIDE_STAGE_BYTES + 1024 /*bias, vec*/ * 2 + 2 * 4 * WIDE_TM * 4 /*row partials*/ + 128;
 
 // 8 consecutive columns of row r -> chunk j of a [128-row] operand slice (hi | lo)
 __device__ __forceinline__ void wide_store_chunk(uint8_t* slice_row, int j, const float (&v)[8]) {
@@ -399,6 +399,14 @@ __device__ __forceinline__ void wide_store_T(uint8_t* tchunk, int row0, int lo_o
     *reinterpret_cast<uint4*>(d + lo_off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }
 
+// 18 warps: 16 epilogue warps (warp w reads TMEM lanes 32 (w & 3) .., columns 64 (w >> 2) ..), one producer warp (bulk copies)
+// and one MMA-issuer warp.  The accumulator is double-buffered in TMEM (2 x 256 columns): while the epilogue warps drain
+// tile t from buffer t & 1, the issuer already runs tile t + 1 into the other buffer -- the CUDA-core epilogue (SiLU, bf16
+// splits, image stores) and the tensor pipe overlap.  Barriers: full / empty per ring stage (complete_tx / tcgen05.commit),
+// acc_full per buffer (tcgen05.commit), acc_empty per buffer (one arrival per epilogue warp); the epilogue warps synchronise
+// among themselves on named barrier 1.
+__device__ __forceinline__ void wide_epi_sync() { asm volatile("bar.sync 1, %0;" ::"r"(WIDE_EPI_THREADS) : "memory"); }
+
 template <int MODE, int NPASS>
 __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -406,12 +414,13 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
     float* sVec = sBias + WIDE_TN;
     float* sDot = sVec + WIDE_TN;      // [4][128]
     float* sDot2 = sDot + 4 * WIDE_TM;  // [4][128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sDot2 + 4 * WIDE_TM);  // full[2], empty[2], acc
-    uint32_t* slot = reinterpret_cast<uint32_t*>(bars + 5);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, q = warp & 3, cg = warp >> 2;
-    if (warp == 0) tc::tmem_alloc(slot, 256);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sDot2 + 4 * WIDE_TM);  // full[2], empty[2], acc_full[2], acc_empty[2]
+    uint32_t* slot = reinterpret_cast<uint32_t*>(bars + 8);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, q = warp & 3, cg = (warp >> 2) & 3;
+    if (warp == 0) tc::tmem_alloc(slot, 512);
     if (tid == 0) {
-        for (int b = 0; b < 5; ++b) tc::mbar_init(&bars[b], 1);
+        for (int b = 0; b < 6; ++b) tc::mbar_init(&bars[b], 1);
+        for (int b = 6; b < 8; ++b) tc::mbar_init(&bars[b], WIDE_EPI_THREADS / 32);
         tc::fence_mbar_init();
     }
     tc::fence_before_sync();
@@ -432,58 +441,64 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
         kb = s * a.KS;
         kc = min(a.KS, a.KS_total - kb);
     };
-    int p_it = 0, p_ks = 0, p_g = 0;  // producer: next slice to request = slice p_ks of this CTA's tile p_it; p_g counts requests
-    int m_g = 0;                      // issuer: slices consumed
     pdl_launch_dependents();
     pdl_wait();  // the A image comes from the kernel in front
 
-    for (int it = 0; it < nit; ++it) {
+    if (warp == WIDE_EPI_THREADS / 32) {  // ---- producer: one thread runs the ring as far ahead as the empty barriers allow
+        if (lane == 0) {
+            int g = 0;
+            for (int it = 0; it < nit; ++it) {
+                int nt, mt, kb, kc;
+                decode(it, nt, mt, kb, kc);
+                for (int k = 0; k < kc; ++k, ++g) {
+                    const int s = g % WIDE_STAGES, u = g / WIDE_STAGES;
+                    if (u > 0) ok = tc::mbar_wait(&bars[2 + s], (u - 1) & 1) && ok;
+                    const int ks = kb + k;
+                    const uint8_t* srcA = ks < a.ks_split ? a.A + ((size_t)mt * a.a_ks + ks) * WIDE_A_SLICE
+                                                          : a.A2 + ((size_t)mt * a.a2_ks + (ks - a.ks_split)) * WIDE_A_SLICE;
+                    const uint32_t full = tc::smem_u32(&bars[s]), dst = sb + s * WIDE_STAGE_BYTES;
+                    tc::mbar_expect_tx(full, WIDE_STAGE_BYTES);
+                    tc::bulk_g2s(dst, srcA, WIDE_A_SLICE, full);
+                    tc::bulk_g2s(dst + WIDE_A_SLICE, a.B + ((size_t)nt * a.b_ks + ks) * WIDE_B_SLICE, WIDE_B_SLICE, full);
+                }
+            }
+        }
+    } else if (warp == WIDE_EPI_THREADS / 32 + 1) {  // ---- MMA issuer
+        if (lane == 0) {
+            int g = 0;
+            for (int it = 0; it < nit; ++it) {
+                int nt, mt, kb, kc;
+                decode(it, nt, mt, kb, kc);
+                const int b = it & 1;
+                if (it >= 2) ok = tc::mbar_wait(&bars[6 + b], ((it >> 1) - 1) & 1) && ok;  // the epilogue has drained this buffer
+                tc::fence_after_sync();
+                for (int k = 0; k < kc; ++k, ++g) {
+                    const int s = g % WIDE_STAGES;
+                    ok = tc::mbar_wait(&bars[s], (g / WIDE_STAGES) & 1) && ok;
+                    tc::fence_after_sync();
+                    const uint32_t base = sb + s * WIDE_STAGE_BYTES;
+                    const TcOperand opA{base, base + WIDE_A_SLICE / 2, WIDE_TM * 16, false};
+                    const TcOperand opB{base + WIDE_A_SLICE, base + WIDE_A_SLICE + WIDE_B_SLICE / 2, WIDE_TN * 16, false};
+                    tc_issue_op<NPASS>(tmem, b * WIDE_TN, opA, opB, WIDE_TK, WIDE_TN, k > 0);
+                    tc::mma_commit(&bars[2 + s]);
+                }
+                tc::mma_commit(&bars[4 + b]);
+            }
+        }
+    } else
+    for (int it = 0; it < nit; ++it) {  // ---- epilogue warps
         int nt, mt, kb, kc;
         decode(it, nt, mt, kb, kc);
-        if (tid == 0) {
-            // this tile's slices plus the first two of the next tile (they land while the epilogue runs)
-            while (p_it < nit && (p_it <= it || (p_it == it + 1 && p_ks < WIDE_STAGES))) {
-                int lnt, lmt, lkb, lkc;
-                decode(p_it, lnt, lmt, lkb, lkc);
-                if (p_ks >= lkc) {
-                    ++p_it;
-                    p_ks = 0;
-                    continue;
-                }
-                const int s = p_g % WIDE_STAGES, u = p_g / WIDE_STAGES;
-                if (u > 0) ok = tc::mbar_wait(&bars[2 + s], (u - 1) & 1) && ok;
-                const int ks = lkb + p_ks;
-                const uint8_t* srcA = ks < a.ks_split ? a.A + ((size_t)lmt * a.a_ks + ks) * WIDE_A_SLICE
-                                                      : a.A2 + ((size_t)lmt * a.a2_ks + (ks - a.ks_split)) * WIDE_A_SLICE;
-                const uint32_t full = tc::smem_u32(&bars[s]), dst = sb + s * WIDE_STAGE_BYTES;
-                tc::mbar_expect_tx(full, WIDE_STAGE_BYTES);
-                tc::bulk_g2s(dst, srcA, WIDE_A_SLICE, full);
-                tc::bulk_g2s(dst + WIDE_A_SLICE, a.B + ((size_t)lnt * a.b_ks + ks) * WIDE_B_SLICE, WIDE_B_SLICE, full);
-                ++p_ks;
-                ++p_g;
-            }
-        } else if (tid == 32) {
-            for (int ks = 0; ks < kc; ++ks, ++m_g) {
-                const int s = m_g % WIDE_STAGES;
-                ok = tc::mbar_wait(&bars[s], (m_g / WIDE_STAGES) & 1) && ok;
-                tc::fence_after_sync();
-                const uint32_t base = sb + s * WIDE_STAGE_BYTES;
-                const TcOperand opA{base, base + WIDE_A_SLICE / 2, WIDE_TM * 16, false};
-                const TcOperand opB{base + WIDE_A_SLICE, base + WIDE_A_SLICE + WIDE_B_SLICE / 2, WIDE_TN * 16, false};
-                tc_issue_op<NPASS>(tmem, 0, opA, opB, WIDE_TK, WIDE_TN, ks > 0);
-                tc::mma_commit(&bars[2 + s]);
-            }
-            tc::mma_commit(&bars[4]);
-        }
+        const int b = it & 1;
         // bias / vector of this N tile (columns past N are zero: their accumulators are zero too, SiLU(0) = 0)
-        if (MODE != WIDE_DGRAD && MODE != WIDE_F32 && MODE != WIDE_WGRAD && tid >= 64 && tid < 64 + WIDE_TN) {
-            const int c = tid - 64, n = nt * WIDE_TN + c;
+        if (MODE != WIDE_DGRAD && MODE != WIDE_F32 && MODE != WIDE_WGRAD && tid < WIDE_TN) {
+            const int c = tid, n = nt * WIDE_TN + c;
             sBias[c] = n < a.N ? a.bias[n] : 0.f;
             if (MODE == WIDE_GATE || MODE == WIDE_ROWDOT || MODE == WIDE_GATE_BWD || MODE == WIDE_ROWDOT_BWD)
                 sVec[c] = n < a.N ? a.vec[n] : 0.f;
         }
-        __syncthreads();
-        ok = tc::mbar_wait(&bars[4], it & 1) && ok;
+        wide_epi_sync();
+        ok = tc::mbar_wait(&bars[4 + b], (it >> 1) & 1) && ok;
         tc::fence_after_sync();
         __syncwarp();
 
@@ -491,7 +506,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
         const bool live = e < a.E;
         const int c0 = cg * 64;                // this thread's 64 columns of the tile
         const int n0 = nt * WIDE_TN + c0;      // ... of the matrix
-        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + c0;
+        const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16) + b * WIDE_TN + c0;
         if (MODE == WIDE_IMG || MODE == WIDE_IMG_BWD) {
             uint8_t* o = a.out_img + ((size_t)mt * a.out_ks + n0 / WIDE_TK) * WIDE_A_SLICE + r * 16;
             uint8_t* t = nullptr;
@@ -564,7 +579,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
             }
             sDot[cg * WIDE_TM + r] = dot;
             if (MODE == WIDE_GATE_BWD) sDot2[cg * WIDE_TM + r] = dot2;
-            __syncthreads();
+            wide_epi_sync();
             const float full = ((sDot[r] + sDot[WIDE_TM + r]) + sDot[2 * WIDE_TM + r]) + sDot[3 * WIDE_TM + r];
             if (MODE == WIDE_ROWDOT || MODE == WIDE_ROWDOT_BWD) {
                 if (cg == 0 && live) a.out[(size_t)nt * a.out_ld + e] = full;
@@ -639,7 +654,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
                 }
             }
         } else {  // WIDE_WGRAD: row e = feature n of the weight matrix, columns = its input features
-            const int s = (blockIdx.x + it * gridDim.x) / (a.NT * a.mtiles);
+            const int s = kb / a.KS;
             float* o = a.out + (size_t)s * a.out_split + (size_t)e * a.out_ld + n0;
 #pragma unroll 1
             for (int j = 0; j < 8; ++j) {
@@ -653,11 +668,14 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
             }
         }
         tc::fence_before_sync();
-        __syncthreads();  // the accumulator, sBias / sVec / sDot are free for the next tile
-        tc::fence_after_sync();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&bars[6 + b]);  // this warp has read its part of the accumulator
+        wide_epi_sync();                                // sBias / sVec / sDot are free for the next tile
     }
     if (!ok) asm volatile("trap;");  // an mbarrier wait timed out: fail loudly instead of returning garbage
-    if (warp == 0) tc::tmem_dealloc(tmem, 256);
+    tc::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
 template <int MODE>
