@@ -127,10 +127,20 @@ def test_tc_forward_edge_cases_and_unsupported(lib):
             assert _relerr(ho, hr) <= tol and _relerr(xo, xr) <= tol, (prec, _relerr(ho, hr), _relerr(xo, xr))
             ho2, xo2 = wide(ei.to(DEV), h.to(DEV), x.to(DEV))
             assert torch.equal(ho, ho2) and torch.equal(xo, xo2)
-    odd = EquivariantGNN(**egnn_ref.net_sizes(1, 96)).to(DEV)  # no tcgen05 tile for d = 96: must refuse, not fall back
-    odd.precision = "bf16"
+    # d = 96 has no fused kernel: the tile-GEMM path (csrc/tc_wide.cu) pads it to 256 columns
+    odd = EquivariantGNN(**egnn_ref.net_sizes(1, 96)).to(DEV)
+    sdo = {k: v.detach().cpu() for k, v in odd.state_dict().items()}
+    odd.precision = "bf16x3"
+    with torch.no_grad():
+        hr, xr = egnn_ref.egnn_forward(sdo, 1, ei, h, x)
+        ho, xo = odd(ei.to(DEV), h.to(DEV), x.to(DEV))
+    assert _relerr(ho, hr) <= 1e-4 and _relerr(xo, xr) <= 1e-4, (_relerr(ho, hr), _relerr(xo, xr))
+    # K0 = 2H+1 = 141 > 128 is outside both tensor-core paths: must refuse, not fall back
+    H = 70
+    far = EquivariantGNN(**egnn_ref.net_sizes(1, 64, H=H)).to(DEV)
+    far.precision = "bf16"
     with pytest.raises(EgnnError):
-        odd(ei.to(DEV), h.to(DEV), x.to(DEV))
+        far(ei.to(DEV), torch.randn(h.shape[0], H, device=DEV), x.to(DEV))
 
 
 # ---------------------------------------------------------------- tensor-core edge BACKWARD vs the reference autograd
