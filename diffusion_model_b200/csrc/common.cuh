@@ -117,7 +117,7 @@ __host__ __device__ static inline LayerOff layer_off(const egnn_net_t& n) {
 }
 // packed = K-major transposes used as the B operand of the forward FFMA GEMMs: Wt[k][n] = W[n][k]
 struct PackOff {
-    int wm1t, wm2t, wx1t, wx2t, wh1t, tc, total;
+    int wm1t, wm2t, wx1t, wx2t, wh1t, tc, wide, total;  // wide: the tile-GEMM weight images (tc_wide.cu), 16-byte aligned
 };
 // the tcgen05 edge kernels cover the uniform-width nets of BASELINE.json: Mh = Ms = Xh = d in {64,128}, 2H+1 <= 16
 __host__ __device__ static inline bool tc_supported(const egnn_net_t& n) {
@@ -189,7 +189,13 @@ struct WideWs {
     int mtiles_n;       // node phase: row tiles of the [h | M] image (ni) and of the hidden image (a1n, nth * 4 slices per tile)
 };
 // the node MLP runs on the tile GEMMs too when its hidden width fits the same limit (else the FFMA node kernels)
-__host__ __device__ static inline bool wide_node_supported(const egnn_net_t& n) { return wide_fwd_supported(n) && n.Hh <= 1024; }
+// -- also for the d = 64 / 128 / 256 networks of the fused edge kernels whose node MLP has no fused tcgen05 kernel (tc_node.cu
+// covers d <= 128 with Hh = d): at d = 256 the FFMA node kernels were 18 % of the cfg4 step
+__host__ __device__ static inline bool wide_node_supported(const egnn_net_t& n) {
+    const bool fused_node = tc_supported(n) && n.Hh == n.Ms && n.H + 1 <= 16;  // = tc_node_supported (defined below)
+    return n.Hh <= 1024 && n.Ms <= WIDE_TN && 2 * n.H + 1 <= 128 && (wide_fwd_supported(n) || (tc_fwd_supported(n) && !fused_node));
+}
+__host__ __device__ static inline bool wide_any(const egnn_net_t& n) { return wide_fwd_supported(n) || wide_node_supported(n); }
 static inline WideWs wide_ws(const egnn_net_t& n, int64_t E, int64_t N) {
     WideWs w;
     const WideOff o = wide_off(n);
@@ -198,10 +204,11 @@ static inline WideWs wide_ws(const egnn_net_t& n, int64_t E, int64_t N) {
     w.a1_ks = npm * (WIDE_TN / WIDE_TK);
     int64_t p = 0;
     auto take = [&](int64_t b) { int64_t q = p; p += (b + 1023) / 1024 * 1024; return q; };
-    w.u = take((int64_t)w.mtiles * o.ks0 * WIDE_A_SLICE);
-    w.a1 = take((int64_t)w.mtiles * w.a1_ks * WIDE_A_SLICE);
-    w.gm = take(E * WIDE_TN * 4);
-    w.phip = take((int64_t)o.ntx2 * E * 4);
+    const bool edges = wide_fwd_supported(n);
+    w.u = take(edges ? (int64_t)w.mtiles * o.ks0 * WIDE_A_SLICE : 0);
+    w.a1 = take(edges ? (int64_t)w.mtiles * w.a1_ks * WIDE_A_SLICE : 0);
+    w.gm = take(edges ? E * WIDE_TN * 4 : 0);
+    w.phip = take(edges ? (int64_t)o.ntx2 * E * 4 : 0);
     w.mtiles_n = (int)((N + WIDE_TM - 1) / WIDE_TM);
     w.ni = take(wide_node_supported(n) ? (int64_t)w.mtiles_n * o.ksn * WIDE_A_SLICE : 0);
     w.a1n = take(wide_node_supported(n) ? (int64_t)w.mtiles_n * o.nth * (WIDE_TN / WIDE_TK) * WIDE_A_SLICE : 0);
@@ -309,7 +316,9 @@ __host__ __device__ static inline PackOff pack_off(const egnn_net_t& n) {
     o.tc = p;
     if (tc_fwd_supported(n)) p += (tc_blob_bytes(n.Mh) + 15) / 16 * 4 + tc_w2t_bytes(n.Mh) / 4;
     if (tc_node_supported(n)) p += tc_node_blob_bytes(n.Mh) / 4;
-    if (wide_fwd_supported(n)) p += wide_off(n).blocks * (WIDE_B_SLICE / 4);  // starts at o.tc (the fused image is absent)
+    p = round4(p);
+    o.wide = p;
+    if (wide_any(n)) p += wide_off(n).blocks * (WIDE_B_SLICE / 4);
     o.total = round4(p);
     return o;
 }
@@ -353,7 +362,7 @@ static inline FwdWs fwd_ws(const egnn_net_t& n, int64_t N, int64_t E, int64_t G)
     w.dxu = take((int64_t)n.L * N * 3);
     w.S = take((int64_t)n.L * G);
     w.phi = take(tc_fwd_supported(n) || wide_fwd_supported(n) ? E : 0);
-    w.wide = take(wide_fwd_supported(n) ? 256 + wide_ws(n, E, N).total / 4 : 0);  // + 256 floats: the caller aligns to 1 KB
+    w.wide = take(wide_any(n) ? 256 + wide_ws(n, E, N).total / 4 : 0);  // + 256 floats: the caller aligns to 1 KB
     w.total = p;
     return w;
 }

@@ -615,7 +615,7 @@ static int net_backward_impl(const egnn_net_t* net, const egnn_graph_t* g, const
     // rows actually used by this call's kernels (the workspace is sized for the larger of the two paths)
     const int rowsE = E > 0 ? (use_tc ? egnn_tc_bwd_grid(E) : use_tc256 ? egnn_tc_bwd256_rows(E) : use_wide ? egnn_wide_bwd_rows(*net, E)
                                                             : (int)std::min<int64_t>((E + bw.TEB - 1) / bw.TEB, kNumSM)) : 0;
-    const bool node_wide = use_wide && wide_node_supported(*net);
+    const bool node_wide = precision != EGNN_PREC_FP32 && wide_node_supported(*net);
     const int rowsN = node_tc ? egnn_tc_node_bwd_grid(N) : node_wide ? egnn_wide_node_bwd_rows(*net, N) : node_bwd_rows(*net, N);
     RowMap256 m256{};
     if (use_tc256 && E > 0) {

@@ -348,8 +348,8 @@ int egnn_wide_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const f
                            const float* h, const float* x, float* agg, float* phi_edge, float* scratch, int precision,
                            cudaStream_t st);
 int egnn_wide_node_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
-                           const float* h, const float* x, const float* agg, const float* phi_edge, float* h_out, float* msum,
-                           float* dxu, float* Dn, float* scratch, int precision, cudaStream_t st);
+                           const float* h, const float* x, const float* agg, const float* part, int TE, const float* phi_edge,
+                           float* h_out, float* msum, float* dxu, float* Dn, float* scratch, int precision, cudaStream_t st);
 
 extern "C" int egnn_pack_weights(const egnn_net_t* net, const float* params, float* packed, void* stream) {
     if (int rc = egnn_validate_net(net)) return rc;
@@ -385,8 +385,8 @@ int egnn_layer_forward_f32(const egnn_net_t& net, const egnn_graph_t& g, const f
         }
         if (rc) return rc;
     }
-    if (wide && g.E > 0 && wide_node_supported(net)) {
-        if (int rc = egnn_wide_node_forward(net, g, P, Pk, h, x, ws + w.agg, ws + w.phi, h_out, ws + w.msum + (size_t)l * g.N * net.Ms,
+    if (tensor && g.E > 0 && wide_node_supported(net)) {
+        if (int rc = egnn_wide_node_forward(net, g, P, Pk, h, x, ws + w.agg, ws + w.part, TE, ws + w.phi, h_out, ws + w.msum + (size_t)l * g.N * net.Ms,
                                             ws + w.dxu + (size_t)l * g.N * 3, ws + w.D, ws + w.wide, precision, st))
             return rc;
     } else if (tensor && tc_node_supported(net)) {

@@ -52,18 +52,20 @@ __global__ void __launch_bounds__(256) wide_pack_kernel(egnn_net_t net, const fl
     const PackOff po = pack_off(net);
     const WideOff wo = wide_off(net);
     const float* P = params + (size_t)blockIdx.y * lo.total;
-    uint8_t* img = reinterpret_cast<uint8_t*>(packed + (size_t)blockIdx.y * po.total + po.tc);
+    uint8_t* img = reinterpret_cast<uint8_t*>(packed + (size_t)blockIdx.y * po.total + po.wide);
     const int K0 = 2 * net.H + 1, t0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
     auto at = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
-    wide_pack_matrix(P + lo.wm1, net.Mh, K0, K0, false, wo.ks0, 0, at(wo.m1), t0, stride);
-    wide_pack_matrix(P + lo.wm2, net.Ms, net.Mh, net.Mh, false, wo.ksm, 0, at(wo.m2), t0, stride);
-    wide_pack_matrix(P + lo.wx1, net.Xh, K0, K0, false, wo.ks0, 0, at(wo.x1), t0, stride);
-    wide_pack_matrix(P + lo.wx2, net.Xh, net.Xh, net.Xh, false, wo.ksx, 0, at(wo.x2), t0, stride);
-    // dgrad images: ga1 = gz2 . W2 -> rows = columns of W2;  gu = [gz1m | gz1x] . [Wm1 ; Wx1] -> rows = the K0 input columns
-    wide_pack_matrix(P + lo.wm2, net.Mh, net.Ms, net.Mh, true, wo.kss, 0, at(wo.m2t), t0, stride);
-    wide_pack_matrix(P + lo.wx2, net.Xh, net.Xh, net.Xh, true, wo.ksx, 0, at(wo.x2t), t0, stride);
-    wide_pack_matrix(P + lo.wm1, K0, net.Mh, K0, true, wo.ksm + wo.ksx, 0, at(wo.w1t), t0, stride);
-    wide_pack_matrix(P + lo.wx1, K0, net.Xh, K0, true, wo.ksm + wo.ksx, wo.ksm, at(wo.w1t), t0, stride);
+    if (wide_fwd_supported(net)) {
+        wide_pack_matrix(P + lo.wm1, net.Mh, K0, K0, false, wo.ks0, 0, at(wo.m1), t0, stride);
+        wide_pack_matrix(P + lo.wm2, net.Ms, net.Mh, net.Mh, false, wo.ksm, 0, at(wo.m2), t0, stride);
+        wide_pack_matrix(P + lo.wx1, net.Xh, K0, K0, false, wo.ks0, 0, at(wo.x1), t0, stride);
+        wide_pack_matrix(P + lo.wx2, net.Xh, net.Xh, net.Xh, false, wo.ksx, 0, at(wo.x2), t0, stride);
+        // dgrad images: ga1 = gz2 . W2 -> rows = columns of W2;  gu = [gz1m | gz1x] . [Wm1 ; Wx1] -> rows = the K0 input columns
+        wide_pack_matrix(P + lo.wm2, net.Mh, net.Ms, net.Mh, true, wo.kss, 0, at(wo.m2t), t0, stride);
+        wide_pack_matrix(P + lo.wx2, net.Xh, net.Xh, net.Xh, true, wo.ksx, 0, at(wo.x2t), t0, stride);
+        wide_pack_matrix(P + lo.wm1, K0, net.Mh, K0, true, wo.ksm + wo.ksx, 0, at(wo.w1t), t0, stride);
+        wide_pack_matrix(P + lo.wx1, K0, net.Xh, K0, true, wo.ksm + wo.ksx, wo.ksm, at(wo.w1t), t0, stride);
+    }
     if (wide_node_supported(net)) {  // mlp_h: forward images, then the dgrad images (rows = input features)
         const int Kn = net.H + net.Ms;
         wide_pack_matrix(P + lo.wh1, net.Hh, Kn, Kn, false, wo.ksn, 0, at(wo.h1), t0, stride);
@@ -235,12 +237,27 @@ __global__ void __launch_bounds__(256) wide_edge_out_kernel(int E, int H, const 
     }
 }
 
+// per-receiver sum of column c from the direct rows and the head / tail partials of the edge tiles that cut the receiver's
+// edge range (egcl_fwd.cu: combine_agg, same order)
+__device__ __forceinline__ float wide_combine(const float* __restrict__ agg, const float* __restrict__ part, const int32_t* __restrict__ row_ptr,
+                                              int i, int c, int AGGW, int TE) {
+    const int ra = row_ptr[i], rb = row_ptr[i + 1];
+    if (ra == rb) return 0.f;
+    const int t0 = ra / TE, t1 = (rb - 1) / TE;
+    if (t0 == t1) return agg[(size_t)i * AGGW + c];
+    float s = part[((size_t)t0 * 2 + 1) * AGGW + c];
+    for (int t = t0 + 1; t <= t1; ++t) s += part[((size_t)t * 2) * AGGW + c];
+    return s;
+}
+
 // ---- node phase (mlp_h on the tile GEMMs) ---------------------------------------------------------------------------------------
 // fp32 rows -> operand image (+ transposed image): value(i, k) = k < W1 ? src1[i * W1 + k] : src2[i * ld2 + (k - W1)] for k < W1 + W2.
 // The node MLP's input [h | M] (W1 = H, W2 = Ms; forward: src2 = the per-receiver sums, copied to copy2 = msum), and with
 // W2 = 0 any row matrix (gh_out).  t_rows = 256: transposed image in the B layout (weight-gradient B operand), 128: A layout
+// part != nullptr: src2 / part are the per-receiver sums of a fused edge kernel, cut at TE-edge segment boundaries (wide_combine)
 __global__ void __launch_bounds__(256) wide_rows_to_img_kernel(int N, int mtiles, int W1, int W2, int KS, const float* __restrict__ src1,
-                                                               const float* __restrict__ src2, int ld2, float* __restrict__ copy2,
+                                                               const float* __restrict__ src2, int ld2, const float* __restrict__ part,
+                                                               const int32_t* __restrict__ row_ptr, int TE, float* __restrict__ copy2,
                                                                uint8_t* __restrict__ img, uint8_t* __restrict__ T, int t_rows, int kst) {
     const int nchunk = KS * (WIDE_TK / 8);
     const long long total = (long long)mtiles * WIDE_TM * nchunk;
@@ -258,7 +275,7 @@ __global__ void __launch_bounds__(256) wide_rows_to_img_kernel(int N, int mtiles
             if (i < N) {
                 if (k < W1) val = src1[(size_t)i * W1 + k];
                 else if (k < W1 + W2) {
-                    val = src2[(size_t)i * ld2 + (k - W1)];
+                    val = part ? wide_combine(src2, part, row_ptr, i, k - W1, ld2, TE) : src2[(size_t)i * ld2 + (k - W1)];
                     if (copy2) copy2[(size_t)i * W2 + (k - W1)] = val;
                 }
             }
@@ -759,11 +776,12 @@ struct WideGrad {
 };
 
 int wide_rows_to_img(int N, int mtiles, int W1, int W2, int KS, const float* src1, const float* src2, int ld2, float* copy2, uint8_t* img,
-                     uint8_t* T, int t_rows, int kst, cudaStream_t st, int prof) {
+                     uint8_t* T, int t_rows, int kst, cudaStream_t st, int prof, const float* part = nullptr,
+                     const int32_t* row_ptr = nullptr, int TE = 1) {
     const long long total = (long long)mtiles * WIDE_TM * KS * (WIDE_TK / 8);
     const int blocks = (int)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
     egnn_prof_begin(prof, st);
-    wide_rows_to_img_kernel<<<blocks, 256, 0, st>>>(N, mtiles, W1, W2, KS, src1, src2, ld2, copy2, img, T, t_rows, kst);
+    wide_rows_to_img_kernel<<<blocks, 256, 0, st>>>(N, mtiles, W1, W2, KS, src1, src2, ld2, part, row_ptr, TE, copy2, img, T, t_rows, kst);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("wide_rows_to_img_kernel");
     return EGNN_OK;
@@ -772,7 +790,7 @@ int wide_rows_to_img(int N, int mtiles, int W1, int W2, int KS, const float* src
 }  // namespace
 
 int egnn_wide_pack(const egnn_net_t& net, const float* params, float* packed, cudaStream_t st) {
-    if (!wide_fwd_supported(net)) return EGNN_OK;
+    if (!wide_any(net)) return EGNN_OK;
     wide_pack_kernel<<<dim3(148, net.L), 256, 0, st>>>(net, params, packed);
     EGNN_CHECK_LAUNCH("wide_pack_kernel");
     return EGNN_OK;
@@ -792,7 +810,7 @@ int egnn_wide_edge_forward(const egnn_net_t& net, const egnn_graph_t& g, const f
     uint8_t* A1 = base + ww.a1;
     float* gm = reinterpret_cast<float*>(base + ww.gm);
     float* phip = reinterpret_cast<float*>(base + ww.phip);
-    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.wide);
     auto blk = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
     const float* P = params_layer;
     const int K = EGNN_K_TC_EDGE_FWD;
@@ -843,7 +861,7 @@ int egnn_wide_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const 
     uint8_t *U = base + w.u, *UT = base + w.ut, *A1 = base + w.a1, *A1T = base + w.a1t, *G2 = base + w.g2, *G2T = base + w.g2t;
     uint8_t *G1m = base + w.g1m, *G1x = base + w.g1x, *G1T = base + w.g1t;
     float *D1 = f32(w.d1), *rows = f32(w.rows), *q = f32(w.q), *gphi = f32(w.gphi), *phip = f32(w.phip), *phi = f32(w.phi), *gu = f32(w.gu);
-    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.wide);
     auto blk = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
     const float* P = params_layer;
     const int K = EGNN_K_TC_EDGE_BWD, K0 = 2 * net.H + 1;
@@ -915,10 +933,11 @@ int egnn_wide_edge_backward(const egnn_net_t& net, const egnn_graph_t& g, const 
 
 // ---- node phase ---------------------------------------------------------------------------------------------------------------
 // h' = mlp_h([h, M]) (EquivariantGraphNeuralNetwork.py:69, no residual) on the tile GEMMs, plus the coordinate sums from phi_e.
-// agg holds complete per-receiver sums (row stride Ms + 4, written by egnn_wide_edge_forward); they are saved to msum.
+// agg (row stride Ms + 4) holds complete per-receiver sums (egnn_wide_edge_forward, TE = 2^30) or, after a fused edge kernel,
+// the sums of receivers inside one TE-edge segment with head / tail partials in part; the combined sums are saved to msum.
 int egnn_wide_node_forward(const egnn_net_t& net, const egnn_graph_t& g, const float* params_layer, const float* packed_layer,
-                           const float* h, const float* x, const float* agg, const float* phi_edge, float* h_out, float* msum,
-                           float* dxu, float* Dn, float* scratch, int precision, cudaStream_t st) {
+                           const float* h, const float* x, const float* agg, const float* part, int TE, const float* phi_edge,
+                           float* h_out, float* msum, float* dxu, float* Dn, float* scratch, int precision, cudaStream_t st) {
     EGNN_REQUIRE(wide_node_supported(net), "egnn_wide_node_forward: network outside the wide path's limits");
     const LayerOff lo = layer_off(net);
     const PackOff po = pack_off(net);
@@ -926,14 +945,16 @@ int egnn_wide_node_forward(const egnn_net_t& net, const egnn_graph_t& g, const f
     const WideWs ww = wide_ws(net, g.E, g.N);
     uint8_t* base = wide_align(scratch);
     uint8_t *NI = base + ww.ni, *A1 = base + ww.a1n;
-    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.wide);
     auto blk = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
     const int K = EGNN_K_NODE_FWD, a1_ks = wo.nth * (WIDE_TN / WIDE_TK);
     egnn_prof_begin(K, st);
     wide_node_geom_kernel<<<wide_cdiv(g.N, 32), 256, 0, st>>>(g.N, g.row_ptr, g.send, x, phi_edge, dxu, Dn);
     egnn_prof_end(st);
     EGNN_CHECK_LAUNCH("wide_node_geom_kernel");
-    if (int rc = wide_rows_to_img(g.N, ww.mtiles_n, net.H, net.Ms, wo.ksn, h, agg, net.Ms + 4, msum, NI, nullptr, 0, 0, st, K)) return rc;
+    if (int rc = wide_rows_to_img(g.N, ww.mtiles_n, net.H, net.Ms, wo.ksn, h, agg, net.Ms + 4, msum, NI, nullptr, 0, 0, st, K,
+                                  TE < (1 << 30) ? part : nullptr, g.row_ptr, TE))
+        return rc;
     WideGemmArgs a = wide_args(ww.mtiles_n, g.N);
     wide_operands(a, NI, wo.ksn, blk(wo.h1), wo.ksn, wo.nth, net.Hh);
     a.bias = params_layer + lo.bh1; a.out_img = A1; a.out_ks = a1_ks;
@@ -959,7 +980,7 @@ int egnn_wide_node_backward(const egnn_net_t& net, int N, const float* params_la
     uint8_t *NI = base + w.ni, *NIT = base + w.nit, *A1 = base + w.a1, *A1T = base + w.a1t, *GO = base + w.go, *GOT = base + w.got;
     uint8_t *G1 = base + w.g1, *G1T = base + w.g1t;
     float *D1 = reinterpret_cast<float*>(base + w.d1), *gin = reinterpret_cast<float*>(base + w.gin);
-    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.tc);
+    const uint8_t* img = reinterpret_cast<const uint8_t*>(packed_layer + po.wide);
     auto blk = [&](int first) { return img + (size_t)first * WIDE_B_SLICE; };
     const int K = EGNN_K_NODE_BWD, Kn = net.H + net.Ms;
     const WideGrad G{w.kst, w.per, w.splits, part, (int64_t)lo.total, precision, st, K};
