@@ -416,6 +416,16 @@ __device__ __forceinline__ void wide_store_T(uint8_t* tchunk, int row0, int lo_o
     *reinterpret_cast<uint4*>(d + lo_off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }
 
+// this thread's accumulator columns [c0 + 8 j, +8) of the tile; the MMAs only write the first ncols columns (a multiple of 16
+// covering the valid outputs of this N tile): the rest of the TMEM buffer holds an older tile and reads as zero
+__device__ __forceinline__ void wide_ld8(uint32_t taddr, int j, int c0, int ncols, float (&v)[8]) {
+    tc::tmem_ld8(taddr + 8 * j, v);
+    if (c0 + 8 * j >= ncols) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+    }
+}
+
 // 18 warps: 16 epilogue warps (warp w reads TMEM lanes 32 (w & 3) .., columns 64 (w >> 2) ..), one producer warp (bulk copies)
 // and one MMA-issuer warp.  The accumulator is double-buffered in TMEM (2 x 256 columns): while the epilogue warps drain
 // tile t from buffer t & 1, the issuer already runs tile t + 1 into the other buffer -- the CUDA-core epilogue (SiLU, bf16
@@ -487,6 +497,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
                 int nt, mt, kb, kc;
                 decode(it, nt, mt, kb, kc);
                 const int b = it & 1;
+                const int ncols = min(WIDE_TN, (a.N - nt * WIDE_TN + 15) & ~15);  // MMA N: the valid outputs of this tile, in 16s
                 if (it >= 2) ok = tc::mbar_wait(&bars[6 + b], ((it >> 1) - 1) & 1) && ok;  // the epilogue has drained this buffer
                 tc::fence_after_sync();
                 for (int k = 0; k < kc; ++k, ++g) {
@@ -496,7 +507,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
                     const uint32_t base = sb + s * WIDE_STAGE_BYTES;
                     const TcOperand opA{base, base + WIDE_A_SLICE / 2, WIDE_TM * 16, false};
                     const TcOperand opB{base + WIDE_A_SLICE, base + WIDE_A_SLICE + WIDE_B_SLICE / 2, WIDE_TN * 16, false};
-                    tc_issue_op<NPASS>(tmem, b * WIDE_TN, opA, opB, WIDE_TK, WIDE_TN, k > 0);
+                    tc_issue_op<NPASS>(tmem, b * WIDE_TN, opA, opB, WIDE_TK, ncols, k > 0);
                     tc::mma_commit(&bars[2 + s]);
                 }
                 tc::mma_commit(&bars[4 + b]);
@@ -520,6 +531,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
         __syncwarp();
 
         const int r = q * 32 + lane, e = mt * WIDE_TM + r;
+        const int ncols = min(WIDE_TN, (a.N - nt * WIDE_TN + 15) & ~15);
         const bool live = e < a.E;
         const int c0 = cg * 64;                // this thread's 64 columns of the tile
         const int n0 = nt * WIDE_TN + c0;      // ... of the matrix
@@ -535,7 +547,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
 #pragma unroll 1
             for (int j = 0; j < 8; ++j) {
                 float v[8];
-                tc::tmem_ld8(taddr + 8 * j, v);
+                wide_ld8(taddr, j, c0, ncols, v);
                 if (MODE == WIDE_IMG) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) v[i] = tc_silu<true>(v[i] + sBias[c0 + 8 * j + i]);
@@ -567,7 +579,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
 #pragma unroll 1
             for (int j = 0; j < 8; ++j) {
                 float v[8];
-                tc::tmem_ld8(taddr + 8 * j, v);
+                wide_ld8(taddr, j, c0, ncols, v);
                 if (MODE == WIDE_ROWDOT_BWD) {
                     // a2 = SiLU(z2), phi part += wx3 . a2;  gz2 = gphi wx3 SiLU'(z2);  rows = gphi a2 (column sums = d wx3)
                     float g2[8], ga[8];
@@ -607,7 +619,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
 #pragma unroll 1
                 for (int j = 0; j < 8; ++j) {
                     float v[8];
-                    tc::tmem_ld8(taddr + 8 * j, v);
+                    wide_ld8(taddr, j, c0, ncols, v);
 #pragma unroll
                     for (int i = 0; i < 8; ++i) v[i] = gate * tc_silu<true>(v[i] + sBias[c0 + 8 * j + i]);
                     if (live) {
@@ -625,7 +637,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
 #pragma unroll 1
                 for (int j = 0; j < 8; ++j) {
                     float v[8], g2[8];
-                    tc::tmem_ld8(taddr + 8 * j, v);
+                    wide_ld8(taddr, j, c0, ncols, v);
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         float m, dm;
@@ -648,7 +660,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
 #pragma unroll 1
             for (int j = 0; j < 8; ++j) {
                 float v[8];
-                tc::tmem_ld8(taddr + 8 * j, v);
+                wide_ld8(taddr, j, c0, ncols, v);
                 const float4 da = *reinterpret_cast<const float4*>(d1 + 8 * j), db = *reinterpret_cast<const float4*>(d1 + 8 * j + 4);
                 const float d[8] = {da.x, da.y, da.z, da.w, db.x, db.y, db.z, db.w};
 #pragma unroll
@@ -661,7 +673,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
 #pragma unroll 1
             for (int j = 0; j < 8; ++j) {
                 float v[8];
-                tc::tmem_ld8(taddr + 8 * j, v);
+                wide_ld8(taddr, j, c0, ncols, v);
                 if (live) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -676,7 +688,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
 #pragma unroll 1
             for (int j = 0; j < 8; ++j) {
                 float v[8];
-                tc::tmem_ld8(taddr + 8 * j, v);
+                wide_ld8(taddr, j, c0, ncols, v);
                 if (live) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
