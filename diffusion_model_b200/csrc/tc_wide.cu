@@ -213,6 +213,33 @@ __global__ void __launch_bounds__(256) wide_colsum_rows_kernel(const float* __re
         part[(size_t)s * part_stride + c] = t;
     }
 }
+// the same for wide row matrices (ld a multiple of 4, 16-byte aligned rows): 128 columns x 32 row lanes per CTA, float4 loads
+__global__ void __launch_bounds__(1024) wide_colsum_rows4_kernel(const float* __restrict__ rows, int ld, int ncols, int E, int per_edges,
+                                                                 float* __restrict__ part, int64_t part_stride) {
+    __shared__ float4 red[32][32];
+    const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5, c = blockIdx.x * 128 + 4 * cl, s = blockIdx.y;
+    const int e0 = s * per_edges, e1 = min(e0 + per_edges, E);
+    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < ncols) {
+#pragma unroll 4
+        for (int e = e0 + rl; e < e1; e += 32) {
+            const float4 v = *reinterpret_cast<const float4*>(rows + (size_t)e * ld + c);
+            sum.x += v.x, sum.y += v.y, sum.z += v.z, sum.w += v.w;
+        }
+    }
+    red[rl][cl] = sum;
+    __syncthreads();
+    if (rl == 0 && c < ncols) {
+        float4 t = red[0][cl];
+#pragma unroll 1
+        for (int k = 1; k < 32; ++k) t.x += red[k][cl].x, t.y += red[k][cl].y, t.z += red[k][cl].z, t.w += red[k][cl].w;
+        float* o = part + (size_t)s * part_stride + c;
+        o[0] = t.x;
+        if (c + 1 < ncols) o[1] = t.y;
+        if (c + 2 < ncols) o[2] = t.z;
+        if (c + 3 < ncols) o[3] = t.w;
+    }
+}
 
 // per-edge outputs of the layer backward (egcl_bwd.cu: egcl_edge_bwd, "per-edge outputs"): receiver / sender contributions
 __global__ void __launch_bounds__(256) wide_edge_out_kernel(int E, int H, const int32_t* __restrict__ recv, const int32_t* __restrict__ send,
@@ -773,7 +800,10 @@ struct WideGrad {
     }
     void colsum_rows(const float* r, int ld, int ncols, int nrows, int off) const {
         egnn_prof_begin(prof, st);
-        wide_colsum_rows_kernel<<<dim3(wide_cdiv(ncols, 32), S), 256, 0, st>>>(r, ld, ncols, nrows, per * WIDE_TK, part + off, pstride);
+        if (ld % 4 == 0 && ncols >= 64)
+            wide_colsum_rows4_kernel<<<dim3(wide_cdiv(ncols, 128), S), 1024, 0, st>>>(r, ld, ncols, nrows, per * WIDE_TK, part + off, pstride);
+        else
+            wide_colsum_rows_kernel<<<dim3(wide_cdiv(ncols, 32), S), 256, 0, st>>>(r, ld, ncols, nrows, per * WIDE_TK, part + off, pstride);
         egnn_prof_end(st);
     }
     // dW [Nout x Kin] = G^T X: A = transposed G image (128-row feature tiles), B = transposed X image (256-row feature tiles)
