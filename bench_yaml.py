@@ -50,7 +50,14 @@ def main(argv=None):
     from diffusion_model_b200.train_per_iretation import _conditioning, batch_loss
     if not torch.cuda.is_available():
         raise SystemExit("bench_yaml.py: no CUDA device; the product has no CPU path")
-    dev = torch.device("cuda", 0)
+    # data parallel under torchrun (weak scaling: --batch graphs on EVERY rank): the flat EGNN gradient (36 MB) is all-reduced
+    # in three buckets of layers on a communication stream while backward runs (distributed.OverlappedGradSync), the
+    # compressor's few small gradients in one call behind it
+    import torch.distributed as dist
+    from diffusion_model_b200.distributed import OverlappedGradSync, broadcast_parameters, init_from_env
+    rank, world, local = init_from_env("nccl")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
     lib = _lib.load()
     y = YAML
     H = y["atom_type_size"] + y["compressed_spectrum_size"] + y["t_size"] + y["exO_size"]      # main.py:102-110
@@ -66,7 +73,7 @@ def main(argv=None):
     cw = {k: v.detach().cpu().clone() for k, v in comp.state_dict().items()}
     params = dict(atom_type_size=2, conditional=True, to_compress_spectrum=True, give_exO=True, optimizer="RAdamScheduleFree")
     dp = E3DiffusionProcess(s=y["s"], power=y["power"], num_diffusion_timestep=y["T"])
-    gen = torch.Generator().manual_seed(7)
+    gen = torch.Generator().manual_seed(7 + rank)
     n, G = args.atoms, args.batch
     graphs = []
     for _ in range(G):
@@ -81,16 +88,34 @@ def main(argv=None):
     opt.train()
     nn_dict = {"egnn": net, "spectrum_compressor": comp}
 
+    sync = None
+    if world > 1:
+        broadcast_parameters(net)
+        for p_ in comp.parameters():
+            dist.broadcast(p_.data, src=0)
+        sync = OverlappedGradSync(net, buckets=3)
+    comp_params = list(comp.parameters())
+
     def step():
-        opt.zero_grad()
+        opt.zero_grad(set_to_none=True) if world > 1 else opt.zero_grad()
         loss, _, _ = batch_loss(net, batch, dp, params, cond=_conditioning(batch, params, nn_dict))
-        loss.backward()
+        (loss / world).backward()  # the all-reduce sums: mean over the global minibatch
+        if world > 1:
+            flat = torch.cat([p_.grad.reshape(-1) for p_ in comp_params])
+            dist.all_reduce(flat)
+            off = 0
+            for p_ in comp_params:
+                p_.grad.copy_(flat[off:off + p_.numel()].view_as(p_))
+                off += p_.numel()
+            sync.finish()
         opt.step()
         return loss
 
     for _ in range(3):
         step()
     torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
     l0 = lib.egnn_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -99,6 +124,11 @@ def main(argv=None):
     e1.record()
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1) / args.steps
+    if world > 1:
+        t_ = torch.tensor([ms], device=dev)
+        dist.barrier()
+        dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+        ms = float(t_.item())
     launches = int(lib.egnn_launch_count() - l0)
     # one denoiser call alone (what every sampler step costs): the network forward on the batch's own input
     with torch.no_grad():
@@ -116,14 +146,14 @@ def main(argv=None):
     K = K0
     flops_fwd = y["L"] * (E * (2 * K * 1024 + 2 * 1024 * 256 + 2 * 256 + 2 * K * 1024 + 2 * 1024 * 1024 + 2 * 1024)
                           + G * n * (2 * (H + 256) * 1024 + 2 * 1024 * H))          # SURVEY.md 8(d), general widths
-    out = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer), parameters.yaml network", value=G / (ms * 1e-3),
-               unit="graph-steps/s", ms_per_step=ms,
+    out = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer), parameters.yaml network", value=G * world / (ms * 1e-3),
+               unit="graph-steps/s", n_gpus=world, scaling="weak", ms_per_step=ms,
                dtype="fp32 (CUDA-core FFMA kernels)" if prec == "fp32" else f"{prec} (tcgen05 tile GEMMs, csrc/tc_wide.cu: edge and node MLPs, forward and backward)",
-               gpu_launches=launches, loss=float(loss.detach()), parameters=P, train_tflops=3 * flops_fwd / (ms * 1e-3) / 1e12,
+               gpu_launches=launches, loss=float(loss.detach()), parameters=P, train_tflops_per_gpu=3 * flops_fwd / (ms * 1e-3) / 1e12,
                denoiser_forward_ms=fwd_ms, forward_tflops=flops_fwd / (fwd_ms * 1e-3) / 1e12,
                config=dict(workload=f"parameters.yaml: conditional EGNN L=5, K0=73, m/x/h hidden 1024, m_size 256, SpectrumCompressor, "
                                     f"RAdamScheduleFree; {G} fully connected graph(s) of {n} atoms (E = {E}), T=1000", atoms=n, batch=G, edges=E))
-    if args.sample_structures > 0:
+    if args.sample_structures > 0 and world == 1:
         # generate()'s loop (parts/train_per_iretation.py:299-442) batched: the reference's published run is this, one structure
         # per call (~6.9 ms per denoiser graph-step, ~0.144 structures/s on the author's GPU, hidden sizes not recorded)
         import copy
@@ -150,7 +180,11 @@ def main(argv=None):
                                published_reference="~144 denoiser graph-steps/s, ~0.144 structures/s, one structure per call (BASELINE.md, author's GPU, "
                                                    "hidden sizes of that run not recorded)",
                                weights="seeded random init, coordinate head x0.002 / distance columns x0.001 (untrained nets diverge)")
-    if not args.skip_cpu:
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    if not args.skip_cpu and world == 1:
         from oracle import diffusion_ref as D, egnn_ref, loops_ref as LP
         from oracle.radam_sf_ref import RAdamScheduleFreeRef
         info = bench.host_info()
@@ -187,6 +221,8 @@ def main(argv=None):
         out["cpu_baseline"] = dict(value=G / sec, unit="graph-steps/s", ms_per_step=1e3 * sec, cores=info["logical_cpus"], kind="port",
                                    cpu_model=info["cpu_model"], sample=f"the same step, {len(times)} timed, oracle/ restatement with torch CPU autograd")
     print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
