@@ -40,7 +40,11 @@ typedef enum {
     EGNN_ERR_UNSUPPORTED = -4
 } egnn_status;
 
-/* arithmetic of the two d x d edge GEMMs */
+/* arithmetic of the MLP GEMMs.  The tcgen05 modes cover two families of network shapes and refuse anything else
+ * (EGNN_ERR_ARG with a message, never a silent fallback):
+ *   fused edge kernels   Mh = Ms = Xh = d in {64, 128, 256} and 2H+1 <= 16 (BASELINE.json cfg1-4);
+ *   tile-GEMM path       Mh, Xh, Hh <= 1024, Ms <= 256, 2H+1 <= 128, ragged widths allowed: the reference's own
+ *                        parameters.yaml network (main.py:102-121: K0 = 73, hidden 1024, m_size 256). */
 typedef enum {
     EGNN_PREC_FP32 = 0,   /* CUDA-core FFMA, true fp32 like the reference */
     EGNN_PREC_BF16X3 = 1, /* tcgen05 kind::f16, operands split hi+lo bf16, 3 products, fp32 accumulate (~2^-16) */
