@@ -1,20 +1,26 @@
-// Generic ("wide") tcgen05 FORWARD path of the edge MLPs, for the network shapes the fused kernels of tc_edge.cu /
-// tc_edge256.cu do not cover: the reference's own parameters.yaml network (K0 = 73, m / x hidden 1024, m_size 256, conditional:
-// main.py:102-121), ragged widths, any 2H+1 <= 128.  EquivariantGraphNeuralNetwork.py:55-65 as a chain per layer
+// Tile-GEMM ("wide") tcgen05 path for the network shapes the fused kernels of tc_edge.cu / tc_edge256.cu do not cover: the
+// reference's own parameters.yaml network (K0 = 73, m / x / h hidden 1024, m_size 256, conditional: main.py:102-121), ragged
+// widths, any 2H+1 <= 128 -- every Linear of an EGCL layer (EquivariantGraphNeuralNetwork.py:13-34, 55-71), forward AND
+// backward, and the node MLP of the d = 256 networks of the fused edge kernels.  Forward of the edge phase per layer:
 //     gather            u = [h_i, h_j, |r|^2]                                   -> U image        [E x K0p]
 //     GEMM + SiLU       a1m = SiLU(u Wm1^T + bm1)                               -> A1 image       [E x Mhp]
 //     GEMM + gate       m = SiLU(a1m Wm2^T + bm2), g = sigmoid(wa.m + ba)       -> g*m fp32       [E x 256]
 //     segment sum       M_i = sum_{e in row i} g*m   (edge order, no atomics)   -> agg rows
 //     GEMM + SiLU       a1x = SiLU(u Wx1^T + bx1)                               -> A1 image (reused)
 //     GEMM + row dot    phi_e = wx3 . SiLU(a1x Wx2^T + bx2) + bx3               -> phi parts per N tile -> phi [E]
-// One GEMM kernel (tc_wide_gemm): a CTA computes [128 edges x 256 outputs] with K streamed in 64-wide slices: both operands
+// node phase: [h | M] image -> GEMM + SiLU -> GEMM + bias -> h'; coordinate sums from phi_e (wide_node_geom_kernel).
+// ONE GEMM kernel (tc_wide_gemm): a CTA computes [128 rows x 256 outputs] with K streamed in 64-wide slices: both operands
 // arrive as ready-made bf16 hi + lo tile images by ONE cp.async.bulk each (32 KB + 64 KB per slice) into a 2-stage ring with
-// full (complete_tx) / empty (tcgen05.commit) mbarriers; a producer thread and an MMA-issuer thread run the ring while the
-// other warps wait for the accumulator; fp32 accumulation in 256 TMEM columns; bf16x3 = hi.hi + lo.hi + hi.lo.  The epilogue
-// adds the bias, applies SiLU and either writes the NEXT GEMM's A operand as a tile image (16-byte chunk stores, 512 contiguous
-// bytes per warp), or the gated message rows, or the per-row dot with wx3.  Activations between GEMMs go through L2 / HBM:
-// for wide layers that traffic (4 K bytes per edge and GEMM) is small against 2 K N FLOPs per edge.
-// The node phase runs the FFMA node kernel on plain per-receiver sums; the backward of such a network runs the FFMA kernels.
+// full (complete_tx) / empty (tcgen05.commit) mbarriers, run by a producer warp and an MMA-issuer warp; fp32 accumulation in
+// TMEM, double-buffered (2 x 256 columns) so that the 16 epilogue warps drain tile t while tile t + 1 is being multiplied;
+// bf16x3 = hi.hi + lo.hi + hi.lo.  The epilogue adds the bias, applies SiLU and writes the NEXT GEMM's A operand as a tile
+// image (16-byte chunk stores, 512 contiguous bytes per warp), or the gated message rows, or the per-row dot with wx3.
+// Activations between GEMMs go through L2 / HBM: 4 bytes per element and GEMM against 2 K FLOPs per element.
+// Backward (egnn_wide_edge_backward, egnn_wide_node_backward): both Linears are recomputed by the same GEMMs with epilogues
+// that also leave SiLU' rows and TRANSPOSED images (rows = features, K = edges); gz2 comes out of the gate / phi epilogues;
+// dgrad = the same GEMM on transposed weight images; weight gradients = split-K GEMMs over the edges whose partial tiles are
+// stored in the parameter layout of the partial buffer reduce_partials_kernel sums; bias gradients = column sums of the
+// transposed images.  Every reduction has a fixed order.  DESIGN.md 4.2 has the measurements and what bounds each GEMM.
 #include "tc_bulk.cuh"
 #include "tc_tile.cuh"
 
