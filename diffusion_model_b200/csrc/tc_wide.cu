@@ -219,6 +219,22 @@ __global__ void __launch_bounds__(256) wide_colsum_rows_kernel(const float* __re
         part[(size_t)s * part_stride + c] = t;
     }
 }
+// sum of a per-edge vector over the edges of split blockIdx.x (d ba, d bx3): 1024 strided partial sums, fixed-order tree
+__global__ void __launch_bounds__(1024) wide_sum_vec_kernel(const float* __restrict__ v, int E, int per_edges, float* __restrict__ part,
+                                                            int64_t part_stride) {
+    __shared__ float red[1024];
+    const int s = blockIdx.x, e0 = s * per_edges, e1 = min(e0 + per_edges, E);
+    float sum = 0.f;
+#pragma unroll 4
+    for (int e = e0 + threadIdx.x; e < e1; e += 1024) sum += v[e];
+    red[threadIdx.x] = sum;
+    __syncthreads();
+    for (int w = 512; w > 0; w >>= 1) {
+        if (threadIdx.x < w) red[threadIdx.x] += red[threadIdx.x + w];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) part[(size_t)s * part_stride] = red[0];
+}
 // the same for wide row matrices (ld a multiple of 4, 16-byte aligned rows): 128 columns x 32 row lanes per CTA, float4 loads
 __global__ void __launch_bounds__(1024) wide_colsum_rows4_kernel(const float* __restrict__ rows, int ld, int ncols, int E, int per_edges,
                                                                  float* __restrict__ part, int64_t part_stride) {
@@ -806,7 +822,9 @@ struct WideGrad {
     }
     void colsum_rows(const float* r, int ld, int ncols, int nrows, int off) const {
         egnn_prof_begin(prof, st);
-        if (ld % 4 == 0 && ncols >= 64)
+        if (ncols == 1 && ld == 1)
+            wide_sum_vec_kernel<<<S, 1024, 0, st>>>(r, nrows, per * WIDE_TK, part + off, pstride);
+        else if (ld % 4 == 0 && ncols >= 64)
             wide_colsum_rows4_kernel<<<dim3(wide_cdiv(ncols, 128), S), 1024, 0, st>>>(r, ld, ncols, nrows, per * WIDE_TK, part + off, pstride);
         else
             wide_colsum_rows_kernel<<<dim3(wide_cdiv(ncols, 32), S), 256, 0, st>>>(r, ld, ncols, nrows, per * WIDE_TK, part + off, pstride);

@@ -124,3 +124,33 @@ def test_outside_the_wide_limits_is_refused(lib):
     h0, x0, ei = _graph([6], H, 12)
     with pytest.raises(_lib.EgnnError):
         net(ei.to(DEV), h0.to(DEV), x0.to(DEV))
+
+
+@pytest.mark.parametrize("d,Hh", [(128, 192), (64, 40), (256, 256)])
+def test_fused_edge_kernels_with_tile_gemm_node_mlp(lib, d, Hh):
+    """d in {64, 128} with a node-MLP width the fused tcgen05 node kernels do not cover (Hh != d), and d = 256 (no fused node
+    kernel at all): the edge phase runs the fused kernels, whose per-receiver sums are cut at 32-edge segment boundaries, and
+    the node MLP the tile GEMMs (forward: wide_combine + [h | M] image; backward: egnn_wide_node_backward)."""
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    H, L = 3, 2
+    sizes = _sizes(L, H, d, d, d, Hh)
+    torch.manual_seed(21)
+    sd = egnn_ref.tame_state_dict(egnn_ref.init_state_dict(**sizes), L)
+    net = EquivariantGNN(**sizes)
+    net.load_state_dict(sd)
+    net = net.to(DEV)
+    assert net.resolved_precision() == "bf16x3"
+    h0, x0, ei = _graph([40, 51, 9], H, 22, drop_node=5)   # receivers with 39 / 50 / 8 edges: ranges straddle the 32-edge segments
+    sdg = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    hc, xc = h0.clone().requires_grad_(True), x0.clone().requires_grad_(True)
+    hr, xr = egnn_ref.egnn_forward(sdg, L, ei, hc, xc)
+    (hr.square().sum() + (xr - xc).square().sum()).backward()
+    hd, xd = h0.to(DEV).requires_grad_(True), x0.to(DEV).requires_grad_(True)
+    ho, xo = net(ei.to(DEV), hd, xd)
+    assert relerr(ho, hr) <= 2e-4 and relerr(xo, xr) <= 2e-4, (relerr(ho, hr), relerr(xo, xr))
+    (ho.square().sum() + (xo - xd).square().sum()).backward()
+    errs = {k: relerr(p.grad, sdg[k].grad) for k, p in net.named_parameters()}
+    errs["h_in"], errs["x_in"] = relerr(hd.grad, hc.grad), relerr(xd.grad, xc.grad)
+    worst = max(errs, key=errs.get)
+    print(f"fused edge + tile-GEMM node, d={d} Hh={Hh}: fwd {relerr(ho, hr):.1e}, worst gradient {worst} {errs[worst]:.2e}")
+    assert errs[worst] <= 1e-3, sorted(errs.items(), key=lambda kv: -kv[1])[:5]
