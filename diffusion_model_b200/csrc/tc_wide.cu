@@ -475,6 +475,21 @@ __device__ __forceinline__ void wide_ld8(uint32_t taddr, int j, int c0, int ncol
     }
 }
 
+// 8 consecutive floats to global memory with the widest store the address allows
+__device__ __forceinline__ void wide_store8(float* o, const float (&v)[8]) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(o);
+    if ((a & 15) == 0) {
+        *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    } else if ((a & 7) == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) *reinterpret_cast<float2*>(o + 2 * i) = make_float2(v[2 * i], v[2 * i + 1]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = v[i];
+    }
+}
+
 // 18 warps: 16 epilogue warps (warp w reads TMEM lanes 32 (w & 3) .., columns 64 (w >> 2) ..), one producer warp (bulk copies)
 // and one MMA-issuer warp.  The accumulator is double-buffered in TMEM (2 x 256 columns): while the epilogue warps drain
 // tile t from buffer t & 1, the issuer already runs tile t + 1 into the other buffer -- the CUDA-core epilogue (SiLU, bf16
@@ -724,10 +739,16 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
                 float v[8];
                 wide_ld8(taddr, j, c0, ncols, v);
                 if (live) {
+                    if (a.bias) {
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int n = n0 + 8 * j + i;
-                        if (n < a.N) o[8 * j + i] = v[i] + (a.bias ? a.bias[n] : 0.f);
+                        for (int i = 0; i < 8; ++i) v[i] += n0 + 8 * j + i < a.N ? a.bias[n0 + 8 * j + i] : 0.f;
+                    }
+                    if (n0 + 8 * j + 8 <= a.N) {
+                        wide_store8(o + 8 * j, v);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (n0 + 8 * j + i < a.N) o[8 * j + i] = v[i];
                     }
                 }
             }
@@ -739,9 +760,13 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) tc_wide_gemm(WideGemmArgs a) 
                 float v[8];
                 wide_ld8(taddr, j, c0, ncols, v);
                 if (live) {
+                    if (n0 + 8 * j + 8 <= a.N) {
+                        wide_store8(o + 8 * j, v);
+                    } else {
 #pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        if (n0 + 8 * j + i < a.N) o[8 * j + i] = v[i];
+                        for (int i = 0; i < 8; ++i)
+                            if (n0 + 8 * j + i < a.N) o[8 * j + i] = v[i];
+                    }
                 }
             }
         }
