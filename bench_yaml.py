@@ -118,11 +118,13 @@ def main(argv=None):
         dist.barrier()
     l0 = lib.egnn_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks = bench.ClockSampler(local)
     e0.record()
     for _ in range(args.steps):
         loss = step()
     e1.record()
     torch.cuda.synchronize(dev)
+    clk = clocks.stop()
     ms = e0.elapsed_time(e1) / args.steps
     if world > 1:
         t_ = torch.tensor([ms], device=dev)
@@ -146,7 +148,20 @@ def main(argv=None):
     K = K0
     flops_fwd = y["L"] * (E * (2 * K * 1024 + 2 * 1024 * 256 + 2 * 256 + 2 * K * 1024 + 2 * 1024 * 1024 + 2 * 1024)
                           + G * n * (2 * (H + 256) * 1024 + 2 * 1024 * H))          # SURVEY.md 8(d), general widths
-    out = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer), parameters.yaml network", value=G * world / (ms * 1e-3),
+    peaks = bench.measured_peaks()
+    tf_train, tf_fwd = 3 * flops_fwd / (ms * 1e-3) / 1e12, flops_fwd / (fwd_ms * 1e-3) / 1e12
+    # tensor-bound path: algorithmic FLOPs (general widths) over the measured time of ALL kernels
+    # of the step / of one denoiser call, against the measured bf16 peak.  bf16x3 issues 3 MMA products per algorithmic one
+    # (and the backward recomputes the forward GEMMs): `issued_frac` counts what the tensor pipe actually executes.
+    roofline = dict(bound="tensor", kernel="tc_wide_gemm (all epilogue variants; whole training step incl. gathers, column sums, optimizer)",
+                    achieved=tf_train, peak=peaks["tflops"], unit="TFLOP/s", frac=tf_train / peaks["tflops"], traffic=None,
+                    peak_source=f"{peaks['source']} bf16 sustained",
+                    issued_frac=(3 if prec == "bf16x3" else 1) * (4.0 / 3.0) * tf_train / peaks["tflops"] if prec != "fp32" else None,
+                    forward=dict(achieved=tf_fwd, frac=tf_fwd / peaks["tflops"],
+                                 issued_frac=(3 if prec == "bf16x3" else 1) * tf_fwd / peaks["tflops"] if prec != "fp32" else None),
+                    ncu="profiles/r2_ncu_wide_gemm.csv: the [E x 1024] x [1024 x 1024] GEMM runs at 83.6 % tensor-pipe active")
+    out = dict(metric="denoiser graph-steps/s (training fwd+bwd+optimizer), parameters.yaml network", higher_is_better=True,
+               steps=args.steps, warmup=3, data="synthetic", vs_baseline=None, clocks=clk, roofline=roofline, value=G * world / (ms * 1e-3),
                unit="graph-steps/s", n_gpus=world, scaling="weak", ms_per_step=ms,
                dtype="fp32 (CUDA-core FFMA kernels)" if prec == "fp32" else f"{prec} (tcgen05 tile GEMMs, csrc/tc_wide.cu: edge and node MLPs, forward and backward)",
                gpu_launches=launches, loss=float(loss.detach()), parameters=P, train_tflops_per_gpu=3 * flops_fwd / (ms * 1e-3) / 1e12,
