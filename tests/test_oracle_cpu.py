@@ -223,3 +223,34 @@ def test_default_precision_resolution():
     assert layer.precision == "auto" and layer.resolved_precision() == "bf16x3"
     layer.precision = "fp32"
     assert layer.resolved_precision() == "fp32"
+
+
+def test_workspace_and_image_sizes_of_the_tile_gemm_path(lib):
+    """Host-side layout arithmetic of csrc/common.cuh (no GPU needed): the reference's parameters.yaml widths get tile-GEMM
+    weight images and forward / backward scratch, the fused-kernel networks of BASELINE.json do not pay for them."""
+    import ctypes as C
+    from diffusion_model_b200 import _lib
+    yaml = _lib.NetDesc(5, 36, 1024, 256, 1024, 1024)
+    P = lib.egnn_param_count(C.byref(yaml))
+    assert P == 9008830                                    # 5 layers x 1 801 766 (main.py:112-122 with the yaml's sizes)
+    packed = lib.egnn_packed_count(C.byref(yaml))
+    # forward images m1 8 + m2 16 + x1 8 + x2 64, dgrad images 16 + 64 + 32, node 20 + 16 + 4 + 32 blocks of 64 KB per layer
+    blocks = 8 + 16 + 8 + 64 + 16 + 64 + 32 + 4 * 5 + 16 + 4 * 1 + 2 * 16
+    assert packed % 4 == 0 and packed >= 5 * blocks * 16384
+    assert packed < 5 * (blocks * 16384 + 2 * 1801766)     # + the K-major fp32 transposes of the CUDA-core path
+    E, N, G = 9120, 96, 1
+    f0 = lib.egnn_forward_workspace_floats(C.byref(yaml), N, 0, G)
+    f1 = lib.egnn_forward_workspace_floats(C.byref(yaml), N, E, G)
+    mt = (E + 127) // 128
+    # U image (2 slices) + A1 image (16 slices) of 32 KB per 128-edge tile, gated messages [E x 256] fp32, 4 phi parts
+    want = mt * 18 * 32768 + E * 256 * 4 + 4 * E * 4
+    assert (f1 - f0) * 4 >= want and (f1 - f0) * 4 < want + (2 * E + 8) * 4 * 300 + (1 << 20)
+    b1 = lib.egnn_backward_workspace_floats(C.byref(yaml), N, E, G)
+    img = mt * 16 * 32768                                  # one [E x 1024] hi | lo image
+    assert b1 * 4 >= 8 * img + 2 * mt * 128 * 1024 * 4     # a1, a1T, g2, g2T, g1m, g1x, g1T (+u) images; SiLU' rows and row sums
+    # ... plus the partial-row buffer, sized for the fp32 path too (up to 148 edge rows + node rows of one layer's parameters)
+    assert b1 * 4 < 16 * img + 2 * 148 * 1801766 * 4
+    # cfg2's network: fused kernels only -- no tile-GEMM images, no tile-GEMM scratch
+    cfg2 = _lib.NetDesc(6, 3, 128, 128, 128, 128)
+    assert lib.egnn_packed_count(C.byref(cfg2)) < 6 * 200000
+    assert lib.egnn_forward_workspace_floats(C.byref(cfg2), 12288, 417000, 64) * 4 < 64 << 20
