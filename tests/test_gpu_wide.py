@@ -154,3 +154,31 @@ def test_fused_edge_kernels_with_tile_gemm_node_mlp(lib, d, Hh):
     worst = max(errs, key=errs.get)
     print(f"fused edge + tile-GEMM node, d={d} Hh={Hh}: fwd {relerr(ho, hr):.1e}, worst gradient {worst} {errs[worst]:.2e}")
     assert errs[worst] <= 1e-3, sorted(errs.items(), key=lambda kv: -kv[1])[:5]
+
+
+def test_tile_gemm_edges_with_cuda_core_node_mlp(lib):
+    """h_hidden = 1100 is past the tile-GEMM limit of the node MLP (1024): the edge MLPs still run on the tile GEMMs (forward
+    and backward), the node MLP on the CUDA-core kernels, which read the per-receiver sums and phi_e the edge phase leaves."""
+    from diffusion_model_b200.EquivariantGraphNeuralNetwork import EquivariantGNN
+    H, L = 7, 2
+    sizes = _sizes(L, H, 300, 96, 260, 1100)
+    torch.manual_seed(31)
+    sd = egnn_ref.tame_state_dict(egnn_ref.init_state_dict(**sizes), L)
+    net = EquivariantGNN(**sizes)
+    net.load_state_dict(sd)
+    net = net.to(DEV)
+    assert net.resolved_precision() == "bf16x3"
+    h0, x0, ei = _graph([23, 14], H, 32, drop_node=2)
+    sdg = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    hc, xc = h0.clone().requires_grad_(True), x0.clone().requires_grad_(True)
+    hr, xr = egnn_ref.egnn_forward(sdg, L, ei, hc, xc)
+    (hr.square().sum() + (xr - xc).square().sum()).backward()
+    hd, xd = h0.to(DEV).requires_grad_(True), x0.to(DEV).requires_grad_(True)
+    ho, xo = net(ei.to(DEV), hd, xd)
+    assert relerr(ho, hr) <= 2e-4 and relerr(xo, xr) <= 2e-4, (relerr(ho, hr), relerr(xo, xr))
+    (ho.square().sum() + (xo - xd).square().sum()).backward()
+    errs = {k: relerr(p.grad, sdg[k].grad) for k, p in net.named_parameters()}
+    errs["h_in"], errs["x_in"] = relerr(hd.grad, hc.grad), relerr(xd.grad, xc.grad)
+    worst = max(errs, key=errs.get)
+    print(f"tile-GEMM edges + CUDA-core node MLP: fwd {relerr(ho, hr):.1e}, worst gradient {worst} {errs[worst]:.2e}")
+    assert errs[worst] <= 1e-3, sorted(errs.items(), key=lambda kv: -kv[1])[:5]
