@@ -613,7 +613,10 @@ def main():
     args = ap.parse_args()
     if args.workload == "yaml":
         import bench_yaml
-        bench_yaml.main(["--steps", str(args.steps), "--batch", str(args.global_batch or 1)] + (["--skip-cpu"] if args.impl != "b200" else []))
+        if args.impl != "b200":
+            raise SystemExit("--workload yaml has no separate reference arm: its CPU oracle timing is the cpu_baseline block of the "
+                             "product line (bench_yaml.py); the reference arm of the contract runs the default workload")
+        bench_yaml.main(["--steps", str(args.steps), "--batch", str(args.global_batch or 1)])
         return
     if args.workload == "cfg4":
         CFG.update(CFG4)
